@@ -1,0 +1,113 @@
+"""TEST INFRASTRUCTURE -- import the UNMODIFIED reference from /root/reference.
+
+Only usable in the build container (the GPU box has no /root/reference).  It is used by
+tests/golden/make_golden.py to generate the committed golden vectors and by the CPU tests
+that pin oracle/ against the reference when the reference tree is present.
+
+No reference source is copied: the reference's Python is imported in place, and the two
+native modules it lazily imports with a relative import
+(reference: DCVC-DC/src/models/entropy_models.py:13,19) are satisfied by pre-registering
+the objects built by oracle/build_ref.sh in sys.modules under the names the relative import
+resolves to.
+"""
+import importlib
+import importlib.util
+import os
+import sys
+import sysconfig
+import types
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_ROOT = os.environ.get("DCVC_REFERENCE_ROOT", "/root/reference")
+_SUF = sysconfig.get_config_var("EXT_SUFFIX")
+
+
+def reference_available(project="DCVC-DC"):
+    return os.path.isdir(os.path.join(REF_ROOT, project, "src")) and \
+        os.path.isfile(os.path.join(HERE, "_ref", "MLCodec_rans" + _SUF))
+
+
+def _load_ext(modname, path, register_as):
+    spec = importlib.util.spec_from_file_location(modname, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    for name in register_as:
+        sys.modules[name] = mod
+    return mod
+
+
+def load_native(project="DCVC-DC"):
+    """Load oracle/_ref/*.so (the reference's own C++ compiled here) as python modules."""
+    if project == "DCVC-DC":
+        rans = _load_ext("MLCodec_rans", os.path.join(HERE, "_ref", "MLCodec_rans" + _SUF),
+                         ["src.models.MLCodec_rans"])
+        cxx = _load_ext("MLCodec_CXX", os.path.join(HERE, "_ref", "MLCodec_CXX" + _SUF),
+                        ["src.models.MLCodec_CXX"])
+    else:
+        rans = _load_ext("MLCodec_rans", os.path.join(HERE, "_ref", "hem", "MLCodec_rans" + _SUF),
+                         ["src.entropy_models.MLCodec_rans"])
+        cxx = _load_ext("MLCodec_CXX", os.path.join(HERE, "_ref", "MLCodec_CXX" + _SUF),
+                        ["src.entropy_models.MLCodec_CXX"])
+    return rans, cxx
+
+
+def _install_shims():
+    # pytorch_msssim is imported unconditionally by the reference harness
+    # (DCVC-DC/test_video.py:23, DCVC-HEM/src/models/common_model.py:9) but absent here.
+    if "pytorch_msssim" not in sys.modules:
+        try:
+            importlib.import_module("pytorch_msssim")
+        except ImportError:
+            stub = types.ModuleType("pytorch_msssim")
+
+            def ms_ssim(*a, **k):
+                raise RuntimeError("pytorch_msssim stub: MS-SSIM not available")
+
+            class MS_SSIM:  # noqa: N801
+                def __init__(self, *a, **k):
+                    pass
+
+                def __call__(self, *a, **k):
+                    return ms_ssim()
+            stub.ms_ssim = ms_ssim
+            stub.MS_SSIM = MS_SSIM
+            sys.modules["pytorch_msssim"] = stub
+    # DMC.encode_decode calls torch.cuda.synchronize unconditionally
+    # (DCVC-DC/src/models/video_model.py:528,533,539).
+    import torch
+    if not torch.cuda.is_available():
+        torch.cuda.synchronize = lambda *a, **k: None
+
+
+def import_reference(project="DCVC-DC"):
+    """Returns the reference `src` package namespace for one project (DC or HEM).
+
+    DC and HEM both call their top-level package `src`; only one may live in a process.
+    """
+    if not reference_available(project):
+        raise RuntimeError("reference tree or oracle/_ref not available")
+    root = os.path.join(REF_ROOT, project)
+    if "src" in sys.modules:
+        cur = getattr(sys.modules["src"], "__path__", [""])
+        if not any(os.path.abspath(p).startswith(root) for p in cur):
+            raise RuntimeError("another reference project is already imported as `src`")
+    _install_shims()
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    importlib.import_module("src")
+    load_native(project)
+    ns = types.SimpleNamespace()
+    if project == "DCVC-DC":
+        ns.video_model = importlib.import_module("src.models.video_model")
+        ns.image_model = importlib.import_module("src.models.image_model")
+        ns.entropy_models = importlib.import_module("src.models.entropy_models")
+        ns.stream_helper = importlib.import_module("src.utils.stream_helper")
+        ns.DMC = ns.video_model.DMC
+        ns.IntraNoAR = ns.image_model.IntraNoAR
+    else:
+        ns.video_model = importlib.import_module("src.models.video_model")
+        ns.image_model = importlib.import_module("src.models.image_model")
+        ns.entropy_models = importlib.import_module("src.entropy_models.entropy_models")
+        ns.DMC = ns.video_model.DMC
+        ns.IntraNoAR = ns.image_model.IntraNoAR
+    return ns
