@@ -1,0 +1,9 @@
+// capi.cu -- library-wide state of libdcvc_b200 (error string, launch counter, version).
+#include "common.cuh"
+
+thread_local char g_dcvc_err[512] = "";
+std::atomic<int64_t> g_dcvc_launches{0};
+
+extern "C" const char *dcvc_last_error(void) { return g_dcvc_err; }
+extern "C" int dcvc_version(void) { return 100; }
+extern "C" int64_t dcvc_launch_count(void) { return g_dcvc_launches.load(); }

@@ -1,0 +1,551 @@
+// rans.cu -- GPU-resident rANS coder (kernel group 4) and the host-side CDF quantiser.
+//
+// Replaces MLCodec_rans.RansEncoder/RansDecoder (reference DCVC-DC/src/cpp/py_rans/py_rans.cpp:11-225,
+// rans/rans.cpp:76-331) and MLCodec_CXX.pmf_to_quantized_cdf (ops/ops.cpp:24-82).
+//
+// Symbols and CDF indexes never leave the device: the entropy kernels write them to device
+// arrays, the coder kernels read them there, and only the finished container (encode) or the
+// received container (decode) crosses PCIe -- versus 10 + 20 blocking .cpu()/.to(device) round
+// trips per P frame in the reference (entropy_models.py:37-55).
+//
+// Containers
+//   compat      : byte 0 = ((parts-1)<<4) | (1 if part sizes are 2-byte else 0); parts-1 LE sizes;
+//                 part streams (py_rans.cpp:74-119).  Byte-identical to the reference.
+//   interleaved : byte 0 = ((warps-1)<<4) | 0xF; warps-1 LE uint32 sizes; per warp: 32 LE uint32
+//                 lane states, then LE uint16 words in decode order.  Symbol k of a warp's chunk
+//                 belongs to lane k%32, round k/32; within a round, operation slot s (0 = the
+//                 symbol, >=1 = escape nibbles) is processed for all lanes that have it, and the
+//                 lanes that renormalise in that slot take consecutive words in lane order.
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+#include "rans_core.h"
+
+namespace {
+
+constexpr int MAX_PARTS = 16;
+constexpr int SLACK_WORDS = 4096;  // per part, 32-bit words beyond one word per symbol
+
+struct CallRec {
+  const int16_t *sym;
+  const uint8_t *idx;
+  int64_t n, plane;
+  rans::Tables t;
+};
+
+struct EncJob {
+  CallRec calls[DCVC_RANS_MAX_CALLS];
+  int ncalls, parts;
+  int64_t reg_off[MAX_PARTS + 1];  // region bounds in 32-bit words
+};
+
+// meta layout (uint32): [0] error flags, [1] container length, [2+i] part length in bytes,
+// [18+i] part start in bytes inside the encode buffer
+constexpr int META_WORDS = 2 + 2 * MAX_PARTS;
+constexpr uint32_t ERR_ENC_OVERFLOW = 1, ERR_DEC_UNDERFLOW = 2, ERR_OUT_CAPACITY = 4, ERR_ESCAPE = 8;
+
+__device__ __forceinline__ void part_range(int64_t n, int parts, int i, int64_t &off, int64_t &cur) {
+  const int64_t each = n / parts;
+  off = (int64_t)i * each;
+  cur = i < parts - 1 ? each : n - each * (parts - 1);
+}
+
+__device__ __forceinline__ int call_index(const CallRec &c, int64_t pos) {
+  return c.idx ? (int)c.idx[pos] : (int)(pos / c.plane);
+}
+
+// ------------------------------------------------------------------ compat kernels
+__global__ void compat_encode_kernel(const EncJob job, uint32_t *buf, uint32_t *meta) {
+  if (threadIdx.x != 0) return;
+  const int i = blockIdx.x;
+  rans::Enc64 e;
+  rans::enc64_init(e, buf + job.reg_off[i + 1], buf + job.reg_off[i]);
+  rans::Op ops[rans::MAX_OPS];
+  for (int c = job.ncalls - 1; c >= 0; --c) {
+    const CallRec &cr = job.calls[c];
+    int64_t off, cur;
+    part_range(cr.n, job.parts, i, off, cur);
+    for (int64_t k = cur - 1; k >= 0; --k) {
+      const int64_t pos = off + k;
+      const int nops = rans::expand_symbol(cr.sym[pos], call_index(cr, pos), cr.t, ops);
+      for (int o = nops - 1; o >= 0; --o) rans::enc64_put(e, ops[o]);
+    }
+  }
+  rans::enc64_flush(e);
+  if (e.overflow) atomicOr(meta, ERR_ENC_OVERFLOW);
+  meta[2 + i] = (uint32_t)((buf + job.reg_off[i + 1] - e.ptr) * 4);
+  meta[2 + MAX_PARTS + i] = (uint32_t)((e.ptr - buf) * 4);
+}
+
+struct DecPart {
+  uint64_t x;            // compat state
+  uint32_t lane_x[32];   // interleaved states
+  uint32_t rp, end;      // read position / end, in words (compat: 32-bit, interleaved: 16-bit)
+  uint32_t base;         // byte offset of the part inside the device stream buffer
+  uint32_t pad;
+};
+
+__global__ void compat_dec_init_kernel(const uint8_t *stream, DecPart *parts, uint32_t *meta) {
+  if (threadIdx.x != 0) return;
+  DecPart &p = parts[blockIdx.x];
+  const uint32_t *w = reinterpret_cast<const uint32_t *>(stream + p.base);
+  rans::Dec64 d;
+  rans::dec64_init(d, w, w + p.end);
+  p.x = d.x;
+  p.rp = (uint32_t)(d.ptr - w);
+  if (d.underflow) atomicOr(meta, ERR_DEC_UNDERFLOW);
+}
+
+__global__ void compat_decode_kernel(const CallRec cr, int nparts, const uint8_t *stream,
+                                     DecPart *parts, int16_t *out, uint32_t *meta) {
+  if (threadIdx.x != 0) return;
+  const int i = blockIdx.x;
+  DecPart &p = parts[i];
+  const uint32_t *w = reinterpret_cast<const uint32_t *>(stream + p.base);
+  rans::Dec64 d;
+  d.x = p.x; d.ptr = w + p.rp; d.end = w + p.end; d.underflow = 0;
+  int64_t off, cur;
+  part_range(cr.n, nparts, i, off, cur);
+  for (int64_t k = 0; k < cur; ++k) {
+    const int64_t pos = off + k;
+    out[pos] = (int16_t)rans::dec64_symbol(d, call_index(cr, pos), cr.t);
+  }
+  p.x = d.x;
+  p.rp = (uint32_t)(d.ptr - w);
+  if (d.underflow) atomicOr(meta, ERR_DEC_UNDERFLOW);
+}
+
+// ------------------------------------------------------------------ interleaved kernels
+__device__ __forceinline__ uint32_t lanemask_lt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+__global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, uint32_t *buf, uint32_t *meta) {
+  const int w = blockIdx.x, lane = threadIdx.x;
+  uint16_t *base = reinterpret_cast<uint16_t *>(buf + job.reg_off[w]);
+  const int64_t cap = (job.reg_off[w + 1] - job.reg_off[w]) * 2;
+  int64_t wp = cap;
+  uint32_t x = rans::L32;
+  bool overflow = false;
+  const uint32_t lt = lanemask_lt();
+  rans::Op ops[8];
+  for (int c = job.ncalls - 1; c >= 0; --c) {
+    const CallRec &cr = job.calls[c];
+    int64_t off, cur;
+    part_range(cr.n, job.parts, w, off, cur);
+    const int64_t rounds = (cur + 31) >> 5;
+    for (int64_t r = rounds - 1; r >= 0; --r) {
+      const int64_t k = r * 32 + lane;
+      int nops = 0;
+      if (k < cur) {
+        const int64_t pos = off + k;
+        rans::Op full[rans::MAX_OPS];
+        nops = rans::expand_symbol(cr.sym[pos], call_index(cr, pos), cr.t, full);
+        if (nops > 8) nops = 8;  // unreachable for int16 symbols
+        for (int o = 0; o < nops; ++o) ops[o] = full[o];
+      }
+      const int maxops = __reduce_max_sync(0xffffffffu, nops);
+      for (int s = maxops - 1; s >= 0; --s) {
+        const bool has = s < nops;
+        const bool emit = has && rans::enc32_needs_emit(x, ops[s]);
+        const uint32_t m = __ballot_sync(0xffffffffu, emit);
+        const int cnt = __popc(m);
+        if (cnt) {
+          if (wp - cnt < 64) {
+            overflow = true;
+          } else {
+            wp -= cnt;
+            if (emit) base[wp + __popc(m & lt)] = (uint16_t)x;
+          }
+          if (emit) x >>= 16;
+        }
+        if (has) x = rans::enc32_update(x, ops[s]);
+      }
+    }
+  }
+  wp -= 64;
+  base[wp + 2 * lane] = (uint16_t)x;
+  base[wp + 2 * lane + 1] = (uint16_t)(x >> 16);
+  if (overflow && lane == 0) atomicOr(meta, ERR_ENC_OVERFLOW);
+  if (lane == 0) {
+    meta[2 + w] = (uint32_t)((cap - wp) * 2);
+    meta[2 + MAX_PARTS + w] = (uint32_t)(job.reg_off[w] * 4 + wp * 2);
+  }
+}
+
+__global__ void ilv_dec_init_kernel(const uint8_t *stream, DecPart *parts, uint32_t *meta) {
+  DecPart &p = parts[blockIdx.x];
+  const uint16_t *w = reinterpret_cast<const uint16_t *>(stream + p.base);
+  const int lane = threadIdx.x;
+  if (p.end < 64) {
+    if (lane == 0) atomicOr(meta, ERR_DEC_UNDERFLOW);
+    p.lane_x[lane] = rans::L32;
+  } else {
+    p.lane_x[lane] = (uint32_t)w[2 * lane] | ((uint32_t)w[2 * lane + 1] << 16);
+  }
+  if (lane == 0) p.rp = 64;
+}
+
+__global__ void __launch_bounds__(32) ilv_decode_kernel(const CallRec cr, int nparts,
+                                                        const uint8_t *stream, DecPart *parts,
+                                                        int16_t *out, uint32_t *meta) {
+  const int wi = blockIdx.x, lane = threadIdx.x;
+  DecPart &p = parts[wi];
+  const uint16_t *w = reinterpret_cast<const uint16_t *>(stream + p.base);
+  uint32_t x = p.lane_x[lane];
+  uint32_t rp = p.rp;
+  const uint32_t end = p.end;
+  const uint32_t lt = lanemask_lt();
+  uint32_t err = 0;
+  int64_t off, cur;
+  part_range(cr.n, nparts, wi, off, cur);
+  const int64_t rounds = (cur + 31) >> 5;
+  for (int64_t r = 0; r < rounds; ++r) {
+    const int64_t k = r * 32 + lane;
+    const bool active = k < cur;
+    int phase = 0, maxv = 0, offset = 0, value = 0, nb = 0, j = 0;
+    uint32_t raw = 0;
+    if (active) {
+      const int index = call_index(cr, off + k);
+      const int32_t *cdf = cr.t.cdf + (int64_t)index * cr.t.stride;
+      const int size = cr.t.sizes[index];
+      maxv = size - 2;
+      offset = cr.t.offsets[index];
+      const uint32_t cum = x & 0xffffu;
+      const int s = rans::find_symbol(cdf, size, cum);
+      const uint32_t start = (uint32_t)cdf[s], freq = (uint32_t)(cdf[s + 1] - cdf[s]);
+      x = freq * (x >> 16) + cum - start;
+      value = s;
+      if (s == maxv) phase = 1;
+    }
+    {
+      const bool need = active && x < rans::L32;
+      const uint32_t m = __ballot_sync(0xffffffffu, need);
+      if (need) {
+        const uint32_t pos = rp + __popc(m & lt);
+        uint32_t word = 0;
+        if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
+        x = (x << 16) | word;
+      }
+      rp += __popc(m);
+    }
+    while (__ballot_sync(0xffffffffu, phase != 0)) {
+      uint32_t val = 0;
+      if (phase) {
+        val = x & 15u;
+        x >>= 4;
+      }
+      const bool need = phase != 0 && x < rans::L32;
+      const uint32_t m = __ballot_sync(0xffffffffu, need);
+      if (need) {
+        const uint32_t pos = rp + __popc(m & lt);
+        uint32_t word = 0;
+        if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
+        x = (x << 16) | word;
+      }
+      rp += __popc(m);
+      bool done = false;
+      if (phase == 1) {
+        nb += (int)val;
+        if (val != 15u) {
+          if (nb == 0) done = true; else phase = 2;
+          if (nb > 8) { err |= ERR_ESCAPE; done = true; }
+        }
+      } else if (phase == 2) {
+        raw |= val << (4 * j);
+        if (++j == nb) done = true;
+      }
+      if (done) {
+        value = (int)(raw >> 1);
+        if (raw & 1u) value = -value - 1; else value += maxv;
+        phase = 0;
+      }
+      if (err & ERR_DEC_UNDERFLOW) phase = 0;  // never spin on a truncated stream
+    }
+    if (active) out[off + k] = (int16_t)(value + offset);
+  }
+  p.lane_x[lane] = x;
+  __syncwarp();
+  if (lane == 0) p.rp = rp;
+  if (err) atomicOr(meta, err);
+}
+
+// ------------------------------------------------------------------ container assembly
+__global__ void assemble_kernel(int mode, int parts, const uint8_t *buf, uint32_t *meta,
+                                uint8_t *out, uint32_t out_cap) {
+  uint32_t len[MAX_PARTS], maximum = 0, total = 0;
+  for (int i = 0; i < parts; ++i) {
+    len[i] = meta[2 + i];
+    if (i < parts - 1 && len[i] > maximum) maximum = len[i];
+    total += len[i];
+  }
+  const int per = (mode == DCVC_RANS_COMPAT && maximum <= 65535u) ? 2 : 4;
+  const uint32_t overhead = 1 + (uint32_t)(parts - 1) * per;
+  const bool fits = total + overhead <= out_cap;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid == 0) {
+    meta[1] = total + overhead;
+    if (!fits) atomicOr(meta, ERR_OUT_CAPACITY);
+  }
+  if (!fits) return;
+  if (tid == 0) {
+    out[0] = (uint8_t)(((parts - 1) << 4) | (mode == DCVC_RANS_COMPAT ? (per == 2 ? 1 : 0) : 0xF));
+    for (int i = 0; i < parts - 1; ++i)
+      for (int b = 0; b < per; ++b) out[1 + i * per + b] = (uint8_t)(len[i] >> (8 * b));
+  }
+  uint32_t dst = overhead;
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+  for (int i = 0; i < parts; ++i) {
+    const uint8_t *src = buf + meta[2 + MAX_PARTS + i];
+    for (int64_t b = tid; b < len[i]; b += nthreads) out[dst + b] = src[b];
+    dst += len[i];
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host context
+struct dcvc_rans {
+  int mode = 0, parts = 1;
+  int64_t max_symbols = 0;
+  EncJob job;
+  uint32_t *d_buf = nullptr;
+  size_t buf_words = 0;
+  uint8_t *d_out = nullptr;
+  size_t out_cap = 0;
+  uint32_t *d_meta = nullptr, *h_meta = nullptr;
+  uint8_t *h_stage = nullptr, *d_stream = nullptr;
+  size_t stream_cap = 0;
+  DecPart *d_parts = nullptr, *h_parts = nullptr;
+  int dec_parts = 0;
+  cudaEvent_t staged = nullptr;
+  bool stage_pending = false;
+};
+
+extern "C" void dcvc_rans_destroy(dcvc_rans *r) {
+  if (!r) return;
+  cudaFree(r->d_buf); cudaFree(r->d_out); cudaFree(r->d_meta); cudaFree(r->d_stream);
+  cudaFree(r->d_parts);
+  cudaFreeHost(r->h_meta); cudaFreeHost(r->h_stage); cudaFreeHost(r->h_parts);
+  if (r->staged) cudaEventDestroy(r->staged);
+  delete r;
+}
+
+#define RANS_TRY(expr)                                                                     \
+  do {                                                                                     \
+    cudaError_t e_ = (expr);                                                               \
+    if (e_ != cudaSuccess) {                                                               \
+      dcvc_fail(DCVC_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #expr,                  \
+                cudaGetErrorString(e_));                                                   \
+      dcvc_rans_destroy(r);                                                                \
+      return DCVC_ERR_CUDA;                                                                \
+    }                                                                                      \
+  } while (0)
+
+extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t max_symbols) {
+  if (!out || (mode != DCVC_RANS_COMPAT && mode != DCVC_RANS_INTERLEAVED) || parts < 1 ||
+      parts > MAX_PARTS || max_symbols < 1)
+    return dcvc_fail(DCVC_ERR_ARG, "rans_create: bad arguments (mode %d parts %d)", mode, parts);
+  dcvc_rans *r = new (std::nothrow) dcvc_rans();
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_create: out of host memory");
+  r->mode = mode; r->parts = parts; r->max_symbols = max_symbols;
+  r->job.ncalls = 0; r->job.parts = parts;
+  r->buf_words = (size_t)max_symbols + (size_t)SLACK_WORDS * MAX_PARTS;
+  r->out_cap = r->buf_words * 4 + 256;
+  r->stream_cap = r->out_cap + 16 * MAX_PARTS;
+  RANS_TRY(cudaMalloc(&r->d_buf, r->buf_words * 4));
+  RANS_TRY(cudaMalloc(&r->d_out, r->out_cap));
+  RANS_TRY(cudaMalloc(&r->d_meta, META_WORDS * 4));
+  RANS_TRY(cudaMemset(r->d_meta, 0, META_WORDS * 4));
+  RANS_TRY(cudaMallocHost(&r->h_meta, META_WORDS * 4));
+  RANS_TRY(cudaMallocHost(&r->h_stage, r->stream_cap));
+  RANS_TRY(cudaMalloc(&r->d_stream, r->stream_cap));
+  RANS_TRY(cudaMalloc(&r->d_parts, sizeof(DecPart) * MAX_PARTS));
+  RANS_TRY(cudaMallocHost(&r->h_parts, sizeof(DecPart) * MAX_PARTS));
+  RANS_TRY(cudaEventCreateWithFlags(&r->staged, cudaEventDisableTiming));
+  *out = r;
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_enc_reset(dcvc_rans *r) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans: null context");
+  r->job.ncalls = 0;
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_enc_push(dcvc_rans *r, const int16_t *symbols, const uint8_t *indexes,
+                                  int64_t n, int64_t plane, const dcvc_tables *t) {
+  if (!r || !symbols || !t || !t->cdf || !t->sizes || !t->offsets || n < 0)
+    return dcvc_fail(DCVC_ERR_ARG, "rans_enc_push: bad arguments");
+  if (!indexes && plane < 1) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_push: plane needed without indexes");
+  if (r->job.ncalls >= DCVC_RANS_MAX_CALLS) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_push: too many calls");
+  int64_t total = n;
+  for (int c = 0; c < r->job.ncalls; ++c) total += r->job.calls[c].n;
+  if (total > r->max_symbols) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_push: more than max_symbols");
+  CallRec &cr = r->job.calls[r->job.ncalls++];
+  cr.sym = symbols; cr.idx = indexes; cr.n = n; cr.plane = plane < 1 ? 1 : plane;
+  cr.t.cdf = t->cdf; cr.t.sizes = t->sizes; cr.t.offsets = t->offsets; cr.t.stride = t->stride;
+  return DCVC_OK;
+}
+
+static int rans_errors(uint32_t flags) {
+  if (!flags) return DCVC_OK;
+  if (flags & ERR_OUT_CAPACITY) return dcvc_fail(DCVC_ERR_ARG, "rans: output capacity too small");
+  if (flags & ERR_ENC_OVERFLOW) return dcvc_fail(DCVC_ERR_ARG, "rans: encode buffer overflow");
+  return dcvc_fail(DCVC_ERR_STREAM, "rans: truncated or corrupt stream (flags %u)", flags);
+}
+
+extern "C" int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_capacity,
+                                   size_t *out_len, void *stream) {
+  if (!r || !out_host || !out_len) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  int64_t off = 0;
+  for (int i = 0; i < r->parts; ++i) {
+    int64_t count = 0;
+    for (int c = 0; c < r->job.ncalls; ++c) {
+      const int64_t n = r->job.calls[c].n, each = n / r->parts;
+      count += i < r->parts - 1 ? each : n - each * (r->parts - 1);
+    }
+    r->job.reg_off[i] = off;
+    off += count + SLACK_WORDS;
+  }
+  r->job.reg_off[r->parts] = off;
+  if ((size_t)off > r->buf_words) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush: buffer too small");
+  DCVC_CUDA(cudaMemsetAsync(r->d_meta, 0, META_WORDS * 4, s));
+  if (r->mode == DCVC_RANS_COMPAT)
+    compat_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_buf, r->d_meta);
+  else
+    ilv_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_buf, r->d_meta);
+  DCVC_LAUNCHED();
+  const uint32_t cap = (uint32_t)(out_capacity < r->out_cap ? out_capacity : r->out_cap);
+  assemble_kernel<<<64, 256, 0, s>>>(r->mode, r->parts, reinterpret_cast<const uint8_t *>(r->d_buf),
+                                     r->d_meta, r->d_out, cap);
+  DCVC_LAUNCHED();
+  DCVC_CUDA(cudaMemcpyAsync(r->h_meta, r->d_meta, META_WORDS * 4, cudaMemcpyDeviceToHost, s));
+  DCVC_CUDA(cudaStreamSynchronize(s));
+  r->job.ncalls = 0;
+  int rc = rans_errors(r->h_meta[0]);
+  if (rc) return rc;
+  const size_t len = r->h_meta[1];
+  DCVC_CUDA(cudaMemcpyAsync(out_host, r->d_out, len, cudaMemcpyDeviceToHost, s));
+  DCVC_CUDA(cudaStreamSynchronize(s));
+  *out_len = len;
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_t len, void *stream) {
+  if (!r || !host || len < 1) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: empty stream");
+  cudaStream_t s = (cudaStream_t)stream;
+  const uint8_t flag = host[0];
+  const int n = (flag >> 4) + 1;
+  const int low = flag & 0x0f;
+  const int mode = low == 0xF ? DCVC_RANS_INTERLEAVED : DCVC_RANS_COMPAT;
+  if (mode != r->mode) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: container mode %d, coder mode %d", mode, r->mode);
+  if (mode == DCVC_RANS_COMPAT && low > 1) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: bad flag byte");
+  const int per = (mode == DCVC_RANS_COMPAT && low == 1) ? 2 : 4;
+  size_t off = 1, total = 0;
+  size_t sizes[MAX_PARTS];
+  for (int i = 0; i < n - 1; ++i) {
+    if (off + per > len) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: truncated header");
+    size_t v = 0;
+    for (int b = 0; b < per; ++b) v |= (size_t)host[off + b] << (8 * b);
+    sizes[i] = v; total += v; off += per;
+  }
+  if (off + total > len) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: part sizes exceed stream");
+  sizes[n - 1] = len - off - total;
+  if (len + 16 * MAX_PARTS > r->stream_cap) return dcvc_fail(DCVC_ERR_ARG, "rans_dec_set_stream: stream larger than coder capacity");
+  if (r->stage_pending) { DCVC_CUDA(cudaEventSynchronize(r->staged)); r->stage_pending = false; }
+  size_t dst = 0;
+  const size_t unit = mode == DCVC_RANS_COMPAT ? 4 : 2;
+  for (int i = 0; i < n; ++i) {
+    memcpy(r->h_stage + dst, host + off, sizes[i]);
+    memset(&r->h_parts[i], 0, sizeof(DecPart));
+    r->h_parts[i].base = (uint32_t)dst;
+    r->h_parts[i].end = (uint32_t)(sizes[i] / unit);
+    off += sizes[i];
+    dst = (dst + sizes[i] + 15) & ~(size_t)15;
+  }
+  r->dec_parts = n;
+  DCVC_CUDA(cudaMemcpyAsync(r->d_stream, r->h_stage, dst ? dst : 16, cudaMemcpyHostToDevice, s));
+  DCVC_CUDA(cudaMemcpyAsync(r->d_parts, r->h_parts, sizeof(DecPart) * n, cudaMemcpyHostToDevice, s));
+  DCVC_CUDA(cudaEventRecord(r->staged, s));
+  r->stage_pending = true;
+  DCVC_CUDA(cudaMemsetAsync(r->d_meta, 0, 4, s));
+  if (mode == DCVC_RANS_COMPAT)
+    compat_dec_init_kernel<<<n, 32, 0, s>>>(r->d_stream, r->d_parts, r->d_meta);
+  else
+    ilv_dec_init_kernel<<<n, 32, 0, s>>>(r->d_stream, r->d_parts, r->d_meta);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t n, int64_t plane,
+                                  const dcvc_tables *t, int16_t *symbols_out, void *stream) {
+  if (!r || !t || !t->cdf || !symbols_out || n < 0 || r->dec_parts < 1)
+    return dcvc_fail(DCVC_ERR_ARG, "rans_dec_pull: bad arguments or no stream set");
+  if (!indexes && plane < 1) return dcvc_fail(DCVC_ERR_ARG, "rans_dec_pull: plane needed without indexes");
+  CallRec cr;
+  cr.sym = nullptr; cr.idx = indexes; cr.n = n; cr.plane = plane < 1 ? 1 : plane;
+  cr.t.cdf = t->cdf; cr.t.sizes = t->sizes; cr.t.offsets = t->offsets; cr.t.stride = t->stride;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (r->mode == DCVC_RANS_COMPAT)
+    compat_decode_kernel<<<r->dec_parts, 32, 0, s>>>(cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+  else
+    ilv_decode_kernel<<<r->dec_parts, 32, 0, s>>>(cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_status(dcvc_rans *r, void *stream) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans: null context");
+  cudaStream_t s = (cudaStream_t)stream;
+  DCVC_CUDA(cudaMemcpyAsync(r->h_meta, r->d_meta, 4, cudaMemcpyDeviceToHost, s));
+  DCVC_CUDA(cudaStreamSynchronize(s));
+  return rans_errors(r->h_meta[0]);
+}
+
+// ------------------------------------------------------------------ CDF quantiser (host)
+// Semantics of ops.cpp:24-82: scale each probability by 2^precision with round-half-away,
+// renormalise the integer frequencies so they sum to 2^precision (truncating division), take the
+// running sum, pin the last entry to 2^precision, and give every empty bin one count taken from
+// the bin with the smallest frequency above one, shifting the entries in between.
+extern "C" int dcvc_pmf_to_quantized_cdf(const float *pmf, int n, int precision, uint32_t *cdf) {
+  if (!pmf || !cdf || n < 1 || precision < 1 || precision > 16)
+    return dcvc_fail(DCVC_ERR_ARG, "pmf_to_quantized_cdf: bad arguments");
+  const uint32_t top = 1u << precision;
+  std::vector<uint32_t> f((size_t)n + 1, 0u);
+  for (int i = 0; i < n; ++i) {
+    const float scaled = roundf(pmf[i] * (float)top);
+    f[i + 1] = (uint32_t)((double)scaled + 0.5);
+  }
+  uint32_t sum = 0;
+  for (uint32_t v : f) sum += v;
+  if (sum == 0) return dcvc_fail(DCVC_ERR_ARG, "pmf_to_quantized_cdf: all-zero pmf");
+  uint32_t run = 0;
+  for (int i = 0; i <= n; ++i) {
+    run += (uint32_t)(((uint64_t)top * f[i]) / sum);
+    cdf[i] = run;
+  }
+  cdf[n] = top;
+  for (int i = 0; i < n; ++i) {
+    if (cdf[i] != cdf[i + 1]) continue;
+    int donor = -1;
+    uint32_t donor_freq = 0xffffffffu;
+    for (int j = 0; j < n; ++j) {
+      const uint32_t fr = cdf[j + 1] - cdf[j];
+      if (fr > 1 && fr < donor_freq) { donor_freq = fr; donor = j; }
+    }
+    if (donor < 0) return dcvc_fail(DCVC_ERR_ARG, "pmf_to_quantized_cdf: no bin to steal from");
+    if (donor < i) {
+      for (int j = donor + 1; j <= i; ++j) cdf[j] -= 1;
+    } else {
+      for (int j = i + 1; j <= donor; ++j) cdf[j] += 1;
+    }
+  }
+  return DCVC_OK;
+}

@@ -1,0 +1,270 @@
+// warp.cu -- motion / resampling kernels (HBM-bound stencil and gather kernels, NHWC fp32).
+//
+// Replaces, on the hot path of the reference (DCVC-DC/src/models):
+//   flow_warp / torch_warp (F.grid_sample bilinear, border, align_corners=True)  video_net.py:8-38
+//   bilinearupsacling / bilineardownsacling (F.interpolate, align_corners=False) video_net.py:41-55
+//   F.avg_pool2d(2,2) pyramid                                                   video_net.py:111-113
+//   nn.MaxPool2d(2,2) in UNet                                                   video_net.py:154,157
+//   OffsetDiversity from the offset tensor onward                               video_model.py:46-63
+//   torch.cat / F.pad(replicate) / negative F.pad                               common_model.py:70-86
+// Every kernel maps consecutive threads to consecutive channels (then pixels), i.e. coalesced
+// NHWC access; all are one read + one write of their tensors.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TPB = 256;
+
+__global__ void nchw_to_nhwc_kernel(const float *__restrict__ src, dcvc_view dst) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t hw = (int64_t)dst.h * dst.w;
+  if (t >= hw * dst.c) return;
+  const int c = (int)(t / hw);
+  const int64_t p = t - (int64_t)c * hw;  // coalesced read of a plane
+  dst.data[p * dst.cstride + dst.coff + c] = src[t];
+}
+
+__global__ void nhwc_to_nchw_kernel(dcvc_view src, float *__restrict__ dst, int clamp01) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t hw = (int64_t)src.h * src.w;
+  if (t >= hw * src.c) return;
+  const int c = (int)(t / hw);
+  const int64_t p = t - (int64_t)c * hw;
+  float v = src.data[p * src.cstride + src.coff + c];
+  if (clamp01) v = fminf(fmaxf(v, 0.f), 1.f);
+  dst[t] = v;
+}
+
+__global__ void copy_kernel(dcvc_view src, dcvc_view dst, float mul, float slope) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)dst.h * dst.w * dst.c) return;
+  const int c = (int)(t % dst.c);
+  const int64_t p = t / dst.c;
+  const int x = (int)(p % dst.w), y = (int)(p / dst.w);
+  const int sy = min(y, src.h - 1), sx = min(x, src.w - 1);
+  dst.data[vidx(dst, y, x) + c] = mul * lrelu(src.data[vidx(src, sy, sx) + c], slope);
+}
+
+__global__ void fill_kernel(dcvc_view dst, float value) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)dst.h * dst.w * dst.c) return;
+  const int c = (int)(t % dst.c);
+  const int64_t p = t / dst.c;
+  dst.data[p * dst.cstride + dst.coff + c] = value;
+}
+
+__global__ void pool2_kernel(dcvc_view src, dcvc_view dst, int mode) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)dst.h * dst.w * dst.c) return;
+  const int c = (int)(t % dst.c);
+  const int64_t p = t / dst.c;
+  const int x = (int)(p % dst.w), y = (int)(p / dst.w);
+  const float a = src.data[vidx(src, 2 * y, 2 * x) + c];
+  const float b = src.data[vidx(src, 2 * y, 2 * x + 1) + c];
+  const float d = src.data[vidx(src, 2 * y + 1, 2 * x) + c];
+  const float e = src.data[vidx(src, 2 * y + 1, 2 * x + 1) + c];
+  float v;
+  if (mode == 0) v = (a + b + d + e) * 0.25f;   // ATen avg_pool2d: sum / pool_size
+  else v = fmaxf(fmaxf(a, b), fmaxf(d, e));
+  dst.data[vidx(dst, y, x) + c] = v;
+}
+
+// ATen upsample_bilinear2d, align_corners=False: src = scale*(dst+0.5)-0.5 clamped at 0
+__device__ __forceinline__ void src_index(float scale, int dst, int in_size, int &i0, int &i1,
+                                          float &l0, float &l1) {
+  float s = scale * (dst + 0.5f) - 0.5f;
+  if (s < 0.f) s = 0.f;
+  i0 = min((int)s, in_size - 1);
+  i1 = min(i0 + 1, in_size - 1);
+  l1 = s - (float)i0;
+  l0 = 1.f - l1;
+}
+
+__device__ __forceinline__ float bilerp_resize(const dcvc_view &src, int c, int y0, int y1,
+                                               int x0, int x1, float hl0, float hl1, float wl0,
+                                               float wl1) {
+  const float v00 = src.data[vidx(src, y0, x0) + c], v01 = src.data[vidx(src, y0, x1) + c];
+  const float v10 = src.data[vidx(src, y1, x0) + c], v11 = src.data[vidx(src, y1, x1) + c];
+  return hl0 * (wl0 * v00 + wl1 * v01) + hl1 * (wl0 * v10 + wl1 * v11);
+}
+
+__global__ void resize_bilinear_kernel(dcvc_view src, dcvc_view dst, float sh, float sw, float mul) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)dst.h * dst.w * dst.c) return;
+  const int c = (int)(t % dst.c);
+  const int64_t p = t / dst.c;
+  const int x = (int)(p % dst.w), y = (int)(p / dst.w);
+  int y0, y1, x0, x1;
+  float hl0, hl1, wl0, wl1;
+  src_index(sh, y, src.h, y0, y1, hl0, hl1);
+  src_index(sw, x, src.w, x0, x1, wl0, wl1);
+  dst.data[vidx(dst, y, x) + c] = mul * bilerp_resize(src, c, y0, y1, x0, x1, hl0, hl1, wl0, wl1);
+}
+
+// torch.linspace(-1, 1, n)[i] in fp32 (symmetric evaluation, ATen RangeFactories)
+__device__ __forceinline__ float linspace_pm1(int i, int n) {
+  const float step = 2.0f / (float)(n - 1);
+  return i < n / 2 ? -1.0f + step * (float)i : 1.0f - step * (float)(n - 1 - i);
+}
+
+struct Bilin {
+  int x0, y0, x1, y1;
+  float nw, ne, sw, se;
+  bool vx1, vy1;
+};
+
+// reference arithmetic: grid = linspace + flow/((size-1)/2); unnormalise ((g+1)*((size-1)/2));
+// clip to [0, size-1]; bilinear with out-of-range corners dropped.
+__device__ __forceinline__ Bilin warp_coords(int x, int y, float fx, float fy, int w, int h) {
+  const float half_w = (float)(w - 1) / 2.0f, half_h = (float)(h - 1) / 2.0f;
+  float gx = linspace_pm1(x, w) + fx / half_w;
+  float gy = linspace_pm1(y, h) + fy / half_h;
+  if (w == 1) gx = -1.0f + fx / half_w;
+  if (h == 1) gy = -1.0f + fy / half_h;
+  float sx = (gx + 1.0f) * half_w;
+  float sy = (gy + 1.0f) * half_h;
+  sx = fminf((float)(w - 1), fmaxf(sx, 0.f));
+  sy = fminf((float)(h - 1), fmaxf(sy, 0.f));
+  Bilin b;
+  const float xf = floorf(sx), yf = floorf(sy);
+  b.x0 = (int)xf; b.y0 = (int)yf;
+  b.x1 = b.x0 + 1; b.y1 = b.y0 + 1;
+  const float e = sx - xf, wv = 1.0f - e, s = sy - yf, n = 1.0f - s;
+  b.nw = n * wv; b.ne = n * e; b.sw = s * wv; b.se = s * e;
+  b.vx1 = b.x1 < w; b.vy1 = b.y1 < h;
+  if (!b.vx1) b.x1 = b.x0;
+  if (!b.vy1) b.y1 = b.y0;
+  return b;
+}
+
+__device__ __forceinline__ float warp_sample(const dcvc_view &f, const Bilin &b, int c) {
+  float v = b.nw * f.data[vidx(f, b.y0, b.x0) + c];
+  if (b.vx1) v += b.ne * f.data[vidx(f, b.y0, b.x1) + c];
+  if (b.vy1) v += b.sw * f.data[vidx(f, b.y1, b.x0) + c];
+  if (b.vx1 && b.vy1) v += b.se * f.data[vidx(f, b.y1, b.x1) + c];
+  return v;
+}
+
+__global__ void flow_warp_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)out.h * out.w * out.c) return;
+  const int c = (int)(t % out.c);
+  const int64_t p = t / out.c;
+  const int x = (int)(p % out.w), y = (int)(p / out.w);
+  const float *fl = flow.data + vidx(flow, y, x);
+  const Bilin b = warp_coords(x, y, fl[0], fl[1], feat.w, feat.h);
+  out.data[vidx(out, y, x) + c] = warp_sample(feat, b, c);
+}
+
+// one thread per (pixel, group q of 16): samples n = 2q, 2q+1
+__global__ void offset_diversity_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
+                                        const float *__restrict__ fw, const float *__restrict__ fb,
+                                        dcvc_view out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)out.h * out.w * 16) return;
+  const int q = (int)(t & 15);
+  const int64_t p = t >> 4;
+  const int px = (int)(p % out.w), py = (int)(p / out.w);
+  // bilinear x2 source coordinates in the half-resolution offset tensor
+  int y0, y1, x0, x1;
+  float hl0, hl1, wl0, wl1;
+  src_index((float)offs.h / (float)out.h, py, offs.h, y0, y1, hl0, hl1);
+  src_index((float)offs.w / (float)out.w, px, offs.w, x0, x1, wl0, wl1);
+  const float *fl = flow.data + vidx(flow, py, px);
+  const float fx = fl[0], fy = fl[1];
+  float v[6];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int n = 2 * q + k;
+    const float ox = bilerp_resize(offs, 2 * n, y0, y1, x0, x1, hl0, hl1, wl0, wl1);
+    const float oy = bilerp_resize(offs, 2 * n + 1, y0, y1, x0, x1, hl0, hl1, wl0, wl1);
+    const float mk = bilerp_resize(offs, 64 + n, y0, y1, x0, x1, hl0, hl1, wl0, wl1);
+    const float mask = 1.0f / (1.0f + expf(-mk));
+    const Bilin b = warp_coords(px, py, 40.0f * tanhf(ox) + fx, 40.0f * tanhf(oy) + fy, x.w, x.h);
+    const int g = n & 15;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) v[k * 3 + j] = warp_sample(x, b, g * 3 + j) * mask;
+  }
+  float *op = out.data + vidx(out, py, px) + 3 * q;
+#pragma unroll
+  for (int o = 0; o < 3; ++o) {
+    const float *wr = fw + (3 * q + o) * 6;
+    float acc = fb ? fb[3 * q + o] : 0.f;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) acc = fmaf(v[r], wr[r], acc);
+    op[o] = acc;
+  }
+}
+
+}  // namespace
+
+#define LAUNCH_1D(kernel, total, stream, ...)                                              \
+  do {                                                                                     \
+    kernel<<<cdiv((total), TPB), TPB, 0, (cudaStream_t)(stream)>>>(__VA_ARGS__);           \
+    DCVC_LAUNCHED();                                                                       \
+  } while (0)
+
+extern "C" int dcvc_nchw_to_nhwc(const float *src, const dcvc_view *dst, void *stream) {
+  if (!src || !view_ok(dst)) return dcvc_fail(DCVC_ERR_ARG, "nchw_to_nhwc: bad args");
+  LAUNCH_1D(nchw_to_nhwc_kernel, (int64_t)dst->h * dst->w * dst->c, stream, src, *dst);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_nhwc_to_nchw(const dcvc_view *src, float *dst, int clamp01, void *stream) {
+  if (!dst || !view_ok(src)) return dcvc_fail(DCVC_ERR_ARG, "nhwc_to_nchw: bad args");
+  LAUNCH_1D(nhwc_to_nchw_kernel, (int64_t)src->h * src->w * src->c, stream, *src, dst, clamp01);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_copy(const dcvc_view *src, const dcvc_view *dst, float mul, float slope,
+                         void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || src->c != dst->c)
+    return dcvc_fail(DCVC_ERR_ARG, "copy: bad args");
+  LAUNCH_1D(copy_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *src, *dst, mul, slope);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_fill(const dcvc_view *dst, float value, void *stream) {
+  if (!view_ok(dst)) return dcvc_fail(DCVC_ERR_ARG, "fill: bad args");
+  LAUNCH_1D(fill_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *dst, value);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || src->c != dst->c || dst->h != src->h / 2 ||
+      dst->w != src->w / 2)
+    return dcvc_fail(DCVC_ERR_ARG, "pool2: bad args");
+  LAUNCH_1D(pool2_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *src, *dst, mode);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_resize_bilinear(const dcvc_view *src, const dcvc_view *dst, float mul,
+                                    void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || src->c != dst->c)
+    return dcvc_fail(DCVC_ERR_ARG, "resize: bad args");
+  const float sh = (float)src->h / (float)dst->h, sw = (float)src->w / (float)dst->w;
+  LAUNCH_1D(resize_bilinear_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *src, *dst, sh, sw,
+            mul);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_flow_warp(const dcvc_view *feat, const dcvc_view *flow, const dcvc_view *out,
+                              void *stream) {
+  if (!view_ok(feat) || !view_ok(flow) || !view_ok(out) || flow->c != 2 || out->c != feat->c ||
+      out->h != flow->h || out->w != flow->w)
+    return dcvc_fail(DCVC_ERR_ARG, "flow_warp: bad args");
+  LAUNCH_1D(flow_warp_kernel, (int64_t)out->h * out->w * out->c, stream, *feat, *flow, *out);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_offset_diversity(const dcvc_view *x, const dcvc_view *offs_half,
+                                     const dcvc_view *flow, const float *fusion_w,
+                                     const float *fusion_b, const dcvc_view *out, void *stream) {
+  if (!view_ok(x) || !view_ok(offs_half) || !view_ok(flow) || !view_ok(out) || !fusion_w ||
+      x->c != 48 || offs_half->c != 96 || flow->c != 2 || out->c != 48 || out->h != x->h ||
+      out->w != x->w || flow->h != x->h || flow->w != x->w)
+    return dcvc_fail(DCVC_ERR_ARG, "offset_diversity: bad args");
+  LAUNCH_1D(offset_diversity_kernel, (int64_t)out->h * out->w * 16, stream, *x, *offs_half, *flow,
+            fusion_w, fusion_b, *out);
+  return DCVC_OK;
+}

@@ -1,0 +1,217 @@
+/* dcvc_b200.h -- C ABI of libdcvc_b200.so (sm_100a CUDA kernels for the DCVC-DC per-frame
+ * coding path).
+ *
+ * This is the inner boundary of the drop-in: the reference reaches native code only through two
+ * pybind11 modules (MLCodec_rans / MLCodec_CXX, reference DCVC-DC/src/cpp/py_rans/py_rans.cpp:227-243,
+ * DCVC-DC/src/cpp/ops/ops.cpp:84-91) and otherwise through stock torch ops (cuDNN/ATen).  Here
+ * every one of those native calls and stock ops on the hot path is an `extern "C"` entry point
+ * taking plain pointers and sizes.  The Python host (dcvc_b200/*.py) binds them with ctypes;
+ * INTEGRATION.md shows the stubs a reference maintainer would add.
+ *
+ * Conventions
+ *   - All device tensors are fp32 NHWC "views": element (y, x, ch) of a view lives at
+ *     data[(y * w + x) * cstride + coff + ch].  cstride >= coff + c lets several producers
+ *     write disjoint channel ranges of one buffer, which replaces torch.cat.
+ *   - Every function returns 0 on success, a negative code on error (message through
+ *     dcvc_last_error()); nothing throws, nothing allocates device memory behind the caller
+ *     (workspaces are caller-provided and sized by *_bytes queries).
+ *   - All kernels are enqueued on the `stream` argument (a cudaStream_t passed as void*);
+ *     calls are asynchronous unless stated otherwise.
+ *   - There is no CPU fallback: without a CUDA device every compute entry returns
+ *     DCVC_ERR_CUDA.
+ */
+#ifndef DCVC_B200_H
+#define DCVC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DCVC_OK 0
+#define DCVC_ERR_ARG (-1)
+#define DCVC_ERR_CUDA (-2)
+#define DCVC_ERR_UNSUPPORTED (-3)
+#define DCVC_ERR_STREAM (-4) /* malformed bitstream / container */
+
+typedef struct dcvc_view {
+  float *data;
+  int32_t h, w, c;   /* logical extent */
+  int32_t cstride;   /* floats between consecutive pixels */
+  int32_t coff;      /* first channel of the view inside the pixel */
+} dcvc_view;
+
+const char *dcvc_last_error(void);
+int dcvc_version(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+int64_t dcvc_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Convolution with fused prologue/epilogue.  Replaces nn.Conv2d (+ LeakyReLU/ReLU, residual
+ * adds, `* q`, nn.PixelShuffle, the ConvFFN2 gate) -- reference DCVC-DC/src/models/layers.py:18-222,
+ * video_net.py:58-251.
+ *
+ *   acc[n]  = bias[n] + sum_{tap,c} lrelu(in[.., c], in_slope) * weight[(tap*cin + c)*cout_w + n]
+ *   gate:   v[i] = acc[2i] * lrelu(acc[2i+1], gate_slope)          (cout_w/2 values)
+ *   v       = lrelu(v, out_slope)                                   (slope 1 = identity, 0 = ReLU)
+ *   v      += res1[dst] + res2[dst]                                 (when present)
+ *   v      *= scale[dst channel]                                    (when present)
+ *   shuffle: raw channel n goes to pixel (2*oy + ((n>>1)&1), 2*ox + (n&1)), channel n>>2
+ *   out[dst] = v ;  out2[dst] = lrelu(v, out2_slope)                (when present)
+ *
+ * weight layout: [ksize*ksize][cin][cout_w] fp32 ("KN"); for the tensor-core path additionally
+ * weight_tc: [cout_pad][ksize*ksize][cin_pad] ("NK", K-major), see dcvc_conv_tc_pack_bytes().
+ * `mode`: 0 = fp32 FMA on CUDA cores (exact mode), 1 = tcgen05 kind::tf32 with fp32 TMEM
+ * accumulators where the shape is eligible (falls back to 0 otherwise; the decision depends
+ * only on the shape, never on data, so encoder and decoder always agree).
+ */
+typedef struct dcvc_conv {
+  dcvc_view in, out, res1, res2, out2;
+  const float *weight;
+  const float *weight_tc; /* may be NULL -> mode 0 */
+  const float *bias;      /* may be NULL */
+  const float *scale;     /* may be NULL */
+  int32_t ksize, stride, pad;
+  int32_t cout_w;         /* raw conv output channels */
+  int32_t gate, shuffle;
+  float in_slope, out_slope, gate_slope, out2_slope;
+  int32_t mode;
+} dcvc_conv;
+
+int dcvc_conv2d(const dcvc_conv *d, void *stream);
+/* returns 1 if the tensor-core kernel would take this descriptor */
+int dcvc_conv_tc_eligible(const dcvc_conv *d);
+/* bytes of the NK packed weight, and the packer (host pointers, runs on the host once per model) */
+size_t dcvc_conv_tc_pack_bytes(int cout_w, int cin, int ksize);
+int dcvc_conv_tc_pack(const float *w_oihw, int cout_w, int cin, int ksize, float *dst);
+
+/* depthwise 3x3, pad 1, stride 1 (DepthConv.depth_conv, layers.py:148); weight [9][c], bias [c] */
+int dcvc_dwconv3x3(const dcvc_view *in, const dcvc_view *out, const float *weight,
+                   const float *bias, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Motion / resampling group (reference DCVC-DC/src/models/video_net.py:8-55,104-126,
+ * video_model.py:26-63).
+ */
+/* NCHW (contiguous, c planes of h*w) <-> NHWC view */
+int dcvc_nchw_to_nhwc(const float *src, const dcvc_view *dst, void *stream);
+int dcvc_nhwc_to_nchw(const dcvc_view *src, float *dst, int clamp01, void *stream);
+/* dst(y,x,:) = mul * lrelu(src(min(y,h-1), min(x,w-1), :), slope): channel-slice copy,
+ * replicate pad (pad_for_y, common_model.py:70-78) and crop (slice_to_y, :85-86) */
+int dcvc_copy(const dcvc_view *src, const dcvc_view *dst, float mul, float slope, void *stream);
+int dcvc_fill(const dcvc_view *dst, float value, void *stream);
+/* 2x2/2 pooling; mode 0 = average (F.avg_pool2d), 1 = max (nn.MaxPool2d) */
+int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream);
+/* F.interpolate(mode='bilinear', align_corners=False) to dst's size, times `mul` */
+int dcvc_resize_bilinear(const dcvc_view *src, const dcvc_view *dst, float mul, void *stream);
+/* flow_warp: grid_sample(bilinear, border, align_corners=True) at (x + flow[0], y + flow[1]) */
+int dcvc_flow_warp(const dcvc_view *feat, const dcvc_view *flow, const dcvc_view *out,
+                   void *stream);
+/* OffsetDiversity from the 96-channel offset/mask tensor at half resolution onward:
+ * bilinear x2, 40*tanh + flow, sigmoid mask, 32 three-channel warps, grouped 1x1 fusion
+ * (video_model.py:46-63).  fusion_w [48][6], fusion_b [48]. */
+int dcvc_offset_diversity(const dcvc_view *x, const dcvc_view *offs_half, const dcvc_view *flow,
+                          const float *fusion_w, const float *fusion_b, const dcvc_view *out,
+                          void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Quad-part entropy model (reference DCVC-DC/src/models/common_model.py:39-61,92-321,
+ * entropy_models.py:269-273).
+ *
+ * Latents are NHWC views with C channels; C4 = C/4.  `params` holds [quant_step | scales |
+ * means] (3C channels).  Step s codes channel group g at the 2x2 position MASK_OF[s][g].
+ * For s >= 1 `prior` is the y_spatial_prior output [scales(C) | means(C)]; for s == 0 pass
+ * prior.data == NULL and scales/means come from `params`.
+ *
+ * edges: 256 fp32 thresholds, index(scale) = (number of edges <= max(scale,1e-5)) - 1, built by
+ * the host so that the result is bit-identical to GaussianEncoder.build_indexes.
+ *
+ * symbols/indexes (may be NULL in estimate mode): int16 / uint8 arrays of C4*h*w entries in the
+ * reference's [1,C4,h,w] order ((j*h + y)*w + x).
+ */
+typedef struct dcvc_quad {
+  dcvc_view y;        /* encoder input (C); unused by the decode step */
+  dcvc_view params;   /* 3C */
+  dcvc_view prior;    /* 2C or data == NULL */
+  dcvc_view y_hat;    /* C, un-scaled y_hat_so_far slice (conv input of the next step) */
+  dcvc_view y_out;    /* C, y_hat * quant_step (final latent), written at coded positions */
+  const float *edges; /* device, 256 */
+  int32_t step;
+  int32_t distribution; /* 0 laplace, 1 gaussian (bit estimate only) */
+} dcvc_quad;
+
+/* encoder: quantise the step's positions, write y_hat/y_out, emit symbols + CDF indexes,
+ * and (bits != NULL) add the estimated bits of the step to *bits via per-block partials
+ * reduced in a fixed order. bits_ws: >= dcvc_quad_bits_ws_bytes(C4*h*w) */
+size_t dcvc_quad_bits_ws_bytes(int64_t n);
+int dcvc_quad_step_enc(const dcvc_quad *q, int16_t *symbols, uint8_t *indexes, float *bits,
+                       void *bits_ws, void *stream);
+/* decoder, phase 1: CDF indexes of the step's positions (scales_r -> build_indexes) */
+int dcvc_quad_step_indexes(const dcvc_quad *q, uint8_t *indexes, void *stream);
+/* decoder, phase 2: scatter decoded symbols: y_hat = sym + mean at the step's positions */
+int dcvc_quad_step_dec(const dcvc_quad *q, const int16_t *symbols, void *stream);
+
+/* hyper latent: z_hat = round(z) (NHWC in place allowed), symbols in [1,C,h,w] order, and
+ * (bits != NULL) factorised-prior bit estimate (BitEstimator, entropy_models.py:58-122;
+ * fparams = [h1 b1 a1 h2 b2 a2 h3 b3 a3 h4 b4][C] raw parameters) */
+int dcvc_z_quant(const dcvc_view *z, const dcvc_view *z_hat, int16_t *symbols,
+                 const float *fparams, float *bits, void *bits_ws, void *stream);
+/* decoded z symbols [1,C,h,w] int16 -> NHWC fp32 view */
+int dcvc_z_dequant(const int16_t *symbols, const dcvc_view *z_hat, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Tables (host side, run once per model).  Replaces MLCodec_CXX.pmf_to_quantized_cdf
+ * (DCVC-DC/src/cpp/ops/ops.cpp:24-82).  cdf has n+1 entries.  Host pointers. */
+int dcvc_pmf_to_quantized_cdf(const float *pmf, int n, int precision, uint32_t *cdf);
+
+/* ------------------------------------------------------------------------------------------
+ * rANS coder on the GPU.  Replaces MLCodec_rans.RansEncoder / RansDecoder
+ * (DCVC-DC/src/cpp/py_rans/py_rans.cpp:11-225, rans/rans.cpp:76-331).
+ *
+ * A table set is {cdf int32 [T][L], sizes int32 [T], offsets int32 [T]} in device memory.
+ * Encoder protocol (mirrors reset / encode_with_indexes* / flush / get_encoded_stream):
+ *   dcvc_rans_enc_reset, then dcvc_rans_enc_push per call (device symbol/index arrays are
+ *   borrowed until flush), then dcvc_rans_enc_flush which runs the coder kernels, assembles the
+ *   container on the device, and copies it to `out_host` (synchronises the stream).
+ * mode DCVC_RANS_COMPAT: byte-identical to the reference container with `parts` in 1..16
+ *   (one device thread per part: this mode exists for interoperability, not speed).
+ * mode DCVC_RANS_INTERLEAVED: `parts` warps x 32 lanes of 32-bit rANS sharing one word stream
+ *   per warp (own container; see DESIGN.md "Interleaved stream").
+ * Decoder protocol (mirrors set_stream / decode_stream*): dcvc_rans_dec_set_stream copies the
+ *   container to the device and initialises the lanes; each dcvc_rans_dec_pull decodes n symbols
+ *   for device-resident indexes into a device int16 array, continuing from the previous call.
+ */
+#define DCVC_RANS_COMPAT 0
+#define DCVC_RANS_INTERLEAVED 1
+#define DCVC_RANS_MAX_CALLS 32
+
+typedef struct dcvc_rans dcvc_rans; /* opaque coder context (encoder + decoder state) */
+
+typedef struct dcvc_tables {
+  const int32_t *cdf;     /* device [T][stride] */
+  const int32_t *sizes;   /* device [T] */
+  const int32_t *offsets; /* device [T] */
+  int32_t count, stride;
+} dcvc_tables;
+
+int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t max_symbols_per_frame);
+void dcvc_rans_destroy(dcvc_rans *r);
+int dcvc_rans_enc_reset(dcvc_rans *r);
+/* index_is_u8: indexes are uint8 table rows (y parts); otherwise NULL indexes means
+ * "index = position / plane" (the factorised z prior: channel id), plane = h*w */
+int dcvc_rans_enc_push(dcvc_rans *r, const int16_t *symbols, const uint8_t *indexes, int64_t n,
+                       int64_t plane, const dcvc_tables *t);
+int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_capacity, size_t *out_len,
+                        void *stream);
+int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_t len, void *stream);
+int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t n, int64_t plane,
+                       const dcvc_tables *t, int16_t *symbols_out, void *stream);
+/* device error flag of the decoder/encoder kernels (0 ok); synchronises the stream */
+int dcvc_rans_status(dcvc_rans *r, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DCVC_B200_H */
