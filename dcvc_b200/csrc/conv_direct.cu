@@ -19,7 +19,7 @@ constexpr int NT = 256;
 struct ConvArgs {
   dcvc_view in, out, res1, res2, out2;
   const float *weight, *bias, *scale;
-  int ksize, stride, pad, cout_w, gate, shuffle;
+  int ksize, stride, pad, cout_w, gate, shuffle, clamp01;
   float in_slope, out_slope, gate_slope, out2_slope;
   int hout, wout;  // raw conv output grid (before shuffle)
 };
@@ -36,6 +36,7 @@ __device__ __forceinline__ void epilogue_store(const ConvArgs &a, int oy, int ox
   if (a.res1.data) v += a.res1.data[vidx(a.res1, y, x) + c];
   if (a.res2.data) v += a.res2.data[vidx(a.res2, y, x) + c];
   if (a.scale) v *= a.scale[c];
+  if (a.clamp01) v = fminf(fmaxf(v, 0.f), 1.f);
   a.out.data[vidx(a.out, y, x) + c] = v;
   if (a.out2.data) a.out2.data[vidx(a.out2, y, x) + c] = lrelu(v, a.out2_slope);
 }
@@ -254,7 +255,7 @@ static int conv_direct_launch(const dcvc_conv *d, int hout, int wout, cudaStream
   a.in = d->in; a.out = d->out; a.res1 = d->res1; a.res2 = d->res2; a.out2 = d->out2;
   a.weight = d->weight; a.bias = d->bias; a.scale = d->scale;
   a.ksize = d->ksize; a.stride = d->stride; a.pad = d->pad; a.cout_w = d->cout_w;
-  a.gate = d->gate; a.shuffle = d->shuffle;
+  a.gate = d->gate; a.shuffle = d->shuffle; a.clamp01 = d->clamp01;
   a.in_slope = d->in_slope; a.out_slope = d->out_slope; a.gate_slope = d->gate_slope;
   a.out2_slope = d->out2_slope;
   a.hout = hout; a.wout = wout;

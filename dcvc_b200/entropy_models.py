@@ -1,0 +1,214 @@
+"""Entropy-model host side: CDF tables, scale->index thresholds and the coder facade.
+
+Mirrors the reference's DCVC-DC/src/models/entropy_models.py: `EntropyCoder` (:9-55),
+`BitEstimator.update` (:124-178), `GaussianEncoder.update` (:203-267) and `build_indexes`
+(:269-273).  Tables are built once per model on the host in fp32 exactly as the reference does
+when its model lives on the CPU (the table content defines the bitstream), then uploaded; the
+per-frame work (index lookup, quantisation, coding) runs in the CUDA kernels and never returns
+to the host except for the finished byte stream.
+"""
+import ctypes
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+
+SCALE_MIN = {"laplace": 0.01, "gaussian": 0.11}
+SCALE_MAX = 64.0
+SCALE_LEVELS = 256
+DIST_ID = {"laplace": 0, "gaussian": 1}
+
+
+def pmf_to_quantized_cdf(pmf, precision=16):
+    """MLCodec_CXX.pmf_to_quantized_cdf (ops.cpp:84-91) through the C ABI (host function)."""
+    p = np.ascontiguousarray(np.asarray(pmf, dtype=np.float32))
+    cdf = np.zeros(p.size + 1, dtype=np.uint32)
+    _lib.check(_lib.lib().dcvc_pmf_to_quantized_cdf(p.ctypes.data, p.size, precision,
+                                                    cdf.ctypes.data))
+    return cdf
+
+
+def _rows_to_cdf(pmf, tail_mass, pmf_length, max_length):
+    cdf = np.zeros((len(pmf_length), max_length + 2), dtype=np.int32)
+    for i in range(len(pmf_length)):
+        n = int(pmf_length[i])
+        prob = torch.cat((pmf[i][:n], tail_mass[i]), dim=0)
+        row = pmf_to_quantized_cdf(prob.numpy())
+        cdf[i, :row.size] = row.astype(np.int32)
+    return cdf
+
+
+def _distribution(name, scale):
+    zero = torch.zeros_like(scale)
+    if name == "laplace":
+        return torch.distributions.laplace.Laplace(zero, scale)
+    return torch.distributions.normal.Normal(zero, scale)
+
+
+def scale_table(distribution):
+    return torch.exp(torch.linspace(math.log(SCALE_MIN[distribution]), math.log(SCALE_MAX),
+                                    SCALE_LEVELS))
+
+
+def gaussian_tables(distribution):
+    """GaussianEncoder.update: per scale level, support half-width = smallest i in [2,50] whose
+    CDF exceeds 0.9999 (else 50), integer PMF, two-sided tail mass -> quantised CDF rows."""
+    table = scale_table(distribution)
+    dist = _distribution(distribution, table)
+    half = torch.full_like(table, 50.0)
+    for i in range(50, 1, -1):
+        covered = dist.cdf(torch.full_like(table, float(i))) > 0.9999
+        half = torch.where(covered, torch.full_like(table, float(i)), half)
+    half = half.int()
+    length = 2 * half + 1
+    max_length = int(length.max())
+    samples = (torch.arange(max_length) - half[:, None]).float()
+    dist2 = _distribution(distribution, torch.zeros_like(samples) + table[:, None])
+    upper = dist2.cdf(samples + 0.5)
+    lower = dist2.cdf(samples - 0.5)
+    cdf = _rows_to_cdf(upper - lower, 2 * lower[:, :1], length, max_length)
+    return cdf, (length + 2).numpy().astype(np.int32), (-half).numpy().astype(np.int32)
+
+
+def factorized_cdf(params, x):
+    """BitEstimator.get_cdf: params = dict f1..f4 -> (h, b[, a]) tensors [1,C,1,1]; x [N,C,H,W]."""
+    for k in ("f1", "f2", "f3"):
+        h, b, a = params[k]
+        x = x * F.softplus(h) + b
+        x = x + torch.tanh(x) * torch.tanh(a)
+    h, b = params["f4"]
+    return torch.sigmoid(x * F.softplus(h) + b)
+
+
+def factorized_tables(params):
+    """BitEstimator.update on the host: per channel, support = [-(smallest i with cdf(-i) < 1e-4),
+    smallest i with cdf(i) > 0.9999] searched downward from 50."""
+    channel = params["f1"][0].numel()
+    zeros = torch.zeros(channel)
+    lo = zeros + 50
+    hi = zeros + 50
+    for i in range(50, 1, -1):
+        p = factorized_cdf(params, (zeros - i)[None, :, None, None]).reshape(-1)
+        lo = torch.where(p < 0.0001, zeros + i, lo)
+    for i in range(50, 1, -1):
+        p = factorized_cdf(params, (zeros + i)[None, :, None, None]).reshape(-1)
+        hi = torch.where(p > 0.9999, zeros + i, hi)
+    lo, hi = lo.int(), hi.int()
+    length = hi + lo + 1
+    max_length = int(length.max())
+    samples = torch.arange(max_length)[None, :] + (zeros - lo)[:, None, None]   # [C,1,L]
+    lower = factorized_cdf(params, samples - 0.5).squeeze(0)
+    upper = factorized_cdf(params, samples + 0.5).squeeze(0)
+    pmf = (upper - lower)[:, 0, :]
+    tail = lower[:, 0, :1] + (1.0 - upper[:, 0, -1:])
+    cdf = _rows_to_cdf(pmf, tail, length, max_length)
+    return cdf, (length + 2).numpy().astype(np.int32), lo.neg().numpy().astype(np.int32)
+
+
+def _index_of(scales, distribution):
+    """GaussianEncoder.build_indexes evaluated with torch CPU ops (the definition)."""
+    log_min = math.log(SCALE_MIN[distribution])
+    step = (math.log(SCALE_MAX) - log_min) / (SCALE_LEVELS - 1)
+    s = torch.maximum(scales, torch.zeros_like(scales) + 1e-5)
+    return ((torch.log(s) - log_min) / step).clamp_(0, SCALE_LEVELS - 1).int()
+
+
+def index_edges(distribution):
+    """edges[k] = smallest fp32 scale whose table index is >= k (edges[0] = 0).  The device
+    kernel's index = (#edges <= scale) - 1 is then bit-identical to build_indexes for every
+    fp32 input, with no dependence on the device's logf rounding."""
+    k = torch.arange(1, SCALE_LEVELS, dtype=torch.int32)
+    lo = torch.full((SCALE_LEVELS - 1,), int(np.float32(1e-5).view(np.int32)), dtype=torch.int32)
+    hi = torch.full((SCALE_LEVELS - 1,), int(np.float32(128.0).view(np.int32)), dtype=torch.int32)
+    # invariant: index(lo) < k <= index(hi)   (positive floats order like their bit patterns)
+    for _ in range(32):
+        mid = lo + (hi - lo) // 2
+        ge = _index_of(mid.view(torch.float32), distribution) >= k
+        hi = torch.where(ge, mid, hi)
+        lo = torch.where(ge, lo, mid)
+    return torch.cat((torch.zeros(1), hi.view(torch.float32)))
+
+
+class DeviceTables:
+    """One table set {cdf, sizes, offsets} resident on the device."""
+
+    def __init__(self, cdf, sizes, offsets, device):
+        self.cdf_np, self.sizes_np, self.offsets_np = cdf, sizes, offsets
+        self.cdf = torch.from_numpy(np.ascontiguousarray(cdf, dtype=np.int32)).to(device)
+        self.sizes = torch.from_numpy(np.ascontiguousarray(sizes, dtype=np.int32)).to(device)
+        self.offsets = torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.int32)).to(device)
+        self.c = _lib.Tables(self.cdf.data_ptr(), self.sizes.data_ptr(), self.offsets.data_ptr(),
+                             cdf.shape[0], cdf.shape[1])
+
+    def get_cdf_info(self):
+        return self.cdf_np, self.sizes_np, self.offsets_np
+
+
+class EntropyCoder:
+    """Facade over the GPU coder; call sequence mirrors entropy_models.py:9-55
+    (reset / encode* / flush / get_encoded_stream, set_stream / decode*).
+
+    mode "compat": the reference's container, byte-identical, stream_part in 1..16.
+    mode "interleaved": stream_part warps x 32 interleaved lanes (own container).
+    """
+
+    def __init__(self, ec_thread=False, stream_part=1, mode="compat", max_symbols=1 << 22,
+                 device="cuda"):
+        del ec_thread  # host threading does not exist here: the coder runs on the GPU
+        self.mode = mode
+        self.parts = int(stream_part)
+        self.max_symbols = int(max_symbols)
+        self.device = torch.device(device)
+        h = ctypes.c_void_p()
+        _lib.check(_lib.lib().dcvc_rans_create(ctypes.byref(h), 0 if mode == "compat" else 1,
+                                               self.parts, self.max_symbols))
+        self._h = h
+        self._cap = self.max_symbols * 4 + 1024
+        self._out = torch.empty(self._cap, dtype=torch.uint8).pin_memory()
+        self._stream_bytes = b""
+        self._keep = []
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            _lib.lib().dcvc_rans_destroy(h)
+            self._h = None
+
+    def reset(self):
+        self._keep = []
+        _lib.check(_lib.lib().dcvc_rans_enc_reset(self._h))
+
+    def encode(self, symbols, indexes, n, plane, tables):
+        """symbols int16 device tensor; indexes uint8 device tensor or None (index = pos//plane)."""
+        self._keep.append((symbols, indexes))   # borrowed until flush
+        _lib.check(_lib.lib().dcvc_rans_enc_push(
+            self._h, symbols.data_ptr(), indexes.data_ptr() if indexes is not None else None,
+            n, plane, ctypes.byref(tables.c)))
+
+    def flush(self):
+        n = ctypes.c_size_t(0)
+        _lib.check(_lib.lib().dcvc_rans_enc_flush(
+            self._h, self._out.data_ptr(), self._cap, ctypes.byref(n),
+            torch.cuda.current_stream().cuda_stream))
+        self._keep = []
+        self._stream_bytes = bytes(self._out[:n.value].numpy().tobytes())
+
+    def get_encoded_stream(self):
+        return self._stream_bytes
+
+    def set_stream(self, stream):
+        buf = np.frombuffer(stream, dtype=np.uint8)
+        _lib.check(_lib.lib().dcvc_rans_dec_set_stream(
+            self._h, buf.ctypes.data, buf.size, torch.cuda.current_stream().cuda_stream))
+
+    def decode(self, indexes, n, plane, tables, out):
+        _lib.check(_lib.lib().dcvc_rans_dec_pull(
+            self._h, indexes.data_ptr() if indexes is not None else None, n, plane,
+            ctypes.byref(tables.c), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        return out
+
+    def status(self):
+        _lib.check(_lib.lib().dcvc_rans_status(self._h, torch.cuda.current_stream().cuda_stream))

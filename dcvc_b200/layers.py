@@ -1,0 +1,163 @@
+"""Building blocks of the DCVC-DC networks as sequences of fused kernel launches.
+
+Each function mirrors one module of the reference (cited per function, paths relative to
+/root/reference/DCVC-DC/src/models) and states which elementwise work it folds into which
+convolution's prologue/epilogue.  `Net` owns the packed device weights of one model.
+"""
+import torch
+
+from . import ops
+from .ops import ConvW
+from .tensor import Act
+
+
+class Net:
+    """Packed weights by reference parameter name (packing happens once per load/.to())."""
+
+    def __init__(self, state_dict, device):
+        self.device = torch.device(device)
+        self.sd = {k: v.detach().to(self.device, torch.float32).contiguous()
+                   for k, v in state_dict.items()}
+        self._conv = {}
+        self._dw = {}
+        self._misc = {}
+
+    def has(self, name):
+        return (name + ".weight") in self.sd
+
+    def cw(self, name, gate=False, cin_perm=None):
+        """KN-packed conv weights: [kh*kw][cin][cout]; gate=True interleaves the two halves of the
+        output channels (ConvFFN2's chunk(2), layers.py:193-195) so the gate pairs are adjacent;
+        cin_perm reorders the input channels (new channel i reads reference channel cin_perm[i])
+        so a concatenated input can be laid out alignment-friendly."""
+        key = (name, gate, cin_perm)
+        r = self._conv.get(key)
+        if r is None:
+            w = self.sd[name + ".weight"]
+            b = self.sd.get(name + ".bias")
+            cout, cin, kh, kw = w.shape
+            assert kh == kw
+            if cin_perm is not None:
+                w = w[:, torch.tensor(cin_perm, device=w.device)]
+            if gate:
+                half = cout // 2
+                perm = torch.stack((torch.arange(half), torch.arange(half) + half), 1).reshape(-1)
+                perm = perm.to(w.device)
+                w = w[perm]
+                b = b[perm] if b is not None else None
+            wp = w.permute(2, 3, 1, 0).reshape(kh * kw * cin, cout).contiguous()
+            r = ConvW(wp, b.contiguous() if b is not None else None, cin, cout, kh, gate)
+            self._conv[key] = r
+        return r
+
+    def dw(self, name):
+        r = self._dw.get(name)
+        if r is None:
+            w = self.sd[name + ".weight"]            # [C,1,3,3]
+            c = w.shape[0]
+            r = (w.reshape(c, 9).t().contiguous(), self.sd[name + ".bias"].contiguous())
+            self._dw[name] = r
+        return r
+
+    def vec(self, name):
+        r = self._misc.get(name)
+        if r is None:
+            r = self.sd[name].reshape(-1).contiguous()
+            self._misc[name] = r
+        return r
+
+
+# ------------------------------------------------------------------------------- blocks
+def subpel(net, p, x, act=1.0, out=None, scale=None, res=None):
+    """subpel_conv1x1/3x3 (layers.py:23-39): conv to 4C with the depth-to-space store fused."""
+    return ops.conv(x, net.cw(p + ".0"), shuffle=True, act=act, out=out, scale=scale, res=res)
+
+
+def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, scale=None):
+    """ResBlock (video_net.py:58-76): lrelu(x) is conv1's input prologue, the second activation
+    conv1's epilogue, `x +` (and an optional outer residual/scale) conv2's epilogue."""
+    t = ops.conv(x, net.cw(p + ".conv1"), in_slope=slope, act=slope)
+    return ops.conv(t, net.cw(p + ".conv2"), act=slope if end_with_relu else 1.0, res=x,
+                    res2=res2, scale=scale, out=out)
+
+
+def depth_conv(net, p, x, out=None):
+    """DepthConv (layers.py:135-163), stride 1."""
+    identity = x
+    if net.has(p + ".adaptor"):
+        identity = ops.conv(x, net.cw(p + ".adaptor"))
+    t = ops.conv(x, net.cw(p + ".conv1.0"), act=0.01)
+    w, b = net.dw(p + ".depth_conv")
+    t = ops.dwconv3x3(t, w, b)
+    return ops.conv(t, net.cw(p + ".conv2"), res=identity, out=out)
+
+
+def dcb(net, p, x, out=None, scale=None):
+    """DepthConvBlock (layers.py:199-209) = DepthConv + ConvFFN (layers.py:166-179); an outer
+    `* q` rides on the last epilogue."""
+    t = depth_conv(net, p + ".block.0", x)
+    u = ops.conv(t, net.cw(p + ".block.1.conv.0"), act=0.1)
+    return ops.conv(u, net.cw(p + ".block.1.conv.2"), act=0.1, res=t, scale=scale, out=out)
+
+
+def dcb2(net, p, x, out=None, scale=None):
+    """DepthConvBlock2 (layers.py:212-222) = DepthConv + ConvFFN2 (layers.py:182-196); the
+    x1 * lrelu(x2) gate is the epilogue of the up-projection."""
+    t = depth_conv(net, p + ".block.0", x)
+    u = ops.conv(t, net.cw(p + ".block.1.conv", gate=True), gate_slope=0.1)
+    return ops.conv(u, net.cw(p + ".block.1.conv_out"), res=t, scale=scale, out=out)
+
+
+def rbws(net, p, x, out=None):
+    """ResidualBlockWithStride (layers.py:42-73), stride 2."""
+    t = ops.conv(x, net.cw(p + ".conv1"), stride=2, act=0.01)
+    idn = ops.conv(x, net.cw(p + ".downsample"), stride=2, pad=0)
+    return ops.conv(t, net.cw(p + ".conv2"), act=0.1, res=idn, out=out)
+
+
+def rbu(net, p, x, out=None, scale=None):
+    """ResidualBlockUpsample (layers.py:76-101)."""
+    up = subpel(net, p + ".upsample", x)
+    t = subpel(net, p + ".subpel_conv", x, act=0.01)
+    return ops.conv(t, net.cw(p + ".conv"), act=0.1, res=up, scale=scale, out=out)
+
+
+def unet(net, p, x, block, out=None):
+    """UNet / UNet2 (video_net.py:129-214); the two skip concatenations are shared buffers."""
+    dev = x.device
+    cat2 = Act.new(x.h, x.w, 64, dev)
+    cat3 = Act.new(x.h // 2, x.w // 2, 128, dev)
+    x1 = block(net, p + ".conv1", x, out=cat2.slice(0, 32))
+    x2 = block(net, p + ".conv2", ops.max_pool2(x1), out=cat3.slice(0, 64))
+    x3 = block(net, p + ".conv3", ops.max_pool2(x2))
+    for i in range(4):
+        x3 = block(net, f"{p}.context_refine.{i}", x3)
+    subpel(net, p + ".up3", x3, out=cat3.slice(64, 64))
+    d3 = block(net, p + ".up_conv3", cat3)
+    subpel(net, p + ".up2", d3, out=cat2.slice(32, 32))
+    return block(net, p + ".up_conv2", cat2, out=out)
+
+
+def hyper_enc5(net, p, x):
+    """get_hyper_enc_dec_models(reduce_enc_layer=False) encoder (video_net.py:226-237)."""
+    x = ops.conv(x, net.cw(p + ".0"), act=0.01)
+    x = ops.conv(x, net.cw(p + ".2"), act=0.01)
+    x = ops.conv(x, net.cw(p + ".4"), stride=2, act=0.01)
+    x = ops.conv(x, net.cw(p + ".6"), act=0.01)
+    return ops.conv(x, net.cw(p + ".8"), stride=2)
+
+
+def hyper_enc3(net, p, x):
+    """reduce_enc_layer=True encoder (video_net.py:218-225)."""
+    x = ops.conv(x, net.cw(p + ".0"), act=0.01)
+    x = ops.conv(x, net.cw(p + ".2"), stride=2, act=0.01)
+    return ops.conv(x, net.cw(p + ".4"), stride=2)
+
+
+def hyper_dec(net, p, x):
+    """hyper synthesis (video_net.py:239-249)."""
+    x = ops.conv(x, net.cw(p + ".0"), act=0.01)
+    x = subpel(net, p + ".2", x, act=0.01)
+    x = ops.conv(x, net.cw(p + ".4"), act=0.01)
+    x = subpel(net, p + ".6", x, act=0.01)
+    return ops.conv(x, net.cw(p + ".8"))

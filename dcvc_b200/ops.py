@@ -1,0 +1,177 @@
+"""Python front end of the kernels in libdcvc_b200.so: one function per C entry point, taking
+`Act`s and packed device weights.  Thin by design -- it builds the C descriptor and launches on
+torch's current stream.  No function here computes anything in Python or torch.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from .tensor import Act, NULL_VIEW, _stream
+
+# conv precision mode: 0 = fp32 FMA on CUDA cores (exact mode), 1 = tcgen05 TF32 where eligible
+CONV_MODE = 0
+
+
+def set_conv_mode(mode):
+    global CONV_MODE
+    assert mode in (0, 1)
+    CONV_MODE = int(mode)
+
+
+class ConvW:
+    """Packed device weights of one convolution (built by layers.pack_conv)."""
+    __slots__ = ("w", "w_tc", "b", "cin", "cout_w", "k", "gate")
+
+    def __init__(self, w, b, cin, cout_w, k, gate=False, w_tc=None):
+        self.w, self.b, self.cin, self.cout_w, self.k, self.gate, self.w_tc = \
+            w, b, cin, cout_w, k, gate, w_tc
+
+
+def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, res2=None,
+         scale=None, shuffle=False, out2=None, out2_slope=1.0, gate_slope=0.1, clamp01=False,
+         stream=None):
+    """Fused convolution; see dcvc_conv2d in include/dcvc_b200.h for the exact semantics."""
+    assert x.c == cw.cin, (x, cw.cin)
+    k = cw.k
+    pad = k // 2 if pad is None else pad
+    ho = (x.h + 2 * pad - k) // stride + 1
+    wo = (x.w + 2 * pad - k) // stride + 1
+    ec, eh, ew = cw.cout_w, ho, wo
+    if shuffle:
+        ec, eh, ew = ec // 4, ho * 2, wo * 2
+    if cw.gate:
+        ec //= 2
+    if out is None:
+        out = Act.new(eh, ew, ec, x.device)
+    d = _lib.Conv()
+    d.inp = x.view()
+    d.out = out.view()
+    d.res1 = res.view() if res is not None else NULL_VIEW
+    d.res2 = res2.view() if res2 is not None else NULL_VIEW
+    d.out2 = out2.view() if out2 is not None else NULL_VIEW
+    d.weight = cw.w.data_ptr()
+    d.weight_tc = cw.w_tc.data_ptr() if cw.w_tc is not None else None
+    d.bias = cw.b.data_ptr() if cw.b is not None else None
+    d.scale = scale.data_ptr() if scale is not None else None
+    d.ksize, d.stride, d.pad, d.cout_w = k, stride, pad, cw.cout_w
+    d.gate, d.shuffle = int(cw.gate), int(shuffle)
+    d.in_slope, d.out_slope, d.gate_slope, d.out2_slope = in_slope, act, gate_slope, out2_slope
+    d.mode = CONV_MODE
+    d.clamp01 = int(clamp01)
+    _lib.check(_lib.lib().dcvc_conv2d(ctypes.byref(d), _stream(stream)))
+    return out
+
+
+def dwconv3x3(x, w, b, out=None, stream=None):
+    if out is None:
+        out = Act.new(x.h, x.w, x.c, x.device)
+    _lib.check(_lib.lib().dcvc_dwconv3x3(x.view(), out.view(), w.data_ptr(),
+                                         b.data_ptr() if b is not None else None, _stream(stream)))
+    return out
+
+
+def copy(src, out=None, h=None, w=None, mul=1.0, slope=1.0, stream=None):
+    """Channel-slice copy; with (h, w) != src size: replicate pad / crop."""
+    if out is None:
+        out = Act.new(src.h if h is None else h, src.w if w is None else w, src.c, src.device)
+    _lib.check(_lib.lib().dcvc_copy(src.view(), out.view(), mul, slope, _stream(stream)))
+    return out
+
+
+def fill(dst, value, stream=None):
+    _lib.check(_lib.lib().dcvc_fill(dst.view(), value, _stream(stream)))
+    return dst
+
+
+def pool2(x, mode, out=None, stream=None):
+    if out is None:
+        out = Act.new(x.h // 2, x.w // 2, x.c, x.device)
+    _lib.check(_lib.lib().dcvc_pool2(x.view(), out.view(), mode, _stream(stream)))
+    return out
+
+
+def avg_pool2(x, out=None):
+    return pool2(x, 0, out)
+
+
+def max_pool2(x, out=None):
+    return pool2(x, 1, out)
+
+
+def resize_bilinear(x, h, w, mul=1.0, out=None, stream=None):
+    if out is None:
+        out = Act.new(h, w, x.c, x.device)
+    _lib.check(_lib.lib().dcvc_resize_bilinear(x.view(), out.view(), mul, _stream(stream)))
+    return out
+
+
+def flow_warp(feat, flow, out=None, stream=None):
+    if out is None:
+        out = Act.new(flow.h, flow.w, feat.c, feat.device)
+    _lib.check(_lib.lib().dcvc_flow_warp(feat.view(), flow.view(), out.view(), _stream(stream)))
+    return out
+
+
+def offset_diversity(x, offs_half, flow, fusion_w, fusion_b, out=None, stream=None):
+    if out is None:
+        out = Act.new(x.h, x.w, 48, x.device)
+    _lib.check(_lib.lib().dcvc_offset_diversity(x.view(), offs_half.view(), flow.view(),
+                                                fusion_w.data_ptr(), fusion_b.data_ptr(),
+                                                out.view(), _stream(stream)))
+    return out
+
+
+def to_nchw(x, clamp01=False, stream=None):
+    """Contiguous NCHW copy [1,C,H,W] of an Act."""
+    out = torch.empty((1, x.c, x.h, x.w), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.lib().dcvc_nhwc_to_nchw(x.view(), out.data_ptr(), int(clamp01),
+                                            _stream(stream)))
+    return out
+
+
+# ---------------------------------------------------------------------------- entropy model
+def _quad(y, params, prior, y_hat, y_out, edges, step, distribution):
+    q = _lib.Quad()
+    q.y = y.view() if y is not None else NULL_VIEW
+    q.params = params.view()
+    q.prior = prior.view() if prior is not None else NULL_VIEW
+    q.y_hat = y_hat.view()
+    q.y_out = y_out.view()
+    q.edges = edges.data_ptr()
+    q.step = step
+    q.distribution = distribution
+    return q
+
+
+def quad_step_enc(y, params, prior, y_hat, y_out, edges, step, distribution, symbols=None,
+                  indexes=None, bits=None, bits_ws=None, stream=None):
+    q = _quad(y, params, prior, y_hat, y_out, edges, step, distribution)
+    _lib.check(_lib.lib().dcvc_quad_step_enc(
+        ctypes.byref(q), symbols.data_ptr() if symbols is not None else None,
+        indexes.data_ptr() if indexes is not None else None,
+        bits.data_ptr() if bits is not None else None,
+        bits_ws.data_ptr() if bits_ws is not None else None, _stream(stream)))
+
+
+def quad_step_indexes(params, prior, y_hat, y_out, edges, step, indexes, stream=None):
+    q = _quad(None, params, prior, y_hat, y_out, edges, step, 0)
+    _lib.check(_lib.lib().dcvc_quad_step_indexes(ctypes.byref(q), indexes.data_ptr(),
+                                                 _stream(stream)))
+
+
+def quad_step_dec(params, prior, y_hat, y_out, edges, step, symbols, stream=None):
+    q = _quad(None, params, prior, y_hat, y_out, edges, step, 0)
+    _lib.check(_lib.lib().dcvc_quad_step_dec(ctypes.byref(q), symbols.data_ptr(), _stream(stream)))
+
+
+def z_quant(z, z_hat, symbols=None, fparams=None, bits=None, bits_ws=None, stream=None):
+    _lib.check(_lib.lib().dcvc_z_quant(
+        z.view(), z_hat.view(), symbols.data_ptr() if symbols is not None else None,
+        fparams.data_ptr() if fparams is not None else None,
+        bits.data_ptr() if bits is not None else None,
+        bits_ws.data_ptr() if bits_ws is not None else None, _stream(stream)))
+
+
+def z_dequant(symbols, z_hat, stream=None):
+    _lib.check(_lib.lib().dcvc_z_dequant(symbols.data_ptr(), z_hat.view(), _stream(stream)))

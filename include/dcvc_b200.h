@@ -59,6 +59,7 @@ int64_t dcvc_launch_count(void);
  *   v      += res1[dst] + res2[dst]                                 (when present)
  *   v      *= scale[dst channel]                                    (when present)
  *   shuffle: raw channel n goes to pixel (2*oy + ((n>>1)&1), 2*ox + (n&1)), channel n>>2
+ *   clamp01: v = min(max(v, 0), 1)                                   (x_hat.clamp_(0, 1))
  *   out[dst] = v ;  out2[dst] = lrelu(v, out2_slope)                (when present)
  *
  * weight layout: [ksize*ksize][cin][cout_w] fp32 ("KN"); for the tensor-core path additionally
@@ -78,6 +79,7 @@ typedef struct dcvc_conv {
   int32_t gate, shuffle;
   float in_slope, out_slope, gate_slope, out2_slope;
   int32_t mode;
+  int32_t clamp01;
 } dcvc_conv;
 
 int dcvc_conv2d(const dcvc_conv *d, void *stream);

@@ -1,0 +1,121 @@
+"""-m gpu end-to-end parity: IntraNoAR + DMC through the reference-facing module API against the
+CPU oracle (and the committed golden vectors produced by the unmodified reference).
+
+Tolerances (BASELINE.json north_star): reconstructions within 0.02 dB PSNR of the reference's,
+bpp within 0.5 %; encoder and decoder reconstructions of the product bit-identical; compat-mode
+streams decodable by the oracle's coder."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import dcvc_b200
+from dcvc_b200 import arch, synth
+from oracle import codec_oracle as co
+
+from gpu_util import dev, psnr
+
+pytestmark = pytest.mark.gpu
+
+
+def _models(seed, part_i, part_p, mode="compat"):
+    sd_i = arch.synth_state_dict(arch.intra_spec(), seed)
+    sd_p = arch.synth_state_dict(arch.dmc_spec(), seed + 100)
+    i_net = dcvc_b200.IntraNoAR(stream_part=part_i, coder_mode=mode)
+    p_net = dcvc_b200.DMC(stream_part=part_p, coder_mode=mode)
+    i_net.load_state_dict(sd_i)
+    p_net.load_state_dict(sd_p)
+    i_net = i_net.to(dev()).eval()
+    p_net = p_net.to(dev()).eval()
+    i_net.update(force=True)
+    p_net.update(force=True)
+    return i_net, p_net, sd_i, sd_p
+
+
+def _run_gop(i_net, p_net, frames, h, w, q_in_ckpt, q_index):
+    out = []
+    dpb = None
+    with torch.no_grad():
+        for k in range(frames.shape[0]):
+            x = frames[k:k + 1].to(dev())
+            if k == 0:
+                enc = i_net.compress(x, q_in_ckpt, q_index)
+                dec = i_net.decompress(enc["bit_stream"], h, w, q_in_ckpt, q_index)
+                assert torch.equal(enc["x_hat"], dec["x_hat"]), "I frame: enc/dec recon differ"
+                dpb = {"ref_frame": dec["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+                       "ref_y": None, "ref_mv_y": None}
+            else:
+                enc = p_net.compress(x, dpb, q_in_ckpt, q_index, k % 4)
+                dec = p_net.decompress(dpb, enc["bit_stream"], h, w, q_in_ckpt, q_index, k % 4)
+                for key in ("ref_frame", "ref_feature", "ref_mv_feature", "ref_y", "ref_mv_y"):
+                    assert torch.equal(enc["dpb"][key], dec["dpb"][key]), f"P frame {k}: {key}"
+                dpb = dec["dpb"]
+            out.append((enc["bit_stream"], dpb["ref_frame"].detach().cpu().contiguous()))
+    return out
+
+
+@pytest.mark.parametrize("name", ["a64", "b96x128"])
+def test_gop_vs_golden(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, f"dc_gop_{name}.npz"))
+    h, w, n, q_in_ckpt, q_index, part_i, part_p, seed = [int(v) for v in g["meta"]]
+    i_net, p_net, _, _ = _models(seed, part_i, part_p)
+    frames = synth.synth_frames(n, h, w, seed=seed)
+    res = _run_gop(i_net, p_net, frames, h, w, bool(q_in_ckpt), q_index)
+    for k, (stream, x_hat) in enumerate(res):
+        ref = torch.from_numpy(g[f"x_hat_{k}"])
+        src = frames[k:k + 1]
+        d_psnr = abs(psnr(x_hat, src) - psnr(ref, src))
+        ref_bits = g[f"stream_{k}"].size * 8
+        d_bpp = abs(len(stream) * 8 - ref_bits) / ref_bits
+        assert d_psnr < 0.02, f"frame {k}: PSNR differs by {d_psnr:.4f} dB"
+        assert d_bpp < 0.005 or abs(len(stream) * 8 - ref_bits) <= 64, \
+            f"frame {k}: bits differ by {d_bpp:.3%}"
+
+
+def test_compat_stream_decodes_with_oracle():
+    """The product's compat-mode frames are decodable by the oracle decoder (same container,
+    same tables): interchange with the reference."""
+    h = w = 64
+    i_net, p_net, sd_i, sd_p = _models(0, 1, 1)
+    frames = synth.synth_frames(2, h, w, seed=0)
+    res = _run_gop(i_net, p_net, frames, h, w, True, 1)
+    o_i = co.OracleIntra(sd_i, 1)
+    o_i.update()
+    with torch.no_grad():
+        dec = o_i.decompress(res[0][0], h, w, True, 1)
+    assert abs(psnr(dec["x_hat"], frames[0:1]) - psnr(res[0][1], frames[0:1])) < 0.02
+    assert float((dec["x_hat"] - res[0][1]).abs().max()) < 2e-2
+
+
+def test_estimate_mode_matches_oracle():
+    h = w = 64
+    i_net, p_net, sd_i, sd_p = _models(0, 1, 1)
+    o_i, o_p = co.OracleIntra(sd_i, 1), co.OracleDMC(sd_p, 1)
+    frames = synth.synth_frames(2, h, w, seed=0)
+    with torch.no_grad():
+        r = i_net.forward(frames[0:1].to(dev()), False, 20)
+        ro = o_i.forward(frames[0:1], False, 20)
+        assert abs(float(r["bit"]) - float(ro["bit"])) < 5e-3 * float(ro["bit"])
+        assert float((r["x_hat"].cpu() - ro["x_hat"]).abs().max()) < 1e-2
+        dpb = {"ref_frame": r["x_hat"].clamp_(0, 1), "ref_feature": None, "ref_mv_feature": None,
+               "ref_y": None, "ref_mv_y": None}
+        dpbo = {"ref_frame": ro["x_hat"].clamp_(0, 1), "ref_feature": None,
+                "ref_mv_feature": None, "ref_y": None, "ref_mv_y": None}
+        p = p_net.forward_one_frame(frames[1:2].to(dev()), dpb, False, 20, 1)
+        po = o_p.forward_one_frame(frames[1:2], dpbo, False, 20, 1)
+        assert abs(float(p["bit"]) - float(po["bit"])) < 5e-3 * float(po["bit"])
+        for key in ("bpp_y", "bpp_z", "bpp_mv_y", "bpp_mv_z"):
+            assert abs(float(p[key]) - float(po[key])) <= 5e-3 * float(po[key]) + 1e-6, key
+
+
+def test_interleaved_mode_round_trip_and_size():
+    h, w = 96, 128
+    i_c, p_c, _, _ = _models(1, 1, 1, "compat")
+    i_v, p_v, _, _ = _models(1, 2, 2, "interleaved")
+    frames = synth.synth_frames(3, h, w, seed=1)
+    rc = _run_gop(i_c, p_c, frames, h, w, False, 37)
+    rv = _run_gop(i_v, p_v, frames, h, w, False, 37)
+    for k in range(3):
+        assert torch.equal(rc[k][1], rv[k][1]), "reconstruction must not depend on the coder mode"
+        assert len(rv[k][0]) <= len(rc[k][0]) * 1.01 + 2 * 132 + 16
