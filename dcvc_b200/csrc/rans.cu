@@ -380,8 +380,9 @@ extern "C" int dcvc_rans_enc_reset(dcvc_rans *r) {
 
 extern "C" int dcvc_rans_enc_push(dcvc_rans *r, const int16_t *symbols, const uint8_t *indexes,
                                   int64_t n, int64_t plane, const dcvc_tables *t) {
-  if (!r || !symbols || !t || !t->cdf || !t->sizes || !t->offsets || n < 0)
+  if (!r || (!symbols && n > 0) || !t || !t->cdf || !t->sizes || !t->offsets || n < 0)
     return dcvc_fail(DCVC_ERR_ARG, "rans_enc_push: bad arguments");
+  if (n == 0) return DCVC_OK;  // an empty call codes nothing (the reference pushes no symbols)
   if (!indexes && plane < 1) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_push: plane needed without indexes");
   if (r->job.ncalls >= DCVC_RANS_MAX_CALLS) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_push: too many calls");
   int64_t total = n;
@@ -486,8 +487,9 @@ extern "C" int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_
 
 extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t n, int64_t plane,
                                   const dcvc_tables *t, int16_t *symbols_out, void *stream) {
-  if (!r || !t || !t->cdf || !symbols_out || n < 0 || r->dec_parts < 1)
+  if (!r || !t || !t->cdf || (!symbols_out && n > 0) || n < 0 || r->dec_parts < 1)
     return dcvc_fail(DCVC_ERR_ARG, "rans_dec_pull: bad arguments or no stream set");
+  if (n == 0) return DCVC_OK;
   if (!indexes && plane < 1) return dcvc_fail(DCVC_ERR_ARG, "rans_dec_pull: plane needed without indexes");
   CallRec cr;
   cr.sym = nullptr; cr.idx = indexes; cr.n = n; cr.plane = plane < 1 ? 1 : plane;

@@ -13,6 +13,35 @@ from .tensor import Act, NULL_VIEW, _stream
 CONV_MODE = 0
 
 
+# bench.py's per-launch profile: when a list, every wrapper appends
+# (kernel name, algorithmic flops, algorithmic bytes, start event, end event)
+PROFILE = None
+
+
+class _Prof:
+    __slots__ = ("name", "flops", "nbytes", "e0")
+
+    def __init__(self, name, flops=0, nbytes=0):
+        self.name, self.flops, self.nbytes = name, flops, nbytes
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if PROFILE is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            PROFILE.append((self.name, self.flops, self.nbytes, self.e0, e1))
+        return False
+
+
+def _nb(*acts):
+    return sum(4 * a.h * a.w * a.c for a in acts if a is not None)
+
+
 def set_conv_mode(mode):
     global CONV_MODE
     assert mode in (0, 1)
@@ -59,15 +88,25 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     d.in_slope, d.out_slope, d.gate_slope, d.out2_slope = in_slope, act, gate_slope, out2_slope
     d.mode = CONV_MODE
     d.clamp01 = int(clamp01)
-    _lib.check(_lib.lib().dcvc_conv2d(ctypes.byref(d), _stream(stream)))
+    if PROFILE is None:
+        _lib.check(_lib.lib().dcvc_conv2d(ctypes.byref(d), _stream(stream)))
+        return out
+    path = "tcgen05" if _lib.lib().dcvc_conv_tc_eligible(ctypes.byref(d)) else "fma"
+    name = f"conv{k}x{k}s{stride} {cw.cin}->{cw.cout_w} @{ho}x{wo} [{path}]"
+    flops = 2 * ho * wo * cw.cout_w * cw.cin * k * k
+    nbytes = _nb(x, out, res, res2, out2) + 4 * cw.w.numel()
+    with _Prof(name, flops, nbytes):
+        _lib.check(_lib.lib().dcvc_conv2d(ctypes.byref(d), _stream(stream)))
     return out
 
 
 def dwconv3x3(x, w, b, out=None, stream=None):
     if out is None:
         out = Act.new(x.h, x.w, x.c, x.device)
-    _lib.check(_lib.lib().dcvc_dwconv3x3(x.view(), out.view(), w.data_ptr(),
-                                         b.data_ptr() if b is not None else None, _stream(stream)))
+    with _Prof("dwconv3x3", 18 * x.h * x.w * x.c, _nb(x, out)):
+        _lib.check(_lib.lib().dcvc_dwconv3x3(x.view(), out.view(), w.data_ptr(),
+                                             b.data_ptr() if b is not None else None,
+                                             _stream(stream)))
     return out
 
 
@@ -75,7 +114,8 @@ def copy(src, out=None, h=None, w=None, mul=1.0, slope=1.0, stream=None):
     """Channel-slice copy; with (h, w) != src size: replicate pad / crop."""
     if out is None:
         out = Act.new(src.h if h is None else h, src.w if w is None else w, src.c, src.device)
-    _lib.check(_lib.lib().dcvc_copy(src.view(), out.view(), mul, slope, _stream(stream)))
+    with _Prof("copy", 0, 2 * _nb(out)):
+        _lib.check(_lib.lib().dcvc_copy(src.view(), out.view(), mul, slope, _stream(stream)))
     return out
 
 
@@ -87,7 +127,8 @@ def fill(dst, value, stream=None):
 def pool2(x, mode, out=None, stream=None):
     if out is None:
         out = Act.new(x.h // 2, x.w // 2, x.c, x.device)
-    _lib.check(_lib.lib().dcvc_pool2(x.view(), out.view(), mode, _stream(stream)))
+    with _Prof("pool2", 0, _nb(x, out)):
+        _lib.check(_lib.lib().dcvc_pool2(x.view(), out.view(), mode, _stream(stream)))
     return out
 
 
@@ -102,23 +143,27 @@ def max_pool2(x, out=None):
 def resize_bilinear(x, h, w, mul=1.0, out=None, stream=None):
     if out is None:
         out = Act.new(h, w, x.c, x.device)
-    _lib.check(_lib.lib().dcvc_resize_bilinear(x.view(), out.view(), mul, _stream(stream)))
+    with _Prof("resize_bilinear", 0, _nb(x, out)):
+        _lib.check(_lib.lib().dcvc_resize_bilinear(x.view(), out.view(), mul, _stream(stream)))
     return out
 
 
 def flow_warp(feat, flow, out=None, stream=None):
     if out is None:
         out = Act.new(flow.h, flow.w, feat.c, feat.device)
-    _lib.check(_lib.lib().dcvc_flow_warp(feat.view(), flow.view(), out.view(), _stream(stream)))
+    with _Prof("flow_warp", 0, _nb(feat, flow, out)):
+        _lib.check(_lib.lib().dcvc_flow_warp(feat.view(), flow.view(), out.view(),
+                                             _stream(stream)))
     return out
 
 
 def offset_diversity(x, offs_half, flow, fusion_w, fusion_b, out=None, stream=None):
     if out is None:
         out = Act.new(x.h, x.w, 48, x.device)
-    _lib.check(_lib.lib().dcvc_offset_diversity(x.view(), offs_half.view(), flow.view(),
-                                                fusion_w.data_ptr(), fusion_b.data_ptr(),
-                                                out.view(), _stream(stream)))
+    with _Prof("offset_diversity", 0, _nb(x, offs_half, flow, out)):
+        _lib.check(_lib.lib().dcvc_offset_diversity(x.view(), offs_half.view(), flow.view(),
+                                                    fusion_w.data_ptr(), fusion_b.data_ptr(),
+                                                    out.view(), _stream(stream)))
     return out
 
 

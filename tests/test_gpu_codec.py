@@ -62,15 +62,56 @@ def test_gop_vs_golden(golden_dir, name):
     i_net, p_net, _, _ = _models(seed, part_i, part_p)
     frames = synth.synth_frames(n, h, w, seed=seed)
     res = _run_gop(i_net, p_net, frames, h, w, bool(q_in_ckpt), q_index)
+    # Free-running GOP: symbol flips at .5 rounding boundaries (different fp32 summation order
+    # than oneDNN) feed back through the dpb, so per-frame drift is allowed 0.05 dB while the
+    # sequence averages -- what an RD point reports -- must meet the 0.02 dB / 0.5 % tolerance.
+    # test_frames_teacher_forced checks every frame at 0.02 dB without the feedback.
+    d_psnrs, bits, ref_bits = [], 0, 0
     for k, (stream, x_hat) in enumerate(res):
         ref = torch.from_numpy(g[f"x_hat_{k}"])
         src = frames[k:k + 1]
-        d_psnr = abs(psnr(x_hat, src) - psnr(ref, src))
-        ref_bits = g[f"stream_{k}"].size * 8
-        d_bpp = abs(len(stream) * 8 - ref_bits) / ref_bits
-        assert d_psnr < 0.02, f"frame {k}: PSNR differs by {d_psnr:.4f} dB"
-        assert d_bpp < 0.005 or abs(len(stream) * 8 - ref_bits) <= 64, \
-            f"frame {k}: bits differ by {d_bpp:.3%}"
+        d_psnrs.append(psnr(x_hat, src) - psnr(ref, src))
+        bits += len(stream) * 8
+        ref_bits += g[f"stream_{k}"].size * 8
+        assert abs(d_psnrs[-1]) < 0.05, f"frame {k}: PSNR differs by {d_psnrs[-1]:.4f} dB"
+        rb = g[f"stream_{k}"].size * 8
+        assert abs(len(stream) * 8 - rb) <= max(0.01 * rb, 64), f"frame {k}: bits {len(stream) * 8} vs {rb}"
+    assert abs(sum(d_psnrs) / len(d_psnrs)) < 0.02, d_psnrs
+    assert abs(bits - ref_bits) <= 0.005 * ref_bits, (bits, ref_bits)
+
+
+def _to_dev(dpb):
+    return {k: (v.to(dev()) if v is not None else None) for k, v in dpb.items()}
+
+
+def test_frames_teacher_forced():
+    """Every frame coded from the ORACLE's decoded-picture buffer (no drift feedback): recon
+    within 0.02 dB PSNR and stream size within 0.5 % (or 8 bytes) of the oracle, per frame."""
+    h, w, n, seed = 64, 64, 4, 0
+    i_net, p_net, sd_i, sd_p = _models(seed, 1, 1)
+    o_i, o_p = co.OracleIntra(sd_i, 1), co.OracleDMC(sd_p, 1)
+    o_i.update()
+    o_p.update()
+    frames = synth.synth_frames(n, h, w, seed=seed)
+    torch.set_num_threads(8)
+    with torch.no_grad():
+        ref = o_i.compress(frames[0:1], False, 10)
+        enc = i_net.compress(frames[0:1].to(dev()), False, 10)
+        pairs = [(enc["bit_stream"], enc["x_hat"].cpu(), ref["bit_stream"], ref["x_hat"])]
+        dpbo = {"ref_frame": ref["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+                "ref_y": None, "ref_mv_y": None}
+        for k in range(1, n):
+            refp = o_p.compress(frames[k:k + 1], dpbo, False, 10, k % 4)
+            encp = p_net.compress(frames[k:k + 1].to(dev()), _to_dev(dpbo), False, 10, k % 4)
+            decp = p_net.decompress(_to_dev(dpbo), encp["bit_stream"], h, w, False, 10, k % 4)
+            assert torch.equal(encp["dpb"]["ref_frame"], decp["dpb"]["ref_frame"])
+            pairs.append((encp["bit_stream"], decp["dpb"]["ref_frame"].cpu(), refp["bit_stream"],
+                          refp["dpb"]["ref_frame"]))
+            dpbo = refp["dpb"]
+    for k, (s, xh, rs, rxh) in enumerate(pairs):
+        d = abs(psnr(xh, frames[k:k + 1]) - psnr(rxh, frames[k:k + 1]))
+        assert d < 0.02, f"frame {k}: dPSNR {d:.4f}"
+        assert abs(len(s) - len(rs)) <= max(8, 0.005 * len(rs)), (k, len(s), len(rs))
 
 
 def test_compat_stream_decodes_with_oracle():
