@@ -48,8 +48,8 @@ SIGNATURES = {
     "dcvc_launch_count": (c_int64, []),
     "dcvc_conv2d": (c_int, [ctypes.POINTER(Conv), c_void_p]),
     "dcvc_conv_tc_eligible": (c_int, [ctypes.POINTER(Conv)]),
-    "dcvc_conv_tc_pack_bytes": (c_size_t, [c_int, c_int, c_int]),
-    "dcvc_conv_tc_pack": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),
+    "dcvc_conv_tc_geometry": (c_int, [c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                      ctypes.POINTER(c_int)]),
     "dcvc_dwconv3x3": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p]),
     "dcvc_nchw_to_nhwc": (c_int, [c_void_p, VP, c_void_p]),
     "dcvc_nhwc_to_nchw": (c_int, [VP, c_void_p, c_int, c_void_p]),

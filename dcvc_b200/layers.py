@@ -11,6 +11,27 @@ from .ops import ConvW
 from .tensor import Act
 
 
+def _round_tf32(w):
+    """fp32 -> nearest TF32 (round half away, like cvt.rna.tf32): the tensor core reads only the
+    top 19 bits, so pre-rounding the weights removes the truncation bias on the B operand."""
+    bits = w.contiguous().view(torch.int32)
+    return ((bits + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+def _pack_tc(w):
+    """NK-packed weights for the tcgen05 path: [n_pad][kh*kw][cin_pad], zero padded, TF32-rounded
+    (geometry from dcvc_conv_tc_geometry)."""
+    import ctypes
+    from . import _lib
+    cout, cin, kh, kw = w.shape
+    n_pad, cin_pad, kc = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _lib.check(_lib.lib().dcvc_conv_tc_geometry(cout, cin, ctypes.byref(n_pad),
+                                                ctypes.byref(cin_pad), ctypes.byref(kc)))
+    out = torch.zeros((n_pad.value, kh * kw, cin_pad.value), dtype=torch.float32, device=w.device)
+    out[:cout, :, :cin] = _round_tf32(w.permute(0, 2, 3, 1).reshape(cout, kh * kw, cin))
+    return out.contiguous()
+
+
 class Net:
     """Packed weights by reference parameter name (packing happens once per load/.to())."""
 
@@ -46,7 +67,8 @@ class Net:
                 w = w[perm]
                 b = b[perm] if b is not None else None
             wp = w.permute(2, 3, 1, 0).reshape(kh * kw * cin, cout).contiguous()
-            r = ConvW(wp, b.contiguous() if b is not None else None, cin, cout, kh, gate)
+            r = ConvW(wp, b.contiguous() if b is not None else None, cin, cout, kh, gate,
+                      w_tc=_pack_tc(w))
             self._conv[key] = r
         return r
 

@@ -73,6 +73,10 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
         ec //= 2
     if out is None:
         out = Act.new(eh, ew, ec, x.device)
+    if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= 512:
+        # the TMA-fed tensor-core kernel has no input prologue: materialise lrelu(x) once
+        x = copy(x, slope=in_slope)
+        in_slope = 1.0
     d = _lib.Conv()
     d.inp = x.view()
     d.out = out.view()

@@ -24,6 +24,11 @@ class DMC(CompressionModel):
         super().__init__(arch.dmc_spec(anchor_num), "laplace",
                          ("bit_estimator_z", "bit_estimator_z_mv"), ec_thread, stream_part,
                          anchor_num, coder_mode)
+        self.taps = None     # tests: dict receiving named intermediates (NCHW clones)
+
+    def _tap(self, name, act):
+        if self.taps is not None:
+            self.taps[name] = act.nchw().detach().clone()
 
     # ------------------------------------------------------------------ q
     @staticmethod
@@ -266,6 +271,13 @@ class DMC(CompressionModel):
         self._res_params(z_hat, dpb, ctx3, catb, y.c)
         y_hat, coded = self.forward_four_part_prior(y, catb, self._prior_fn("y"), write, b(0))
         x_hat, feature = self._recon(y_hat, bufs, y_q_dec)
+        if self.taps is not None:
+            for k, v in (("est_mv", est_mv), ("mv_y", mv_y), ("mv_z_hat", mv_z_hat),
+                         ("mv_params", mv_catb.slice(mv_y.c, 3 * mv_y.c)), ("mv_y_hat", mv_y_hat),
+                         ("mv_hat", mv_hat), ("ctx1", ctx1), ("ctx2", ctx2), ("ctx3", ctx3),
+                         ("y", y), ("z_hat", z_hat), ("params", catb.slice(y.c, 3 * y.c)),
+                         ("y_hat", y_hat), ("x_hat", x_hat)):
+                self._tap("p_" + k, v)
         new_dpb = {"ref_frame": x_hat.nchw(), "ref_feature": feature.nchw(),
                    "ref_mv_feature": mv_feature.nchw(), "ref_y": y_hat.nchw(),
                    "ref_mv_y": mv_y_hat.nchw()}

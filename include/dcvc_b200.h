@@ -85,9 +85,10 @@ typedef struct dcvc_conv {
 int dcvc_conv2d(const dcvc_conv *d, void *stream);
 /* returns 1 if the tensor-core kernel would take this descriptor */
 int dcvc_conv_tc_eligible(const dcvc_conv *d);
-/* bytes of the NK packed weight, and the packer (host pointers, runs on the host once per model) */
-size_t dcvc_conv_tc_pack_bytes(int cout_w, int cin, int ksize);
-int dcvc_conv_tc_pack(const float *w_oihw, int cout_w, int cin, int ksize, float *dst);
+/* geometry of the NK packed weight for the tensor-core path: rows n_pad = cout_w rounded up to
+ * 16, each row [ksize*ksize][cin_pad] with cin_pad = cin rounded up to the K chunk kc (32, 16 or
+ * 8 floats = one 128/64/32-byte swizzle row).  Padding entries must be zero. */
+int dcvc_conv_tc_geometry(int cout_w, int cin, int *n_pad, int *cin_pad, int *kc);
 
 /* depthwise 3x3, pad 1, stride 1 (DepthConv.depth_conv, layers.py:148); weight [9][c], bias [c] */
 int dcvc_dwconv3x3(const dcvc_view *in, const dcvc_view *out, const float *weight,

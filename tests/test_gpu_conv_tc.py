@@ -1,0 +1,126 @@
+"""-m gpu: the tcgen05/TMEM/TMA convolution (mode 1, kind::tf32, fp32 accumulate) against the
+fp32 oracle convolution.  Tolerance: TF32 keeps 10 mantissa bits per operand, so each product
+carries <= 2^-10 relative error; with K-term sums of random-sign terms the error of an output
+is ~ 2^-10 * |x||w| * sqrt(K).  The test bounds max|diff| by 4e-3 * sqrt(K) * rms(x) * rms(w)
+and the MEAN signed error (bias) by 10x less."""
+import ctypes
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from dcvc_b200 import _lib, layers, ops
+
+from gpu_util import dev, from_act, to_act
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _tc_mode():
+    ops.set_conv_mode(1)
+    yield
+    ops.set_conv_mode(0)
+
+
+def _rand(*shape, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return torch.rand(*shape, generator=g) * 2 - 1
+
+
+def _sd(cin, cout, k, seed):
+    g = torch.Generator().manual_seed(seed)
+    b = 1.0 / (cin * k * k) ** 0.5
+    return {"c.weight": (torch.rand(cout, cin, k, k, generator=g) * 2 - 1) * b,
+            "c.bias": (torch.rand(cout, generator=g) * 2 - 1) * b}
+
+
+def _check(out, ref, cin, k):
+    bound = 4e-3 * (cin * k * k) ** 0.5 * 0.58 * 0.58 / (cin * k * k) ** 0.5 + 1e-5
+    d = out - ref
+    assert float(d.abs().max()) < 4 * bound, float(d.abs().max())
+    assert abs(float(d.mean())) < bound / 10, float(d.mean())
+
+
+SHAPES = [
+    # cin, cout, k, stride, h, w
+    (48, 48, 3, 1, 48, 64), (64, 64, 3, 1, 32, 48), (32, 64, 7, 1, 40, 40), (8, 32, 7, 1, 40, 56),
+    (128, 192, 3, 1, 24, 40), (64, 256, 1, 1, 32, 32), (512, 128, 1, 1, 24, 24),
+    (16, 2, 7, 1, 32, 32), (48, 3, 3, 1, 32, 48), (80, 48, 3, 1, 30, 50), (96, 96, 3, 1, 17, 67),
+    (3, 48, 3, 1, 32, 32), (384, 384, 1, 1, 20, 28), (20, 24, 3, 1, 33, 47),
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,h,w", SHAPES)
+def test_tc_conv_stride1(cin, cout, k, stride, h, w):
+    sd = _sd(cin, cout, k, seed=cin * 7 + cout)
+    x = _rand(1, cin, h, w, seed=1)
+    pad = k // 2
+    ref = F.conv2d(x, sd["c.weight"], sd["c.bias"], stride, pad)
+    net = layers.Net(sd, dev())
+    xa = to_act(x)
+    cw = net.cw("c")
+    d = _lib.Conv()
+    out = ops.conv(xa, cw, stride=stride, pad=pad)
+    torch.cuda.synchronize()
+    _check(from_act(out), ref, cin, k)
+
+
+@pytest.mark.parametrize("cin,cout,k,h,w", [(53, 64, 3, 64, 96), (128, 96, 3, 48, 48),
+                                            (2, 64, 3, 64, 64), (64, 64, 1, 40, 56),
+                                            (3, 128, 3, 64, 64)])
+def test_tc_conv_stride2(cin, cout, k, h, w):
+    sd = _sd(cin, cout, k, seed=cin + cout)
+    x = _rand(1, cin, h, w, seed=2)
+    pad = k // 2
+    ref = F.conv2d(x, sd["c.weight"], sd["c.bias"], 2, pad)
+    net = layers.Net(sd, dev())
+    out = ops.conv(to_act(x), net.cw("c"), stride=2, pad=pad)
+    torch.cuda.synchronize()
+    _check(from_act(out), ref, cin, k)
+
+
+def test_tc_conv_epilogues_and_slices():
+    cin, cout, h, w = 32, 64, 40, 48
+    sd = _sd(cin, cout, 3, seed=5)
+    x, r1, r2 = _rand(1, cin, h, w, seed=1), _rand(1, cout, h, w, seed=2), _rand(1, cout, h, w, seed=3)
+    q = torch.rand(cout) + 0.5
+    conv = F.conv2d(x, sd["c.weight"], sd["c.bias"], 1, 1)
+    net = layers.Net(sd, dev())
+    xa = to_act(x, cstride=48, coff=8)
+    # lrelu + two residuals + scale + second output, into a channel slice
+    out = to_act(torch.zeros(1, cout, h, w), cstride=80, coff=12)
+    out2 = to_act(torch.zeros(1, cout, h, w))
+    ops.conv(xa, net.cw("c"), act=0.01, res=to_act(r1), res2=to_act(r2, 68, 4), scale=q.to(dev()),
+             out=out, out2=out2, out2_slope=0.2)
+    ref = (F.leaky_relu(conv, 0.01) + r1 + r2) * q.view(1, -1, 1, 1)
+    _check(from_act(out), ref, cin, 3)
+    _check(from_act(out2), F.leaky_relu(ref, 0.2), cin, 3)
+    # depth-to-space
+    out = ops.conv(xa, net.cw("c"), shuffle=True, act=0.01)
+    _check(from_act(out), F.leaky_relu(F.pixel_shuffle(conv, 2), 0.01), cin, 3)
+    # gate
+    x1, x2 = conv.chunk(2, 1)
+    out = ops.conv(xa, net.cw("c", gate=True), gate_slope=0.1)
+    _check(from_act(out), x1 * F.leaky_relu(x2, 0.1), cin, 3)
+    # clamp + input prologue (materialised copy)
+    out = ops.conv(xa, net.cw("c"), in_slope=0.1, clamp01=True)
+    _check(from_act(out), F.conv2d(F.leaky_relu(x, 0.1), sd["c.weight"], sd["c.bias"], 1, 1).clamp(0, 1), cin, 3)
+
+
+def test_tc_path_is_taken_and_deterministic():
+    sd = _sd(64, 64, 3, seed=1)
+    net = layers.Net(sd, dev())
+    xa = to_act(_rand(1, 64, 64, 64, seed=3))
+    cw = net.cw("c")
+    out = ops.Act.new(64, 64, 64, dev())
+    d = _lib.Conv()
+    d.inp, d.out = xa.view(), out.view()
+    d.weight, d.weight_tc, d.bias = cw.w.data_ptr(), cw.w_tc.data_ptr(), cw.b.data_ptr()
+    d.ksize, d.stride, d.pad, d.cout_w = 3, 1, 1, 64
+    d.in_slope = d.out_slope = d.gate_slope = d.out2_slope = 1.0
+    d.mode = 1
+    assert _lib.lib().dcvc_conv_tc_eligible(ctypes.byref(d)) == 1
+    a = from_act(ops.conv(xa, cw))
+    b = from_act(ops.conv(xa, cw))
+    assert torch.equal(a, b)            # run-to-run bit-identical (encoder/decoder agreement)
