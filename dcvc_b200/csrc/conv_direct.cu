@@ -176,7 +176,8 @@ __global__ void __launch_bounds__(NT) conv_direct_kernel(const ConvArgs a) {
   }
 }
 
-// depthwise 3x3 pad 1: one thread per (pixel, 4 channels)
+// depthwise 3x3 pad 1: one thread per (pixel, 4 channels); float4 path when the views allow it
+template <bool VEC>
 __global__ void dwconv3x3_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
                                  const float *__restrict__ b, int c4n) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -186,10 +187,15 @@ __global__ void dwconv3x3_kernel(dcvc_view in, dcvc_view out, const float *__res
   const int64_t p = t / c4n;
   const int x = (int)(p % in.w), y = (int)(p / in.w);
   const int c = cq * 4;
-  const int nc = min(4, in.c - c);
+  const int nc = VEC ? 4 : min(4, in.c - c);
   float acc[4];
+  if (VEC) {
+    const float4 bv = b ? *reinterpret_cast<const float4 *>(b + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    acc[0] = bv.x; acc[1] = bv.y; acc[2] = bv.z; acc[3] = bv.w;
+  } else {
 #pragma unroll
-  for (int j = 0; j < 4; ++j) acc[j] = (b && j < nc) ? b[c + j] : 0.f;
+    for (int j = 0; j < 4; ++j) acc[j] = (b && j < nc) ? b[c + j] : 0.f;
+  }
 #pragma unroll
   for (int dy = 0; dy < 3; ++dy) {
     const int iy = y + dy - 1;
@@ -200,15 +206,26 @@ __global__ void dwconv3x3_kernel(dcvc_view in, dcvc_view out, const float *__res
       if (ix < 0 || ix >= in.w) continue;
       const float *ip = in.data + vidx(in, iy, ix) + c;
       const float *wp = w + (dy * 3 + dx) * in.c + c;
+      if (VEC) {
+        const float4 iv = *reinterpret_cast<const float4 *>(ip);
+        const float4 wv = __ldg(reinterpret_cast<const float4 *>(wp));
+        acc[0] = fmaf(iv.x, wv.x, acc[0]); acc[1] = fmaf(iv.y, wv.y, acc[1]);
+        acc[2] = fmaf(iv.z, wv.z, acc[2]); acc[3] = fmaf(iv.w, wv.w, acc[3]);
+      } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (j < nc) acc[j] = fmaf(ip[j], wp[j], acc[j]);
+        for (int j = 0; j < 4; ++j)
+          if (j < nc) acc[j] = fmaf(ip[j], wp[j], acc[j]);
+      }
     }
   }
   float *op = out.data + vidx(out, y, x) + c;
+  if (VEC) {
+    *reinterpret_cast<float4 *>(op) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  } else {
 #pragma unroll
-  for (int j = 0; j < 4; ++j)
-    if (j < nc) op[j] = acc[j];
+    for (int j = 0; j < 4; ++j)
+      if (j < nc) op[j] = acc[j];
+  }
 }
 
 }  // namespace
@@ -297,7 +314,13 @@ extern "C" int dcvc_dwconv3x3(const dcvc_view *in, const dcvc_view *out, const f
     return dcvc_fail(DCVC_ERR_ARG, "dwconv: extent mismatch");
   const int c4n = (in->c + 3) / 4;
   const int64_t total = (int64_t)in->h * in->w * c4n;
-  dwconv3x3_kernel<<<cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(*in, *out, weight, bias, c4n);
+  const bool vec = (in->c & 3) == 0 && ((in->cstride | in->coff | out->cstride | out->coff) & 3) == 0 &&
+                   ((reinterpret_cast<uintptr_t>(in->data) | reinterpret_cast<uintptr_t>(out->data) |
+                     reinterpret_cast<uintptr_t>(weight) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0;
+  if (vec)
+    dwconv3x3_kernel<true><<<cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(*in, *out, weight, bias, c4n);
+  else
+    dwconv3x3_kernel<false><<<cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(*in, *out, weight, bias, c4n);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }

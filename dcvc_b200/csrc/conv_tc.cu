@@ -15,6 +15,7 @@
 // Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
 // warps 2..5 = epilogue (TMEM -> registers -> fused epilogue -> NHWC global stores).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <unordered_map>
@@ -24,18 +25,23 @@
 namespace {
 
 constexpr int TILE_M = 128;
-constexpr int NTHREADS = 192;
+constexpr int MAX_THREADS = 64 + 32 * 16;   // warp 0 TMA, warp 1 MMA, then 4/8/16 epilogue warps
 constexpr long long SPIN_CYCLES = 4000000000ll;  // ~2 s: a protocol bug faults instead of hanging
 
 struct TcArgs {
   dcvc_view out, res1, res2, out2;
   const float *bias, *scale;
-  int cout_w, n_pad, gate, shuffle, clamp01;
+  int cout_w, n_tile, tiles_n, gate, shuffle, clamp01;
   float out_slope, gate_slope, out2_slope;
-  int hout, wout, th, tw, tiles_x;
-  int ksize, stride, pad, kc, chunks_per_tap, stages;
-  uint32_t a_bytes, b_bytes, tx_bytes, tmem_cols, sbo, layout_type;
+  int hout, wout, th, tw, tiles_x, total_tiles;
+  int ksize, stride, pad, kc, chunks_per_tap, units, group, stages;
+  uint32_t unit_a, unit_b, unit_tx, tmem_cols, acc_stride, sbo, layout_type, stage_off;
+  int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
+  int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
+
+constexpr int STG_PITCH = 36;                    // floats per staged row (32 + 4: conflict-free)
+constexpr int STG_WARP_FLOATS = 32 * STG_PITCH;  // one epilogue warp's staging tile
 
 // ------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -127,43 +133,134 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr, uint32_t sbo_b
   return d;
 }
 
-// ------------------------------------------------------------------ epilogue store helpers
-__device__ __forceinline__ float finish(const TcArgs &a, float v, size_t o1, size_t o2, int c,
-                                        bool has1, bool has2) {
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// ------------------------------------------------------------------ epilogue (coalesced phase)
+// Code size matters here (the instruction cache is shared by three warp roles), so the general
+// case is one out-of-line scalar routine and only the common fully-aligned case is vectorised.
+
+// scalar fused epilogue for final channel c at final pixel (y, x)
+__device__ __noinline__ void finish_store(const TcArgs &a, int y, int x, int c, float v) {
   v = lrelu(v, a.out_slope);
-  if (has1) v += a.res1.data[o1 + c];
-  if (has2) v += a.res2.data[o2 + c];
+  if (a.res1.data) v += a.res1.data[vidx(a.res1, y, x) + c];
+  if (a.res2.data) v += a.res2.data[vidx(a.res2, y, x) + c];
   if (a.scale) v *= a.scale[c];
   if (a.clamp01) v = fminf(fmaxf(v, 0.f), 1.f);
-  return v;
+  a.out.data[vidx(a.out, y, x) + c] = v;
+  if (a.out2.data) a.out2.data[vidx(a.out2, y, x) + c] = lrelu(v, a.out2_slope);
+}
+
+__device__ __forceinline__ bool view_vec4(const dcvc_view &v) {
+  return ((v.cstride | v.coff) & 3) == 0 && (reinterpret_cast<uintptr_t>(v.data) & 15) == 0;
+}
+
+// phase 2 for one staged chunk (32 rows x ncols): lanes run along channels, so each group of
+// 8 (or 4) lanes reads/writes one pixel's 128 (64) contiguous bytes.
+// EPI: 0 plain, 1 gate (pairs), 2 shuffle (depth-to-space quads)
+template <int EPI>
+__device__ __noinline__ void epilogue_chunk(const TcArgs &a, const float *stg, int lane, int q,
+                                            int oy0, int ox0, int n_first, int ncols) {
+  const int vshift = ncols == 32 ? 3 : 2, vpr = 1 << vshift;
+  const int c4 = lane & (vpr - 1), rstep = 32 >> vshift;
+  const int n = n_first + 4 * c4;
+  if (n >= a.cout_w) return;
+  const int n_ok = min(4, a.cout_w - n);
+  float4 b = make_float4(0.f, 0.f, 0.f, 0.f), sc = make_float4(1.f, 1.f, 1.f, 1.f);
+  if (a.bias) {
+    b.x = __ldg(a.bias + n);
+    if (n_ok > 1) b.y = __ldg(a.bias + n + 1);
+    if (n_ok > 2) b.z = __ldg(a.bias + n + 2);
+    if (n_ok > 3) b.w = __ldg(a.bias + n + 3);
+  }
+  // fully vectorisable plain epilogue: every view 16-byte aligned and all four channels valid
+  const bool fast = EPI == 0 && n_ok == 4 && view_vec4(a.out) &&
+                    (!a.res1.data || view_vec4(a.res1)) && (!a.res2.data || view_vec4(a.res2)) &&
+                    (!a.out2.data || view_vec4(a.out2)) &&
+                    (!a.scale || (reinterpret_cast<uintptr_t>(a.scale) & 15) == 0);
+  if (fast && a.scale) sc = __ldg(reinterpret_cast<const float4 *>(a.scale + n));
+  const int tw_mask = a.tw - 1, tw_shift = 31 - __clz(a.tw);
+#pragma unroll 2
+  for (int r = lane >> vshift; r < 32; r += rstep) {
+    const int row = q * 32 + r;
+    const int oy = oy0 + (row >> tw_shift), ox = ox0 + (row & tw_mask);
+    if (oy >= a.hout || ox >= a.wout) continue;
+    float4 t = *reinterpret_cast<const float4 *>(stg + r * STG_PITCH + 4 * c4);
+    t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+    if (fast) {
+      t.x = lrelu(t.x, a.out_slope); t.y = lrelu(t.y, a.out_slope);
+      t.z = lrelu(t.z, a.out_slope); t.w = lrelu(t.w, a.out_slope);
+      if (a.res1.data) {
+        const float4 u = *reinterpret_cast<const float4 *>(a.res1.data + vidx(a.res1, oy, ox) + n);
+        t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+      }
+      if (a.res2.data) {
+        const float4 u = *reinterpret_cast<const float4 *>(a.res2.data + vidx(a.res2, oy, ox) + n);
+        t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+      }
+      t.x *= sc.x; t.y *= sc.y; t.z *= sc.z; t.w *= sc.w;
+      if (a.clamp01) {
+        t.x = fminf(fmaxf(t.x, 0.f), 1.f); t.y = fminf(fmaxf(t.y, 0.f), 1.f);
+        t.z = fminf(fmaxf(t.z, 0.f), 1.f); t.w = fminf(fmaxf(t.w, 0.f), 1.f);
+      }
+      *reinterpret_cast<float4 *>(a.out.data + vidx(a.out, oy, ox) + n) = t;
+      if (a.out2.data) {
+        t.x = lrelu(t.x, a.out2_slope); t.y = lrelu(t.y, a.out2_slope);
+        t.z = lrelu(t.z, a.out2_slope); t.w = lrelu(t.w, a.out2_slope);
+        *reinterpret_cast<float4 *>(a.out2.data + vidx(a.out2, oy, ox) + n) = t;
+      }
+    } else if (EPI == 0) {
+      const float w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll 1
+      for (int j = 0; j < n_ok; ++j) finish_store(a, oy, ox, n + j, w[j]);
+    } else if (EPI == 1) {
+      if (n_ok >= 2) finish_store(a, oy, ox, n >> 1, t.x * lrelu(t.y, a.gate_slope));
+      if (n_ok >= 4) finish_store(a, oy, ox, (n >> 1) + 1, t.z * lrelu(t.w, a.gate_slope));
+    } else {
+      // raw channel n+sp -> pixel (2oy + (sp>>1), 2ox + (sp&1)), channel n>>2
+      const float w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll 1
+      for (int sp = 0; sp < n_ok; ++sp)
+        finish_store(a, 2 * oy + (sp >> 1), 2 * ox + (sp & 1), n >> 2, w[sp]);
+    }
+  }
 }
 
 // ------------------------------------------------------------------ the kernel
-__global__ void __launch_bounds__(NTHREADS)
+// Persistent: each CTA walks tiles blockIdx.x, +gridDim.x, ...; the smem ring and the two TMEM
+// accumulators keep the TMA producer, the MMA issuer and the epilogue warps of consecutive
+// tiles overlapped.
+__global__ void __launch_bounds__(MAX_THREADS)
 conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-               const TcArgs a) {
+               const __grid_constant__ TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment for the swizzled tiles
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t stage_bytes = a.a_bytes + a.b_bytes;
-  const uint32_t bars = base + a.stages * stage_bytes;       // full[s], empty[s], acc_full
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t unit_bytes = a.unit_a + a.unit_b;
+  const uint32_t stage_bytes = a.group * unit_bytes;
+  const uint32_t bars = base + a.stages * stage_bytes;   // full[s], empty[s], tfull[2], tempty[2]
+  float *staging = reinterpret_cast<float *>(smem_raw + (base - raw) + a.stage_off);
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tile_x = blockIdx.x % a.tiles_x, tile_y = blockIdx.x / a.tiles_x;
-  const int ox0 = tile_x * a.tw, oy0 = tile_y * a.th;
-  const int iters = a.ksize * a.ksize * a.chunks_per_tap;
+  const int groups = (a.units + a.group - 1) / a.group;
 
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (a.stages + s); };
-  const uint32_t acc_bar = bars + 8u * (2 * a.stages);
+  auto tfull_bar = [&](int s) { return bars + 8u * (2 * a.stages + s); };
+  auto tempty_bar = [&](int s) { return bars + 8u * (2 * a.stages + 2 + s); };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < a.stages; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
     }
-    mbar_init(acc_bar, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), a.epi_warps);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -178,20 +275,32 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   const uint32_t tmem_base = tmem_base_slot;
 
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer: one stage = `group` (tap, channel-chunk) units =====
     if (lane == 0) {
-      int it = 0;
-      for (int tap = 0; tap < a.ksize * a.ksize; ++tap) {
-        const int dy = tap / a.ksize, dx = tap - dy * a.ksize;
-        const int ix = ox0 * a.stride + dx - a.pad, iy = oy0 * a.stride + dy - a.pad;
-        for (int ch = 0; ch < a.chunks_per_tap; ++ch, ++it) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+        const int mt = tile / a.tiles_n, nt = tile - mt * a.tiles_n;
+        const int ty = mt / a.tiles_x, tx = mt - ty * a.tiles_x;
+        const int ox0 = tx * a.tw, oy0 = ty * a.th, n_base = nt * a.n_tile;
+        for (int gi = 0; gi < groups; ++gi, ++it) {
           const int s = it % a.stages;
-          const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+          const uint32_t ph = (it / a.stages) & 1u;
           mbar_wait(empty_bar(s), ph ^ 1u);
-          const uint32_t sa = base + s * stage_bytes, sb = sa + a.a_bytes;
-          mbar_expect_tx(full_bar(s), a.tx_bytes);
-          tma_load_4d(sa, &map_a, full_bar(s), ch * a.kc, ix, iy, 0);
-          tma_load_2d(sb, &map_b, full_bar(s), (tap * a.chunks_per_tap + ch) * a.kc, 0);
+          const int u0 = gi * a.group, cnt = min(a.group, a.units - u0);
+          if (a.debug & 1) {
+            mbar_expect_tx(full_bar(s), 0);
+            continue;
+          }
+          mbar_expect_tx(full_bar(s), cnt * a.unit_tx);
+          for (int g = 0; g < cnt; ++g) {
+            const int u = u0 + g;
+            const int tap = u / a.chunks_per_tap, ch = u - tap * a.chunks_per_tap;
+            const int dy = tap / a.ksize, dx = tap - dy * a.ksize;
+            const uint32_t sa = base + s * stage_bytes + g * unit_bytes, sb = sa + a.unit_a;
+            tma_load_4d(sa, &map_a, full_bar(s), ch * a.kc, ox0 * a.stride + dx - a.pad,
+                        oy0 * a.stride + dy - a.pad, 0);
+            tma_load_2d(sb, &map_b, full_bar(s), u * a.kc, n_base);
+          }
         }
       }
     }
@@ -199,91 +308,76 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // ===== MMA issuer =====
     if (lane == 0) {
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
-                             ((uint32_t)(a.n_pad >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
-      const int kk_n = a.kc / 8;
-      for (int it = 0; it < iters; ++it) {
-        const int s = it % a.stages;
-        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
-        mbar_wait(full_bar(s), ph);
+                             ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
+      const int kk_n = (a.debug & 2) ? 0 : a.kc / 8;
+      uint32_t it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++lt) {
+        const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
+        mbar_wait(tempty_bar(as), aph ^ 1u);       // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t sa = base + s * stage_bytes, sb = sa + a.a_bytes;
-        const uint64_t da = make_smem_desc(sa, a.sbo, a.layout_type);
-        const uint64_t db = make_smem_desc(sb, a.sbo, a.layout_type);
-        for (int kk = 0; kk < kk_n; ++kk)      // +32 bytes along K per MMA: +2 in the >>4 field
-          umma_tf32(tmem_base, da + 2u * kk, db + 2u * kk, idesc, (it | kk) ? 1u : 0u);
-        umma_commit(empty_bar(s));             // frees the smem slot when these MMAs retire
+        const uint32_t tacc = tmem_base + as * a.acc_stride;
+        for (int gi = 0; gi < groups; ++gi, ++it) {
+          const int s = it % a.stages;
+          const uint32_t ph = (it / a.stages) & 1u;
+          mbar_wait(full_bar(s), ph);
+          tc_fence_after();
+          const int u0 = gi * a.group, cnt = min(a.group, a.units - u0);
+          for (int g = 0; g < cnt; ++g) {
+            const uint32_t sa = base + s * stage_bytes + g * unit_bytes, sb = sa + a.unit_a;
+            const uint64_t da = make_smem_desc(sa, a.sbo, a.layout_type);
+            const uint64_t db = make_smem_desc(sb, a.sbo, a.layout_type);
+            for (int kk = 0; kk < kk_n; ++kk)  // +32 bytes along K per MMA: +2 in the >>4 field
+              umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, ((u0 + g) | kk) ? 1u : 0u);
+          }
+          umma_commit(empty_bar(s));           // frees the smem slot when these MMAs retire
+        }
+        umma_commit(tfull_bar(as));            // accumulator complete
       }
-      umma_commit(acc_bar);                    // accumulator complete
     }
   } else {
-    // ===== epilogue: warp w owns TMEM lanes 32*(w%4) .. +31 =====
-    const int q = warp & 3;
-    const int row = q * 32 + lane;             // pixel of the tile
-    const int oy = oy0 + row / a.tw, ox = ox0 + row % a.tw;
-    const bool valid = oy < a.hout && ox < a.wout;
-    mbar_wait(acc_bar, 0);
-    tc_fence_after();
-    const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
-    const bool has1 = a.res1.data != nullptr, has2 = a.res2.data != nullptr;
-    for (int n0 = 0; n0 < a.n_pad; n0 += 16) {
-      float v[16];
-      tmem_ld16(trow + (uint32_t)n0, v);       // warp-collective: every lane takes part
-      if (!valid || n0 >= a.cout_w) continue;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) v[j] += (a.bias && n0 + j < a.cout_w) ? a.bias[n0 + j] : 0.f;
-      if (a.shuffle) {
-        // raw channel n -> pixel (2oy + ((n>>1)&1), 2ox + (n&1)), channel n>>2
-#pragma unroll
-        for (int sp = 0; sp < 4; ++sp) {
-          const int y = 2 * oy + (sp >> 1), x = 2 * ox + (sp & 1);
-          const size_t oo = vidx(a.out, y, x);
-          const size_t o1 = has1 ? vidx(a.res1, y, x) : 0, o2 = has2 ? vidx(a.res2, y, x) : 0;
-          const size_t oo2 = a.out2.data ? vidx(a.out2, y, x) : 0;
-#pragma unroll
-          for (int cc = 0; cc < 4; ++cc) {
-            const int n = n0 + 4 * cc + sp, c = n >> 2;
-            if (n < a.cout_w) {
-              const float r = finish(a, v[4 * cc + sp], o1, o2, c, has1, has2);
-              a.out.data[oo + c] = r;
-              if (a.out2.data) a.out2.data[oo2 + c] = lrelu(r, a.out2_slope);
-            }
-          }
+    // ===== epilogue: warps 2..2+epi_warps; warp w owns TMEM lanes 32*(w%4).., column chunks
+    // ci with ci % (epi_warps/4) == part.  Phase 1: thread = pixel row, tcgen05.ld 32 columns, park them in a
+    // padded smem tile; phase 2: lanes along channels -> coalesced fused epilogue.
+    const int q = warp & 3, part = (warp - 2) >> 2, parts = a.epi_warps >> 2;
+    float *stg = staging + (warp - 2) * STG_WARP_FLOATS;
+    const int nchunks = (a.n_tile + 31) >> 5;
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++lt) {
+      const int mt = tile / a.tiles_n, nt = tile - mt * a.tiles_n;
+      const int ty = mt / a.tiles_x, tx = mt - ty * a.tiles_x;
+      const int ox0 = tx * a.tw, oy0 = ty * a.th, n_base = nt * a.n_tile;
+      const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
+      mbar_wait(tfull_bar(as), aph);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + as * a.acc_stride + ((uint32_t)(q * 32) << 16);
+      int last = -1;
+      for (int ci = part; ci < nchunks; ci += parts) last = ci;
+      if (last < 0) {                                  // no columns for this warp: just release
+        if (lane == 0) mbar_arrive(tempty_bar(as));
+        continue;
+      }
+      for (int ci = part; ci < nchunks; ci += parts) {
+        const int n0 = ci * 32;
+        const int ncols = min(32, a.n_tile - n0);      // 16 or 32
+        float v[32];
+        tmem_ld16(trow + (uint32_t)n0, v);             // warp-collective
+        if (ncols == 32) tmem_ld16(trow + (uint32_t)n0 + 16u, v + 16);
+        if (ci == last) {                              // accumulator fully read: hand it back
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(as));
         }
-      } else {
-        const size_t oo = vidx(a.out, oy, ox);
-        const size_t o1 = has1 ? vidx(a.res1, oy, ox) : 0, o2 = has2 ? vidx(a.res2, oy, ox) : 0;
-        const size_t oo2 = a.out2.data ? vidx(a.out2, oy, ox) : 0;
-        if (a.gate) {
+        if (n_base + n0 >= a.cout_w || (a.debug & 4)) continue;   // warp-uniform
 #pragma unroll
-          for (int j = 0; j < 16; j += 2) {
-            const int c = (n0 + j) >> 1;
-            if (n0 + j + 1 < a.cout_w) {
-              const float r = finish(a, v[j] * lrelu(v[j + 1], a.gate_slope), o1, o2, c, has1, has2);
-              a.out.data[oo + c] = r;
-              if (a.out2.data) a.out2.data[oo2 + c] = lrelu(r, a.out2_slope);
-            }
-          }
-        } else {
-          float r[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            r[j] = (n0 + j < a.cout_w) ? finish(a, v[j], o1, o2, n0 + j, has1, has2) : 0.f;
-          float *op = a.out.data + oo + n0;
-          if (n0 + 16 <= a.cout_w && ((reinterpret_cast<uintptr_t>(op) & 15) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 16; j += 4)
-              *reinterpret_cast<float4 *>(op + j) = make_float4(r[j], r[j + 1], r[j + 2], r[j + 3]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (n0 + j < a.cout_w) op[j] = r[j];
-          }
-          if (a.out2.data) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (n0 + j < a.cout_w) a.out2.data[oo2 + n0 + j] = lrelu(r[j], a.out2_slope);
-          }
-        }
+        for (int j = 0; j < 8; ++j)
+          if (4 * j < ncols)
+            *reinterpret_cast<float4 *>(stg + lane * STG_PITCH + 4 * j) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+        if (a.shuffle) epilogue_chunk<2>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        else if (a.gate) epilogue_chunk<1>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        else epilogue_chunk<0>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        __syncwarp();
       }
     }
   }
@@ -367,11 +461,11 @@ int make_map_a(const dcvc_view &in, int kc, int th, int tw, int stride, CUtensor
   return DCVC_OK;
 }
 
-// weight map: dims (Ktot, N_pad), box (KC, N_pad)
-int make_map_b(const float *w, int ktot, int n_pad, int kc, CUtensorMap *out) {
+// weight map: dims (Ktot, N_pad), box (KC, N_tile)
+int make_map_b(const float *w, int ktot, int n_pad, int n_tile, int kc, CUtensorMap *out) {
   MapKey k{};
   k.ptr = (uint64_t)w; k.d0 = ktot; k.d1 = n_pad; k.s1 = (uint64_t)ktot * 4;
-  k.b0 = kc; k.b1 = n_pad; k.swz = swizzle_of(kc); k.rank = 2;
+  k.b0 = kc; k.b1 = n_tile; k.swz = swizzle_of(kc); k.rank = 2;
   std::lock_guard<std::mutex> g(g_maps_mu);
   auto it = g_maps.find(k);
   if (it != g_maps.end()) { *out = it->second; return DCVC_OK; }
@@ -391,6 +485,13 @@ int make_map_b(const float *w, int ktot, int n_pad, int kc, CUtensorMap *out) {
 
 inline int ru(int v, int m) { return (v + m - 1) / m * m; }
 
+// N tiling: all output channels in one CTA when they fit 256 TMEM columns, else equal tiles
+inline void n_tiling(int cout_w, int *tiles_n, int *n_tile) {
+  const int n16 = ru(cout_w, 16);
+  *tiles_n = (n16 + 255) / 256;
+  *n_tile = ru((n16 + *tiles_n - 1) / *tiles_n, 16);
+}
+
 }  // namespace
 
 // K chunk: the candidate in {32,16,8} that pads Cin least (ties -> larger chunk)
@@ -399,7 +500,9 @@ extern "C" int dcvc_conv_tc_geometry(int cout_w, int cin, int *n_pad, int *cin_p
   int best = 32, best_pad = ru(cin, 32);
   for (int c : {16, 8})
     if (ru(cin, c) < best_pad) { best = c; best_pad = ru(cin, c); }
-  if (n_pad) *n_pad = ru(cout_w, 16);
+  int tiles_n, n_tile;
+  n_tiling(cout_w, &tiles_n, &n_tile);
+  if (n_pad) *n_pad = tiles_n * n_tile;
   if (cin_pad) *cin_pad = best_pad;
   if (kc) *kc = best;
   return DCVC_OK;
@@ -408,7 +511,6 @@ extern "C" int dcvc_conv_tc_geometry(int cout_w, int cin, int *n_pad, int *cin_p
 bool conv_tc_ok(const dcvc_conv *d) {
   if (d->in_slope != 1.0f) return false;                       // no input prologue on the TMA path
   if (d->stride != 1 && d->stride != 2) return false;
-  if (d->cout_w > 256) return false;
   if ((d->in.cstride & 3) || (d->in.coff & 3)) return false;   // TMA: 16-byte strides/base
   if (reinterpret_cast<uintptr_t>(d->in.data) & 15) return false;
   if (reinterpret_cast<uintptr_t>(d->weight_tc) & 15) return false;
@@ -426,9 +528,11 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.out_slope = d->out_slope; a.gate_slope = d->gate_slope; a.out2_slope = d->out2_slope;
   a.hout = hout; a.wout = wout;
   a.ksize = d->ksize; a.stride = d->stride; a.pad = d->pad;
-  int cin_pad;
-  dcvc_conv_tc_geometry(d->cout_w, d->in.c, &a.n_pad, &cin_pad, &a.kc);
+  int cin_pad, n_pad, tiles_n;
+  dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
+  n_tiling(d->cout_w, &tiles_n, &a.n_tile);
   a.chunks_per_tap = cin_pad / a.kc;
+  a.units = a.ksize * a.ksize * a.chunks_per_tap;
   // tile shape: the (TH, TW) with TH*TW = 128 that covers the output with least padding
   int best_area = 1 << 30;
   for (int tw : {16, 8, 32, 4, 64, 128, 2}) {
@@ -439,27 +543,68 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   }
   a.tiles_x = cdiv(wout, a.tw);
   const int tiles_y = cdiv(hout, a.th);
-  a.a_bytes = (uint32_t)ru(TILE_M * a.kc * 4, 1024);
-  a.b_bytes = (uint32_t)ru(a.n_pad * a.kc * 4, 1024);
-  a.tx_bytes = (uint32_t)(TILE_M * a.kc * 4 + a.n_pad * a.kc * 4);
-  const uint32_t stage = a.a_bytes + a.b_bytes;
-  int stages = (int)(98304u / stage);
-  if (stages < 4) stages = 4;
-  if (stages > 8) stages = 8;
-  const int iters = a.ksize * a.ksize * a.chunks_per_tap;
-  if (stages > iters) stages = iters < 2 ? 2 : iters;
-  a.stages = stages;
+  a.unit_a = (uint32_t)ru(TILE_M * a.kc * 4, 1024);
+  a.unit_b = (uint32_t)ru(a.n_tile * a.kc * 4, 1024);
+  a.unit_tx = (uint32_t)(TILE_M * a.kc * 4 + a.n_tile * a.kc * 4);
+  const uint32_t unit = a.unit_a + a.unit_b;
+  static const int dbg = getenv("DCVC_TC_DEBUG") ? atoi(getenv("DCVC_TC_DEBUG")) : 0;
+  static const int dbg_stages = getenv("DCVC_TC_STAGES") ? atoi(getenv("DCVC_TC_STAGES")) : 0;
+  static const int dbg_group = getenv("DCVC_TC_GROUP") ? atoi(getenv("DCVC_TC_GROUP")) : 0;
+  static const int stage_kb = getenv("DCVC_TC_STAGE_KB") ? atoi(getenv("DCVC_TC_STAGE_KB")) : 18;
+  static const int dbg_ctas = getenv("DCVC_TC_CTAS") ? atoi(getenv("DCVC_TC_CTAS")) : 3;
+  static const int dbg_epi = getenv("DCVC_TC_EPI") ? atoi(getenv("DCVC_TC_EPI")) : 0;
+  static int num_sms = 0;
+  if (!num_sms) {
+    int dev = 0;
+    DCVC_CUDA(cudaGetDevice(&dev));
+    DCVC_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  a.debug = dbg;
+  a.tiles_n = tiles_n;
+  a.total_tiles = a.tiles_x * tiles_y * tiles_n;
+  // two TMEM accumulators (epilogue of tile i overlaps the MMAs of tile i+1)
+  a.acc_stride = (uint32_t)a.n_tile;
   a.tmem_cols = 32;
-  while ((int)a.tmem_cols < a.n_pad) a.tmem_cols *= 2;
+  while ((int)a.tmem_cols < 2 * a.n_tile) a.tmem_cols *= 2;
+  // one pipeline stage = `group` units (~18 KB): amortises the barrier/commit round trip
+  int group = (int)((uint32_t)stage_kb * 1024u / unit);
+  if (group < 1) group = 1;
+  if (dbg_group) group = dbg_group;
+  if (group > a.units) group = a.units;
+  a.group = group;
+  const uint32_t stage = (uint32_t)group * unit;
+  const int groups = cdiv(a.units, group);
+  // co-resident CTAs per SM: bounded by TMEM columns, then by what the smem ring needs
+  int ctas = (int)(512u / a.tmem_cols);
+  if (ctas > dbg_ctas) ctas = dbg_ctas;
+  if (ctas < 1) ctas = 1;
+  // epilogue warps: 4 per 32-column chunk group; a lone CTA on the SM gets 16 so that enough
+  // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
+  const int nchunks = cdiv(a.n_tile, 32);
+  int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi : (ctas == 1 ? 16 : 8);
+  while (epi > 4 && epi / 4 > nchunks) epi >>= 1;
+  while (ctas > 1 && ctas * (64 + 32 * epi) > 680) --ctas;
+  a.epi_warps = epi;
+  const uint32_t fixed = 1024u /*align*/ + 1024u /*barriers*/ + (uint32_t)epi * STG_WARP_FLOATS * 4u;
+  while (ctas > 1 && (227u * 1024u / ctas) - 1024u < fixed + 2u * stage) --ctas;
+  const uint32_t budget = (227u * 1024u / ctas) - 1024u - fixed;
+  int stages = (int)(budget / stage);
+  if (stages < 2) stages = 2;
+  if (stages > 6) stages = 6;
+  if (dbg_stages) stages = dbg_stages;
+  if (stages > groups && a.total_tiles <= ctas * num_sms) stages = groups < 2 ? 2 : groups;
+  a.stages = stages;
   a.sbo = 8u * a.kc * 4u;
   a.layout_type = a.kc == 32 ? 2u : a.kc == 16 ? 4u : 6u;
-  const size_t smem = 1024 + (size_t)stages * stage + 8 * (2 * stages + 1) + 16;
+  // smem: [stages x stage][barriers (1 KB)][epi_warps epilogue staging tiles]
+  a.stage_off = (uint32_t)stages * stage + 1024u;
+  const size_t smem = 1024 + (size_t)a.stage_off + (size_t)epi * STG_WARP_FLOATS * sizeof(float);
   if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: smem %zu too large", smem);
 
   CUtensorMap ma, mb;
   int rc = make_map_a(d->in, a.kc, a.th, a.tw, d->stride, &ma);
   if (rc) return rc;
-  rc = make_map_b(d->weight_tc, a.ksize * a.ksize * cin_pad, a.n_pad, a.kc, &mb);
+  rc = make_map_b(d->weight_tc, a.ksize * a.ksize * cin_pad, n_pad, a.n_tile, a.kc, &mb);
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
@@ -467,7 +612,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
                                    226 * 1024));
     attr_set = true;
   }
-  conv_tc_kernel<<<a.tiles_x * tiles_y, NTHREADS, smem, s>>>(ma, mb, a);
+  const int grid = a.total_tiles < ctas * num_sms ? a.total_tiles : ctas * num_sms;
+  conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, a);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }

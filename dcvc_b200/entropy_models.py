@@ -174,7 +174,10 @@ class EntropyCoder:
     def __del__(self):
         h = getattr(self, "_h", None)
         if h:
-            _lib.lib().dcvc_rans_destroy(h)
+            try:
+                _lib.lib().dcvc_rans_destroy(h)
+            except Exception:      # interpreter shutdown: modules may already be torn down
+                pass
             self._h = None
 
     def reset(self):

@@ -238,7 +238,10 @@ class DMC(CompressionModel):
         t = layers.res_block(net, cd + ".res2", bufs["D2"], 0.1, True)
         layers.subpel(net, cd + ".up4", t, out=bufs["R"].slice(48, 32))
         rg = "recon_generation_net"
-        t = ops.conv(bufs["R"], net.cw(rg + ".first_conv"))
+        # the reference calls recon_generation_net(recon_image_feature, context1) (:403), so
+        # first_conv's input channels are [res 32 | ctx1 48]; the buffer is [ctx1 | res]
+        perm = tuple(range(32, 80)) + tuple(range(0, 32))
+        t = ops.conv(bufs["R"], net.cw(rg + ".first_conv", cin_perm=perm))
         t = layers.unet(net, rg + ".unet_1", t, layers.dcb)
         feature = layers.unet(net, rg + ".unet_2", t, layers.dcb)
         x_hat = ops.conv(feature, net.cw(rg + ".recon_conv"), clamp01=True)
@@ -276,7 +279,8 @@ class DMC(CompressionModel):
                          ("mv_params", mv_catb.slice(mv_y.c, 3 * mv_y.c)), ("mv_y_hat", mv_y_hat),
                          ("mv_hat", mv_hat), ("ctx1", ctx1), ("ctx2", ctx2), ("ctx3", ctx3),
                          ("y", y), ("z_hat", z_hat), ("params", catb.slice(y.c, 3 * y.c)),
-                         ("y_hat", y_hat), ("x_hat", x_hat)):
+                         ("y_hat", y_hat), ("x_hat", x_hat), ("feature", feature),
+                         ("recon_res", bufs["R"].slice(48, 32))):
                 self._tap("p_" + k, v)
         new_dpb = {"ref_frame": x_hat.nchw(), "ref_feature": feature.nchw(),
                    "ref_mv_feature": mv_feature.nchw(), "ref_y": y_hat.nchw(),

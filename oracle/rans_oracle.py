@@ -85,7 +85,10 @@ class RansEncoder:
 
     def __del__(self):
         if getattr(self, "_h", None):
-            lib().oracle_enc_free(self._h)
+            try:
+                lib().oracle_enc_free(self._h)
+            except Exception:
+                pass
             self._h = None
 
     def reset(self):
@@ -113,7 +116,10 @@ class RansDecoder:
 
     def __del__(self):
         if getattr(self, "_h", None):
-            lib().oracle_dec_free(self._h)
+            try:
+                lib().oracle_dec_free(self._h)
+            except Exception:
+                pass
             self._h = None
 
     def set_stream(self, encoded):

@@ -48,6 +48,7 @@ SHAPES = [
     (128, 192, 3, 1, 24, 40), (64, 256, 1, 1, 32, 32), (512, 128, 1, 1, 24, 24),
     (16, 2, 7, 1, 32, 32), (48, 3, 3, 1, 32, 48), (80, 48, 3, 1, 30, 50), (96, 96, 3, 1, 17, 67),
     (3, 48, 3, 1, 32, 32), (384, 384, 1, 1, 20, 28), (20, 24, 3, 1, 33, 47),
+    (128, 512, 1, 1, 24, 32), (384, 1024, 1, 1, 17, 31), (64, 320, 3, 1, 24, 24),
 ]
 
 
@@ -106,6 +107,20 @@ def test_tc_conv_epilogues_and_slices():
     # clamp + input prologue (materialised copy)
     out = ops.conv(xa, net.cw("c"), in_slope=0.1, clamp01=True)
     _check(from_act(out), F.conv2d(F.leaky_relu(x, 0.1), sd["c.weight"], sd["c.bias"], 1, 1).clamp(0, 1), cin, 3)
+
+
+def test_tc_conv_n_tiled_gate_and_shuffle():
+    """cout > 256 is split over grid.y; gate pairs / shuffle quads never straddle a tile."""
+    cin, cout, h, w = 64, 768, 24, 32
+    sd = _sd(cin, cout, 1, seed=11)
+    x = _rand(1, cin, h, w, seed=4)
+    conv = F.conv2d(x, sd["c.weight"], sd["c.bias"])
+    net = layers.Net(sd, dev())
+    xa = to_act(x)
+    x1, x2 = conv.chunk(2, 1)
+    _check(from_act(ops.conv(xa, net.cw("c", gate=True), pad=0, gate_slope=0.1)),
+           x1 * F.leaky_relu(x2, 0.1), cin, 1)
+    _check(from_act(ops.conv(xa, net.cw("c"), pad=0, shuffle=True)), F.pixel_shuffle(conv, 2), cin, 1)
 
 
 def test_tc_path_is_taken_and_deterministic():
