@@ -23,6 +23,7 @@ collective is one NCCL all-reduce of the rate/distortion statistics after the ti
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -219,7 +220,7 @@ def main():
         return
     import torch.distributed as dist
     import dcvc_b200
-    from dcvc_b200 import _lib, arch, ops, synth
+    from dcvc_b200 import _lib, arch, ops, sharding, synth
 
     dev = torch.device(f"cuda:{local_rank}")
     torch.cuda.set_device(dev)
@@ -297,9 +298,7 @@ def main():
                "ms_per_step": ms_e / args.steps}
 
     # rate/distortion statistics: the only collective on this path
-    rd = torch.tensor([seq.bits, stats["sse"], stats["n"], seq.idx], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(rd, op=dist.ReduceOp.SUM)
+    rd, _ = sharding.reduce_stats([seq.bits, stats["sse"], stats["n"], seq.idx], ms, dev)
 
     # per-kernel profile of one P frame (CUDA events per launch, outside the timed region)
     roofline, table = None, None
@@ -321,8 +320,7 @@ def main():
                 "clocks": clock_info, "gpu_launches": int(launches), "e2e": e2e,
                 "roofline": roofline, "cpu_baseline": cpu,
                 "bits_per_frame": bits_per_frame,
-                "psnr_db": (10 * torch.log10(torch.tensor(rd[2].item() / max(rd[1].item(), 1e-12))).item()
-                            if rd[2].item() else None)}
+                "psnr_db": (10 * math.log10(rd[2] / max(rd[1], 1e-12)) if rd[2] else None)}
         print(json.dumps(line), flush=True)
         if args.profile_out and table is not None:
             with open(args.profile_out, "w") as f:
