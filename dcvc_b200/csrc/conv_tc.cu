@@ -36,6 +36,8 @@ struct TcArgs {
   int hout, wout, th, tw, tiles_x, total_tiles;
   int ksize, stride, pad, kc, chunks_per_tap, units, group, stages;
   uint32_t unit_a, unit_b, unit_tx, tmem_cols, acc_stride, sbo, layout_type, stage_off;
+  uint64_t rcp_tiles_n, rcp_tiles_x;  // ceil(2^40 / d), see tile_coords()
+  int fast;       // 0 generic epilogue, 1 plain fast path, 2 gated fast path (see fast_chunk)
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
@@ -227,11 +229,105 @@ __device__ __noinline__ void epilogue_chunk(const TcArgs &a, const float *stg, i
   }
 }
 
+// Lean phase 2 for the common case (host sets a.fast: no shuffle, every view and the bias/scale
+// vectors 16-byte aligned, cout_w % 4 == 0, slopes in [0,1]).  `a` lives in the kernel parameter
+// bank here (forceinline), so nothing is re-read through memory inside the row loop; ~35
+// instructions per row of four channels.  GATE: raw column pairs (v, g) -> v * lrelu(g).
+__device__ __forceinline__ float lrelu01(float v, float slope) { return fmaxf(v, v * slope); }
+
+template <bool GATE>
+__device__ __forceinline__ void fast_chunk(const TcArgs &a, const float *stg, int lane, int q,
+                                           int oy0, int ox0, int n_first, int ncols) {
+  const int vshift = ncols == 32 ? 3 : 2;
+  const int c4 = lane & ((1 << vshift) - 1), rstep = 32 >> vshift;
+  const int n = n_first + 4 * c4;                      // raw GEMM column of this lane's float4
+  if (n >= a.cout_w) return;
+  const int c = GATE ? n >> 1 : n;                     // first output channel of this lane
+  float4 b = make_float4(0.f, 0.f, 0.f, 0.f), sc = make_float4(1.f, 1.f, 1.f, 1.f);
+  if (a.bias) b = __ldg(reinterpret_cast<const float4 *>(a.bias + n));
+  if (a.scale) {
+    if (GATE) {
+      const float2 s2 = __ldg(reinterpret_cast<const float2 *>(a.scale + c));
+      sc.x = s2.x; sc.y = s2.y;
+    } else {
+      sc = __ldg(reinterpret_cast<const float4 *>(a.scale + c));
+    }
+  }
+  float *const o = a.out.data + a.out.coff + c;
+  const float *const r1 = a.res1.data ? a.res1.data + a.res1.coff + c : nullptr;
+  const float *const r2 = a.res2.data ? a.res2.data + a.res2.coff + c : nullptr;
+  float *const o2 = a.out2.data ? a.out2.data + a.out2.coff + c : nullptr;
+  const int tw_mask = a.tw - 1, tw_shift = 31 - __clz(a.tw);
+  const float *src = stg + (lane >> vshift) * STG_PITCH + 4 * c4;
+#pragma unroll 2
+  for (int r = lane >> vshift; r < 32; r += rstep, src += rstep * STG_PITCH) {
+    const int row = q * 32 + r;
+    const int oy = oy0 + (row >> tw_shift), ox = ox0 + (row & tw_mask);
+    if (oy >= a.hout || ox >= a.wout) continue;
+    const int pix = oy * a.wout + ox;
+    float4 t = *reinterpret_cast<const float4 *>(src);
+    t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+    if (GATE) {
+      float2 g = make_float2(t.x * lrelu01(t.y, a.gate_slope), t.z * lrelu01(t.w, a.gate_slope));
+      if (a.out_slope != 1.f) { g.x = lrelu01(g.x, a.out_slope); g.y = lrelu01(g.y, a.out_slope); }
+      if (r1) {
+        const float2 u = __ldg(reinterpret_cast<const float2 *>(r1 + (size_t)pix * a.res1.cstride));
+        g.x += u.x; g.y += u.y;
+      }
+      if (r2) {
+        const float2 u = __ldg(reinterpret_cast<const float2 *>(r2 + (size_t)pix * a.res2.cstride));
+        g.x += u.x; g.y += u.y;
+      }
+      g.x *= sc.x; g.y *= sc.y;
+      if (a.clamp01) { g.x = fminf(fmaxf(g.x, 0.f), 1.f); g.y = fminf(fmaxf(g.y, 0.f), 1.f); }
+      *reinterpret_cast<float2 *>(o + (size_t)pix * a.out.cstride) = g;
+      if (o2) {
+        g.x = lrelu01(g.x, a.out2_slope); g.y = lrelu01(g.y, a.out2_slope);
+        *reinterpret_cast<float2 *>(o2 + (size_t)pix * a.out2.cstride) = g;
+      }
+    } else {
+      if (a.out_slope != 1.f) {
+        t.x = lrelu01(t.x, a.out_slope); t.y = lrelu01(t.y, a.out_slope);
+        t.z = lrelu01(t.z, a.out_slope); t.w = lrelu01(t.w, a.out_slope);
+      }
+      if (r1) {
+        const float4 u = __ldg(reinterpret_cast<const float4 *>(r1 + (size_t)pix * a.res1.cstride));
+        t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+      }
+      if (r2) {
+        const float4 u = __ldg(reinterpret_cast<const float4 *>(r2 + (size_t)pix * a.res2.cstride));
+        t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+      }
+      if (a.scale) { t.x *= sc.x; t.y *= sc.y; t.z *= sc.z; t.w *= sc.w; }
+      if (a.clamp01) {
+        t.x = fminf(fmaxf(t.x, 0.f), 1.f); t.y = fminf(fmaxf(t.y, 0.f), 1.f);
+        t.z = fminf(fmaxf(t.z, 0.f), 1.f); t.w = fminf(fmaxf(t.w, 0.f), 1.f);
+      }
+      *reinterpret_cast<float4 *>(o + (size_t)pix * a.out.cstride) = t;
+      if (o2) {
+        t.x = lrelu01(t.x, a.out2_slope); t.y = lrelu01(t.y, a.out2_slope);
+        t.z = lrelu01(t.z, a.out2_slope); t.w = lrelu01(t.w, a.out2_slope);
+        *reinterpret_cast<float4 *>(o2 + (size_t)pix * a.out2.cstride) = t;
+      }
+    }
+  }
+}
+
+// tile -> (m tile, n tile, tile row, tile column) with host-made reciprocals:
+// q = (n * ceil(2^40 / d)) >> 40 is exact for n * d < 2^40
+__device__ __forceinline__ void tile_coords(const TcArgs &a, int tile, int &mt, int &nt, int &ty,
+                                            int &tx) {
+  mt = (int)(((uint64_t)(uint32_t)tile * a.rcp_tiles_n) >> 40);
+  nt = tile - mt * a.tiles_n;
+  ty = (int)(((uint64_t)(uint32_t)mt * a.rcp_tiles_x) >> 40);
+  tx = mt - ty * a.tiles_x;
+}
+
 // ------------------------------------------------------------------ the kernel
 // Persistent: each CTA walks tiles blockIdx.x, +gridDim.x, ...; the smem ring and the two TMEM
 // accumulators keep the TMA producer, the MMA issuer and the epilogue warps of consecutive
 // tiles overlapped.
-__global__ void __launch_bounds__(MAX_THREADS)
+__global__ void __launch_bounds__(MAX_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -276,31 +372,37 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 
   if (warp == 0) {
     // ===== TMA producer: one stage = `group` (tap, channel-chunk) units =====
+    // Single-thread loops are latency-bound instruction by instruction, so they carry running
+    // counters (ring slot, phase, tap position) instead of dividing.
     if (lane == 0) {
-      uint32_t it = 0;
+      int s = 0;
+      uint32_t ph = 0, stage_addr = base;
       for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
-        const int mt = tile / a.tiles_n, nt = tile - mt * a.tiles_n;
-        const int ty = mt / a.tiles_x, tx = mt - ty * a.tiles_x;
-        const int ox0 = tx * a.tw, oy0 = ty * a.th, n_base = nt * a.n_tile;
-        for (int gi = 0; gi < groups; ++gi, ++it) {
-          const int s = it % a.stages;
-          const uint32_t ph = (it / a.stages) & 1u;
+        int mt, nt, ty, tx;
+        tile_coords(a, tile, mt, nt, ty, tx);
+        const int x0 = tx * a.tw * a.stride - a.pad, y0 = ty * a.th * a.stride - a.pad;
+        const int n_base = nt * a.n_tile;
+        int u = 0, dx = 0, dy = 0, ch = 0;
+        for (int gi = 0; gi < groups; ++gi) {
           mbar_wait(empty_bar(s), ph ^ 1u);
-          const int u0 = gi * a.group, cnt = min(a.group, a.units - u0);
+          const int cnt = min(a.group, a.units - u);
           if (a.debug & 1) {
             mbar_expect_tx(full_bar(s), 0);
-            continue;
+            u += cnt;
+          } else {
+            mbar_expect_tx(full_bar(s), cnt * a.unit_tx);
+            uint32_t sa = stage_addr;
+            for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
+              tma_load_4d(sa, &map_a, full_bar(s), ch * a.kc, x0 + dx, y0 + dy, 0);
+              tma_load_2d(sa + a.unit_a, &map_b, full_bar(s), u * a.kc, n_base);
+              if (++ch == a.chunks_per_tap) {
+                ch = 0;
+                if (++dx == a.ksize) { dx = 0; ++dy; }
+              }
+            }
           }
-          mbar_expect_tx(full_bar(s), cnt * a.unit_tx);
-          for (int g = 0; g < cnt; ++g) {
-            const int u = u0 + g;
-            const int tap = u / a.chunks_per_tap, ch = u - tap * a.chunks_per_tap;
-            const int dy = tap / a.ksize, dx = tap - dy * a.ksize;
-            const uint32_t sa = base + s * stage_bytes + g * unit_bytes, sb = sa + a.unit_a;
-            tma_load_4d(sa, &map_a, full_bar(s), ch * a.kc, ox0 * a.stride + dx - a.pad,
-                        oy0 * a.stride + dy - a.pad, 0);
-            tma_load_2d(sb, &map_b, full_bar(s), u * a.kc, n_base);
-          }
+          stage_addr += stage_bytes;
+          if (++s == a.stages) { s = 0; ph ^= 1u; stage_addr = base; }
         }
       }
     }
@@ -310,28 +412,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
                              ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
       const int kk_n = (a.debug & 2) ? 0 : a.kc / 8;
-      uint32_t it = 0, lt = 0;
-      for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++lt) {
-        const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
+      // descriptor = constant high word | (smem address >> 4) in the low 14 bits
+      const uint64_t desc_hi = make_smem_desc(0, a.sbo, a.layout_type);
+      int s = 0;
+      uint32_t ph = 0, stage_addr = base, as = 0, aph = 0;
+      for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
         mbar_wait(tempty_bar(as), aph ^ 1u);       // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t tacc = tmem_base + as * a.acc_stride;
-        for (int gi = 0; gi < groups; ++gi, ++it) {
-          const int s = it % a.stages;
-          const uint32_t ph = (it / a.stages) & 1u;
+        int u = 0;
+        for (int gi = 0; gi < groups; ++gi) {
           mbar_wait(full_bar(s), ph);
           tc_fence_after();
-          const int u0 = gi * a.group, cnt = min(a.group, a.units - u0);
-          for (int g = 0; g < cnt; ++g) {
-            const uint32_t sa = base + s * stage_bytes + g * unit_bytes, sb = sa + a.unit_a;
-            const uint64_t da = make_smem_desc(sa, a.sbo, a.layout_type);
-            const uint64_t db = make_smem_desc(sb, a.sbo, a.layout_type);
+          const int cnt = min(a.group, a.units - u);
+          uint32_t sa = stage_addr;
+          for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
+            const uint64_t da = desc_hi | (uint64_t)(sa >> 4);
+            const uint64_t db = desc_hi | (uint64_t)((sa + a.unit_a) >> 4);
             for (int kk = 0; kk < kk_n; ++kk)  // +32 bytes along K per MMA: +2 in the >>4 field
-              umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, ((u0 + g) | kk) ? 1u : 0u);
+              umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
           }
-          umma_commit(empty_bar(s));           // frees the smem slot when these MMAs retire
+          if (a.debug & 8) mbar_arrive(empty_bar(s));   // experiment (with bit1): no commit
+          else umma_commit(empty_bar(s));      // frees the smem slot when these MMAs retire
+          stage_addr += stage_bytes;
+          if (++s == a.stages) { s = 0; ph ^= 1u; stage_addr = base; }
         }
-        umma_commit(tfull_bar(as));            // accumulator complete
+        if (a.debug & 8) mbar_arrive(tfull_bar(as));
+        else umma_commit(tfull_bar(as));       // accumulator complete
+        if ((as ^= 1u) == 0) aph ^= 1u;
       }
     }
   } else {
@@ -343,8 +451,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int nchunks = (a.n_tile + 31) >> 5;
     uint32_t lt = 0;
     for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++lt) {
-      const int mt = tile / a.tiles_n, nt = tile - mt * a.tiles_n;
-      const int ty = mt / a.tiles_x, tx = mt - ty * a.tiles_x;
+      int mt, nt, ty, tx;
+      tile_coords(a, tile, mt, nt, ty, tx);
       const int ox0 = tx * a.tw, oy0 = ty * a.th, n_base = nt * a.n_tile;
       const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
       mbar_wait(tfull_bar(as), aph);
@@ -360,8 +468,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         const int n0 = ci * 32;
         const int ncols = min(32, a.n_tile - n0);      // 16 or 32
         float v[32];
-        tmem_ld16(trow + (uint32_t)n0, v);             // warp-collective
-        if (ncols == 32) tmem_ld16(trow + (uint32_t)n0 + 16u, v + 16);
+        if (!(a.debug & 16)) {
+          tmem_ld16(trow + (uint32_t)n0, v);           // warp-collective
+          if (ncols == 32) tmem_ld16(trow + (uint32_t)n0 + 16u, v + 16);
+        }
         if (ci == last) {                              // accumulator fully read: hand it back
           tc_fence_before();
           __syncwarp();
@@ -374,7 +484,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             *reinterpret_cast<float4 *>(stg + lane * STG_PITCH + 4 * j) =
                 make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         __syncwarp();
-        if (a.shuffle) epilogue_chunk<2>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        if (a.fast == 1) fast_chunk<false>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        else if (a.fast == 2) fast_chunk<true>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        else if (a.shuffle) epilogue_chunk<2>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
         else if (a.gate) epilogue_chunk<1>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
         else epilogue_chunk<0>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
         __syncwarp();
@@ -527,6 +639,21 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.cout_w = d->cout_w; a.gate = d->gate; a.shuffle = d->shuffle; a.clamp01 = d->clamp01;
   a.out_slope = d->out_slope; a.gate_slope = d->gate_slope; a.out2_slope = d->out2_slope;
   a.hout = hout; a.wout = wout;
+  {
+    auto al16 = [](const dcvc_view &v) {
+      return !v.data || ((((unsigned)v.cstride | (unsigned)v.coff) & 3u) == 0 &&
+                         (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
+    };
+    auto unit = [](float s) { return s >= 0.f && s <= 1.f; };
+    const bool ok = !d->shuffle && d->cout_w % 4 == 0 && al16(d->out) && al16(d->res1) &&
+                    al16(d->res2) && al16(d->out2) &&
+                    (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
+                    (reinterpret_cast<uintptr_t>(d->scale) & 15u) == 0 && unit(d->out_slope) &&
+                    unit(d->gate_slope) && unit(d->out2_slope);
+    a.fast = ok ? (d->gate ? 2 : 1) : 0;
+    static const int no_fast = getenv("DCVC_TC_NOFAST") ? atoi(getenv("DCVC_TC_NOFAST")) : 0;
+    if (no_fast) a.fast = 0;
+  }
   a.ksize = d->ksize; a.stride = d->stride; a.pad = d->pad;
   int cin_pad, n_pad, tiles_n;
   dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
@@ -550,7 +677,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   static const int dbg = getenv("DCVC_TC_DEBUG") ? atoi(getenv("DCVC_TC_DEBUG")) : 0;
   static const int dbg_stages = getenv("DCVC_TC_STAGES") ? atoi(getenv("DCVC_TC_STAGES")) : 0;
   static const int dbg_group = getenv("DCVC_TC_GROUP") ? atoi(getenv("DCVC_TC_GROUP")) : 0;
-  static const int stage_kb = getenv("DCVC_TC_STAGE_KB") ? atoi(getenv("DCVC_TC_STAGE_KB")) : 18;
+  static const int stage_kb = getenv("DCVC_TC_STAGE_KB") ? atoi(getenv("DCVC_TC_STAGE_KB")) : 36;
   static const int dbg_ctas = getenv("DCVC_TC_CTAS") ? atoi(getenv("DCVC_TC_CTAS")) : 3;
   static const int dbg_epi = getenv("DCVC_TC_EPI") ? atoi(getenv("DCVC_TC_EPI")) : 0;
   static int num_sms = 0;
@@ -562,11 +689,13 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.debug = dbg;
   a.tiles_n = tiles_n;
   a.total_tiles = a.tiles_x * tiles_y * tiles_n;
+  a.rcp_tiles_n = ((1ull << 40) + (uint64_t)tiles_n - 1) / (uint64_t)tiles_n;
+  a.rcp_tiles_x = ((1ull << 40) + (uint64_t)a.tiles_x - 1) / (uint64_t)a.tiles_x;
   // two TMEM accumulators (epilogue of tile i overlaps the MMAs of tile i+1)
   a.acc_stride = (uint32_t)a.n_tile;
   a.tmem_cols = 32;
   while ((int)a.tmem_cols < 2 * a.n_tile) a.tmem_cols *= 2;
-  // one pipeline stage = `group` units (~18 KB): amortises the barrier/commit round trip
+  // one pipeline stage = `group` units (~36 KB): amortises the barrier/commit round trip
   int group = (int)((uint32_t)stage_kb * 1024u / unit);
   if (group < 1) group = 1;
   if (dbg_group) group = dbg_group;
