@@ -37,7 +37,7 @@ struct TcArgs {
   int ksize, stride, pad, kc, chunks_per_tap, units, group, stages;
   uint32_t unit_a, unit_b, unit_tx, tmem_cols, acc_stride, sbo, layout_type, stage_off;
   uint64_t rcp_tiles_n, rcp_tiles_x;  // ceil(2^40 / d), see tile_coords()
-  int fast;       // 0 generic epilogue, 1 plain fast path, 2 gated fast path (see fast_chunk)
+  int fast;       // lean epilogue: 0 none, 1 plain, 2 gated, 3 planar depth-to-space (tc_fast_mode)
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
@@ -235,16 +235,27 @@ __device__ __noinline__ void epilogue_chunk(const TcArgs &a, const float *stg, i
 // instructions per row of four channels.  GATE: raw column pairs (v, g) -> v * lrelu(g).
 __device__ __forceinline__ float lrelu01(float v, float slope) { return fmaxf(v, v * slope); }
 
-template <bool GATE>
+template <int MODE>
 __device__ __forceinline__ void fast_chunk(const TcArgs &a, const float *stg, int lane, int q,
                                            int oy0, int ox0, int n_first, int ncols) {
   const int vshift = ncols == 32 ? 3 : 2;
   const int c4 = lane & ((1 << vshift) - 1), rstep = 32 >> vshift;
   const int n = n_first + 4 * c4;                      // raw GEMM column of this lane's float4
   if (n >= a.cout_w) return;
-  const int c = GATE ? n >> 1 : n;                     // first output channel of this lane
+  constexpr bool GATE = MODE == 1, SHUF = MODE == 2;
+  // SHUF: GEMM columns are ordered (subpixel sp, channel c); reference channel = 4c + sp
+  const int c_out = a.cout_w >> 2;
+  const int sp = SHUF ? n / c_out : 0;
+  const int c = GATE ? n >> 1 : SHUF ? n - sp * c_out : n;   // first output channel of this lane
   float4 b = make_float4(0.f, 0.f, 0.f, 0.f), sc = make_float4(1.f, 1.f, 1.f, 1.f);
-  if (a.bias) b = __ldg(reinterpret_cast<const float4 *>(a.bias + n));
+  if (a.bias) {
+    if (SHUF) {
+      b.x = __ldg(a.bias + 4 * c + sp);      b.y = __ldg(a.bias + 4 * c + 4 + sp);
+      b.z = __ldg(a.bias + 4 * c + 8 + sp);  b.w = __ldg(a.bias + 4 * c + 12 + sp);
+    } else {
+      b = __ldg(reinterpret_cast<const float4 *>(a.bias + n));
+    }
+  }
   if (a.scale) {
     if (GATE) {
       const float2 s2 = __ldg(reinterpret_cast<const float2 *>(a.scale + c));
@@ -264,7 +275,7 @@ __device__ __forceinline__ void fast_chunk(const TcArgs &a, const float *stg, in
     const int row = q * 32 + r;
     const int oy = oy0 + (row >> tw_shift), ox = ox0 + (row & tw_mask);
     if (oy >= a.hout || ox >= a.wout) continue;
-    const int pix = oy * a.wout + ox;
+    const int pix = SHUF ? (2 * oy + (sp >> 1)) * (2 * a.wout) + 2 * ox + (sp & 1) : oy * a.wout + ox;
     float4 t = *reinterpret_cast<const float4 *>(src);
     t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
     if (GATE) {
@@ -484,8 +495,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             *reinterpret_cast<float4 *>(stg + lane * STG_PITCH + 4 * j) =
                 make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         __syncwarp();
-        if (a.fast == 1) fast_chunk<false>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
-        else if (a.fast == 2) fast_chunk<true>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        if (a.fast == 1) fast_chunk<0>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        else if (a.fast == 2) fast_chunk<1>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
+        else if (a.fast == 3) fast_chunk<2>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
         else if (a.shuffle) epilogue_chunk<2>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
         else if (a.gate) epilogue_chunk<1>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
         else epilogue_chunk<0>(a, stg, lane, q, oy0, ox0, n_base + n0, ncols);
@@ -620,12 +632,32 @@ extern "C" int dcvc_conv_tc_geometry(int cout_w, int cin, int *n_pad, int *cin_p
   return DCVC_OK;
 }
 
+// Which lean epilogue (fast_chunk) a descriptor can use: 0 none (generic epilogue), 1 plain,
+// 2 gated, 3 depth-to-space with weight_tc packed in (subpixel, channel) column order.
+int tc_fast_mode(const dcvc_conv *d) {
+  static const int no_fast = getenv("DCVC_TC_NOFAST") ? atoi(getenv("DCVC_TC_NOFAST")) : 0;
+  if (no_fast) return 0;
+  auto al16 = [](const dcvc_view &v) {
+    return !v.data || ((((unsigned)v.cstride | (unsigned)v.coff) & 3u) == 0 &&
+                       (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
+  };
+  auto unit = [](float s) { return s >= 0.f && s <= 1.f; };
+  const bool ok = d->cout_w % 4 == 0 && al16(d->out) && al16(d->res1) && al16(d->res2) &&
+                  al16(d->out2) && (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
+                  (reinterpret_cast<uintptr_t>(d->scale) & 15u) == 0 && unit(d->out_slope) &&
+                  unit(d->gate_slope) && unit(d->out2_slope);
+  if (!ok) return 0;
+  if (d->shuffle) return d->shuffle == 2 && d->cout_w % 16 == 0 && !d->gate ? 3 : 0;
+  return d->gate ? 2 : 1;
+}
+
 bool conv_tc_ok(const dcvc_conv *d) {
   if (d->in_slope != 1.0f) return false;                       // no input prologue on the TMA path
   if (d->stride != 1 && d->stride != 2) return false;
   if ((d->in.cstride & 3) || (d->in.coff & 3)) return false;   // TMA: 16-byte strides/base
   if (reinterpret_cast<uintptr_t>(d->in.data) & 15) return false;
   if (reinterpret_cast<uintptr_t>(d->weight_tc) & 15) return false;
+  if (d->shuffle == 2 && tc_fast_mode(d) != 3) return false;   // planar packing needs the lean path
   const int ho = (d->in.h + 2 * d->pad - d->ksize) / d->stride + 1;
   const int wo = (d->in.w + 2 * d->pad - d->ksize) / d->stride + 1;
   if ((int64_t)ho * wo < 4 * TILE_M) return false;             // tiny layers stay on CUDA cores
@@ -639,21 +671,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.cout_w = d->cout_w; a.gate = d->gate; a.shuffle = d->shuffle; a.clamp01 = d->clamp01;
   a.out_slope = d->out_slope; a.gate_slope = d->gate_slope; a.out2_slope = d->out2_slope;
   a.hout = hout; a.wout = wout;
-  {
-    auto al16 = [](const dcvc_view &v) {
-      return !v.data || ((((unsigned)v.cstride | (unsigned)v.coff) & 3u) == 0 &&
-                         (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
-    };
-    auto unit = [](float s) { return s >= 0.f && s <= 1.f; };
-    const bool ok = !d->shuffle && d->cout_w % 4 == 0 && al16(d->out) && al16(d->res1) &&
-                    al16(d->res2) && al16(d->out2) &&
-                    (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
-                    (reinterpret_cast<uintptr_t>(d->scale) & 15u) == 0 && unit(d->out_slope) &&
-                    unit(d->gate_slope) && unit(d->out2_slope);
-    a.fast = ok ? (d->gate ? 2 : 1) : 0;
-    static const int no_fast = getenv("DCVC_TC_NOFAST") ? atoi(getenv("DCVC_TC_NOFAST")) : 0;
-    if (no_fast) a.fast = 0;
-  }
+  a.fast = tc_fast_mode(d);
   a.ksize = d->ksize; a.stride = d->stride; a.pad = d->pad;
   int cin_pad, n_pad, tiles_n;
   dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);

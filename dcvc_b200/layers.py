@@ -18,12 +18,18 @@ def _round_tf32(w):
     return ((bits + 0x1000) & ~0x1FFF).view(torch.float32)
 
 
-def _pack_tc(w):
+def _pack_tc(w, planar=False):
     """NK-packed weights for the tcgen05 path: [n_pad][kh*kw][cin_pad], zero padded, TF32-rounded
-    (geometry from dcvc_conv_tc_geometry)."""
+    (geometry from dcvc_conv_tc_geometry).  planar=True (depth-to-space convs, dcvc_conv.shuffle
+    = 2) orders the GEMM columns (subpixel, channel) instead of the reference's (channel,
+    subpixel), so that one 32-column chunk of the epilogue is 32 consecutive output channels of
+    one output pixel."""
     import ctypes
     from . import _lib
     cout, cin, kh, kw = w.shape
+    if planar:
+        c = cout // 4
+        w = w.reshape(c, 4, cin, kh, kw).permute(1, 0, 2, 3, 4).reshape(cout, cin, kh, kw)
     n_pad, cin_pad, kc = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
     _lib.check(_lib.lib().dcvc_conv_tc_geometry(cout, cin, ctypes.byref(n_pad),
                                                 ctypes.byref(cin_pad), ctypes.byref(kc)))
@@ -46,12 +52,13 @@ class Net:
     def has(self, name):
         return (name + ".weight") in self.sd
 
-    def cw(self, name, gate=False, cin_perm=None):
+    def cw(self, name, gate=False, cin_perm=None, shuffle=False):
         """KN-packed conv weights: [kh*kw][cin][cout]; gate=True interleaves the two halves of the
         output channels (ConvFFN2's chunk(2), layers.py:193-195) so the gate pairs are adjacent;
         cin_perm reorders the input channels (new channel i reads reference channel cin_perm[i])
-        so a concatenated input can be laid out alignment-friendly."""
-        key = (name, gate, cin_perm)
+        so a concatenated input can be laid out alignment-friendly; shuffle=True marks a
+        depth-to-space conv: its tensor-core copy is packed planar (see _pack_tc)."""
+        key = (name, gate, cin_perm, shuffle)
         r = self._conv.get(key)
         if r is None:
             w = self.sd[name + ".weight"]
@@ -68,7 +75,8 @@ class Net:
                 b = b[perm] if b is not None else None
             wp = w.permute(2, 3, 1, 0).reshape(kh * kw * cin, cout).contiguous()
             r = ConvW(wp, b.contiguous() if b is not None else None, cin, cout, kh, gate,
-                      w_tc=_pack_tc(w))
+                      w_tc=_pack_tc(w, planar=shuffle and cout % 16 == 0),
+                      tc_planar=shuffle and cout % 16 == 0)
             self._conv[key] = r
         return r
 
@@ -92,7 +100,8 @@ class Net:
 # ------------------------------------------------------------------------------- blocks
 def subpel(net, p, x, act=1.0, out=None, scale=None, res=None):
     """subpel_conv1x1/3x3 (layers.py:23-39): conv to 4C with the depth-to-space store fused."""
-    return ops.conv(x, net.cw(p + ".0"), shuffle=True, act=act, out=out, scale=scale, res=res)
+    return ops.conv(x, net.cw(p + ".0", shuffle=True), shuffle=True, act=act, out=out, scale=scale,
+                    res=res)
 
 
 def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, scale=None):

@@ -50,11 +50,12 @@ def set_conv_mode(mode):
 
 class ConvW:
     """Packed device weights of one convolution (built by layers.pack_conv)."""
-    __slots__ = ("w", "w_tc", "b", "cin", "cout_w", "k", "gate")
+    __slots__ = ("w", "w_tc", "b", "cin", "cout_w", "k", "gate", "tc_planar")
 
-    def __init__(self, w, b, cin, cout_w, k, gate=False, w_tc=None):
+    def __init__(self, w, b, cin, cout_w, k, gate=False, w_tc=None, tc_planar=False):
         self.w, self.b, self.cin, self.cout_w, self.k, self.gate, self.w_tc = \
             w, b, cin, cout_w, k, gate, w_tc
+        self.tc_planar = tc_planar    # w_tc columns ordered (subpixel, channel): shuffle = 2
 
 
 def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, res2=None,
@@ -88,7 +89,8 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     d.bias = cw.b.data_ptr() if cw.b is not None else None
     d.scale = scale.data_ptr() if scale is not None else None
     d.ksize, d.stride, d.pad, d.cout_w = k, stride, pad, cw.cout_w
-    d.gate, d.shuffle = int(cw.gate), int(shuffle)
+    assert shuffle or not cw.tc_planar, "planar-packed weights are for depth-to-space convs"
+    d.gate, d.shuffle = int(cw.gate), (2 if cw.tc_planar else 1) if shuffle else 0
     d.in_slope, d.out_slope, d.gate_slope, d.out2_slope = in_slope, act, gate_slope, out2_slope
     d.mode = CONV_MODE
     d.clamp01 = int(clamp01)

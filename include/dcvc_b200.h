@@ -76,7 +76,10 @@ typedef struct dcvc_conv {
   const float *scale;     /* may be NULL */
   int32_t ksize, stride, pad;
   int32_t cout_w;         /* raw conv output channels */
-  int32_t gate, shuffle;
+  int32_t gate;
+  int32_t shuffle;        /* 0 none; 1 depth-to-space; 2 the same, and weight_tc is packed with
+                             its cout rows ordered (subpixel, channel) instead of (channel,
+                             subpixel) -- `weight` and `bias` always keep the reference order */
   float in_slope, out_slope, gate_slope, out2_slope;
   int32_t mode;
   int32_t clamp01;

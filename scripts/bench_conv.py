@@ -29,7 +29,7 @@ for cin, cout, k, s, h, w, kw in SHAPES:
     sd = {"c.weight": torch.randn(cout, cin, k, k, generator=g) * 0.05, "c.bias": torch.randn(cout, generator=g)}
     net = layers.Net(sd, dev)
     x = Act(torch.randn(h, w, (cin + 3) // 4 * 4, device=dev), 0, cin)
-    cw = net.cw("c")
+    cw = net.cw("c", shuffle=bool(kw.get("shuffle")))
     out = ops.conv(x, cw, stride=s, **kw)
     torch.cuda.synchronize()
     ms = 0.0

@@ -139,3 +139,29 @@ def test_tc_path_is_taken_and_deterministic():
     a = from_act(ops.conv(xa, cw))
     b = from_act(ops.conv(xa, cw))
     assert torch.equal(a, b)            # run-to-run bit-identical (encoder/decoder agreement)
+
+
+@pytest.mark.parametrize("cin,cout,k,h,w", [(32, 64, 3, 40, 48), (64, 768, 1, 24, 32),
+                                            (48, 128, 3, 37, 53), (64, 256, 1, 68, 120)])
+def test_tc_conv_planar_shuffle(cin, cout, k, h, w):
+    """Depth-to-space with weight_tc packed (subpixel, channel) (dcvc_conv.shuffle = 2, the lean
+    epilogue): same result as the reference-order packing, with residual / scale / activation in
+    the shuffled output space, into a channel slice, ragged tiles included."""
+    sd = _sd(cin, cout, k, seed=21)
+    x = _rand(1, cin, h, w, seed=6)
+    c4 = cout // 4
+    r1 = _rand(1, c4, 2 * h, 2 * w, seed=7)
+    q = torch.rand(c4) + 0.5
+    conv = F.conv2d(x, sd["c.weight"], sd["c.bias"], 1, k // 2)
+    net = layers.Net(sd, dev())
+    xa = to_act(x)
+    cw = net.cw("c", shuffle=True)
+    assert cw.tc_planar
+    out = to_act(torch.zeros(1, c4, 2 * h, 2 * w), cstride=c4 + 8, coff=4)
+    ops.conv(xa, cw, shuffle=True, act=0.01, res=to_act(r1), scale=q.to(dev()), out=out)
+    ref = (F.leaky_relu(F.pixel_shuffle(conv, 2), 0.01) + r1) * q.view(1, -1, 1, 1)
+    _check(from_act(out), ref, cin, k)
+    # and it agrees with the generic (reference-order) epilogue
+    out_ref = ops.conv(xa, net.cw("c"), shuffle=True)
+    out_pl = ops.conv(xa, cw, shuffle=True)
+    assert torch.equal(from_act(out_ref), from_act(out_pl))
