@@ -48,7 +48,7 @@ def parse_args():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--coder", default="interleaved", choices=["interleaved", "compat"])
-    p.add_argument("--stream-part", type=int, default=4)
+    p.add_argument("--stream-part", type=int, default=8)
     p.add_argument("--conv-mode", type=int, default=int(os.environ.get("DCVC_CONV_MODE", "1")))
     p.add_argument("--height", type=int, default=HEIGHT)
     p.add_argument("--width", type=int, default=WIDTH)

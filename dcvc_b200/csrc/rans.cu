@@ -27,6 +27,7 @@
 namespace {
 
 constexpr int MAX_PARTS = 16;
+constexpr size_t DEC_TAB_SMEM_MAX = 200 * 1024;  // decoder's shared-memory table budget
 constexpr int SLACK_WORDS = 4096;  // per part, 32-bit words beyond one word per symbol
 
 struct CallRec {
@@ -36,10 +37,12 @@ struct CallRec {
   rans::Tables t;
 };
 
+
 struct EncJob {
   CallRec calls[DCVC_RANS_MAX_CALLS];
   int ncalls, parts;
   int64_t reg_off[MAX_PARTS + 1];  // region bounds in 32-bit words
+  int64_t op_off[DCVC_RANS_MAX_CALLS + 1];  // first prepared operation of each call
 };
 
 // meta layout (uint32): [0] error flags, [1] container length, [2+i] part length in bytes,
@@ -125,7 +128,34 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
   return m;
 }
 
-__global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, uint32_t *buf, uint32_t *meta) {
+// Pass 1 (whole grid): every symbol's coding interval, looked up in parallel so that the
+// sequential pass below never waits on a table load.  ops[i] = {start | freq << 16,
+// (floor((2^32-1)/freq) & ~1) | escape flag}; the reciprocal turns the per-symbol x / freq of the
+// state update into a multiply plus a short correction.
+__global__ void ilv_prepare_kernel(const EncJob job, uint2 *ops) {
+  const int64_t total = job.op_off[job.ncalls];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int c = 0;
+    while (c + 1 < job.ncalls && i >= job.op_off[c + 1]) ++c;
+    const CallRec &cr = job.calls[c];
+    const int64_t pos = i - job.op_off[c];
+    const int index = call_index(cr, pos);
+    const int32_t *cdf = cr.t.cdf + (int64_t)index * cr.t.stride;
+    const int32_t max_value = cr.t.sizes[index] - 2;
+    int32_t value = (int32_t)cr.sym[pos] - cr.t.offsets[index];
+    uint32_t esc = 0;
+    if (value < 0 || value >= max_value) { value = max_value; esc = 1; }
+    const uint32_t start = (uint32_t)cdf[value], freq = (uint32_t)(cdf[value + 1] - cdf[value]);
+    ops[i] = make_uint2(start | (freq << 16), ((0xffffffffu / freq) & ~1u) | esc);
+  }
+}
+
+constexpr int ENC_BATCH = 8;  // rounds whose operations are fetched before the dependent chain
+
+// Pass 2 (one warp per stream): the dependent rANS chain, fed from the prepared operations.
+__global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, const uint2 *ops_all,
+                                                        uint32_t *buf, uint32_t *meta) {
   const int w = blockIdx.x, lane = threadIdx.x;
   uint16_t *base = reinterpret_cast<uint16_t *>(buf + job.reg_off[w]);
   const int64_t cap = (job.reg_off[w + 1] - job.reg_off[w]) * 2;
@@ -133,38 +163,72 @@ __global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, uint32
   uint32_t x = rans::L32;
   bool overflow = false;
   const uint32_t lt = lanemask_lt();
-  rans::Op ops[8];
   for (int c = job.ncalls - 1; c >= 0; --c) {
     const CallRec &cr = job.calls[c];
     int64_t off, cur;
     part_range(cr.n, job.parts, w, off, cur);
+    const uint2 *ops = ops_all + job.op_off[c] + off;
     const int64_t rounds = (cur + 31) >> 5;
-    for (int64_t r = rounds - 1; r >= 0; --r) {
-      const int64_t k = r * 32 + lane;
-      int nops = 0;
-      if (k < cur) {
-        const int64_t pos = off + k;
-        rans::Op full[rans::MAX_OPS];
-        nops = rans::expand_symbol(cr.sym[pos], call_index(cr, pos), cr.t, full);
-        if (nops > 8) nops = 8;  // unreachable for int16 symbols
-        for (int o = 0; o < nops; ++o) ops[o] = full[o];
+    for (int64_t r_hi = rounds; r_hi > 0; r_hi -= ENC_BATCH) {
+      uint2 o[ENC_BATCH];
+#pragma unroll
+      for (int j = 0; j < ENC_BATCH; ++j) {
+        const int64_t k = (r_hi - 1 - j) * 32 + lane;
+        o[j] = (k >= 0 && k < cur) ? __ldg(ops + k) : make_uint2(0u, 0u);   // freq 0: inactive
       }
-      const int maxops = __reduce_max_sync(0xffffffffu, nops);
-      for (int s = maxops - 1; s >= 0; --s) {
-        const bool has = s < nops;
-        const bool emit = has && rans::enc32_needs_emit(x, ops[s]);
-        const uint32_t m = __ballot_sync(0xffffffffu, emit);
-        const int cnt = __popc(m);
-        if (cnt) {
-          if (wp - cnt < 64) {
-            overflow = true;
-          } else {
-            wp -= cnt;
-            if (emit) base[wp + __popc(m & lt)] = (uint16_t)x;
+#pragma unroll
+      for (int j = 0; j < ENC_BATCH; ++j) {
+        if (r_hi - 1 - j < 0) break;                     // warp-uniform
+        const uint32_t freq = o[j].x >> 16, start = o[j].x & 0xffffu;
+        const bool active = freq != 0;
+        if (__ballot_sync(0xffffffffu, active && (o[j].y & 1u)) == 0) {
+          // common case: one interval per lane
+          const bool emit = active && x >= (freq << 16);
+          const uint32_t m = __ballot_sync(0xffffffffu, emit);
+          if (m) {
+            const int cnt = __popc(m);
+            if (wp - cnt < 64) {
+              overflow = true;
+            } else {
+              wp -= cnt;
+              if (emit) base[wp + __popc(m & lt)] = (uint16_t)x;
+            }
+            if (emit) x >>= 16;
           }
-          if (emit) x >>= 16;
+          if (active) {
+            uint32_t q = __umulhi(x, o[j].y & ~1u);      // <= x / freq, short by at most 3
+            uint32_t rem = x - q * freq;
+            while (rem >= freq) { rem -= freq; ++q; }
+            x = (q << 16) + rem + start;
+          }
+        } else {
+          // some lane escapes its table's support: expand to (interval, nibbles...) and walk the
+          // operation slots backwards (rans.cpp:76-139)
+          const int64_t k = (r_hi - 1 - j) * 32 + lane;
+          rans::Op full[rans::MAX_OPS];
+          int nops = 0;
+          if (active) {
+            const int64_t pos = off + k;
+            nops = rans::expand_symbol(cr.sym[pos], call_index(cr, pos), cr.t, full);
+          }
+          const int maxops = __reduce_max_sync(0xffffffffu, nops);
+          for (int s = maxops - 1; s >= 0; --s) {
+            const bool has = s < nops;
+            const bool emit = has && rans::enc32_needs_emit(x, full[has ? s : 0]);
+            const uint32_t m = __ballot_sync(0xffffffffu, emit);
+            const int cnt = __popc(m);
+            if (cnt) {
+              if (wp - cnt < 64) {
+                overflow = true;
+              } else {
+                wp -= cnt;
+                if (emit) base[wp + __popc(m & lt)] = (uint16_t)x;
+              }
+              if (emit) x >>= 16;
+            }
+            if (has) x = rans::enc32_update(x, full[s]);
+          }
         }
-        if (has) x = rans::enc32_update(x, ops[s]);
       }
     }
   }
@@ -191,9 +255,37 @@ __global__ void ilv_dec_init_kernel(const uint8_t *stream, DecPart *parts, uint3
   if (lane == 0) p.rp = 64;
 }
 
-__global__ void __launch_bounds__(32) ilv_decode_kernel(const CallRec cr, int nparts,
-                                                        const uint8_t *stream, DecPart *parts,
-                                                        int16_t *out, uint32_t *meta) {
+constexpr int DEC_THREADS = 128;   // warp 0 decodes; all four warps stage the tables
+constexpr int DEC_BATCH = 8;       // rounds whose table indexes are fetched ahead of the chain
+
+// One warp per stream.  The CDF rows of this call's table set are staged in shared memory first
+// (TAB_SMEM; the 7-probe symbol search per round is the dependent chain, and a shared-memory
+// probe costs a tenth of an L2 one); table sets larger than the budget are searched in place.
+template <bool TAB_SMEM>
+__global__ void __launch_bounds__(DEC_THREADS) ilv_decode_kernel(const CallRec cr, int nparts,
+                                                                 const uint8_t *stream,
+                                                                 DecPart *parts, int16_t *out,
+                                                                 uint32_t *meta) {
+  extern __shared__ int32_t tab[];     // [count][stride] cdf, [count] sizes, [count] offsets
+  const int32_t *cdf_all = cr.t.cdf, *sizes = cr.t.sizes, *offsets = cr.t.offsets;
+  if (TAB_SMEM) {
+    const int ncdf = cr.t.count * cr.t.stride;
+    if ((ncdf & 3) == 0 && (reinterpret_cast<uintptr_t>(cr.t.cdf) & 15) == 0) {
+      const int4 *src = reinterpret_cast<const int4 *>(cr.t.cdf);
+      int4 *dst = reinterpret_cast<int4 *>(tab);
+#pragma unroll 4
+      for (int i = threadIdx.x; i < (ncdf >> 2); i += DEC_THREADS) dst[i] = __ldg(src + i);
+    } else {
+      for (int i = threadIdx.x; i < ncdf; i += DEC_THREADS) tab[i] = cr.t.cdf[i];
+    }
+    for (int i = threadIdx.x; i < cr.t.count; i += DEC_THREADS) {
+      tab[ncdf + i] = cr.t.sizes[i];
+      tab[ncdf + cr.t.count + i] = cr.t.offsets[i];
+    }
+    __syncthreads();
+    cdf_all = tab; sizes = tab + ncdf; offsets = tab + ncdf + cr.t.count;
+  }
+  if (threadIdx.x >= 32) return;
   const int wi = blockIdx.x, lane = threadIdx.x;
   DecPart &p = parts[wi];
   const uint16_t *w = reinterpret_cast<const uint16_t *>(stream + p.base);
@@ -205,69 +297,94 @@ __global__ void __launch_bounds__(32) ilv_decode_kernel(const CallRec cr, int np
   int64_t off, cur;
   part_range(cr.n, nparts, wi, off, cur);
   const int64_t rounds = (cur + 31) >> 5;
-  for (int64_t r = 0; r < rounds; ++r) {
-    const int64_t k = r * 32 + lane;
-    const bool active = k < cur;
-    int phase = 0, maxv = 0, offset = 0, value = 0, nb = 0, j = 0;
-    uint32_t raw = 0;
-    if (active) {
-      const int index = call_index(cr, off + k);
-      const int32_t *cdf = cr.t.cdf + (int64_t)index * cr.t.stride;
-      const int size = cr.t.sizes[index];
-      maxv = size - 2;
-      offset = cr.t.offsets[index];
-      const uint32_t cum = x & 0xffffu;
-      const int s = rans::find_symbol(cdf, size, cum);
-      const uint32_t start = (uint32_t)cdf[s], freq = (uint32_t)(cdf[s + 1] - cdf[s]);
-      x = freq * (x >> 16) + cum - start;
-      value = s;
-      if (s == maxv) phase = 1;
+  for (int64_t r0 = 0; r0 < rounds; r0 += DEC_BATCH) {
+    int idx[DEC_BATCH];
+#pragma unroll
+    for (int j = 0; j < DEC_BATCH; ++j) {
+      const int64_t k = (r0 + j) * 32 + lane;
+      idx[j] = k < cur ? call_index(cr, off + k) : -1;
     }
-    {
-      const bool need = active && x < rans::L32;
-      const uint32_t m = __ballot_sync(0xffffffffu, need);
-      if (need) {
-        const uint32_t pos = rp + __popc(m & lt);
-        uint32_t word = 0;
-        if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
-        x = (x << 16) | word;
-      }
-      rp += __popc(m);
+    // a batch consumes about 256 words; pull the lines of the batch after next towards L1
+    if (lane < 8) {
+      const uint32_t ahead = rp + 512u + 64u * lane;
+      if (ahead < end) asm volatile("prefetch.global.L1 [%0];" ::"l"(w + ahead));
     }
-    while (__ballot_sync(0xffffffffu, phase != 0)) {
-      uint32_t val = 0;
-      if (phase) {
-        val = x & 15u;
-        x >>= 4;
-      }
-      const bool need = phase != 0 && x < rans::L32;
-      const uint32_t m = __ballot_sync(0xffffffffu, need);
-      if (need) {
-        const uint32_t pos = rp + __popc(m & lt);
-        uint32_t word = 0;
-        if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
-        x = (x << 16) | word;
-      }
-      rp += __popc(m);
-      bool done = false;
-      if (phase == 1) {
-        nb += (int)val;
-        if (val != 15u) {
-          if (nb == 0) done = true; else phase = 2;
-          if (nb > 8) { err |= ERR_ESCAPE; done = true; }
+#pragma unroll
+    for (int j = 0; j < DEC_BATCH; ++j) {
+      if (r0 + j >= rounds) break;                       // warp-uniform
+      const int64_t k = (r0 + j) * 32 + lane;
+      const bool active = idx[j] >= 0;
+      int phase = 0, maxv = 0, offset = 0, value = 0, nb = 0, jn = 0;
+      uint32_t raw = 0;
+      if (active) {
+        const int index = idx[j];
+        const int32_t *cdf = cdf_all + (int64_t)index * cr.t.stride;
+        const int size = sizes[index];
+        maxv = size - 2;
+        offset = offsets[index];
+        const uint32_t cum = x & 0xffffu;
+        // largest s with cdf[s] <= cum (== find_symbol), as seven branch-free probes
+        int sidx = 0;
+        if (size <= 128) {
+#pragma unroll
+          for (int step = 64; step; step >>= 1) {
+            const int mid = sidx + step;
+            if (mid < size && (uint32_t)cdf[mid < size ? mid : 0] <= cum) sidx = mid;
+          }
+        } else {
+          sidx = rans::find_symbol(cdf, size, cum);
         }
-      } else if (phase == 2) {
-        raw |= val << (4 * j);
-        if (++j == nb) done = true;
+        const uint32_t start = (uint32_t)cdf[sidx], freq = (uint32_t)(cdf[sidx + 1] - cdf[sidx]);
+        x = freq * (x >> 16) + cum - start;
+        value = sidx;
+        if (sidx == maxv) phase = 1;
       }
-      if (done) {
-        value = (int)(raw >> 1);
-        if (raw & 1u) value = -value - 1; else value += maxv;
-        phase = 0;
+      {
+        const bool need = active && x < rans::L32;
+        const uint32_t m = __ballot_sync(0xffffffffu, need);
+        if (need) {
+          const uint32_t pos = rp + __popc(m & lt);
+          uint32_t word = 0;
+          if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
+          x = (x << 16) | word;
+        }
+        rp += __popc(m);
       }
-      if (err & ERR_DEC_UNDERFLOW) phase = 0;  // never spin on a truncated stream
+      while (__ballot_sync(0xffffffffu, phase != 0)) {
+        uint32_t val = 0;
+        if (phase) {
+          val = x & 15u;
+          x >>= 4;
+        }
+        const bool need = phase != 0 && x < rans::L32;
+        const uint32_t m = __ballot_sync(0xffffffffu, need);
+        if (need) {
+          const uint32_t pos = rp + __popc(m & lt);
+          uint32_t word = 0;
+          if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
+          x = (x << 16) | word;
+        }
+        rp += __popc(m);
+        bool done = false;
+        if (phase == 1) {
+          nb += (int)val;
+          if (val != 15u) {
+            if (nb == 0) done = true; else phase = 2;
+            if (nb > 8) { err |= ERR_ESCAPE; done = true; }
+          }
+        } else if (phase == 2) {
+          raw |= val << (4 * jn);
+          if (++jn == nb) done = true;
+        }
+        if (done) {
+          value = (int)(raw >> 1);
+          if (raw & 1u) value = -value - 1; else value += maxv;
+          phase = 0;
+        }
+        if (err & ERR_DEC_UNDERFLOW) phase = 0;  // never spin on a truncated stream
+      }
+      if (active) out[off + k] = (int16_t)(value + offset);
     }
-    if (active) out[off + k] = (int16_t)(value + offset);
   }
   p.lane_x[lane] = x;
   __syncwarp();
@@ -315,6 +432,7 @@ struct dcvc_rans {
   int64_t max_symbols = 0;
   EncJob job;
   uint32_t *d_buf = nullptr;
+  uint2 *d_ops = nullptr;          // interleaved: prepared operations, one per symbol
   size_t buf_words = 0;
   uint8_t *d_out = nullptr;
   size_t out_cap = 0;
@@ -329,7 +447,7 @@ struct dcvc_rans {
 
 extern "C" void dcvc_rans_destroy(dcvc_rans *r) {
   if (!r) return;
-  cudaFree(r->d_buf); cudaFree(r->d_out); cudaFree(r->d_meta); cudaFree(r->d_stream);
+  cudaFree(r->d_buf); cudaFree(r->d_ops); cudaFree(r->d_out); cudaFree(r->d_meta); cudaFree(r->d_stream);
   cudaFree(r->d_parts);
   cudaFreeHost(r->h_meta); cudaFreeHost(r->h_stage); cudaFreeHost(r->h_parts);
   if (r->staged) cudaEventDestroy(r->staged);
@@ -359,6 +477,7 @@ extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t ma
   r->out_cap = r->buf_words * 4 + 256;
   r->stream_cap = r->out_cap + 16 * MAX_PARTS;
   RANS_TRY(cudaMalloc(&r->d_buf, r->buf_words * 4));
+  if (mode == DCVC_RANS_INTERLEAVED) RANS_TRY(cudaMalloc(&r->d_ops, (size_t)max_symbols * sizeof(uint2)));
   RANS_TRY(cudaMalloc(&r->d_out, r->out_cap));
   RANS_TRY(cudaMalloc(&r->d_meta, META_WORDS * 4));
   RANS_TRY(cudaMemset(r->d_meta, 0, META_WORDS * 4));
@@ -391,6 +510,7 @@ extern "C" int dcvc_rans_enc_push(dcvc_rans *r, const int16_t *symbols, const ui
   CallRec &cr = r->job.calls[r->job.ncalls++];
   cr.sym = symbols; cr.idx = indexes; cr.n = n; cr.plane = plane < 1 ? 1 : plane;
   cr.t.cdf = t->cdf; cr.t.sizes = t->sizes; cr.t.offsets = t->offsets; cr.t.stride = t->stride;
+  cr.t.count = t->count;
   return DCVC_OK;
 }
 
@@ -420,8 +540,17 @@ extern "C" int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_c
   DCVC_CUDA(cudaMemsetAsync(r->d_meta, 0, META_WORDS * 4, s));
   if (r->mode == DCVC_RANS_COMPAT)
     compat_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_buf, r->d_meta);
-  else
-    ilv_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_buf, r->d_meta);
+  else {
+    int64_t total = 0;
+    for (int c = 0; c < r->job.ncalls; ++c) { r->job.op_off[c] = total; total += r->job.calls[c].n; }
+    r->job.op_off[r->job.ncalls] = total;
+    if (total > 0) {
+      const int blocks = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+      ilv_prepare_kernel<<<blocks, 256, 0, s>>>(r->job, r->d_ops);
+      DCVC_LAUNCHED();
+    }
+    ilv_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_ops, r->d_buf, r->d_meta);
+  }
   DCVC_LAUNCHED();
   const uint32_t cap = (uint32_t)(out_capacity < r->out_cap ? out_capacity : r->out_cap);
   assemble_kernel<<<64, 256, 0, s>>>(r->mode, r->parts, reinterpret_cast<const uint8_t *>(r->d_buf),
@@ -494,11 +623,27 @@ extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t 
   CallRec cr;
   cr.sym = nullptr; cr.idx = indexes; cr.n = n; cr.plane = plane < 1 ? 1 : plane;
   cr.t.cdf = t->cdf; cr.t.sizes = t->sizes; cr.t.offsets = t->offsets; cr.t.stride = t->stride;
+  cr.t.count = t->count;
   cudaStream_t s = (cudaStream_t)stream;
   if (r->mode == DCVC_RANS_COMPAT)
     compat_decode_kernel<<<r->dec_parts, 32, 0, s>>>(cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
-  else
-    ilv_decode_kernel<<<r->dec_parts, 32, 0, s>>>(cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+  else {
+    const size_t tab_bytes = ((size_t)cr.t.count * cr.t.stride + 2 * (size_t)cr.t.count) * 4;
+    if (cr.t.count > 0 && tab_bytes <= DEC_TAB_SMEM_MAX) {
+      static bool attr_set = false;
+      if (!attr_set) {
+        DCVC_CUDA(cudaFuncSetAttribute(ilv_decode_kernel<true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)DEC_TAB_SMEM_MAX));
+        attr_set = true;
+      }
+      ilv_decode_kernel<true><<<r->dec_parts, DEC_THREADS, tab_bytes, s>>>(
+          cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+    } else {
+      ilv_decode_kernel<false><<<r->dec_parts, DEC_THREADS, 0, s>>>(
+          cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+    }
+  }
   DCVC_LAUNCHED();
   return DCVC_OK;
 }

@@ -35,6 +35,7 @@ struct Tables {
   const int32_t *sizes;
   const int32_t *offsets;
   int32_t stride;
+  int32_t count;   // rows (table sets of `stride` entries)
 };
 
 // One coding operation: bits==16 -> (start,freq) interval; bits==4 -> raw nibble `start`.

@@ -15,6 +15,7 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
+from .ops import _Prof
 
 SCALE_MIN = {"laplace": 0.01, "gaussian": 0.11}
 SCALE_MAX = 64.0
@@ -193,9 +194,10 @@ class EntropyCoder:
 
     def flush(self):
         n = ctypes.c_size_t(0)
-        _lib.check(_lib.lib().dcvc_rans_enc_flush(
-            self._h, self._out.data_ptr(), self._cap, ctypes.byref(n),
-            torch.cuda.current_stream().cuda_stream))
+        with _Prof("rans_enc_flush"):
+            _lib.check(_lib.lib().dcvc_rans_enc_flush(
+                self._h, self._out.data_ptr(), self._cap, ctypes.byref(n),
+                torch.cuda.current_stream().cuda_stream))
         self._keep = []
         self._stream_bytes = bytes(self._out[:n.value].numpy().tobytes())
 
@@ -208,9 +210,10 @@ class EntropyCoder:
             self._h, buf.ctypes.data, buf.size, torch.cuda.current_stream().cuda_stream))
 
     def decode(self, indexes, n, plane, tables, out):
-        _lib.check(_lib.lib().dcvc_rans_dec_pull(
-            self._h, indexes.data_ptr() if indexes is not None else None, n, plane,
-            ctypes.byref(tables.c), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        with _Prof("rans_dec_pull"):
+            _lib.check(_lib.lib().dcvc_rans_dec_pull(
+                self._h, indexes.data_ptr() if indexes is not None else None, n, plane,
+                ctypes.byref(tables.c), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
         return out
 
     def status(self):

@@ -120,7 +120,8 @@ def copy(src, out=None, h=None, w=None, mul=1.0, slope=1.0, stream=None):
     """Channel-slice copy; with (h, w) != src size: replicate pad / crop."""
     if out is None:
         out = Act.new(src.h if h is None else h, src.w if w is None else w, src.c, src.device)
-    with _Prof("copy", 0, 2 * _nb(out)):
+    with _Prof(f"copy {out.c}ch @{out.h}x{out.w}" + (" lrelu" if slope != 1.0 else ""), 0,
+               2 * _nb(out)):
         _lib.check(_lib.lib().dcvc_copy(src.view(), out.view(), mul, slope, _stream(stream)))
     return out
 
@@ -198,31 +199,36 @@ def _quad(y, params, prior, y_hat, y_out, edges, step, distribution):
 def quad_step_enc(y, params, prior, y_hat, y_out, edges, step, distribution, symbols=None,
                   indexes=None, bits=None, bits_ws=None, stream=None):
     q = _quad(y, params, prior, y_hat, y_out, edges, step, distribution)
-    _lib.check(_lib.lib().dcvc_quad_step_enc(
-        ctypes.byref(q), symbols.data_ptr() if symbols is not None else None,
-        indexes.data_ptr() if indexes is not None else None,
-        bits.data_ptr() if bits is not None else None,
-        bits_ws.data_ptr() if bits_ws is not None else None, _stream(stream)))
+    with _Prof("quad_step_enc"):
+        _lib.check(_lib.lib().dcvc_quad_step_enc(
+            ctypes.byref(q), symbols.data_ptr() if symbols is not None else None,
+            indexes.data_ptr() if indexes is not None else None,
+            bits.data_ptr() if bits is not None else None,
+            bits_ws.data_ptr() if bits_ws is not None else None, _stream(stream)))
 
 
 def quad_step_indexes(params, prior, y_hat, y_out, edges, step, indexes, stream=None):
     q = _quad(None, params, prior, y_hat, y_out, edges, step, 0)
-    _lib.check(_lib.lib().dcvc_quad_step_indexes(ctypes.byref(q), indexes.data_ptr(),
-                                                 _stream(stream)))
+    with _Prof("quad_step_indexes"):
+        _lib.check(_lib.lib().dcvc_quad_step_indexes(ctypes.byref(q), indexes.data_ptr(),
+                                                     _stream(stream)))
 
 
 def quad_step_dec(params, prior, y_hat, y_out, edges, step, symbols, stream=None):
     q = _quad(None, params, prior, y_hat, y_out, edges, step, 0)
-    _lib.check(_lib.lib().dcvc_quad_step_dec(ctypes.byref(q), symbols.data_ptr(), _stream(stream)))
+    with _Prof("quad_step_dec"):
+        _lib.check(_lib.lib().dcvc_quad_step_dec(ctypes.byref(q), symbols.data_ptr(), _stream(stream)))
 
 
 def z_quant(z, z_hat, symbols=None, fparams=None, bits=None, bits_ws=None, stream=None):
-    _lib.check(_lib.lib().dcvc_z_quant(
-        z.view(), z_hat.view(), symbols.data_ptr() if symbols is not None else None,
-        fparams.data_ptr() if fparams is not None else None,
-        bits.data_ptr() if bits is not None else None,
-        bits_ws.data_ptr() if bits_ws is not None else None, _stream(stream)))
+    with _Prof("z_quant"):
+        _lib.check(_lib.lib().dcvc_z_quant(
+            z.view(), z_hat.view(), symbols.data_ptr() if symbols is not None else None,
+            fparams.data_ptr() if fparams is not None else None,
+            bits.data_ptr() if bits is not None else None,
+            bits_ws.data_ptr() if bits_ws is not None else None, _stream(stream)))
 
 
 def z_dequant(symbols, z_hat, stream=None):
-    _lib.check(_lib.lib().dcvc_z_dequant(symbols.data_ptr(), z_hat.view(), _stream(stream)))
+    with _Prof("z_dequant"):
+        _lib.check(_lib.lib().dcvc_z_dequant(symbols.data_ptr(), z_hat.view(), _stream(stream)))
