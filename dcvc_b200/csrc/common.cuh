@@ -42,6 +42,11 @@ static inline bool view_ok(const dcvc_view *v) {
          v->cstride >= v->coff + v->c;
 }
 
+// every pixel's channel slice starts 16-byte aligned and holds whole float4 groups
+static inline bool view_al16(const dcvc_view *v) {
+  return ((v->cstride | v->coff | v->c) & 3) == 0 && (reinterpret_cast<uintptr_t>(v->data) & 15) == 0;
+}
+
 __device__ __forceinline__ float lrelu(float v, float slope) { return v >= 0.f ? v : v * slope; }
 
 __device__ __forceinline__ size_t vidx(const dcvc_view &v, int y, int x) {

@@ -45,6 +45,27 @@ __global__ void copy_kernel(dcvc_view src, dcvc_view dst, float mul, float slope
   dst.data[vidx(dst, y, x) + c] = mul * lrelu(src.data[vidx(src, sy, sx) + c], slope);
 }
 
+// float4 path of copy: one thread per (pixel, 4 channels), 32-bit index math.  SAME: source and
+// destination have equal sizes (no replicate pad / crop), so the pixel index is shared.
+template <bool SAME>
+__global__ void copy_v4_kernel(dcvc_view src, dcvc_view dst, float mul, float slope, uint32_t c4n,
+                               uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t p = t / c4n, cq = t - p * c4n;
+  size_t so;
+  if (SAME) {
+    so = (size_t)p * src.cstride;
+  } else {
+    const uint32_t y = p / (uint32_t)dst.w, x = p - y * (uint32_t)dst.w;
+    so = ((size_t)min((int)y, src.h - 1) * src.w + min((int)x, src.w - 1)) * src.cstride;
+  }
+  float4 v = *reinterpret_cast<const float4 *>(src.data + so + src.coff + 4 * cq);
+  v.x = mul * lrelu(v.x, slope); v.y = mul * lrelu(v.y, slope);
+  v.z = mul * lrelu(v.z, slope); v.w = mul * lrelu(v.w, slope);
+  *reinterpret_cast<float4 *>(dst.data + (size_t)p * dst.cstride + dst.coff + 4 * cq) = v;
+}
+
 __global__ void fill_kernel(dcvc_view dst, float value) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (int64_t)dst.h * dst.w * dst.c) return;
@@ -156,6 +177,35 @@ __global__ void flow_warp_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out) 
   out.data[vidx(out, y, x) + c] = warp_sample(feat, b, c);
 }
 
+// float4 path: one thread per (pixel, 4 channels); the four bilinear taps are 16-byte gathers
+__global__ void flow_warp_v4_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out, uint32_t c4n,
+                                    uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t p = t / c4n, cq = t - p * c4n;
+  const uint32_t y = p / (uint32_t)out.w, x = p - y * (uint32_t)out.w;
+  const float2 fl = *reinterpret_cast<const float2 *>(flow.data + (size_t)p * flow.cstride + flow.coff);
+  const Bilin b = warp_coords((int)x, (int)y, fl.x, fl.y, feat.w, feat.h);
+  const float *base = feat.data + feat.coff + 4 * cq;
+  const size_t r0 = (size_t)b.y0 * feat.w, r1 = (size_t)b.y1 * feat.w;
+  // same accumulation order as warp_sample (dropped corners contribute nothing)
+  float4 a = *reinterpret_cast<const float4 *>(base + (r0 + b.x0) * feat.cstride);
+  float4 v = make_float4(b.nw * a.x, b.nw * a.y, b.nw * a.z, b.nw * a.w);
+  if (b.vx1) {
+    a = *reinterpret_cast<const float4 *>(base + (r0 + b.x1) * feat.cstride);
+    v.x += b.ne * a.x; v.y += b.ne * a.y; v.z += b.ne * a.z; v.w += b.ne * a.w;
+  }
+  if (b.vy1) {
+    a = *reinterpret_cast<const float4 *>(base + (r1 + b.x0) * feat.cstride);
+    v.x += b.sw * a.x; v.y += b.sw * a.y; v.z += b.sw * a.z; v.w += b.sw * a.w;
+  }
+  if (b.vx1 && b.vy1) {
+    a = *reinterpret_cast<const float4 *>(base + (r1 + b.x1) * feat.cstride);
+    v.x += b.se * a.x; v.y += b.se * a.y; v.z += b.se * a.z; v.w += b.se * a.w;
+  }
+  *reinterpret_cast<float4 *>(out.data + (size_t)p * out.cstride + out.coff + 4 * cq) = v;
+}
+
 // one thread per (pixel, group q of 16): samples n = 2q, 2q+1
 __global__ void offset_diversity_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
                                         const float *__restrict__ fw, const float *__restrict__ fb,
@@ -220,6 +270,16 @@ extern "C" int dcvc_copy(const dcvc_view *src, const dcvc_view *dst, float mul, 
                          void *stream) {
   if (!view_ok(src) || !view_ok(dst) || src->c != dst->c)
     return dcvc_fail(DCVC_ERR_ARG, "copy: bad args");
+  const int64_t total4 = (int64_t)dst->h * dst->w * (dst->c / 4);
+  if (view_al16(src) && view_al16(dst) && total4 < (1ll << 31)) {
+    if (src->h == dst->h && src->w == dst->w)
+      LAUNCH_1D(copy_v4_kernel<true>, total4, stream, *src, *dst, mul, slope,
+                (uint32_t)(dst->c / 4), (uint32_t)total4);
+    else
+      LAUNCH_1D(copy_v4_kernel<false>, total4, stream, *src, *dst, mul, slope,
+                (uint32_t)(dst->c / 4), (uint32_t)total4);
+    return DCVC_OK;
+  }
   LAUNCH_1D(copy_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *src, *dst, mul, slope);
   return DCVC_OK;
 }
@@ -253,6 +313,13 @@ extern "C" int dcvc_flow_warp(const dcvc_view *feat, const dcvc_view *flow, cons
   if (!view_ok(feat) || !view_ok(flow) || !view_ok(out) || flow->c != 2 || out->c != feat->c ||
       out->h != flow->h || out->w != flow->w)
     return dcvc_fail(DCVC_ERR_ARG, "flow_warp: bad args");
+  const int64_t total4 = (int64_t)out->h * out->w * (out->c / 4);
+  if (view_al16(feat) && view_al16(out) && ((flow->cstride | flow->coff) & 1) == 0 &&
+      (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total4 < (1ll << 31)) {
+    LAUNCH_1D(flow_warp_v4_kernel, total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
+              (uint32_t)total4);
+    return DCVC_OK;
+  }
   LAUNCH_1D(flow_warp_kernel, (int64_t)out->h * out->w * out->c, stream, *feat, *flow, *out);
   return DCVC_OK;
 }
