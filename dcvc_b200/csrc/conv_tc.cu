@@ -38,6 +38,8 @@ struct TcArgs {
   uint32_t unit_a, unit_b, unit_tx, tmem_cols, acc_stride, sbo, layout_type, stage_off;
   uint64_t rcp_tiles_n, rcp_tiles_x;  // ceil(2^40 / d), see tile_coords()
   int fast;       // lean epilogue: 0 none, 1 plain, 2 gated, 3 planar depth-to-space (tc_fast_mode)
+  int tma_epi;    // 1: TMA-store epilogue (stage_off region = 8 KB per warp, vec_off = bias/scale)
+  uint32_t vec_off;
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
@@ -139,6 +141,35 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
+
+// ---- TMA store side (epilogue): smem tile -> global through a tensor map, bulk async-groups
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar,
+                                            int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, uint32_t src, int c0, int c1,
+                                             int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {   // all but the N newest groups have read smem
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+__device__ __forceinline__ void fence_async_smem() {  // generic-proxy smem writes -> async proxy
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
 // ------------------------------------------------------------------ epilogue (coalesced phase)
 // Code size matters here (the instruction cache is shared by three warp roles), so the general
 // case is one out-of-line scalar routine and only the common fully-aligned case is vectorised.
@@ -340,6 +371,7 @@ __device__ __forceinline__ void tile_coords(const TcArgs &a, int tile, int &mt, 
 // tiles overlapped.
 __global__ void __launch_bounds__(MAX_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_r,
                const __grid_constant__ TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment for the swizzled tiles
@@ -358,6 +390,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   auto empty_bar = [&](int s) { return bars + 8u * (a.stages + s); };
   auto tfull_bar = [&](int s) { return bars + 8u * (2 * a.stages + s); };
   auto tempty_bar = [&](int s) { return bars + 8u * (2 * a.stages + 2 + s); };
+  auto res_bar = [&](int s) { return bars + 8u * (2 * a.stages + 4 + s); };   // 2 per epilogue warp
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < a.stages; ++s) {
@@ -368,7 +401,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       mbar_init(tfull_bar(s), 1);
       mbar_init(tempty_bar(s), a.epi_warps);
     }
+    if (a.tma_epi)
+      for (int s = 0; s < 2 * a.epi_warps; ++s) mbar_init(res_bar(s), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (a.tma_epi) {
+    // bias / scale of every GEMM column, padded with 0 / 1, for broadcast reads in the epilogue
+    float *vec = reinterpret_cast<float *>(smem_raw + (base - raw) + a.vec_off);
+    const int n_all = a.tiles_n * ((a.n_tile + 31) & ~31);   // whole 32-column chunks
+    for (int i = threadIdx.x; i < n_all; i += blockDim.x) {
+      vec[i] = (a.bias && i < a.cout_w) ? __ldg(a.bias + i) : 0.f;
+      vec[n_all + i] = (a.scale && i < a.cout_w) ? __ldg(a.scale + i) : 1.f;
+    }
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
@@ -453,6 +497,119 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if ((as ^= 1u) == 0) aph ^= 1u;
       }
     }
+  } else if (a.tma_epi) {
+    // ===== epilogue, TMA-store flavour (plain convs): each warp owns TMEM lanes 32q..32q+31 =
+    // 32 output pixels, and walks its 32-column chunks.  Thread = pixel row: tcgen05.ld gives it
+    // 32 consecutive channels; bias / activation / residual / scale / clamp are applied in
+    // registers, the row is parked in a 128B-swizzled 4 KB smem tile, and one elected lane sends
+    // the tile out with a tensor-map store (clipping ragged edges and padded channels).  The
+    // residual tile arrives the same way (TMA load into the very buffer the result will leave
+    // from), so no per-element address arithmetic or global LD/ST is issued by the warp.
+    const int we = warp - 2, q = warp & 3, part = we >> 2, parts = a.epi_warps >> 2;
+    const uint32_t buf0 = base + a.stage_off + (uint32_t)we * 8192u;
+    uint8_t *const buf0_g = smem_raw + (base - raw) + a.stage_off + (size_t)we * 8192u;
+    const float4 *const vec4 = reinterpret_cast<const float4 *>(smem_raw + (base - raw) + a.vec_off);
+    const int n_all4 = (a.tiles_n * ((a.n_tile + 31) & ~31)) >> 2;
+    const int nchunks = (a.n_tile + 31) >> 5;
+    const int tw_mask = a.tw - 1, tw_shift = 31 - __clz(a.tw);
+    const int bx = (q * 32) & tw_mask, by = (q * 32) >> tw_shift;
+    const bool has_res = a.res1.data != nullptr;
+    const uint32_t row_off = (uint32_t)lane * 128u, sw = (uint32_t)(lane & 7);
+    uint32_t rph0 = 0, rph1 = 0, b = 0, lt = 0;
+    int tile = blockIdx.x, ci = part;
+    if (has_res && lane == 0 && tile < a.total_tiles) {
+      int mt, nt, ty, tx;
+      tile_coords(a, tile, mt, nt, ty, tx);
+      mbar_expect_tx(res_bar(2 * we), 4096u);
+      tma_load_3d(buf0, &map_r, res_bar(2 * we), nt * a.n_tile + ci * 32, tx * a.tw + bx,
+                  ty * a.th + by);
+    }
+    while (tile < a.total_tiles) {
+      int mt, nt, ty, tx;
+      tile_coords(a, tile, mt, nt, ty, tx);
+      const int n0 = ci * 32, c0 = nt * a.n_tile + n0, x0 = tx * a.tw + bx, y0 = ty * a.th + by;
+      const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
+      if (ci == part) {                                   // first chunk of this tile for the warp
+        mbar_wait(tfull_bar(as), aph);
+        tc_fence_after();
+      }
+      const uint32_t trow = tmem_base + as * a.acc_stride + ((uint32_t)(q * 32) << 16);
+      float v[32];
+      if (!(a.debug & 16)) {
+        tmem_ld16(trow + (uint32_t)n0, v);
+        if (a.n_tile - n0 >= 32) tmem_ld16(trow + (uint32_t)n0 + 16u, v + 16);
+      }
+      // next chunk of this warp (possibly in its next tile)
+      int ntile = tile, nci = ci + parts;
+      if (nci >= nchunks) { nci = part; ntile += gridDim.x; }
+      if (nci == part) {                                  // accumulator fully read: hand it back
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(as));
+        ++lt;
+      }
+      const uint32_t buf = buf0 + b * 4096u;
+      uint8_t *const buf_g = buf0_g + b * 4096u;
+      if (!(a.debug & 4)) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 bb = vec4[(c0 >> 2) + j];
+          v[4 * j] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
+        }
+        if (a.out_slope != 1.f) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = lrelu01(v[j], a.out_slope);
+        }
+        if (has_res) {
+          mbar_wait(res_bar(2 * we + b), b ? rph1 : rph0);
+          if (b) rph1 ^= 1u; else rph0 ^= 1u;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 u = *reinterpret_cast<const float4 *>(buf_g + row_off + (((uint32_t)j ^ sw) << 4));
+            v[4 * j] += u.x; v[4 * j + 1] += u.y; v[4 * j + 2] += u.z; v[4 * j + 3] += u.w;
+          }
+        }
+        if (a.scale) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 s4 = vec4[n_all4 + (c0 >> 2) + j];
+            v[4 * j] *= s4.x; v[4 * j + 1] *= s4.y; v[4 * j + 2] *= s4.z; v[4 * j + 3] *= s4.w;
+          }
+        }
+        if (a.clamp01) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fminf(fmaxf(v[j], 0.f), 1.f);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4 *>(buf_g + row_off + (((uint32_t)j ^ sw) << 4)) =
+              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(&map_o, buf, c0, x0, y0);
+          bulk_commit();
+        }
+      } else if (has_res) {                               // experiment: no stores, still drain loads
+        mbar_wait(res_bar(2 * we + b), b ? rph1 : rph0);
+        if (b) rph1 ^= 1u; else rph0 ^= 1u;
+      }
+      if (lane == 0) {
+        bulk_wait_read<1>();                              // the store issued a chunk ago has left smem
+        if (has_res && ntile < a.total_tiles) {
+          int mt2, nt2, ty2, tx2;
+          tile_coords(a, ntile, mt2, nt2, ty2, tx2);
+          mbar_expect_tx(res_bar(2 * we + (b ^ 1u)), 4096u);
+          tma_load_3d(buf0 + (b ^ 1u) * 4096u, &map_r, res_bar(2 * we + (b ^ 1u)),
+                      nt2 * a.n_tile + nci * 32, tx2 * a.tw + bx, ty2 * a.th + by);
+        }
+      }
+      __syncwarp();
+      b ^= 1u;
+      tile = ntile;
+      ci = nci;
+    }
+    if (lane == 0) bulk_wait_all();
   } else {
     // ===== epilogue: warps 2..2+epi_warps; warp w owns TMEM lanes 32*(w%4).., column chunks
     // ci with ci % (epi_warps/4) == part.  Phase 1: thread = pixel row, tcgen05.ld 32 columns, park them in a
@@ -585,6 +742,33 @@ int make_map_a(const dcvc_view &in, int kc, int th, int tw, int stride, CUtensor
   return DCVC_OK;
 }
 
+// epilogue map over an output-side view (out / residual): dims (C, W, H), box (32 channels,
+// w_box, 32 / w_box rows) = the 32 pixels one epilogue warp owns, 128B swizzle
+int make_map_epi(const dcvc_view &v, int channels, int w_box, CUtensorMap *out) {
+  MapKey k{};
+  k.ptr = (uint64_t)(v.data + v.coff);
+  k.d0 = channels; k.d1 = v.w; k.d2 = v.h;
+  k.s1 = (uint64_t)v.cstride * 4; k.s2 = (uint64_t)v.cstride * 4 * v.w;
+  k.b0 = 32; k.b1 = w_box; k.b2 = 32 / w_box;
+  k.e1 = 1; k.e2 = 1; k.swz = CU_TENSOR_MAP_SWIZZLE_128B; k.rank = 3;
+  std::lock_guard<std::mutex> g(g_maps_mu);
+  auto it = g_maps.find(k);
+  if (it != g_maps.end()) { *out = it->second; return DCVC_OK; }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return dcvc_fail(DCVC_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t dims[3] = {k.d0, k.d1, k.d2};
+  cuuint64_t strides[2] = {k.s1, k.s2};
+  cuuint32_t box[3] = {k.b0, k.b1, k.b2};
+  cuuint32_t es[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)k.ptr, dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return dcvc_fail(DCVC_ERR_CUDA, "cuTensorMapEncodeTiled(epilogue) failed: %d", (int)r);
+  if (g_maps.size() > 8192) g_maps.clear();
+  g_maps[k] = *out;
+  return DCVC_OK;
+}
+
 // weight map: dims (Ktot, N_pad), box (KC, N_tile)
 int make_map_b(const float *w, int ktot, int n_pad, int n_tile, int kc, CUtensorMap *out) {
   MapKey k{};
@@ -613,7 +797,8 @@ inline int ru(int v, int m) { return (v + m - 1) / m * m; }
 inline void n_tiling(int cout_w, int *tiles_n, int *n_tile) {
   const int n16 = ru(cout_w, 16);
   *tiles_n = (n16 + 255) / 256;
-  *n_tile = ru((n16 + *tiles_n - 1) / *tiles_n, 16);
+  // several N tiles: whole 32-column epilogue chunks per tile (a chunk never straddles tiles)
+  *n_tile = *tiles_n == 1 ? n16 : ru((n16 + *tiles_n - 1) / *tiles_n, 32);
 }
 
 }  // namespace
@@ -698,6 +883,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   static const int stage_kb = getenv("DCVC_TC_STAGE_KB") ? atoi(getenv("DCVC_TC_STAGE_KB")) : 36;
   static const int dbg_ctas = getenv("DCVC_TC_CTAS") ? atoi(getenv("DCVC_TC_CTAS")) : 3;
   static const int dbg_epi = getenv("DCVC_TC_EPI") ? atoi(getenv("DCVC_TC_EPI")) : 0;
+  static const int tma_epi_on = getenv("DCVC_TC_TMA_EPI") ? atoi(getenv("DCVC_TC_TMA_EPI")) : 1;
   static int num_sms = 0;
   if (!num_sms) {
     int dev = 0;
@@ -728,11 +914,16 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // epilogue warps: 4 per 32-column chunk group; a lone CTA on the SM gets 16 so that enough
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
-  int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi : (ctas == 1 ? 16 : 8);
+  // TMA-store epilogue: plain convs with at most one residual, views TMA-addressable
+  a.tma_epi = tma_epi_on && a.fast == 1 && !d->res2.data && !d->out2.data;
+  int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi
+            : a.tma_epi ? (ctas == 1 ? 8 : 4) : (ctas == 1 ? 16 : 8);
   while (epi > 4 && epi / 4 > nchunks) epi >>= 1;
   while (ctas > 1 && ctas * (64 + 32 * epi) > 680) --ctas;
   a.epi_warps = epi;
-  const uint32_t fixed = 1024u /*align*/ + 1024u /*barriers*/ + (uint32_t)epi * STG_WARP_FLOATS * 4u;
+  const uint32_t epi_bytes = (uint32_t)epi * (a.tma_epi ? 8192u : STG_WARP_FLOATS * 4u) +
+                             (a.tma_epi ? 8u * (uint32_t)(tiles_n * ru(a.n_tile, 32)) : 0u);
+  const uint32_t fixed = 1024u /*align*/ + 1024u /*barriers*/ + epi_bytes;
   while (ctas > 1 && (227u * 1024u / ctas) - 1024u < fixed + 2u * stage) --ctas;
   const uint32_t budget = (227u * 1024u / ctas) - 1024u - fixed;
   int stages = (int)(budget / stage);
@@ -743,14 +934,28 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.stages = stages;
   a.sbo = 8u * a.kc * 4u;
   a.layout_type = a.kc == 32 ? 2u : a.kc == 16 ? 4u : 6u;
-  // smem: [stages x stage][barriers (1 KB)][epi_warps epilogue staging tiles]
+  // smem: [stages x stage][barriers (1 KB)][epi_warps epilogue tiles][bias, scale vectors]
   a.stage_off = (uint32_t)stages * stage + 1024u;
-  const size_t smem = 1024 + (size_t)a.stage_off + (size_t)epi * STG_WARP_FLOATS * sizeof(float);
+  a.vec_off = a.stage_off + (uint32_t)epi * 8192u;
+  const size_t smem = 1024 + (size_t)a.stage_off + epi_bytes;
   if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: smem %zu too large", smem);
 
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, mo, mr;
   int rc = make_map_a(d->in, a.kc, a.th, a.tw, d->stride, &ma);
   if (rc) return rc;
+  if (a.tma_epi) {
+    const int w_box = a.tw < 32 ? a.tw : 32;
+    rc = make_map_epi(d->out, d->cout_w, w_box, &mo);
+    if (rc) return rc;
+    if (d->res1.data) {
+      rc = make_map_epi(d->res1, d->cout_w, w_box, &mr);
+      if (rc) return rc;
+    } else {
+      mr = mo;
+    }
+  } else {
+    mo = ma; mr = ma;   // unused by the kernel
+  }
   rc = make_map_b(d->weight_tc, a.ksize * a.ksize * cin_pad, n_pad, a.n_tile, a.kc, &mb);
   if (rc) return rc;
   static bool attr_set = false;
@@ -760,7 +965,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
     attr_set = true;
   }
   const int grid = a.total_tiles < ctas * num_sms ? a.total_tiles : ctas * num_sms;
-  conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, a);
+  conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, mo, mr, a);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }

@@ -19,6 +19,7 @@ SHAPES = [  # cin, cout, k, stride, h, w, kwargs
     (512, 128, 1, 1, 272, 480, {}), (64, 256, 1, 1, 544, 960, {}), (96, 96, 3, 1, 272, 480, {}),
     (384, 384, 1, 1, 68, 120, {}), (384, 1024, 1, 1, 68, 120, {}), (1024, 384, 1, 1, 68, 120, {}),
     (128, 128, 3, 1, 544, 960, {"shuffle": True}), (53, 64, 3, 2, 1088, 1920, {}),
+    (64, 48, 1, 1, 1088, 1920, {}), (48, 32, 1, 1, 1088, 1920, {}), (48, 48, 1, 1, 1088, 1920, {}),
 ]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 for cin, cout, k, s, h, w, kw in SHAPES:

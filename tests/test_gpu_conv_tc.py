@@ -10,6 +10,7 @@ import torch
 import torch.nn.functional as F
 
 from dcvc_b200 import _lib, layers, ops
+from dcvc_b200.tensor import Act
 
 from gpu_util import dev, from_act, to_act
 
@@ -165,3 +166,27 @@ def test_tc_conv_planar_shuffle(cin, cout, k, h, w):
     out_ref = ops.conv(xa, net.cw("c"), shuffle=True)
     out_pl = ops.conv(xa, cw, shuffle=True)
     assert torch.equal(from_act(out_ref), from_act(out_pl))
+
+
+@pytest.mark.parametrize("cin,cout,k,h,w", [(64, 48, 1, 40, 48), (48, 192, 1, 37, 53),
+                                            (32, 64, 3, 33, 70), (64, 768, 1, 24, 32),
+                                            (16, 40, 3, 24, 200), (128, 128, 1, 68, 120)])
+def test_tc_conv_tma_store_epilogue(cin, cout, k, h, w):
+    """Plain convs leave through the tensor-map store epilogue: bias + LeakyReLU + one residual
+    (fetched by TMA into the outgoing tile) + per-channel scale + clamp, into a channel slice of
+    a wider buffer whose neighbours must stay untouched; ragged tiles and N-tiled outputs."""
+    sd = _sd(cin, cout, k, seed=31)
+    x, r1 = _rand(1, cin, h, w, seed=8), _rand(1, cout, h, w, seed=9)
+    q = torch.rand(cout) + 0.5
+    conv = F.conv2d(x, sd["c.weight"], sd["c.bias"], 1, k // 2)
+    net = layers.Net(sd, dev())
+    xa = to_act(x)
+    wide = torch.full((h, w, cout + 16), 7.0, device=dev())
+    out = Act(wide, 8, cout)
+    ops.conv(xa, net.cw("c"), act=0.1, res=to_act(r1, cout + 4, 4), scale=q.to(dev()), out=out)
+    ref = (F.leaky_relu(conv, 0.1) + r1) * q.view(1, -1, 1, 1)
+    _check(from_act(out), ref, cin, k)
+    assert bool((wide[:, :, :8] == 7.0).all()) and bool((wide[:, :, 8 + cout:] == 7.0).all())
+    # no residual, clamp
+    out = ops.conv(xa, net.cw("c"), clamp01=True)
+    _check(from_act(out), conv.clamp(0, 1), cin, k)
