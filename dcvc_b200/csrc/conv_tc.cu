@@ -26,7 +26,7 @@ namespace {
 
 constexpr int TILE_M = 128;
 constexpr int MAX_THREADS = 64 + 32 * 16;   // warp 0 TMA, warp 1 MMA, then 4/8/16 epilogue warps
-constexpr long long SPIN_CYCLES = 4000000000ll;  // ~2 s: a protocol bug faults instead of hanging
+constexpr uint32_t SPIN_LIMIT = 1u << 26;   // failed try_wait polls before a wait gives up and traps
 
 struct TcArgs {
   dcvc_view out, res1, res2, out2;
@@ -38,6 +38,9 @@ struct TcArgs {
   uint32_t unit_a, unit_b, unit_tx, tmem_cols, acc_stride, sbo, layout_type, stage_off;
   uint64_t rcp_tiles_n, rcp_tiles_x;  // ceil(2^40 / d), see tile_coords()
   int fast;       // lean epilogue: 0 none, 1 plain, 2 gated, 3 planar depth-to-space (tc_fast_mode)
+  // halo mode (stride-1 k>1 convs): A stage = whole input window, B ring per tap
+  int halo, halo_sa, halo_sb, halo_pw, halo_bg;   // halo_bg: taps per B stage
+  uint32_t halo_sbo;
   int tma_epi;    // 1: TMA-store epilogue (stage_off region = 8 KB per warp, vec_off = bias/scale)
   uint32_t vec_off;
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
@@ -50,6 +53,23 @@ constexpr int STG_WARP_FLOATS = 32 * STG_PITCH;  // one epilogue warp's staging 
 // ------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
   return (uint32_t)__cvta_generic_to_shared(p);
+}
+// Loop invariants that come from the kernel parameter block: without this the compiler
+// re-reads them from the constant bank inside the single-warp producer / MMA loops (it treats
+// LDC as free to rematerialise), and every reload is ~50 cycles on a latency-bound chain.
+__device__ __forceinline__ int keep(int v) { asm volatile("" : "+r"(v)); return v; }
+__device__ __forceinline__ uint32_t keep(uint32_t v) { asm volatile("" : "+r"(v)); return v; }
+__device__ __forceinline__ uint64_t keep(uint64_t v) { asm volatile("" : "+l"(v)); return v; }
+
+// one lane of the (fully active) warp, the same one every time
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
@@ -69,12 +89,24 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// bounded wait: a protocol bug must fault, not hang the GPU
+// bounded wait: a protocol bug must fault, not hang the GPU.  The retry loop is nothing but
+// try_wait (which sleeps in hardware until the phase flips or a time slice ends) and a counter:
+// reading the clock between polls costs ~140 cycles per hand-off (scripts/ub/mbar_pingpong.cu).
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity))
-    if (clock64() - t0 > SPIN_CYCLES) __trap();
+  for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins)
+    if (spins > SPIN_LIMIT) __trap();
+}
+// Whole-warp wait used by the epilogue warps: one lane polls (with a back-off) and the warp
+// reconverges behind it.  32 lanes x 8-16 warps hammering try_wait on the tile barriers slows the
+// shared-memory barrier unit for the two threads that drive the TMA/MMA pipeline.
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity, int lane) {
+  if (lane == 0) {
+    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
+      __nanosleep(40);
+      if (spins > SPIN_LIMIT) __trap();
+    }
+  }
+  __syncwarp();
 }
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map, uint32_t bar,
                                             int c0, int c1, int c2, int c3) {
@@ -377,14 +409,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   // 1024-byte alignment for the swizzled tiles
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t unit_bytes = a.unit_a + a.unit_b;
-  const uint32_t stage_bytes = a.group * unit_bytes;
-  const uint32_t bars = base + a.stages * stage_bytes;   // full[s], empty[s], tfull[2], tempty[2]
+  const uint32_t unit_bytes = keep(a.unit_a + a.unit_b);
+  const uint32_t stage_bytes = keep(a.group * unit_bytes);
+  const uint32_t bars = keep(base + a.stage_off - 1024u);   // full[s], empty[s], tfull[2], tempty[2], res
   float *staging = reinterpret_cast<float *>(smem_raw + (base - raw) + a.stage_off);
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int groups = (a.units + a.group - 1) / a.group;
+  const int groups = keep((a.units + a.group - 1) / a.group);
 
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (a.stages + s); };
@@ -425,75 +457,178 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
+  // Warps 0 and 1 run their loops warp-wide (uniform control flow, operands in uniform
+  // registers) and only the asynchronous instructions themselves are issued by one elected lane:
+  // wrapping the whole loop in `if (lane == 0)` makes the compiler treat every operand as
+  // thread-divergent and surround each UTCHMMA / UTMALDG with an elect-and-retry loop.
   if (warp == 0) {
-    // ===== TMA producer: one stage = `group` (tap, channel-chunk) units =====
-    // Single-thread loops are latency-bound instruction by instruction, so they carry running
-    // counters (ring slot, phase, tap position) instead of dividing.
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0, stage_addr = base;
-      for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+    // ===== TMA producer =====
+    const bool leader = elect_one();
+    const int total = keep((int)(a.total_tiles)), step = keep((int)(gridDim.x)), kc = keep((int)(a.kc)), n_tile = keep((int)(a.n_tile));
+    const int chunks = keep((int)(a.chunks_per_tap)), ksize = keep((int)(a.ksize)), pad = keep((int)(a.pad));
+    const bool no_tma = (a.debug & 1) != 0;
+    if (a.halo) {
+      // ----- halo mode: one A load per (tile, channel chunk) = the (TH+k-1) x PW pixel window
+      // all k*k taps read through shifted descriptors; B streams per tap through its own ring.
+      // A of step i+1 is issued before the B taps of step i so it has a whole step to arrive.
+      const int taps = keep((int)(ksize * ksize)), sa_n = keep((int)(a.halo_sa)), sb_n = keep((int)(a.halo_sb));
+      const int bg = keep((int)(a.halo_bg));
+      const uint32_t stage_b = keep((uint32_t)(a.halo_bg * a.unit_b));
+      const uint32_t unit_a = a.unit_a, unit_b = a.unit_b, tx_a = a.unit_tx,
+                     tx_b = (uint32_t)(n_tile * kc * 4), b_base = base + sa_n * unit_a;
+      int sa = 0, sb = 0;
+      uint32_t pha = 0, phb = 0;
+      int a_tile = blockIdx.x, a_ch = 0;             // iterator of the A loads
+      auto issue_a = [&]() {
+        if (a_tile >= total) return;
+        int mt, nt, ty, tx;
+        tile_coords(a, a_tile, mt, nt, ty, tx);
+        mbar_wait(empty_bar(sa), pha ^ 1u);
+        if (leader) {
+          mbar_expect_tx(full_bar(sa), no_tma ? 0u : tx_a);
+          if (!no_tma)
+            tma_load_4d(base + sa * unit_a, &map_a, full_bar(sa), a_ch * kc, tx * a.tw - pad,
+                        ty * a.th - pad, 0);
+        }
+        if (++sa == sa_n) { sa = 0; pha ^= 1u; }
+        if (++a_ch == chunks) { a_ch = 0; a_tile += step; }
+      };
+      issue_a();
+      for (int tile = blockIdx.x; tile < total; tile += step) {
         int mt, nt, ty, tx;
         tile_coords(a, tile, mt, nt, ty, tx);
-        const int x0 = tx * a.tw * a.stride - a.pad, y0 = ty * a.th * a.stride - a.pad;
-        const int n_base = nt * a.n_tile;
+        const int n_base = nt * n_tile;
+        for (int ch = 0; ch < chunks; ++ch) {
+          issue_a();
+          for (int t0 = 0; t0 < taps; t0 += bg) {          // one B stage = `bg` consecutive taps
+            const int sbar = sa_n + sb, cnt = min(bg, taps - t0);
+            mbar_wait(empty_bar(sbar), phb ^ 1u);
+            if (leader) {
+              mbar_expect_tx(full_bar(sbar), no_tma ? 0u : (uint32_t)cnt * tx_b);
+              if (!no_tma)
+                for (int g = 0; g < cnt; ++g)
+                  tma_load_2d(b_base + sb * stage_b + g * unit_b, &map_b, full_bar(sbar),
+                              ((t0 + g) * chunks + ch) * kc, n_base);
+            }
+            if (++sb == sb_n) { sb = 0; phb ^= 1u; }
+          }
+        }
+      }
+    } else {
+      // ----- one stage = `group` (tap, channel-chunk) units, running counters instead of
+      // divisions (a single instruction stream is latency-bound instruction by instruction)
+      const int stages = keep((int)(a.stages)), group = keep((int)(a.group)), units = keep((int)(a.units)), stride = keep((int)(a.stride));
+      const uint32_t unit_a = keep((uint32_t)(a.unit_a)), unit_tx = keep((uint32_t)(a.unit_tx));
+      int s = 0;
+      uint32_t ph = 0, stage_addr = base;
+      for (int tile = blockIdx.x; tile < total; tile += step) {
+        int mt, nt, ty, tx;
+        tile_coords(a, tile, mt, nt, ty, tx);
+        const int x0 = tx * a.tw * stride - pad, y0 = ty * a.th * stride - pad;
+        const int n_base = nt * n_tile;
         int u = 0, dx = 0, dy = 0, ch = 0;
         for (int gi = 0; gi < groups; ++gi) {
           mbar_wait(empty_bar(s), ph ^ 1u);
-          const int cnt = min(a.group, a.units - u);
-          if (a.debug & 1) {
-            mbar_expect_tx(full_bar(s), 0);
-            u += cnt;
-          } else {
-            mbar_expect_tx(full_bar(s), cnt * a.unit_tx);
-            uint32_t sa = stage_addr;
-            for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
-              tma_load_4d(sa, &map_a, full_bar(s), ch * a.kc, x0 + dx, y0 + dy, 0);
-              tma_load_2d(sa + a.unit_a, &map_b, full_bar(s), u * a.kc, n_base);
-              if (++ch == a.chunks_per_tap) {
-                ch = 0;
-                if (++dx == a.ksize) { dx = 0; ++dy; }
-              }
+          const int cnt = min(group, units - u);
+          if (leader) mbar_expect_tx(full_bar(s), no_tma ? 0u : cnt * unit_tx);
+          uint32_t sa = stage_addr;
+          for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
+            if (leader && !no_tma) {
+              tma_load_4d(sa, &map_a, full_bar(s), ch * kc, x0 + dx, y0 + dy, 0);
+              tma_load_2d(sa + unit_a, &map_b, full_bar(s), u * kc, n_base);
+            }
+            if (++ch == chunks) {
+              ch = 0;
+              if (++dx == ksize) { dx = 0; ++dy; }
             }
           }
           stage_addr += stage_bytes;
-          if (++s == a.stages) { s = 0; ph ^= 1u; stage_addr = base; }
+          if (++s == stages) { s = 0; ph ^= 1u; stage_addr = base; }
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
-                             ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
-      const int kk_n = (a.debug & 2) ? 0 : a.kc / 8;
-      // descriptor = constant high word | (smem address >> 4) in the low 14 bits
-      const uint64_t desc_hi = make_smem_desc(0, a.sbo, a.layout_type);
+    const bool leader = elect_one();
+    const int total = keep((int)(a.total_tiles)), step = keep((int)(gridDim.x));
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
+                           ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
+    const int kk_n = keep((int)((a.debug & 2) ? 0 : a.kc / 8));
+    // descriptor = constant high word | (smem address >> 4) in the low 14 bits
+    const uint64_t desc_hi = keep((uint64_t)(make_smem_desc(0, a.sbo, a.layout_type)));
+    const uint32_t acc_stride = keep((uint32_t)(a.acc_stride)), unit_a = keep((uint32_t)(a.unit_a)), unit_b = keep((uint32_t)(a.unit_b));
+    uint32_t as = 0, aph = 0;
+    if (a.halo) {
+      // A descriptor of tap (dy, dx): the window shifted by (dy * PW + dx) pixels; 8-row groups
+      // (= image rows of the 16x8 tile) are PW pixels apart (halo_sbo).  The start address is
+      // not aligned to the 1024-byte swizzle pattern: the tensor core swizzles on absolute
+      // shared-memory address bits, exactly as TMA wrote the window, so the base-offset field of
+      // the descriptor stays 0 (any other value reads the wrong 16-byte chunks; measured).
+      const int taps = keep((int)(a.ksize * a.ksize)), chunks = keep((int)(a.chunks_per_tap)), ksize = keep((int)(a.ksize));
+      const int sa_n = keep((int)(a.halo_sa)), sb_n = keep((int)(a.halo_sb)), pw = keep((int)(a.halo_pw));
+      const int bg = keep((int)(a.halo_bg));
+      const uint32_t stage_b = keep((uint32_t)(a.halo_bg * a.unit_b));
+      const uint64_t desc_a_hi = keep((uint64_t)(make_smem_desc(0, a.halo_sbo, a.layout_type)));
+      const uint32_t b_base = keep((uint32_t)(base + sa_n * unit_a)), pitch = keep((uint32_t)((uint32_t)a.kc * 4u));
+      int sa = 0, sb = 0;
+      uint32_t pha = 0, phb = 0;
+      for (int tile = blockIdx.x; tile < total; tile += step) {
+        mbar_wait(tempty_bar(as), aph ^ 1u);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + as * acc_stride;
+        for (int ch = 0; ch < chunks; ++ch) {
+          mbar_wait(full_bar(sa), pha);
+          tc_fence_after();
+          const uint32_t a_addr = base + sa * unit_a;
+          int dx = 0, dy = 0;
+          for (int t0 = 0; t0 < taps; t0 += bg) {          // one B stage = `bg` consecutive taps
+            const int sbar = sa_n + sb, cnt = min(bg, taps - t0);
+            mbar_wait(full_bar(sbar), phb);
+            tc_fence_after();
+            for (int g = 0; g < cnt; ++g) {
+              const uint32_t start = a_addr + (uint32_t)(dy * pw + dx) * pitch;
+              const uint64_t da = desc_a_hi | (uint64_t)(start >> 4);
+              const uint64_t db = desc_hi | (uint64_t)((b_base + sb * stage_b + g * unit_b) >> 4);
+              if (leader)
+                for (int kk = 0; kk < kk_n; ++kk)
+                  umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
+              if (++dx == ksize) { dx = 0; ++dy; }
+            }
+            if (leader) umma_commit(empty_bar(sbar));
+            if (++sb == sb_n) { sb = 0; phb ^= 1u; }
+          }
+          if (leader) umma_commit(empty_bar(sa));
+          if (++sa == sa_n) { sa = 0; pha ^= 1u; }
+        }
+        if (leader) umma_commit(tfull_bar(as));
+        if ((as ^= 1u) == 0) aph ^= 1u;
+      }
+    } else {
+      const int stages = keep((int)(a.stages)), group = keep((int)(a.group)), units = keep((int)(a.units));
       int s = 0;
-      uint32_t ph = 0, stage_addr = base, as = 0, aph = 0;
-      for (int tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x) {
+      uint32_t ph = 0, stage_addr = base;
+      for (int tile = blockIdx.x; tile < total; tile += step) {
         mbar_wait(tempty_bar(as), aph ^ 1u);       // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t tacc = tmem_base + as * a.acc_stride;
+        const uint32_t tacc = tmem_base + as * acc_stride;
         int u = 0;
         for (int gi = 0; gi < groups; ++gi) {
           mbar_wait(full_bar(s), ph);
           tc_fence_after();
-          const int cnt = min(a.group, a.units - u);
+          const int cnt = min(group, units - u);
           uint32_t sa = stage_addr;
           for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
             const uint64_t da = desc_hi | (uint64_t)(sa >> 4);
-            const uint64_t db = desc_hi | (uint64_t)((sa + a.unit_a) >> 4);
-            for (int kk = 0; kk < kk_n; ++kk)  // +32 bytes along K per MMA: +2 in the >>4 field
-              umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
+            const uint64_t db = desc_hi | (uint64_t)((sa + unit_a) >> 4);
+            if (leader)
+              for (int kk = 0; kk < kk_n; ++kk)  // +32 bytes along K per MMA: +2 in the >>4 field
+                umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
           }
-          if (a.debug & 8) mbar_arrive(empty_bar(s));   // experiment (with bit1): no commit
-          else umma_commit(empty_bar(s));      // frees the smem slot when these MMAs retire
+          if (leader) umma_commit(empty_bar(s));   // frees the smem slot when these MMAs retire
           stage_addr += stage_bytes;
-          if (++s == a.stages) { s = 0; ph ^= 1u; stage_addr = base; }
+          if (++s == stages) { s = 0; ph ^= 1u; stage_addr = base; }
         }
-        if (a.debug & 8) mbar_arrive(tfull_bar(as));
-        else umma_commit(tfull_bar(as));       // accumulator complete
+        if (leader) umma_commit(tfull_bar(as));    // accumulator complete
         if ((as ^= 1u) == 0) aph ^= 1u;
       }
     }
@@ -505,6 +640,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // the tile out with a tensor-map store (clipping ragged edges and padded channels).  The
     // residual tile arrives the same way (TMA load into the very buffer the result will leave
     // from), so no per-element address arithmetic or global LD/ST is issued by the warp.
+    const bool leader = elect_one();
     const int we = warp - 2, q = warp & 3, part = we >> 2, parts = a.epi_warps >> 2;
     const uint32_t buf0 = base + a.stage_off + (uint32_t)we * 8192u;
     uint8_t *const buf0_g = smem_raw + (base - raw) + a.stage_off + (size_t)we * 8192u;
@@ -517,7 +653,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const uint32_t row_off = (uint32_t)lane * 128u, sw = (uint32_t)(lane & 7);
     uint32_t rph0 = 0, rph1 = 0, b = 0, lt = 0;
     int tile = blockIdx.x, ci = part;
-    if (has_res && lane == 0 && tile < a.total_tiles) {
+    if (has_res && leader && tile < a.total_tiles) {
       int mt, nt, ty, tx;
       tile_coords(a, tile, mt, nt, ty, tx);
       mbar_expect_tx(res_bar(2 * we), 4096u);
@@ -530,7 +666,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       const int n0 = ci * 32, c0 = nt * a.n_tile + n0, x0 = tx * a.tw + bx, y0 = ty * a.th + by;
       const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
       if (ci == part) {                                   // first chunk of this tile for the warp
-        mbar_wait(tfull_bar(as), aph);
+        mbar_wait_warp(tfull_bar(as), aph, lane);
         tc_fence_after();
       }
       const uint32_t trow = tmem_base + as * a.acc_stride + ((uint32_t)(q * 32) << 16);
@@ -561,7 +697,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           for (int j = 0; j < 32; ++j) v[j] = lrelu01(v[j], a.out_slope);
         }
         if (has_res) {
-          mbar_wait(res_bar(2 * we + b), b ? rph1 : rph0);
+          mbar_wait_warp(res_bar(2 * we + b), b ? rph1 : rph0, lane);
           if (b) rph1 ^= 1u; else rph0 ^= 1u;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -586,15 +722,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
               make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         fence_async_smem();
         __syncwarp();
-        if (lane == 0) {
+        if (leader) {
           tma_store_3d(&map_o, buf, c0, x0, y0);
           bulk_commit();
         }
       } else if (has_res) {                               // experiment: no stores, still drain loads
-        mbar_wait(res_bar(2 * we + b), b ? rph1 : rph0);
+        mbar_wait_warp(res_bar(2 * we + b), b ? rph1 : rph0, lane);
         if (b) rph1 ^= 1u; else rph0 ^= 1u;
       }
-      if (lane == 0) {
+      if (leader) {
         bulk_wait_read<1>();                              // the store issued a chunk ago has left smem
         if (has_res && ntile < a.total_tiles) {
           int mt2, nt2, ty2, tx2;
@@ -609,7 +745,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       tile = ntile;
       ci = nci;
     }
-    if (lane == 0) bulk_wait_all();
+    if (leader) bulk_wait_all();
   } else {
     // ===== epilogue: warps 2..2+epi_warps; warp w owns TMEM lanes 32*(w%4).., column chunks
     // ci with ci % (epi_warps/4) == part.  Phase 1: thread = pixel row, tcgen05.ld 32 columns, park them in a
@@ -623,7 +759,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       tile_coords(a, tile, mt, nt, ty, tx);
       const int ox0 = tx * a.tw, oy0 = ty * a.th, n_base = nt * a.n_tile;
       const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
-      mbar_wait(tfull_bar(as), aph);
+      mbar_wait_warp(tfull_bar(as), aph, lane);
       tc_fence_after();
       const uint32_t trow = tmem_base + as * a.acc_stride + ((uint32_t)(q * 32) << 16);
       int last = -1;
@@ -871,11 +1007,28 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
     const int area = ru(wout, tw) * ru(hout, th);
     if (area < best_area) { best_area = area; a.tw = tw; a.th = th; }
   }
+  // halo mode: stride-1 k x k convs load the (16+k-1) x 16 pixel input window of a 16x8 tile
+  // once per channel chunk and feed all k*k taps from it through shifted smem descriptors
+  // DCVC_TC_HALO: 0 off, 1 where it measured faster (3x3 with 64-byte channel chunks or wide N;
+  // both modes are MMA-issue-bound for small N, so the gain is the saved L2 traffic only), 2 all
+  static const int halo_on = getenv("DCVC_TC_HALO") ? atoi(getenv("DCVC_TC_HALO")) : 1;
+  a.halo = halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 9 && a.kc >= 16 &&
+           d->pad == d->ksize / 2;
+  if (a.halo && halo_on == 1)
+    a.halo = d->ksize == 3 && !d->shuffle && (a.kc == 16 || a.n_tile >= 96);
+  const int halo_ph = TILE_M / 8 + d->ksize - 1;
+  static const int halo_pw16 = getenv("DCVC_TC_HALO_PW16") ? atoi(getenv("DCVC_TC_HALO_PW16")) : 0;
+  if (a.halo) { a.tw = 8; a.th = TILE_M / 8; a.halo_pw = halo_pw16 ? 16 : 8 + d->ksize - 1; }
   a.tiles_x = cdiv(wout, a.tw);
   const int tiles_y = cdiv(hout, a.th);
   a.unit_a = (uint32_t)ru(TILE_M * a.kc * 4, 1024);
   a.unit_b = (uint32_t)ru(a.n_tile * a.kc * 4, 1024);
   a.unit_tx = (uint32_t)(TILE_M * a.kc * 4 + a.n_tile * a.kc * 4);
+  if (a.halo) {
+    a.unit_tx = (uint32_t)(halo_ph * a.halo_pw * a.kc * 4);
+    a.unit_a = (uint32_t)ru((int)a.unit_tx, 1024);
+    a.halo_sbo = (uint32_t)(a.halo_pw * a.kc * 4);
+  }
   const uint32_t unit = a.unit_a + a.unit_b;
   static const int dbg = getenv("DCVC_TC_DEBUG") ? atoi(getenv("DCVC_TC_DEBUG")) : 0;
   static const int dbg_stages = getenv("DCVC_TC_STAGES") ? atoi(getenv("DCVC_TC_STAGES")) : 0;
@@ -911,6 +1064,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   int ctas = (int)(512u / a.tmem_cols);
   if (ctas > dbg_ctas) ctas = dbg_ctas;
   if (ctas < 1) ctas = 1;
+  static const int halo_ctas = getenv("DCVC_TC_HALO_CTAS") ? atoi(getenv("DCVC_TC_HALO_CTAS")) : 2;
+  if (a.halo && ctas > halo_ctas) ctas = halo_ctas;
   // epilogue warps: 4 per 32-column chunk group; a lone CTA on the SM gets 16 so that enough
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
@@ -936,12 +1091,33 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.layout_type = a.kc == 32 ? 2u : a.kc == 16 ? 4u : 6u;
   // smem: [stages x stage][barriers (1 KB)][epi_warps epilogue tiles][bias, scale vectors]
   a.stage_off = (uint32_t)stages * stage + 1024u;
+  if (a.halo) {
+    // [SA x window][SB x (bg weight taps)][barriers]...: a B stage carries a group of taps (about
+    // 24 KB, at most one kernel row) so that one barrier round trip covers several MMAs
+    static const int bg_kb = getenv("DCVC_TC_HALO_BKB") ? atoi(getenv("DCVC_TC_HALO_BKB")) : 24;
+    int bg = (int)((uint32_t)bg_kb * 1024u / a.unit_b);
+    if (bg > a.ksize) bg = a.ksize;
+    if (bg < 1) bg = 1;
+    a.halo_bg = bg;
+    const uint32_t stage_b = (uint32_t)bg * a.unit_b;
+    while (ctas > 1 && (227u * 1024u / ctas) - 1024u < fixed + 2u * a.unit_a + 2u * stage_b) --ctas;
+    const uint32_t room = (227u * 1024u / ctas) - 1024u - fixed;
+    a.halo_sa = room >= 3u * a.unit_a + 3u * stage_b ? 3 : 2;
+    if (room < 2u * a.unit_a + 2u * stage_b)
+      return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: halo window does not fit shared memory");
+    int sb = (int)((room - (uint32_t)a.halo_sa * a.unit_a) / stage_b);
+    static const int sb_cap = getenv("DCVC_TC_HALO_SB") ? atoi(getenv("DCVC_TC_HALO_SB")) : 8;
+    a.halo_sb = sb > sb_cap ? sb_cap : sb;
+    a.stages = a.halo_sa + a.halo_sb;
+    a.stage_off = (uint32_t)a.halo_sa * a.unit_a + (uint32_t)a.halo_sb * stage_b + 1024u;
+  }
   a.vec_off = a.stage_off + (uint32_t)epi * 8192u;
   const size_t smem = 1024 + (size_t)a.stage_off + epi_bytes;
   if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: smem %zu too large", smem);
 
   CUtensorMap ma, mb, mo, mr;
-  int rc = make_map_a(d->in, a.kc, a.th, a.tw, d->stride, &ma);
+  int rc = a.halo ? make_map_a(d->in, a.kc, halo_ph, a.halo_pw, 1, &ma)
+                  : make_map_a(d->in, a.kc, a.th, a.tw, d->stride, &ma);
   if (rc) return rc;
   if (a.tma_epi) {
     const int w_box = a.tw < 32 ? a.tw : 32;
