@@ -129,3 +129,30 @@ def test_gop_matches_reference(golden_dir, name):
                 dpb = r["dpb"]
             assert abs(float(r["bit"]) - float(g[f"est_bit_{k}"])) <= 1e-3 * float(g[f"est_bit_{k}"])
             np.testing.assert_allclose(dpb["ref_frame"].numpy(), g[f"est_x_hat_{k}"], atol=1e-6)
+
+
+@pytest.mark.parametrize("warps,n", [(1, 0), (1, 1), (1, 33), (2, 100), (4, 1000)])
+def test_interleaved_restatement_round_trips(warps, n):
+    """The CPU restatement of the product's interleaved container is lossless (escapes included)
+    and its size stays within the per-warp state overhead of the reference coder's size."""
+    from oracle import rans_interleaved_oracle as rio
+    tabs = eo.gaussian_tables("laplace")
+    rng = np.random.default_rng(n + warps)
+    calls = []
+    for m in (n, n // 3 + 1):
+        idx = rng.integers(0, 256, m).astype(np.int16)
+        scale = 0.01 * (64.0 / 0.01) ** (idx / 255.0)
+        sym = np.round(rng.laplace(0, scale)).clip(-30000, 30000).astype(np.int16)
+        sym[rng.random(m) < 0.03] *= 41
+        calls.append((sym, idx))
+    stream = rio.encode(calls, tabs, warps)
+    assert stream[0] == ((warps - 1) << 4 | 0xF)
+    back = rio.decode(stream, [c[1] for c in calls], tabs)
+    for (sym, _), out in zip(calls, back):
+        assert np.array_equal(sym, out)
+    enc = rans_oracle.RansEncoder(False, 1)
+    enc.reset()
+    for sym, idx in calls:
+        enc.encode_with_indexes(sym, idx, *tabs)
+    enc.flush()
+    assert len(stream) <= enc.get_encoded_stream().size * 1.02 + 132 * warps + 8
