@@ -21,6 +21,8 @@ SHAPES = [  # cin, cout, k, stride, h, w, kwargs
     (128, 128, 3, 1, 544, 960, {"shuffle": True}), (53, 64, 3, 2, 1088, 1920, {}),
     (64, 48, 1, 1, 1088, 1920, {}), (48, 32, 1, 1, 1088, 1920, {}), (48, 48, 1, 1, 1088, 1920, {}),
 ]
+if os.environ.get("SHAPES"):   # "cin,cout,k,stride,h,w;..."
+    SHAPES = [tuple(int(v) for v in t.split(",")) + ({},) for t in os.environ["SHAPES"].split(";")]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 for cin, cout, k, s, h, w, kw in SHAPES:
     name = f"conv{k}x{k}s{s} {cin}->{cout} @{h}x{w} {kw}"

@@ -1,5 +1,7 @@
-echo HALO
-DCVC_TC_HALO=1 timeout 300 python -m pytest tests/test_gpu_conv_tc.py -x -q 2>&1 | tail -2
-DCVC_TC_HALO=1 python scripts/bench_conv.py 1 | grep -E "3x3s1|7x7" | cut -c1-40,60-100
-echo HALO ctas1
-DCVC_TC_HALO_CTAS=1 DCVC_TC_HALO=1 python scripts/bench_conv.py 1 | grep -E "3x3s1|7x7" | cut -c1-40,60-100
+export SHAPES="1024,32,1,1,272,480;1024,48,1,1,272,480;1024,64,1,1,272,480;1024,96,1,1,272,480;1024,128,1,1,272,480;1024,192,1,1,272,480;1024,256,1,1,272,480"
+echo "DEBUG=5 (no TMA, no stores): MMA + handshakes only"
+DCVC_TC_DEBUG=5 python scripts/bench_conv.py 1 | cut -c1-40,60-100
+echo "DEBUG=7 (no MMA either)"
+DCVC_TC_DEBUG=7 python scripts/bench_conv.py 1 | cut -c1-40,60-100
+echo "DEBUG=5 CTAS=1"
+DCVC_TC_CTAS=1 DCVC_TC_DEBUG=5 python scripts/bench_conv.py 1 | cut -c1-40,60-100
