@@ -26,7 +26,8 @@ class Conv(ctypes.Structure):
                 ("ksize", c_int32), ("stride", c_int32), ("pad", c_int32), ("cout_w", c_int32),
                 ("gate", c_int32), ("shuffle", c_int32),
                 ("in_slope", c_float), ("out_slope", c_float), ("gate_slope", c_float),
-                ("out2_slope", c_float), ("mode", c_int32), ("clamp01", c_int32)]
+                ("out2_slope", c_float), ("mode", c_int32), ("clamp01", c_int32),
+                ("weight_tc16", c_void_p), ("in_f16", c_int32), ("out_f16", c_int32)]
 
 
 class Quad(ctypes.Structure):
@@ -50,10 +51,13 @@ SIGNATURES = {
     "dcvc_conv_tc_eligible": (c_int, [ctypes.POINTER(Conv)]),
     "dcvc_conv_tc_geometry": (c_int, [c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                       ctypes.POINTER(c_int)]),
+    "dcvc_conv_tc_geometry16": (c_int, [c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                        ctypes.POINTER(c_int)]),
     "dcvc_dwconv3x3": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p]),
     "dcvc_nchw_to_nhwc": (c_int, [c_void_p, VP, c_void_p]),
     "dcvc_nhwc_to_nchw": (c_int, [VP, c_void_p, c_int, c_void_p]),
     "dcvc_copy": (c_int, [VP, VP, c_float, c_float, c_void_p]),
+    "dcvc_copy_f16": (c_int, [VP, VP, c_float, c_float, c_void_p]),
     "dcvc_fill": (c_int, [VP, c_float, c_void_p]),
     "dcvc_pool2": (c_int, [VP, VP, c_int, c_void_p]),
     "dcvc_resize_bilinear": (c_int, [VP, VP, c_float, c_void_p]),

@@ -44,6 +44,9 @@ struct TcArgs {
   int tma_epi;    // 1: TMA-store epilogue (stage_off region = 8 KB per warp, vec_off = bias/scale)
   uint32_t vec_off;
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
+  int kcb;        // bytes of one K chunk row (128/64/32) = kc * element size
+  int f16_in;     // A/B operands are binary16: kind::f16, K = 16 per instruction
+  int f16_out;    // TMA-store epilogue writes binary16 (64-byte rows, 64B swizzle)
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
 
@@ -139,6 +142,15 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                         uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                ::"r"(bar)
@@ -198,6 +210,11 @@ __device__ __forceinline__ void bulk_wait_read() {   // all but the N newest gro
 }
 __device__ __forceinline__ void bulk_wait_all() {
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {   // two floats -> half2 bits (RN)
+  uint32_t r;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 __device__ __forceinline__ void fence_async_smem() {  // generic-proxy smem writes -> async proxy
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -475,7 +492,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       const int bg = keep((int)(a.halo_bg));
       const uint32_t stage_b = keep((uint32_t)(a.halo_bg * a.unit_b));
       const uint32_t unit_a = a.unit_a, unit_b = a.unit_b, tx_a = a.unit_tx,
-                     tx_b = (uint32_t)(n_tile * kc * 4), b_base = base + sa_n * unit_a;
+                     tx_b = (uint32_t)(n_tile * a.kcb), b_base = base + sa_n * unit_a;
       int sa = 0, sb = 0;
       uint32_t pha = 0, phb = 0;
       int a_tile = blockIdx.x, a_ch = 0;             // iterator of the A loads
@@ -551,9 +568,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // ===== MMA issuer =====
     const bool leader = elect_one();
     const int total = keep((int)(a.total_tiles)), step = keep((int)(gridDim.x));
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
-                           ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
-    const int kk_n = keep((int)((a.debug & 2) ? 0 : a.kc / 8));
+    // instruction descriptor: D = F32 (bit 4), A/B format (bits 7, 10: 2 = TF32, 0 = F16),
+    // K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+    const bool f16 = a.f16_in != 0;
+    const uint32_t idesc = keep((uint32_t)((1u << 4) | (f16 ? 0u : (2u << 7) | (2u << 10)) |
+                           ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24)));
+    // one MMA consumes 32 bytes of K per row: 8 TF32 or 16 binary16 values
+    const int kk_n = keep((int)((a.debug & 2) ? 0 : a.kcb / 32));
     // descriptor = constant high word | (smem address >> 4) in the low 14 bits
     const uint64_t desc_hi = keep((uint64_t)(make_smem_desc(0, a.sbo, a.layout_type)));
     const uint32_t acc_stride = keep((uint32_t)(a.acc_stride)), unit_a = keep((uint32_t)(a.unit_a)), unit_b = keep((uint32_t)(a.unit_b));
@@ -569,7 +590,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       const int bg = keep((int)(a.halo_bg));
       const uint32_t stage_b = keep((uint32_t)(a.halo_bg * a.unit_b));
       const uint64_t desc_a_hi = keep((uint64_t)(make_smem_desc(0, a.halo_sbo, a.layout_type)));
-      const uint32_t b_base = keep((uint32_t)(base + sa_n * unit_a)), pitch = keep((uint32_t)((uint32_t)a.kc * 4u));
+      const uint32_t b_base = keep((uint32_t)(base + sa_n * unit_a)), pitch = keep((uint32_t)a.kcb);
       int sa = 0, sb = 0;
       uint32_t pha = 0, phb = 0;
       for (int tile = blockIdx.x; tile < total; tile += step) {
@@ -589,9 +610,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
               const uint32_t start = a_addr + (uint32_t)(dy * pw + dx) * pitch;
               const uint64_t da = desc_a_hi | (uint64_t)(start >> 4);
               const uint64_t db = desc_hi | (uint64_t)((b_base + sb * stage_b + g * unit_b) >> 4);
-              if (leader)
-                for (int kk = 0; kk < kk_n; ++kk)
-                  umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
+              if (leader) {
+                if (f16)
+                  for (int kk = 0; kk < kk_n; ++kk)
+                    umma_f16(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
+                else
+                  for (int kk = 0; kk < kk_n; ++kk)
+                    umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
+              }
               if (++dx == ksize) { dx = 0; ++dy; }
             }
             if (leader) umma_commit(empty_bar(sbar));
@@ -620,9 +646,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
             const uint64_t da = desc_hi | (uint64_t)(sa >> 4);
             const uint64_t db = desc_hi | (uint64_t)((sa + unit_a) >> 4);
-            if (leader)
-              for (int kk = 0; kk < kk_n; ++kk)  // +32 bytes along K per MMA: +2 in the >>4 field
-                umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
+            if (leader) {                        // +32 bytes along K per MMA: +2 in the >>4 field
+              if (f16)
+                for (int kk = 0; kk < kk_n; ++kk)
+                  umma_f16(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
+              else
+                for (int kk = 0; kk < kk_n; ++kk)
+                  umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
+            }
           }
           if (leader) umma_commit(empty_bar(s));   // frees the smem slot when these MMAs retire
           stage_addr += stage_bytes;
@@ -716,10 +747,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fminf(fmaxf(v[j], 0.f), 1.f);
         }
+        if (a.f16_out) {
+          // binary16 rows of 64 bytes, 64B swizzle: 16-byte chunk j of row r sits at
+          // j ^ ((r >> 1) & 3) (address bits [4,6) ^= bits [7,9))
+          const uint32_t row16 = (uint32_t)lane * 64u, sw4 = (uint32_t)(lane >> 1) & 3u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4 *>(buf_g + row_off + (((uint32_t)j ^ sw) << 4)) =
-              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          for (int j = 0; j < 4; ++j) {
+            uint4 pk;
+            pk.x = pack_h2(v[8 * j], v[8 * j + 1]);     pk.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
+            pk.z = pack_h2(v[8 * j + 4], v[8 * j + 5]); pk.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
+            *reinterpret_cast<uint4 *>(buf_g + row16 + (((uint32_t)j ^ sw4) << 4)) = pk;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4 *>(buf_g + row_off + (((uint32_t)j ^ sw) << 4)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
         fence_async_smem();
         __syncwarp();
         if (leader) {
@@ -847,19 +891,25 @@ struct MapHash {
 std::unordered_map<MapKey, CUtensorMap, MapHash> g_maps;
 std::mutex g_maps_mu;
 
-CUtensorMapSwizzle swizzle_of(int kc) {
-  return kc == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : kc == 16 ? CU_TENSOR_MAP_SWIZZLE_64B
-                                                          : CU_TENSOR_MAP_SWIZZLE_32B;
+CUtensorMapSwizzle swizzle_of(int row_bytes) {
+  return row_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : row_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                                        : CU_TENSOR_MAP_SWIZZLE_32B;
+}
+// element size / tensor-map type of a view; the MapKey carries the type in the high bits of rank
+inline uint64_t esz_of(bool f16) { return f16 ? 2 : 4; }
+inline CUtensorMapDataType dt_of(bool f16) {
+  return f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
 }
 
 // activation map: dims (C, W, H, 1), box (KC, TW', TH', 1), traversal strides (1, s, s, 1)
-int make_map_a(const dcvc_view &in, int kc, int th, int tw, int stride, CUtensorMap *out) {
+int make_map_a(const dcvc_view &in, int kc, int th, int tw, int stride, bool f16, CUtensorMap *out) {
   MapKey k{};
-  k.ptr = (uint64_t)(in.data + in.coff);
+  const uint64_t esz = esz_of(f16);
+  k.ptr = (uint64_t)in.data + (uint64_t)in.coff * esz;
   k.d0 = in.c; k.d1 = in.w; k.d2 = in.h;
-  k.s1 = (uint64_t)in.cstride * 4; k.s2 = (uint64_t)in.cstride * 4 * in.w;
+  k.s1 = (uint64_t)in.cstride * esz; k.s2 = (uint64_t)in.cstride * esz * in.w;
   k.b0 = kc; k.b1 = stride == 1 ? tw : tw * 2 - 1; k.b2 = stride == 1 ? th : th * 2 - 1;
-  k.e1 = stride; k.e2 = stride; k.swz = swizzle_of(kc); k.rank = 4;
+  k.e1 = stride; k.e2 = stride; k.swz = swizzle_of(kc * (int)esz); k.rank = 4 | (f16 ? 0x100 : 0);
   std::lock_guard<std::mutex> g(g_maps_mu);
   auto it = g_maps.find(k);
   if (it != g_maps.end()) { *out = it->second; return DCVC_OK; }
@@ -869,7 +919,7 @@ int make_map_a(const dcvc_view &in, int kc, int th, int tw, int stride, CUtensor
   cuuint64_t strides[3] = {k.s1, k.s2, k.s2 * in.h};
   cuuint32_t box[4] = {k.b0, k.b1, k.b2, 1};
   cuuint32_t es[4] = {1, k.e1, k.e2, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void *)k.ptr, dims, strides, box, es,
+  CUresult r = enc(out, dt_of(f16), 4, (void *)k.ptr, dims, strides, box, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)k.swz,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return dcvc_fail(DCVC_ERR_CUDA, "cuTensorMapEncodeTiled(A) failed: %d", (int)r);
@@ -880,13 +930,14 @@ int make_map_a(const dcvc_view &in, int kc, int th, int tw, int stride, CUtensor
 
 // epilogue map over an output-side view (out / residual): dims (C, W, H), box (32 channels,
 // w_box, 32 / w_box rows) = the 32 pixels one epilogue warp owns, 128B swizzle
-int make_map_epi(const dcvc_view &v, int channels, int w_box, CUtensorMap *out) {
+int make_map_epi(const dcvc_view &v, int channels, int w_box, bool f16, CUtensorMap *out) {
   MapKey k{};
-  k.ptr = (uint64_t)(v.data + v.coff);
+  const uint64_t esz = esz_of(f16);
+  k.ptr = (uint64_t)v.data + (uint64_t)v.coff * esz;
   k.d0 = channels; k.d1 = v.w; k.d2 = v.h;
-  k.s1 = (uint64_t)v.cstride * 4; k.s2 = (uint64_t)v.cstride * 4 * v.w;
+  k.s1 = (uint64_t)v.cstride * esz; k.s2 = (uint64_t)v.cstride * esz * v.w;
   k.b0 = 32; k.b1 = w_box; k.b2 = 32 / w_box;
-  k.e1 = 1; k.e2 = 1; k.swz = CU_TENSOR_MAP_SWIZZLE_128B; k.rank = 3;
+  k.e1 = 1; k.e2 = 1; k.swz = swizzle_of(32 * (int)esz); k.rank = 3 | (f16 ? 0x100 : 0);
   std::lock_guard<std::mutex> g(g_maps_mu);
   auto it = g_maps.find(k);
   if (it != g_maps.end()) { *out = it->second; return DCVC_OK; }
@@ -896,8 +947,8 @@ int make_map_epi(const dcvc_view &v, int channels, int w_box, CUtensorMap *out) 
   cuuint64_t strides[2] = {k.s1, k.s2};
   cuuint32_t box[3] = {k.b0, k.b1, k.b2};
   cuuint32_t es[3] = {1, 1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)k.ptr, dims, strides, box, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  CUresult r = enc(out, dt_of(f16), 3, (void *)k.ptr, dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)k.swz,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return dcvc_fail(DCVC_ERR_CUDA, "cuTensorMapEncodeTiled(epilogue) failed: %d", (int)r);
   if (g_maps.size() > 8192) g_maps.clear();
@@ -906,10 +957,11 @@ int make_map_epi(const dcvc_view &v, int channels, int w_box, CUtensorMap *out) 
 }
 
 // weight map: dims (Ktot, N_pad), box (KC, N_tile)
-int make_map_b(const float *w, int ktot, int n_pad, int n_tile, int kc, CUtensorMap *out) {
+int make_map_b(const void *w, int ktot, int n_pad, int n_tile, int kc, bool f16, CUtensorMap *out) {
   MapKey k{};
-  k.ptr = (uint64_t)w; k.d0 = ktot; k.d1 = n_pad; k.s1 = (uint64_t)ktot * 4;
-  k.b0 = kc; k.b1 = n_tile; k.swz = swizzle_of(kc); k.rank = 2;
+  const uint64_t esz = esz_of(f16);
+  k.ptr = (uint64_t)w; k.d0 = ktot; k.d1 = n_pad; k.s1 = (uint64_t)ktot * esz;
+  k.b0 = kc; k.b1 = n_tile; k.swz = swizzle_of(kc * (int)esz); k.rank = 2 | (f16 ? 0x100 : 0);
   std::lock_guard<std::mutex> g(g_maps_mu);
   auto it = g_maps.find(k);
   if (it != g_maps.end()) { *out = it->second; return DCVC_OK; }
@@ -919,7 +971,7 @@ int make_map_b(const float *w, int ktot, int n_pad, int n_tile, int kc, CUtensor
   cuuint64_t strides[1] = {k.s1};
   cuuint32_t box[2] = {k.b0, k.b1};
   cuuint32_t es[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)k.ptr, dims, strides, box, es,
+  CUresult r = enc(out, dt_of(f16), 2, (void *)k.ptr, dims, strides, box, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)k.swz,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return dcvc_fail(DCVC_ERR_CUDA, "cuTensorMapEncodeTiled(B) failed: %d", (int)r);
@@ -939,12 +991,43 @@ inline void n_tiling(int cout_w, int *tiles_n, int *n_tile) {
 
 }  // namespace
 
-// K chunk: the candidate in {32,16,8} that pads Cin least (ties -> larger chunk)
+// K chunk in {32,16,8} floats
 extern "C" int dcvc_conv_tc_geometry(int cout_w, int cin, int *n_pad, int *cin_pad, int *kc) {
   if (cout_w < 1 || cin < 1) return dcvc_fail(DCVC_ERR_ARG, "conv_tc_geometry: bad arguments");
   int best = 32, best_pad = ru(cin, 32);
-  for (int c : {16, 8})
+  for (int c : {16, 8})                   // DCVC_TC_KC=0: least padding, ties -> larger chunk
     if (ru(cin, c) < best_pad) { best = c; best_pad = ru(cin, c); }
+  // default: fewest (tap, chunk) units, ties -> smaller chunk; zero padding costs MMAs but a
+  // unit's fixed cost is larger (3x3 s2 53->64 at 1080p: 7 chunks of 8 -> 0.275 ms, 2 of 32 -> 0.151)
+  static const int force = getenv("DCVC_TC_KC") ? atoi(getenv("DCVC_TC_KC")) : 1;
+  if (force == 1) {
+    int bu = 1 << 30;
+    for (int c : {8, 16, 32})
+      if (cdiv(cin, c) < bu) { bu = cdiv(cin, c); best = c; best_pad = ru(cin, c); }
+  }
+  int tiles_n, n_tile;
+  n_tiling(cout_w, &tiles_n, &n_tile);
+  if (n_pad) *n_pad = tiles_n * n_tile;
+  if (cin_pad) *cin_pad = best_pad;
+  if (kc) *kc = best;
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_conv_tc_geometry16(int cout_w, int cin, int *n_pad, int *cin_pad, int *kc) {
+  if (cout_w < 1 || cin < 1) return dcvc_fail(DCVC_ERR_ARG, "conv_tc_geometry16: bad arguments");
+  int best = 64, best_pad = ru(cin, 64);
+  for (int c : {32, 16})
+    if (ru(cin, c) < best_pad) { best = c; best_pad = ru(cin, c); }
+  // Fewest (tap, chunk) units wins (ties -> smaller chunk): a unit's fixed cost (two TMA
+  // instructions, descriptor set-up, narrow smem rows) outweighs the MMAs spent on zero padding;
+  // measured 3x3 48->48 at 1080p: chunk 16 -> 0.50 ms, 32 -> 0.37 ms, 64 (zero padded) -> 0.26 ms
+  static const int force = getenv("DCVC_TC_KC16") ? atoi(getenv("DCVC_TC_KC16")) : 1;
+  if (force == 1) {
+    int bu = 1 << 30;
+    for (int c : {16, 32, 64})
+      if (cdiv(cin, c) < bu) { bu = cdiv(cin, c); best = c; best_pad = ru(cin, c); }
+  }
+  if (force == 64 || force == 32 || force == 16) { best = force; best_pad = ru(cin, force); }
   int tiles_n, n_tile;
   n_tiling(cout_w, &tiles_n, &n_tile);
   if (n_pad) *n_pad = tiles_n * n_tile;
@@ -963,7 +1046,12 @@ int tc_fast_mode(const dcvc_conv *d) {
                        (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
   };
   auto unit = [](float s) { return s >= 0.f && s <= 1.f; };
-  const bool ok = d->cout_w % 4 == 0 && al16(d->out) && al16(d->res1) && al16(d->res2) &&
+  auto al16h = [](const dcvc_view &v) {     // binary16 view: 8 elements per 16 bytes
+    return ((((unsigned)v.cstride | (unsigned)v.coff) & 7u) == 0 &&
+            (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
+  };
+  const bool ok = d->cout_w % 4 == 0 && (d->out_f16 ? al16h(d->out) : al16(d->out)) &&
+                  al16(d->res1) && al16(d->res2) &&
                   al16(d->out2) && (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
                   (reinterpret_cast<uintptr_t>(d->scale) & 15u) == 0 && unit(d->out_slope) &&
                   unit(d->gate_slope) && unit(d->out2_slope);
@@ -975,9 +1063,15 @@ int tc_fast_mode(const dcvc_conv *d) {
 bool conv_tc_ok(const dcvc_conv *d) {
   if (d->in_slope != 1.0f) return false;                       // no input prologue on the TMA path
   if (d->stride != 1 && d->stride != 2) return false;
-  if ((d->in.cstride & 3) || (d->in.coff & 3)) return false;   // TMA: 16-byte strides/base
+  const int amask = d->in_f16 ? 7 : 3;
+  if ((d->in.cstride & amask) || (d->in.coff & amask)) return false;   // TMA: 16-byte strides/base
   if (reinterpret_cast<uintptr_t>(d->in.data) & 15) return false;
   if (reinterpret_cast<uintptr_t>(d->weight_tc) & 15) return false;
+  if (d->in_f16 && (!d->weight_tc16 || (reinterpret_cast<uintptr_t>(d->weight_tc16) & 15)))
+    return false;
+  // binary16 output leaves through the TMA-store epilogue only
+  if (d->out_f16 && (tc_fast_mode(d) != 1 || d->res1.data || d->res2.data || d->out2.data))
+    return false;
   if (d->shuffle == 2 && tc_fast_mode(d) != 3) return false;   // planar packing needs the lean path
   const int ho = (d->in.h + 2 * d->pad - d->ksize) / d->stride + 1;
   const int wo = (d->in.w + 2 * d->pad - d->ksize) / d->stride + 1;
@@ -995,7 +1089,11 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.fast = tc_fast_mode(d);
   a.ksize = d->ksize; a.stride = d->stride; a.pad = d->pad;
   int cin_pad, n_pad, tiles_n;
-  dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
+  const bool f16 = d->in_f16 != 0;
+  a.f16_in = f16; a.f16_out = d->out_f16 != 0;
+  if (f16) dcvc_conv_tc_geometry16(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
+  else dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
+  a.kcb = a.kc * (f16 ? 2 : 4);
   n_tiling(d->cout_w, &tiles_n, &a.n_tile);
   a.chunks_per_tap = cin_pad / a.kc;
   a.units = a.ksize * a.ksize * a.chunks_per_tap;
@@ -1012,22 +1110,22 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // DCVC_TC_HALO: 0 off, 1 where it measured faster (3x3 with 64-byte channel chunks or wide N;
   // both modes are MMA-issue-bound for small N, so the gain is the saved L2 traffic only), 2 all
   static const int halo_on = getenv("DCVC_TC_HALO") ? atoi(getenv("DCVC_TC_HALO")) : 1;
-  a.halo = halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 9 && a.kc >= 16 &&
-           d->pad == d->ksize / 2;
+  a.halo = halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 9 &&
+           a.kcb >= (f16 ? 32 : 64) && d->pad == d->ksize / 2;
   if (a.halo && halo_on == 1)
-    a.halo = d->ksize == 3 && !d->shuffle && (a.kc == 16 || a.n_tile >= 96);
+    a.halo = d->ksize == 3 && !d->shuffle && (a.kcb == 64 || a.n_tile >= 96);
   const int halo_ph = TILE_M / 8 + d->ksize - 1;
   static const int halo_pw16 = getenv("DCVC_TC_HALO_PW16") ? atoi(getenv("DCVC_TC_HALO_PW16")) : 0;
   if (a.halo) { a.tw = 8; a.th = TILE_M / 8; a.halo_pw = halo_pw16 ? 16 : 8 + d->ksize - 1; }
   a.tiles_x = cdiv(wout, a.tw);
   const int tiles_y = cdiv(hout, a.th);
-  a.unit_a = (uint32_t)ru(TILE_M * a.kc * 4, 1024);
-  a.unit_b = (uint32_t)ru(a.n_tile * a.kc * 4, 1024);
-  a.unit_tx = (uint32_t)(TILE_M * a.kc * 4 + a.n_tile * a.kc * 4);
+  a.unit_a = (uint32_t)ru(TILE_M * a.kcb, 1024);
+  a.unit_b = (uint32_t)ru(a.n_tile * a.kcb, 1024);
+  a.unit_tx = (uint32_t)(TILE_M * a.kcb + a.n_tile * a.kcb);
   if (a.halo) {
-    a.unit_tx = (uint32_t)(halo_ph * a.halo_pw * a.kc * 4);
+    a.unit_tx = (uint32_t)(halo_ph * a.halo_pw * a.kcb);
     a.unit_a = (uint32_t)ru((int)a.unit_tx, 1024);
-    a.halo_sbo = (uint32_t)(a.halo_pw * a.kc * 4);
+    a.halo_sbo = (uint32_t)(a.halo_pw * a.kcb);
   }
   const uint32_t unit = a.unit_a + a.unit_b;
   static const int dbg = getenv("DCVC_TC_DEBUG") ? atoi(getenv("DCVC_TC_DEBUG")) : 0;
@@ -1070,7 +1168,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
   // TMA-store epilogue: plain convs with at most one residual, views TMA-addressable
-  a.tma_epi = tma_epi_on && a.fast == 1 && !d->res2.data && !d->out2.data;
+  a.tma_epi = (tma_epi_on || a.f16_out) && a.fast == 1 && !d->res2.data && !d->out2.data;
   int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi
             : a.tma_epi ? (ctas == 1 ? 8 : 4) : (ctas == 1 ? 16 : 8);
   while (epi > 4 && epi / 4 > nchunks) epi >>= 1;
@@ -1087,8 +1185,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   if (dbg_stages) stages = dbg_stages;
   if (stages > groups && a.total_tiles <= ctas * num_sms) stages = groups < 2 ? 2 : groups;
   a.stages = stages;
-  a.sbo = 8u * a.kc * 4u;
-  a.layout_type = a.kc == 32 ? 2u : a.kc == 16 ? 4u : 6u;
+  a.sbo = 8u * (uint32_t)a.kcb;
+  a.layout_type = a.kcb == 128 ? 2u : a.kcb == 64 ? 4u : 6u;
   // smem: [stages x stage][barriers (1 KB)][epi_warps epilogue tiles][bias, scale vectors]
   a.stage_off = (uint32_t)stages * stage + 1024u;
   if (a.halo) {
@@ -1116,15 +1214,15 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: smem %zu too large", smem);
 
   CUtensorMap ma, mb, mo, mr;
-  int rc = a.halo ? make_map_a(d->in, a.kc, halo_ph, a.halo_pw, 1, &ma)
-                  : make_map_a(d->in, a.kc, a.th, a.tw, d->stride, &ma);
+  int rc = a.halo ? make_map_a(d->in, a.kc, halo_ph, a.halo_pw, 1, f16, &ma)
+                  : make_map_a(d->in, a.kc, a.th, a.tw, d->stride, f16, &ma);
   if (rc) return rc;
   if (a.tma_epi) {
     const int w_box = a.tw < 32 ? a.tw : 32;
-    rc = make_map_epi(d->out, d->cout_w, w_box, &mo);
+    rc = make_map_epi(d->out, d->cout_w, w_box, a.f16_out != 0, &mo);
     if (rc) return rc;
     if (d->res1.data) {
-      rc = make_map_epi(d->res1, d->cout_w, w_box, &mr);
+      rc = make_map_epi(d->res1, d->cout_w, w_box, false, &mr);
       if (rc) return rc;
     } else {
       mr = mo;
@@ -1132,7 +1230,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   } else {
     mo = ma; mr = ma;   // unused by the kernel
   }
-  rc = make_map_b(d->weight_tc, a.ksize * a.ksize * cin_pad, n_pad, a.n_tile, a.kc, &mb);
+  rc = make_map_b(f16 ? d->weight_tc16 : (const void *)d->weight_tc, a.ksize * a.ksize * cin_pad,
+                  n_pad, a.n_tile, a.kc, f16, &mb);
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {

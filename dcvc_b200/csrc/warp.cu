@@ -66,6 +66,28 @@ __global__ void copy_v4_kernel(dcvc_view src, dcvc_view dst, float mul, float sl
   *reinterpret_cast<float4 *>(dst.data + (size_t)p * dst.cstride + dst.coff + 4 * cq) = v;
 }
 
+// fp32 -> binary16 converting copy: one thread per (pixel, 8 channels): two float4 loads, one
+// 16-byte store of four half2 (round to nearest even)
+__global__ void copy_f16_kernel(dcvc_view src, dcvc_view dst, float mul, float slope, uint32_t c8n,
+                                uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t p = t / c8n, cq = t - p * c8n;
+  const float4 *sp = reinterpret_cast<const float4 *>(src.data + (size_t)p * src.cstride + src.coff + 8 * cq);
+  const float4 u = sp[0], v = sp[1];
+  auto f = [&](float x) { return mul * lrelu(x, slope); };
+  auto pk = [](float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+  };
+  uint4 o;
+  o.x = pk(f(u.x), f(u.y)); o.y = pk(f(u.z), f(u.w));
+  o.z = pk(f(v.x), f(v.y)); o.w = pk(f(v.z), f(v.w));
+  uint16_t *dp = reinterpret_cast<uint16_t *>(dst.data) + (size_t)p * dst.cstride + dst.coff + 8 * cq;
+  *reinterpret_cast<uint4 *>(dp) = o;
+}
+
 __global__ void fill_kernel(dcvc_view dst, float value) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (int64_t)dst.h * dst.w * dst.c) return;
@@ -281,6 +303,19 @@ extern "C" int dcvc_copy(const dcvc_view *src, const dcvc_view *dst, float mul, 
     return DCVC_OK;
   }
   LAUNCH_1D(copy_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *src, *dst, mul, slope);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_copy_f16(const dcvc_view *src, const dcvc_view *dst, float mul, float slope,
+                             void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || src->c != dst->c || src->h != dst->h || src->w != dst->w)
+    return dcvc_fail(DCVC_ERR_ARG, "copy_f16: bad args");
+  const int64_t total8 = (int64_t)dst->h * dst->w * (dst->c / 8);
+  if (!view_al16(src) || ((dst->cstride | dst->coff | dst->c) & 7) ||
+      (reinterpret_cast<uintptr_t>(dst->data) & 15) || total8 >= (1ll << 31))
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "copy_f16: views must hold whole 16-byte channel groups");
+  LAUNCH_1D(copy_f16_kernel, total8, stream, *src, *dst, mul, slope, (uint32_t)(dst->c / 8),
+            (uint32_t)total8);
   return DCVC_OK;
 }
 

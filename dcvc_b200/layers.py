@@ -38,6 +38,20 @@ def _pack_tc(w, planar=False):
     return out.contiguous()
 
 
+def _pack_tc16(w):
+    """binary16 NK packing for convs whose input is a binary16 activation (dcvc_conv.in_f16):
+    [n_pad][kh*kw][cin_pad16], geometry from dcvc_conv_tc_geometry16."""
+    import ctypes
+    from . import _lib
+    cout, cin, kh, kw = w.shape
+    n_pad, cin_pad, kc = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _lib.check(_lib.lib().dcvc_conv_tc_geometry16(cout, cin, ctypes.byref(n_pad),
+                                                  ctypes.byref(cin_pad), ctypes.byref(kc)))
+    out = torch.zeros((n_pad.value, kh * kw, cin_pad.value), dtype=torch.float16, device=w.device)
+    out[:cout, :, :cin] = w.permute(0, 2, 3, 1).reshape(cout, kh * kw, cin).to(torch.float16)
+    return out.contiguous()
+
+
 class Net:
     """Packed weights by reference parameter name (packing happens once per load/.to())."""
 
@@ -77,6 +91,8 @@ class Net:
             r = ConvW(wp, b.contiguous() if b is not None else None, cin, cout, kh, gate,
                       w_tc=_pack_tc(w, planar=shuffle and cout % 16 == 0),
                       tc_planar=shuffle and cout % 16 == 0)
+            if not shuffle:
+                r.pack16 = lambda w=w: _pack_tc16(w)
             self._conv[key] = r
         return r
 
@@ -107,7 +123,7 @@ def subpel(net, p, x, act=1.0, out=None, scale=None, res=None):
 def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, scale=None):
     """ResBlock (video_net.py:58-76): lrelu(x) is conv1's input prologue, the second activation
     conv1's epilogue, `x +` (and an optional outer residual/scale) conv2's epilogue."""
-    t = ops.conv(x, net.cw(p + ".conv1"), in_slope=slope, act=slope)
+    t = ops.conv(x, net.cw(p + ".conv1"), in_slope=slope, act=slope, f16_out=True)
     return ops.conv(t, net.cw(p + ".conv2"), act=slope if end_with_relu else 1.0, res=x,
                     res2=res2, scale=scale, out=out)
 
@@ -127,7 +143,7 @@ def dcb(net, p, x, out=None, scale=None):
     """DepthConvBlock (layers.py:199-209) = DepthConv + ConvFFN (layers.py:166-179); an outer
     `* q` rides on the last epilogue."""
     t = depth_conv(net, p + ".block.0", x)
-    u = ops.conv(t, net.cw(p + ".block.1.conv.0"), act=0.1)
+    u = ops.conv(t, net.cw(p + ".block.1.conv.0"), act=0.1, f16_out=True)
     return ops.conv(u, net.cw(p + ".block.1.conv.2"), act=0.1, res=t, scale=scale, out=out)
 
 
@@ -141,7 +157,7 @@ def dcb2(net, p, x, out=None, scale=None):
 
 def rbws(net, p, x, out=None):
     """ResidualBlockWithStride (layers.py:42-73), stride 2."""
-    t = ops.conv(x, net.cw(p + ".conv1"), stride=2, act=0.01)
+    t = ops.conv(x, net.cw(p + ".conv1"), stride=2, act=0.01, f16_out=True)
     idn = ops.conv(x, net.cw(p + ".downsample"), stride=2, pad=0)
     return ops.conv(t, net.cw(p + ".conv2"), act=0.1, res=idn, out=out)
 

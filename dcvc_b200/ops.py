@@ -39,7 +39,20 @@ class _Prof:
 
 
 def _nb(*acts):
-    return sum(4 * a.h * a.w * a.c for a in acts if a is not None)
+    return sum((2 if a.f16 else 4) * a.h * a.w * a.c for a in acts if a is not None)
+
+
+# binary16 storage of private conv -> conv intermediates on the tensor-core path (DCVC_F16=0
+# keeps every activation fp32).  Same 11-bit significand the TF32 MMA reads from fp32 storage.
+import os as _os
+F16 = _os.environ.get("DCVC_F16", "1") != "0"
+
+
+def f16_ok(h, w, c):
+    """May an h x w x c activation that only convolutions read be stored as binary16?  Both its
+    producer and its consumers must be on the tensor-core path (>= 512 output pixels) and the
+    pixel's channel vector must be whole 16-byte groups."""
+    return F16 and CONV_MODE == 1 and h * w >= 512 and c % 8 == 0
 
 
 def set_conv_mode(mode):
@@ -50,18 +63,21 @@ def set_conv_mode(mode):
 
 class ConvW:
     """Packed device weights of one convolution (built by layers.pack_conv)."""
-    __slots__ = ("w", "w_tc", "b", "cin", "cout_w", "k", "gate", "tc_planar")
+    __slots__ = ("w", "w_tc", "b", "cin", "cout_w", "k", "gate", "tc_planar", "w_tc16", "pack16")
 
     def __init__(self, w, b, cin, cout_w, k, gate=False, w_tc=None, tc_planar=False):
         self.w, self.b, self.cin, self.cout_w, self.k, self.gate, self.w_tc = \
             w, b, cin, cout_w, k, gate, w_tc
         self.tc_planar = tc_planar    # w_tc columns ordered (subpixel, channel): shuffle = 2
+        self.w_tc16 = None            # binary16 NK packing, made on first use by pack16()
+        self.pack16 = None
 
 
 def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, res2=None,
          scale=None, shuffle=False, out2=None, out2_slope=1.0, gate_slope=0.1, clamp01=False,
-         stream=None):
-    """Fused convolution; see dcvc_conv2d in include/dcvc_b200.h for the exact semantics."""
+         stream=None, f16_out=False):
+    """Fused convolution; see dcvc_conv2d in include/dcvc_b200.h for the exact semantics.
+    f16_out=True asks for a binary16 result (granted when f16_ok() holds for it)."""
     assert x.c == cw.cin, (x, cw.cin)
     k = cw.k
     pad = k // 2 if pad is None else pad
@@ -73,10 +89,13 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     if cw.gate:
         ec //= 2
     if out is None:
-        out = Act.new(eh, ew, ec, x.device)
+        f16_out = (f16_out and f16_ok(eh, ew, ec) and cw.w_tc is not None and not shuffle
+                   and not cw.gate and res is None and res2 is None and out2 is None)
+        out = Act.new(eh, ew, ec, x.device, f16=f16_out)
     if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= 512:
         # the TMA-fed tensor-core kernel has no input prologue: materialise lrelu(x) once
-        x = copy(x, slope=in_slope)
+        # (as binary16 when the copy is private to this conv)
+        x = copy(x, slope=in_slope, f16=f16_ok(ho, wo, x.c) and cw.pack16 is not None)
         in_slope = 1.0
     d = _lib.Conv()
     d.inp = x.view()
@@ -86,6 +105,11 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     d.out2 = out2.view() if out2 is not None else NULL_VIEW
     d.weight = cw.w.data_ptr()
     d.weight_tc = cw.w_tc.data_ptr() if cw.w_tc is not None else None
+    d.in_f16, d.out_f16 = int(x.f16), int(out.f16)
+    if x.f16:
+        if cw.w_tc16 is None:
+            cw.w_tc16 = cw.pack16()
+        d.weight_tc16 = cw.w_tc16.data_ptr()
     d.bias = cw.b.data_ptr() if cw.b is not None else None
     d.scale = scale.data_ptr() if scale is not None else None
     d.ksize, d.stride, d.pad, d.cout_w = k, stride, pad, cw.cout_w
@@ -116,13 +140,16 @@ def dwconv3x3(x, w, b, out=None, stream=None):
     return out
 
 
-def copy(src, out=None, h=None, w=None, mul=1.0, slope=1.0, stream=None):
-    """Channel-slice copy; with (h, w) != src size: replicate pad / crop."""
+def copy(src, out=None, h=None, w=None, mul=1.0, slope=1.0, stream=None, f16=False):
+    """Channel-slice copy; with (h, w) != src size: replicate pad / crop.  f16=True: a new
+    binary16 destination (same size only)."""
     if out is None:
-        out = Act.new(src.h if h is None else h, src.w if w is None else w, src.c, src.device)
-    with _Prof(f"copy {out.c}ch @{out.h}x{out.w}" + (" lrelu" if slope != 1.0 else ""), 0,
-               2 * _nb(out)):
-        _lib.check(_lib.lib().dcvc_copy(src.view(), out.view(), mul, slope, _stream(stream)))
+        out = Act.new(src.h if h is None else h, src.w if w is None else w, src.c, src.device,
+                      f16=f16)
+    fn = _lib.lib().dcvc_copy_f16 if out.f16 else _lib.lib().dcvc_copy
+    with _Prof(f"copy {out.c}ch @{out.h}x{out.w}" + (" lrelu" if slope != 1.0 else "") +
+               (" f16" if out.f16 else ""), 0, _nb(src, out)):
+        _lib.check(fn(src.view(), out.view(), mul, slope, _stream(stream)))
     return out
 
 

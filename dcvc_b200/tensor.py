@@ -1,4 +1,6 @@
-"""Device activations as fp32 NHWC channel-slice views (`Act`), the unit every kernel works on.
+"""Device activations as NHWC channel-slice views (`Act`), the unit every kernel works on.
+fp32 everywhere a kernel other than the tensor-core convolution reads them; private conv -> conv
+intermediates may be binary16 (`Act.new(..., f16=True)`, see dcvc_conv.in_f16 / out_f16).
 
 An `Act` is (buffer [h, w, cstride] fp32 on the GPU, first channel, channel count).  Several Acts
 may alias disjoint channel ranges of one buffer, which is how torch.cat on the reference's hot
@@ -19,7 +21,7 @@ class Act:
     __slots__ = ("buf", "c0", "c")
 
     def __init__(self, buf, c0=0, c=None):
-        assert buf.dim() == 3 and buf.dtype == torch.float32 and buf.is_contiguous()
+        assert buf.dim() == 3 and buf.dtype in (torch.float32, torch.float16) and buf.is_contiguous()
         self.buf = buf
         self.c0 = c0
         self.c = buf.shape[2] - c0 if c is None else c
@@ -27,9 +29,10 @@ class Act:
 
     # ------------------------------------------------------------------ constructors
     @staticmethod
-    def new(h, w, c, device, cstride=None, zero=False):
-        cs = _ru4(c) if cstride is None else cstride
-        buf = (torch.zeros if zero else torch.empty)((h, w, cs), dtype=torch.float32, device=device)
+    def new(h, w, c, device, cstride=None, zero=False, f16=False):
+        cs = ((c + 7) // 8 * 8 if f16 else _ru4(c)) if cstride is None else cstride
+        buf = (torch.zeros if zero else torch.empty)(
+            (h, w, cs), dtype=torch.float16 if f16 else torch.float32, device=device)
         return Act(buf, 0, c)
 
     @staticmethod
@@ -62,6 +65,10 @@ class Act:
     @property
     def cs(self):
         return self.buf.shape[2]
+
+    @property
+    def f16(self):
+        return self.buf.dtype == torch.float16
 
     @property
     def device(self):

@@ -65,10 +65,10 @@ class DMC(CompressionModel):
             up = ops.resize_bilinear(flow, h, w, mul=2.0, out=inp.slice(6, 2))
             ops.flow_warp(p2[k], up, out=inp.slice(3, 3))
             p = f"optic_flow.moduleBasic.{lv}"
-            t = ops.conv(inp, net.cw(p + ".conv1"), act=0.0)
-            t = ops.conv(t, net.cw(p + ".conv2"), act=0.0)
-            t = ops.conv(t, net.cw(p + ".conv3"), act=0.0)
-            t = ops.conv(t, net.cw(p + ".conv4"), act=0.0)
+            t = ops.conv(inp, net.cw(p + ".conv1"), act=0.0, f16_out=True)
+            t = ops.conv(t, net.cw(p + ".conv2"), act=0.0, f16_out=True)
+            t = ops.conv(t, net.cw(p + ".conv3"), act=0.0, f16_out=True)
+            t = ops.conv(t, net.cw(p + ".conv4"), act=0.0, f16_out=True)
             flow = ops.conv(t, net.cw(p + ".conv5"), res=up)
         return flow
 
@@ -173,8 +173,8 @@ class DMC(CompressionModel):
                               ops.conv(l2, net.cw(fe + ".conv3"), stride=2))
         ops.flow_warp(l1, mv, out=aux.slice(0, 48))
         # OffsetDiversity (align)
-        t = ops.conv(aux, net.cw("align.conv_offset.0"), stride=2, act=0.1)
-        t = ops.conv(t, net.cw("align.conv_offset.2"), act=0.1)
+        t = ops.conv(aux, net.cw("align.conv_offset.0"), stride=2, act=0.1, f16_out=True)
+        t = ops.conv(t, net.cw("align.conv_offset.2"), act=0.1, f16_out=True)
         offs = ops.conv(t, net.cw("align.conv_offset.4"))
         cat1 = Act.new(H, W, 96, dev)                      # [context2_up 48 | context1 48]
         cat2 = Act.new(H // 2, W // 2, 128, dev)           # [context3_up 64 | context2 64]

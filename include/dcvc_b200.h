@@ -83,6 +83,16 @@ typedef struct dcvc_conv {
   float in_slope, out_slope, gate_slope, out2_slope;
   int32_t mode;
   int32_t clamp01;
+  /* half-precision storage of private conv -> conv intermediates (tensor-core path only; the
+   * call fails with DCVC_ERR_UNSUPPORTED where that path is not eligible, it never falls back):
+   * in_f16:  in.data points at IEEE binary16 elements (cstride/coff count elements) and the MMA
+   *          runs kind::f16 on weight_tc16; both operands then carry the 11-bit significand
+   *          kind::tf32 would have read from fp32 storage, accumulation stays fp32 in TMEM.
+   * out_f16: out.data points at binary16 elements, written round-to-nearest-even after the
+   *          fused epilogue; plain epilogues only (no gate, shuffle, residual or out2). */
+  const void *weight_tc16; /* [cout_pad][ksize*ksize][cin_pad16] binary16, dcvc_conv_tc_geometry16 */
+  int32_t in_f16;
+  int32_t out_f16;
 } dcvc_conv;
 
 int dcvc_conv2d(const dcvc_conv *d, void *stream);
@@ -92,6 +102,8 @@ int dcvc_conv_tc_eligible(const dcvc_conv *d);
  * 16, each row [ksize*ksize][cin_pad] with cin_pad = cin rounded up to the K chunk kc (32, 16 or
  * 8 floats = one 128/64/32-byte swizzle row).  Padding entries must be zero. */
 int dcvc_conv_tc_geometry(int cout_w, int cin, int *n_pad, int *cin_pad, int *kc);
+/* the same for weight_tc16: kc in {64, 32, 16} binary16 elements */
+int dcvc_conv_tc_geometry16(int cout_w, int cin, int *n_pad, int *cin_pad, int *kc);
 
 /* depthwise 3x3, pad 1, stride 1 (DepthConv.depth_conv, layers.py:148); weight [9][c], bias [c] */
 int dcvc_dwconv3x3(const dcvc_view *in, const dcvc_view *out, const float *weight,
@@ -107,6 +119,9 @@ int dcvc_nhwc_to_nchw(const dcvc_view *src, float *dst, int clamp01, void *strea
 /* dst(y,x,:) = mul * lrelu(src(min(y,h-1), min(x,w-1), :), slope): channel-slice copy,
  * replicate pad (pad_for_y, common_model.py:70-78) and crop (slice_to_y, :85-86) */
 int dcvc_copy(const dcvc_view *src, const dcvc_view *dst, float mul, float slope, void *stream);
+/* dcvc_copy (equal sizes only) with a binary16 destination: dst->data points at binary16
+ * elements, dst->cstride/coff count elements; feeds dcvc_conv.in_f16 */
+int dcvc_copy_f16(const dcvc_view *src, const dcvc_view *dst, float mul, float slope, void *stream);
 int dcvc_fill(const dcvc_view *dst, float value, void *stream);
 /* 2x2/2 pooling; mode 0 = average (F.avg_pool2d), 1 = max (nn.MaxPool2d) */
 int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream);

@@ -32,6 +32,11 @@ for cin, cout, k, s, h, w, kw in SHAPES:
     sd = {"c.weight": torch.randn(cout, cin, k, k, generator=g) * 0.05, "c.bias": torch.randn(cout, generator=g)}
     net = layers.Net(sd, dev)
     x = Act(torch.randn(h, w, (cin + 3) // 4 * 4, device=dev), 0, cin)
+    f16 = os.environ.get("BENCH_F16", "")          # "in", "out" or "io"
+    if "i" in f16 and cin % 8 == 0 and not kw.get("shuffle"):
+        x = ops.copy(x, f16=True)
+    if "o" in f16 and cout % 8 == 0 and not kw.get("shuffle"):
+        kw = dict(kw, f16_out=True)
     cw = net.cw("c", shuffle=bool(kw.get("shuffle")))
     out = ops.conv(x, cw, stride=s, **kw)
     torch.cuda.synchronize()
@@ -47,5 +52,6 @@ for cin, cout, k, s, h, w, kw in SHAPES:
     ms /= iters
     ho, wo = (h + 2 * (k // 2) - k) // s + 1, (w + 2 * (k // 2) - k) // s + 1
     fl = 2.0 * ho * wo * cout * cin * k * k
-    by = 4.0 * (h * w * cin + ho * wo * cout + cout * cin * k * k)
-    print(f"{name:60s} {ms:8.3f} ms {fl / ms / 1e9:8.1f} TFLOP/s {by / ms / 1e6:8.0f} GB/s", flush=True)
+    by = (2.0 if x.f16 else 4.0) * h * w * cin + (2.0 if out.f16 else 4.0) * ho * wo * cout + 4.0 * cout * cin * k * k
+    name += (" f16in" if x.f16 else "") + (" f16out" if out.f16 else "")
+    print(f"{name:72s} {ms:8.3f} ms {fl / ms / 1e9:8.1f} TFLOP/s {by / ms / 1e6:8.0f} GB/s", flush=True)

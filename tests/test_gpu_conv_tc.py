@@ -190,3 +190,82 @@ def test_tc_conv_tma_store_epilogue(cin, cout, k, h, w):
     # no residual, clamp
     out = ops.conv(xa, net.cw("c"), clamp01=True)
     _check(from_act(out), conv.clamp(0, 1), cin, k)
+
+
+F16_SHAPES = [
+    # cin, cout, k, stride, h, w     (binary16 K chunks: 64 -> 128 B rows, 32 -> 64 B, 16 -> 32 B)
+    (64, 64, 3, 1, 32, 48), (32, 128, 3, 1, 40, 40), (48, 48, 3, 1, 48, 64), (8, 32, 7, 1, 40, 56),
+    (128, 192, 3, 1, 24, 40), (192, 48, 1, 1, 37, 53), (512, 128, 1, 1, 24, 24),
+    (32, 64, 7, 1, 40, 40), (16, 2, 7, 1, 32, 32), (64, 64, 3, 2, 64, 96), (256, 64, 1, 1, 33, 70),
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,h,w", F16_SHAPES)
+def test_tc_conv_f16_input(cin, cout, k, stride, h, w):
+    """binary16 activations + binary16 weights (kind::f16, fp32 accumulate) against the fp32
+    convolution of the same rounded operands: only the summation order differs, so the bound is
+    fp32 accumulation noise, not an operand-precision bound.  Residual / scale epilogue rides
+    along (fp32 views)."""
+    sd = _sd(cin, cout, k, seed=cin * 3 + cout)
+    x, r1 = _rand(1, cin, h, w, seed=11), None
+    pad = k // 2
+    xa = ops.copy(to_act(x, cstride=(cin + 7) // 8 * 8), f16=True)
+    assert xa.f16
+    w16 = sd["c.weight"].half().float()
+    ref = F.conv2d(x.half().float(), w16, sd["c.bias"], stride, pad)
+    ho, wo = ref.shape[2], ref.shape[3]
+    r1 = _rand(1, cout, ho, wo, seed=12)
+    q = torch.rand(cout) + 0.5
+    net = layers.Net(sd, dev())
+    out = ops.conv(xa, net.cw("c"), stride=stride, pad=pad, act=0.1,
+                   res=to_act(r1) if cout % 4 == 0 else None,
+                   scale=q.to(dev()) if cout % 4 == 0 else None)
+    assert not out.f16
+    want = F.leaky_relu(ref, 0.1)
+    if cout % 4 == 0:
+        want = (want + r1) * q.view(1, -1, 1, 1)
+    d = from_act(out) - want
+    assert float(d.abs().max()) < 2e-5 * max(1.0, (cin * k * k) ** 0.5 / 8), float(d.abs().max())
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,h,w", [(48, 192, 1, 1, 37, 53), (32, 64, 3, 1, 33, 70),
+                                                  (64, 48, 3, 2, 64, 96), (8, 32, 7, 1, 40, 56),
+                                                  (64, 768, 1, 1, 24, 32), (48, 40, 3, 1, 24, 200)])
+def test_tc_conv_f16_output_and_chain(cin, cout, k, stride, h, w):
+    """binary16 output through the tensor-map store (64-byte swizzled rows): equals the fp32
+    result rounded to binary16 up to the TF32 bound, leaves neighbouring channels of a wider
+    buffer untouched, and feeds a second convolution as a binary16 input."""
+    sd = _sd(cin, cout, k, seed=41)
+    x = _rand(1, cin, h, w, seed=13)
+    pad = k // 2
+    conv = F.leaky_relu(F.conv2d(x, sd["c.weight"], sd["c.bias"], stride, pad), 0.1)
+    ho, wo = conv.shape[2], conv.shape[3]
+    net = layers.Net(sd, dev())
+    wide = torch.full((ho, wo, cout + 16), 7.0, device=dev(), dtype=torch.float16)
+    out = Act(wide, 8, cout)
+    ops.conv(to_act(x), net.cw("c"), stride=stride, pad=pad, act=0.1, out=out)
+    got = from_act(Act(wide.float(), 8, cout))
+    _check(got, conv, cin, k)
+    assert float((got - conv).abs().max()) < 4 * (4e-3 * 0.58 * 0.58 + 1e-5) + float(conv.abs().max()) * 2 ** -11
+    assert bool((wide[:, :, :8] == 7.0).all()) and bool((wide[:, :, 8 + cout:] == 7.0).all())
+    # requested through the layer-level switch: granted only when f16_ok() holds
+    t = ops.conv(to_act(x), net.cw("c"), stride=stride, pad=pad, act=0.1, f16_out=True)
+    assert t.f16 == (ops.F16 and ho * wo >= 512 and cout % 8 == 0)
+    if not t.f16:
+        return
+    sd2 = {"c.weight": _sd(cout, 32, 3, seed=43)["c.weight"], "c.bias": _sd(cout, 32, 3, seed=43)["c.bias"]}
+    net2 = layers.Net(sd2, dev())
+    y = ops.conv(t, net2.cw("c"))
+    t32 = t.buf[:, :, :cout].float().permute(2, 0, 1).unsqueeze(0).cpu()
+    ref2 = F.conv2d(t32, sd2["c.weight"].half().float(), sd2["c.bias"], 1, 1)
+    assert float((from_act(y) - ref2).abs().max()) < 2e-5 * max(1.0, (cout * 9) ** 0.5 / 8)
+
+
+def test_f16_views_never_fall_back():
+    """A binary16 view on a descriptor the tensor-core path cannot take is an error, not a
+    silent fp32 reinterpretation."""
+    sd = _sd(16, 16, 3, seed=2)
+    net = layers.Net(sd, dev())
+    small = Act.new(8, 8, 16, dev(), f16=True)            # 64 pixels: below the tensor-core floor
+    with pytest.raises(_lib.DcvcError):
+        ops.conv(small, net.cw("c"))
