@@ -54,6 +54,7 @@ SIGNATURES = {
     "dcvc_conv_tc_geometry16": (c_int, [c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                         ctypes.POINTER(c_int)]),
     "dcvc_dwconv3x3": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p]),
+    "dcvc_dwconv3x3_f16": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p]),
     "dcvc_nchw_to_nhwc": (c_int, [c_void_p, VP, c_void_p]),
     "dcvc_nhwc_to_nchw": (c_int, [VP, c_void_p, c_int, c_void_p]),
     "dcvc_copy": (c_int, [VP, VP, c_float, c_float, c_void_p]),

@@ -217,6 +217,29 @@ __global__ void dwconv3x3_kernel(dcvc_view in, dcvc_view out, const float *__res
 // than L1-bound.  Taps are accumulated in the same (dy, dx) order as the scalar kernel.
 constexpr int DW_TX = 4, DW_TY = 2;
 
+// four consecutive channels of an fp32 (16 bytes) or binary16 (8 bytes) view; `off` in elements
+template <bool H>
+__device__ __forceinline__ float4 ld4(const float *data, size_t off) {
+  if (!H) return *reinterpret_cast<const float4 *>(data + off);
+  const uint2 u = *reinterpret_cast<const uint2 *>(reinterpret_cast<const uint16_t *>(data) + off);
+  float4 r;
+  asm("{\n\t.reg .f16 lo, hi;\n\tmov.b32 {lo, hi}, %2;\n\tcvt.f32.f16 %0, lo;\n\tcvt.f32.f16 %1, hi;\n\t}"
+      : "=f"(r.x), "=f"(r.y) : "r"(u.x));
+  asm("{\n\t.reg .f16 lo, hi;\n\tmov.b32 {lo, hi}, %2;\n\tcvt.f32.f16 %0, lo;\n\tcvt.f32.f16 %1, hi;\n\t}"
+      : "=f"(r.z), "=f"(r.w) : "r"(u.y));
+  return r;
+}
+template <bool H>
+__device__ __forceinline__ void st4(float *data, size_t off, float4 v) {
+  if (!H) { *reinterpret_cast<float4 *>(data + off) = v; return; }
+  uint2 u;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(u.x) : "f"(v.y), "f"(v.x));
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(u.y) : "f"(v.w), "f"(v.z));
+  *reinterpret_cast<uint2 *>(reinterpret_cast<uint16_t *>(data) + off) = u;
+}
+
+// H: both views hold binary16 elements (dcvc_dwconv3x3_f16); arithmetic is fp32 either way
+template <bool H>
 __global__ void __launch_bounds__(128)
 dwconv3x3_v4_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
                     const float *__restrict__ b, uint32_t c4n, uint32_t bx_n, uint32_t total) {
@@ -234,7 +257,7 @@ dwconv3x3_v4_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
   for (int i = 0; i < DW_TY; ++i)
 #pragma unroll
     for (int j = 0; j < DW_TX; ++j) acc[i][j] = bv;
-  const float *ibase = in.data + in.coff + c;
+  const size_t ibase = (size_t)in.coff + c;
 #pragma unroll
   for (int r = 0; r < DW_TY + 2; ++r) {
     const int iy = y0 + r - 1;
@@ -244,7 +267,7 @@ dwconv3x3_v4_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
     for (int q = 0; q < DW_TX + 2; ++q) {
       const int ix = x0 + q - 1;
       row[q] = (ix >= 0 && ix < in.w)
-                   ? *reinterpret_cast<const float4 *>(ibase + ((size_t)iy * in.w + ix) * in.cstride)
+                   ? ld4<H>(in.data, ibase + ((size_t)iy * in.w + ix) * in.cstride)
                    : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
@@ -269,8 +292,7 @@ dwconv3x3_v4_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
     for (int j = 0; j < DW_TX; ++j) {
       const int ox = x0 + j;
       if (ox < out.w)
-        *reinterpret_cast<float4 *>(out.data + ((size_t)oy * out.w + ox) * out.cstride + out.coff + c) =
-            acc[i][j];
+        st4<H>(out.data, ((size_t)oy * out.w + ox) * out.cstride + out.coff + c, acc[i][j]);
     }
   }
 }
@@ -371,10 +393,30 @@ extern "C" int dcvc_dwconv3x3(const dcvc_view *in, const dcvc_view *out, const f
   const int64_t bx_n = cdiv(in->w, DW_TX), by_n = cdiv(in->h, DW_TY);
   const int64_t total_v = bx_n * by_n * c4n;
   if (vec && total_v < (1ll << 31))
-    dwconv3x3_v4_kernel<<<(unsigned)cdiv(total_v, 128), 128, 0, (cudaStream_t)stream>>>(
+    dwconv3x3_v4_kernel<false><<<(unsigned)cdiv(total_v, 128), 128, 0, (cudaStream_t)stream>>>(
         *in, *out, weight, bias, (uint32_t)c4n, (uint32_t)bx_n, (uint32_t)total_v);
   else
     dwconv3x3_kernel<<<cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(*in, *out, weight, bias, c4n);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_dwconv3x3_f16(const dcvc_view *in, const dcvc_view *out, const float *weight,
+                                  const float *bias, void *stream) {
+  if (!view_ok(in) || !view_ok(out) || !weight) return dcvc_fail(DCVC_ERR_ARG, "dwconv_f16: bad args");
+  if (in->h != out->h || in->w != out->w || in->c != out->c)
+    return dcvc_fail(DCVC_ERR_ARG, "dwconv_f16: extent mismatch");
+  const int c4n = in->c / 4;
+  const int64_t bx_n = cdiv(in->w, DW_TX), by_n = cdiv(in->h, DW_TY);
+  const int64_t total_v = bx_n * by_n * c4n;
+  // 8-byte channel groups of binary16; weights/bias are fp32 float4 groups
+  const bool vec = (in->c & 3) == 0 && ((in->cstride | in->coff | out->cstride | out->coff) & 3) == 0 &&
+                   ((reinterpret_cast<uintptr_t>(in->data) | reinterpret_cast<uintptr_t>(out->data)) & 7) == 0 &&
+                   ((reinterpret_cast<uintptr_t>(weight) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0;
+  if (!vec || total_v >= (1ll << 31))
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "dwconv_f16: views must hold whole 4-channel groups");
+  dwconv3x3_v4_kernel<true><<<(unsigned)cdiv(total_v, 128), 128, 0, (cudaStream_t)stream>>>(
+      *in, *out, weight, bias, (uint32_t)c4n, (uint32_t)bx_n, (uint32_t)total_v);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }

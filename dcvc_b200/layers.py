@@ -133,7 +133,7 @@ def depth_conv(net, p, x, out=None):
     identity = x
     if net.has(p + ".adaptor"):
         identity = ops.conv(x, net.cw(p + ".adaptor"))
-    t = ops.conv(x, net.cw(p + ".conv1.0"), act=0.01)
+    t = ops.conv(x, net.cw(p + ".conv1.0"), act=0.01, f16_out=True)
     w, b = net.dw(p + ".depth_conv")
     t = ops.dwconv3x3(t, w, b)
     return ops.conv(t, net.cw(p + ".conv2"), res=identity, out=out)

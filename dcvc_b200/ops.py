@@ -132,11 +132,12 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
 
 def dwconv3x3(x, w, b, out=None, stream=None):
     if out is None:
-        out = Act.new(x.h, x.w, x.c, x.device)
-    with _Prof("dwconv3x3", 18 * x.h * x.w * x.c, _nb(x, out)):
-        _lib.check(_lib.lib().dcvc_dwconv3x3(x.view(), out.view(), w.data_ptr(),
-                                             b.data_ptr() if b is not None else None,
-                                             _stream(stream)))
+        out = Act.new(x.h, x.w, x.c, x.device, f16=x.f16)
+    assert out.f16 == x.f16
+    fn = _lib.lib().dcvc_dwconv3x3_f16 if x.f16 else _lib.lib().dcvc_dwconv3x3
+    with _Prof("dwconv3x3" + (" f16" if x.f16 else ""), 18 * x.h * x.w * x.c, _nb(x, out)):
+        _lib.check(fn(x.view(), out.view(), w.data_ptr(), b.data_ptr() if b is not None else None,
+                      _stream(stream)))
     return out
 
 

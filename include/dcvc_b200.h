@@ -108,6 +108,10 @@ int dcvc_conv_tc_geometry16(int cout_w, int cin, int *n_pad, int *cin_pad, int *
 /* depthwise 3x3, pad 1, stride 1 (DepthConv.depth_conv, layers.py:148); weight [9][c], bias [c] */
 int dcvc_dwconv3x3(const dcvc_view *in, const dcvc_view *out, const float *weight,
                    const float *bias, void *stream);
+/* the same with both views holding binary16 elements (fp32 weights, fp32 arithmetic, result
+ * rounded to nearest even): the private conv1 -> depth_conv -> conv2 intermediates of DepthConv */
+int dcvc_dwconv3x3_f16(const dcvc_view *in, const dcvc_view *out, const float *weight,
+                       const float *bias, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * Motion / resampling group (reference DCVC-DC/src/models/video_net.py:8-55,104-126,

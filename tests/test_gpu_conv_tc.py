@@ -269,3 +269,48 @@ def test_f16_views_never_fall_back():
     small = Act.new(8, 8, 16, dev(), f16=True)            # 64 pixels: below the tensor-core floor
     with pytest.raises(_lib.DcvcError):
         ops.conv(small, net.cw("c"))
+
+
+def test_dwconv_f16():
+    c, h, w = 72, 21, 35
+    g = torch.Generator().manual_seed(3)
+    sd = {"d.weight": torch.rand(c, 1, 3, 3, generator=g) - 0.5, "d.bias": torch.rand(c, generator=g) - 0.5}
+    x = _rand(1, c, h, w, seed=8)
+    net = layers.Net(sd, dev())
+    wt, b = net.dw("d")
+    x16 = ops.copy(to_act(x), f16=True)
+    out = ops.dwconv3x3(x16, wt, b)
+    assert out.f16
+    ref = F.conv2d(x.half().float(), sd["d.weight"], sd["d.bias"], 1, 1, 1, c)
+    got = out.buf[:, :, :c].float().permute(2, 0, 1).unsqueeze(0).cpu()
+    assert float((got - ref.half().float()).abs().max()) <= float(ref.abs().max()) * 2 ** -10
+
+
+@pytest.mark.parametrize("block", ["dcb", "res_block", "rbws"])
+def test_blocks_with_f16_intermediates(block, monkeypatch):
+    """The reference's blocks with their private intermediates stored as binary16 (the default in
+    tensor-core mode) against the fp32 oracle and against the all-fp32-storage run: storage
+    rounding of an intermediate is the same 11-bit significand the TF32 MMA reads, so both
+    comparisons share one bound."""
+    from dcvc_b200 import arch
+    from oracle import nets_oracle as no
+    spec = arch.Spec()
+    if block == "dcb":
+        spec.dcb("b", 48, 48)
+    elif block == "res_block":
+        spec.res_block("b", 48)
+    else:
+        spec.rbws("b", 48, 64)
+    sd = arch.synth_state_dict(spec, 7)
+    x = _rand(1, 48, 40, 56, seed=5)
+    ref = getattr(no, block)(sd, "b", x)
+    fn = getattr(layers, block)
+    monkeypatch.setattr(ops, "F16", True)
+    out16 = from_act(fn(layers.Net(sd, dev()), "b", to_act(x)))
+    monkeypatch.setattr(ops, "F16", False)
+    out32 = from_act(fn(layers.Net(sd, dev()), "b", to_act(x)))
+    scale = float(ref.abs().max())
+    assert float((out16 - ref).abs().max()) < 6e-3 * scale
+    assert float((out32 - ref).abs().max()) < 6e-3 * scale
+    assert float((out16 - out32).abs().max()) < 6e-3 * scale
+    assert not torch.equal(out16, out32)          # the binary16 path really ran
