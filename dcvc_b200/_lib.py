@@ -27,7 +27,8 @@ class Conv(ctypes.Structure):
                 ("gate", c_int32), ("shuffle", c_int32),
                 ("in_slope", c_float), ("out_slope", c_float), ("gate_slope", c_float),
                 ("out2_slope", c_float), ("mode", c_int32), ("clamp01", c_int32),
-                ("weight_tc16", c_void_p), ("in_f16", c_int32), ("out_f16", c_int32)]
+                ("weight_tc16", c_void_p), ("in_f16", c_int32), ("out_f16", c_int32),
+                ("res1_f16", c_int32)]
 
 
 class Quad(ctypes.Structure):

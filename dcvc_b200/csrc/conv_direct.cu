@@ -238,37 +238,38 @@ __device__ __forceinline__ void st4(float *data, size_t off, float4 v) {
   *reinterpret_cast<uint2 *>(reinterpret_cast<uint16_t *>(data) + off) = u;
 }
 
-// H: both views hold binary16 elements (dcvc_dwconv3x3_f16); arithmetic is fp32 either way
-template <bool H>
-__global__ void __launch_bounds__(128)
-dwconv3x3_v4_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
-                    const float *__restrict__ b, uint32_t c4n, uint32_t bx_n, uint32_t total) {
-  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= total) return;
-  const uint32_t blk = t / c4n, cq = t - blk * c4n;
-  const uint32_t by = blk / bx_n, bx = blk - by * bx_n;
-  const int x0 = (int)bx * DW_TX, y0 = (int)by * DW_TY, c = (int)cq * 4;
-  float4 wv[9];
-#pragma unroll
-  for (int k = 0; k < 9; ++k) wv[k] = __ldg(reinterpret_cast<const float4 *>(w + k * in.c + c));
-  const float4 bv = b ? __ldg(reinterpret_cast<const float4 *>(b + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+// H: both views hold binary16 elements (dcvc_dwconv3x3_f16); arithmetic is fp32 either way.
+// EDGE = false is the interior instantiation: the whole (TY+2) x (TX+2) window and all outputs
+// are inside the image, so the body is straight-line loads / FMAs / stores with 32-bit offsets
+// (the bounds-checked form spends ~8 instructions per FMA on predicates and is issue-bound).
+template <bool H, bool EDGE>
+__device__ __forceinline__ void dwconv_tile(const dcvc_view &in, const dcvc_view &out,
+                                            const float4 (&wv)[9], const float4 bv, int x0, int y0,
+                                            int c) {
   float4 acc[DW_TY][DW_TX];
 #pragma unroll
   for (int i = 0; i < DW_TY; ++i)
 #pragma unroll
     for (int j = 0; j < DW_TX; ++j) acc[i][j] = bv;
   const size_t ibase = (size_t)in.coff + c;
+  // interior: element offset of window pixel (0, 0), then constant strides
+  const size_t iorg = EDGE ? 0 : ibase + ((size_t)(y0 - 1) * in.w + (x0 - 1)) * in.cstride;
+  const uint32_t irow = (uint32_t)in.w * (uint32_t)in.cstride, ipix = (uint32_t)in.cstride;
 #pragma unroll
   for (int r = 0; r < DW_TY + 2; ++r) {
     const int iy = y0 + r - 1;
-    if (iy < 0 || iy >= in.h) continue;               // zero padding: the row contributes nothing
+    if (EDGE && (iy < 0 || iy >= in.h)) continue;     // zero padding: the row contributes nothing
     float4 row[DW_TX + 2];
 #pragma unroll
     for (int q = 0; q < DW_TX + 2; ++q) {
-      const int ix = x0 + q - 1;
-      row[q] = (ix >= 0 && ix < in.w)
-                   ? ld4<H>(in.data, ibase + ((size_t)iy * in.w + ix) * in.cstride)
-                   : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (EDGE) {
+        const int ix = x0 + q - 1;
+        row[q] = (ix >= 0 && ix < in.w)
+                     ? ld4<H>(in.data, ibase + ((size_t)iy * in.w + ix) * in.cstride)
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        row[q] = ld4<H>(in.data, iorg + (uint32_t)r * irow + (uint32_t)q * ipix);
+      }
     }
 #pragma unroll
     for (int i = 0; i < DW_TY; ++i) {
@@ -284,17 +285,34 @@ dwconv3x3_v4_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
         }
     }
   }
+  const size_t oorg = (size_t)out.coff + c + ((size_t)y0 * out.w + x0) * out.cstride;
+  const uint32_t orow = (uint32_t)out.w * (uint32_t)out.cstride, opix = (uint32_t)out.cstride;
 #pragma unroll
   for (int i = 0; i < DW_TY; ++i) {
-    const int oy = y0 + i;
-    if (oy >= out.h) continue;
+    if (EDGE && y0 + i >= out.h) continue;
 #pragma unroll
-    for (int j = 0; j < DW_TX; ++j) {
-      const int ox = x0 + j;
-      if (ox < out.w)
-        st4<H>(out.data, ((size_t)oy * out.w + ox) * out.cstride + out.coff + c, acc[i][j]);
-    }
+    for (int j = 0; j < DW_TX; ++j)
+      if (!EDGE || x0 + j < out.w)
+        st4<H>(out.data, oorg + (uint32_t)i * orow + (uint32_t)j * opix, acc[i][j]);
   }
+}
+
+template <bool H>
+__global__ void __launch_bounds__(128)
+dwconv3x3_v4_kernel(dcvc_view in, dcvc_view out, const float *__restrict__ w,
+                    const float *__restrict__ b, uint32_t c4n, uint32_t bx_n, uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t blk = t / c4n, cq = t - blk * c4n;
+  const uint32_t by = blk / bx_n, bx = blk - by * bx_n;
+  const int x0 = (int)bx * DW_TX, y0 = (int)by * DW_TY, c = (int)cq * 4;
+  float4 wv[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) wv[k] = __ldg(reinterpret_cast<const float4 *>(w + k * in.c + c));
+  const float4 bv = b ? __ldg(reinterpret_cast<const float4 *>(b + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const bool interior = x0 >= 1 && y0 >= 1 && x0 + DW_TX + 1 <= in.w && y0 + DW_TY + 1 <= in.h;
+  if (interior) dwconv_tile<H, false>(in, out, wv, bv, x0, y0, c);
+  else dwconv_tile<H, true>(in, out, wv, bv, x0, y0, c);
 }
 
 }  // namespace
@@ -373,7 +391,7 @@ extern "C" int dcvc_conv2d(const dcvc_conv *d, void *stream) {
   if (rc != DCVC_OK) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   if (d->mode == 1 && d->weight_tc && conv_tc_ok(d)) return conv_tc_launch(d, ho, wo, s);
-  if (d->in_f16 || d->out_f16)
+  if (d->in_f16 || d->out_f16 || (d->res1_f16 && d->res1.data))
     return dcvc_fail(DCVC_ERR_UNSUPPORTED,
                      "conv: binary16 views need the tensor-core path, which this descriptor "
                      "does not qualify for (mode, shape, alignment or epilogue)");

@@ -45,8 +45,10 @@ struct TcArgs {
   uint32_t vec_off;
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
   int kcb;        // bytes of one K chunk row (128/64/32) = kc * element size
+  int kk_last;    // MMAs of a tap's last chunk: its zero-padded tail is not multiplied at all
   int f16_in;     // A/B operands are binary16: kind::f16, K = 16 per instruction
   int f16_out;    // TMA-store epilogue writes binary16 (64-byte rows, 64B swizzle)
+  int f16_res;    // res1 holds binary16 (fetched as 64-byte rows, 64B swizzle)
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
 
@@ -214,6 +216,12 @@ __device__ __forceinline__ void bulk_wait_all() {
 __device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {   // two floats -> half2 bits (RN)
   uint32_t r;
   asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float2 unpack_h2(uint32_t h2) {
+  float2 r;
+  asm("{\n\t.reg .f16 lo, hi;\n\tmov.b32 {lo, hi}, %2;\n\tcvt.f32.f16 %0, lo;\n\tcvt.f32.f16 %1, hi;\n\t}"
+      : "=f"(r.x), "=f"(r.y) : "r"(h2));
   return r;
 }
 __device__ __forceinline__ void fence_async_smem() {  // generic-proxy smem writes -> async proxy
@@ -575,6 +583,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                            ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24)));
     // one MMA consumes 32 bytes of K per row: 8 TF32 or 16 binary16 values
     const int kk_n = keep((int)((a.debug & 2) ? 0 : a.kcb / 32));
+    const int kk_last = keep((int)((a.debug & 2) ? 0 : a.kk_last));
     // descriptor = constant high word | (smem address >> 4) in the low 14 bits
     const uint64_t desc_hi = keep((uint64_t)(make_smem_desc(0, a.sbo, a.layout_type)));
     const uint32_t acc_stride = keep((uint32_t)(a.acc_stride)), unit_a = keep((uint32_t)(a.unit_a)), unit_b = keep((uint32_t)(a.unit_b));
@@ -601,6 +610,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           mbar_wait(full_bar(sa), pha);
           tc_fence_after();
           const uint32_t a_addr = base + sa * unit_a;
+          const int kn = ch == chunks - 1 ? kk_last : kk_n;
           int dx = 0, dy = 0;
           for (int t0 = 0; t0 < taps; t0 += bg) {          // one B stage = `bg` consecutive taps
             const int sbar = sa_n + sb, cnt = min(bg, taps - t0);
@@ -612,10 +622,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
               const uint64_t db = desc_hi | (uint64_t)((b_base + sb * stage_b + g * unit_b) >> 4);
               if (leader) {
                 if (f16)
-                  for (int kk = 0; kk < kk_n; ++kk)
+                  for (int kk = 0; kk < kn; ++kk)
                     umma_f16(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
                 else
-                  for (int kk = 0; kk < kk_n; ++kk)
+                  for (int kk = 0; kk < kn; ++kk)
                     umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
               }
               if (++dx == ksize) { dx = 0; ++dy; }
@@ -631,13 +641,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       }
     } else {
       const int stages = keep((int)(a.stages)), group = keep((int)(a.group)), units = keep((int)(a.units));
+      const int last_ch = keep((int)(a.chunks_per_tap - 1));
       int s = 0;
       uint32_t ph = 0, stage_addr = base;
       for (int tile = blockIdx.x; tile < total; tile += step) {
         mbar_wait(tempty_bar(as), aph ^ 1u);       // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t tacc = tmem_base + as * acc_stride;
-        int u = 0;
+        int u = 0, ch = 0;
         for (int gi = 0; gi < groups; ++gi) {
           mbar_wait(full_bar(s), ph);
           tc_fence_after();
@@ -646,14 +657,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
             const uint64_t da = desc_hi | (uint64_t)(sa >> 4);
             const uint64_t db = desc_hi | (uint64_t)((sa + unit_a) >> 4);
+            const int kn = ch == last_ch ? kk_last : kk_n;
             if (leader) {                        // +32 bytes along K per MMA: +2 in the >>4 field
               if (f16)
-                for (int kk = 0; kk < kk_n; ++kk)
+                for (int kk = 0; kk < kn; ++kk)
                   umma_f16(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
               else
-                for (int kk = 0; kk < kk_n; ++kk)
+                for (int kk = 0; kk < kn; ++kk)
                   umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
             }
+            ch = ch == last_ch ? 0 : ch + 1;
           }
           if (leader) umma_commit(empty_bar(s));   // frees the smem slot when these MMAs retire
           stage_addr += stage_bytes;
@@ -681,13 +694,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int tw_mask = a.tw - 1, tw_shift = 31 - __clz(a.tw);
     const int bx = (q * 32) & tw_mask, by = (q * 32) >> tw_shift;
     const bool has_res = a.res1.data != nullptr;
+    const uint32_t res_bytes = a.f16_res ? 2048u : 4096u;
+    const bool mixed = has_res && (a.f16_res != a.f16_out);   // residual / result rows differ in pitch
     const uint32_t row_off = (uint32_t)lane * 128u, sw = (uint32_t)(lane & 7);
+    const uint32_t row16 = (uint32_t)lane * 64u, sw4 = (uint32_t)(lane >> 1) & 3u;
     uint32_t rph0 = 0, rph1 = 0, b = 0, lt = 0;
     int tile = blockIdx.x, ci = part;
     if (has_res && leader && tile < a.total_tiles) {
       int mt, nt, ty, tx;
       tile_coords(a, tile, mt, nt, ty, tx);
-      mbar_expect_tx(res_bar(2 * we), 4096u);
+      mbar_expect_tx(res_bar(2 * we), res_bytes);
       tma_load_3d(buf0, &map_r, res_bar(2 * we), nt * a.n_tile + ci * 32, tx * a.tw + bx,
                   ty * a.th + by);
     }
@@ -730,11 +746,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if (has_res) {
           mbar_wait_warp(res_bar(2 * we + b), b ? rph1 : rph0, lane);
           if (b) rph1 ^= 1u; else rph0 ^= 1u;
+          if (a.f16_res) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 u = *reinterpret_cast<const float4 *>(buf_g + row_off + (((uint32_t)j ^ sw) << 4));
-            v[4 * j] += u.x; v[4 * j + 1] += u.y; v[4 * j + 2] += u.z; v[4 * j + 3] += u.w;
+            for (int j = 0; j < 4; ++j) {
+              const uint4 u = *reinterpret_cast<const uint4 *>(buf_g + row16 + (((uint32_t)j ^ sw4) << 4));
+              float2 f;
+              f = unpack_h2(u.x); v[8 * j] += f.x;     v[8 * j + 1] += f.y;
+              f = unpack_h2(u.y); v[8 * j + 2] += f.x; v[8 * j + 3] += f.y;
+              f = unpack_h2(u.z); v[8 * j + 4] += f.x; v[8 * j + 5] += f.y;
+              f = unpack_h2(u.w); v[8 * j + 6] += f.x; v[8 * j + 7] += f.y;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 u = *reinterpret_cast<const float4 *>(buf_g + row_off + (((uint32_t)j ^ sw) << 4));
+              v[4 * j] += u.x; v[4 * j + 1] += u.y; v[4 * j + 2] += u.z; v[4 * j + 3] += u.w;
+            }
           }
+          // rows of the two element sizes overlap other lanes' rows: everyone reads first
+          if (mixed) __syncwarp();
         }
         if (a.scale) {
 #pragma unroll
@@ -750,7 +780,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if (a.f16_out) {
           // binary16 rows of 64 bytes, 64B swizzle: 16-byte chunk j of row r sits at
           // j ^ ((r >> 1) & 3) (address bits [4,6) ^= bits [7,9))
-          const uint32_t row16 = (uint32_t)lane * 64u, sw4 = (uint32_t)(lane >> 1) & 3u;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 pk;
@@ -779,7 +808,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if (has_res && ntile < a.total_tiles) {
           int mt2, nt2, ty2, tx2;
           tile_coords(a, ntile, mt2, nt2, ty2, tx2);
-          mbar_expect_tx(res_bar(2 * we + (b ^ 1u)), 4096u);
+          mbar_expect_tx(res_bar(2 * we + (b ^ 1u)), res_bytes);
           tma_load_3d(buf0 + (b ^ 1u) * 4096u, &map_r, res_bar(2 * we + (b ^ 1u)),
                       nt2 * a.n_tile + nci * 32, tx2 * a.tw + bx, ty2 * a.th + by);
         }
@@ -1051,7 +1080,7 @@ int tc_fast_mode(const dcvc_conv *d) {
             (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
   };
   const bool ok = d->cout_w % 4 == 0 && (d->out_f16 ? al16h(d->out) : al16(d->out)) &&
-                  al16(d->res1) && al16(d->res2) &&
+                  (d->res1_f16 ? al16h(d->res1) : al16(d->res1)) && al16(d->res2) &&
                   al16(d->out2) && (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
                   (reinterpret_cast<uintptr_t>(d->scale) & 15u) == 0 && unit(d->out_slope) &&
                   unit(d->gate_slope) && unit(d->out2_slope);
@@ -1069,8 +1098,9 @@ bool conv_tc_ok(const dcvc_conv *d) {
   if (reinterpret_cast<uintptr_t>(d->weight_tc) & 15) return false;
   if (d->in_f16 && (!d->weight_tc16 || (reinterpret_cast<uintptr_t>(d->weight_tc16) & 15)))
     return false;
-  // binary16 output leaves through the TMA-store epilogue only
-  if (d->out_f16 && (tc_fast_mode(d) != 1 || d->res1.data || d->res2.data || d->out2.data))
+  // binary16 output / residual go through the TMA-store epilogue only
+  if ((d->out_f16 || (d->res1_f16 && d->res1.data)) &&
+      (tc_fast_mode(d) != 1 || d->res2.data || d->out2.data))
     return false;
   if (d->shuffle == 2 && tc_fast_mode(d) != 3) return false;   // planar packing needs the lean path
   const int ho = (d->in.h + 2 * d->pad - d->ksize) / d->stride + 1;
@@ -1090,10 +1120,15 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.ksize = d->ksize; a.stride = d->stride; a.pad = d->pad;
   int cin_pad, n_pad, tiles_n;
   const bool f16 = d->in_f16 != 0;
-  a.f16_in = f16; a.f16_out = d->out_f16 != 0;
+  a.f16_in = f16; a.f16_out = d->out_f16 != 0; a.f16_res = d->res1.data && d->res1_f16;
   if (f16) dcvc_conv_tc_geometry16(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
   else dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
   a.kcb = a.kc * (f16 ? 2 : 4);
+  {
+    const int per_mma = f16 ? 16 : 8;                 // K elements one instruction multiplies
+    const int tail = d->in.c - (cin_pad / a.kc - 1) * a.kc;   // valid channels in the last chunk
+    a.kk_last = cdiv(tail, per_mma);
+  }
   n_tiling(d->cout_w, &tiles_n, &a.n_tile);
   a.chunks_per_tap = cin_pad / a.kc;
   a.units = a.ksize * a.ksize * a.chunks_per_tap;
@@ -1168,7 +1203,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
   // TMA-store epilogue: plain convs with at most one residual, views TMA-addressable
-  a.tma_epi = (tma_epi_on || a.f16_out) && a.fast == 1 && !d->res2.data && !d->out2.data;
+  a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res) && a.fast == 1 && !d->res2.data && !d->out2.data;
   int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi
             : a.tma_epi ? (ctas == 1 ? 8 : 4) : (ctas == 1 ? 16 : 8);
   while (epi > 4 && epi / 4 > nchunks) epi >>= 1;
@@ -1222,7 +1257,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
     rc = make_map_epi(d->out, d->cout_w, w_box, a.f16_out != 0, &mo);
     if (rc) return rc;
     if (d->res1.data) {
-      rc = make_map_epi(d->res1, d->cout_w, w_box, false, &mr);
+      rc = make_map_epi(d->res1, d->cout_w, w_box, a.f16_res != 0, &mr);
       if (rc) return rc;
     } else {
       mr = mo;

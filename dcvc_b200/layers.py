@@ -38,12 +38,15 @@ def _pack_tc(w, planar=False):
     return out.contiguous()
 
 
-def _pack_tc16(w):
+def _pack_tc16(w, planar=False):
     """binary16 NK packing for convs whose input is a binary16 activation (dcvc_conv.in_f16):
-    [n_pad][kh*kw][cin_pad16], geometry from dcvc_conv_tc_geometry16."""
+    [n_pad][kh*kw][cin_pad16], geometry from dcvc_conv_tc_geometry16; planar as in _pack_tc."""
     import ctypes
     from . import _lib
     cout, cin, kh, kw = w.shape
+    if planar:
+        c = cout // 4
+        w = w.reshape(c, 4, cin, kh, kw).permute(1, 0, 2, 3, 4).reshape(cout, cin, kh, kw)
     n_pad, cin_pad, kc = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
     _lib.check(_lib.lib().dcvc_conv_tc_geometry16(cout, cin, ctypes.byref(n_pad),
                                                   ctypes.byref(cin_pad), ctypes.byref(kc)))
@@ -91,8 +94,8 @@ class Net:
             r = ConvW(wp, b.contiguous() if b is not None else None, cin, cout, kh, gate,
                       w_tc=_pack_tc(w, planar=shuffle and cout % 16 == 0),
                       tc_planar=shuffle and cout % 16 == 0)
-            if not shuffle:
-                r.pack16 = lambda w=w: _pack_tc16(w)
+            if not shuffle or r.tc_planar:
+                r.pack16 = lambda w=w, pl=r.tc_planar: _pack_tc16(w, pl)
             self._conv[key] = r
         return r
 
@@ -128,31 +131,35 @@ def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, s
                     res2=res2, scale=scale, out=out)
 
 
-def depth_conv(net, p, x, out=None):
-    """DepthConv (layers.py:135-163), stride 1."""
+def depth_conv(net, p, x, out=None, f16_out=False):
+    """DepthConv (layers.py:135-163), stride 1.  Everything only the next kernel of the block
+    reads (the adaptor's identity, conv1 and depth_conv outputs) is binary16 in tensor-core mode."""
     identity = x
     if net.has(p + ".adaptor"):
-        identity = ops.conv(x, net.cw(p + ".adaptor"))
+        identity = ops.conv(x, net.cw(p + ".adaptor"), f16_out=True)
     t = ops.conv(x, net.cw(p + ".conv1.0"), act=0.01, f16_out=True)
     w, b = net.dw(p + ".depth_conv")
     t = ops.dwconv3x3(t, w, b)
-    return ops.conv(t, net.cw(p + ".conv2"), res=identity, out=out)
+    return ops.conv(t, net.cw(p + ".conv2"), res=identity, out=out, f16_out=f16_out)
 
 
-def dcb(net, p, x, out=None, scale=None):
+def dcb(net, p, x, out=None, scale=None, f16_out=False):
     """DepthConvBlock (layers.py:199-209) = DepthConv + ConvFFN (layers.py:166-179); an outer
-    `* q` rides on the last epilogue."""
-    t = depth_conv(net, p + ".block.0", x)
+    `* q` rides on the last epilogue.  f16_out: the caller is the only reader of the result and
+    reads it with a convolution (block chains)."""
+    t = depth_conv(net, p + ".block.0", x, f16_out=True)
     u = ops.conv(t, net.cw(p + ".block.1.conv.0"), act=0.1, f16_out=True)
-    return ops.conv(u, net.cw(p + ".block.1.conv.2"), act=0.1, res=t, scale=scale, out=out)
+    return ops.conv(u, net.cw(p + ".block.1.conv.2"), act=0.1, res=t, scale=scale, out=out,
+                    f16_out=f16_out)
 
 
-def dcb2(net, p, x, out=None, scale=None):
+def dcb2(net, p, x, out=None, scale=None, f16_out=False):
     """DepthConvBlock2 (layers.py:212-222) = DepthConv + ConvFFN2 (layers.py:182-196); the
     x1 * lrelu(x2) gate is the epilogue of the up-projection."""
-    t = depth_conv(net, p + ".block.0", x)
+    t = depth_conv(net, p + ".block.0", x, f16_out=True)
     u = ops.conv(t, net.cw(p + ".block.1.conv", gate=True), gate_slope=0.1)
-    return ops.conv(u, net.cw(p + ".block.1.conv_out"), res=t, scale=scale, out=out)
+    return ops.conv(u, net.cw(p + ".block.1.conv_out"), res=t, scale=scale, out=out,
+                    f16_out=f16_out)
 
 
 def rbws(net, p, x, out=None):
@@ -176,9 +183,9 @@ def unet(net, p, x, block, out=None):
     cat3 = Act.new(x.h // 2, x.w // 2, 128, dev)
     x1 = block(net, p + ".conv1", x, out=cat2.slice(0, 32))
     x2 = block(net, p + ".conv2", ops.max_pool2(x1), out=cat3.slice(0, 64))
-    x3 = block(net, p + ".conv3", ops.max_pool2(x2))
+    x3 = block(net, p + ".conv3", ops.max_pool2(x2), f16_out=True)
     for i in range(4):
-        x3 = block(net, f"{p}.context_refine.{i}", x3)
+        x3 = block(net, f"{p}.context_refine.{i}", x3, f16_out=True)
     subpel(net, p + ".up3", x3, out=cat3.slice(64, 64))
     d3 = block(net, p + ".up_conv3", cat3)
     subpel(net, p + ".up2", d3, out=cat2.slice(32, 32))

@@ -90,7 +90,7 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
         ec //= 2
     if out is None:
         f16_out = (f16_out and f16_ok(eh, ew, ec) and cw.w_tc is not None and not shuffle
-                   and not cw.gate and res is None and res2 is None and out2 is None)
+                   and not cw.gate and res2 is None and out2 is None)
         out = Act.new(eh, ew, ec, x.device, f16=f16_out)
     if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= 512:
         # the TMA-fed tensor-core kernel has no input prologue: materialise lrelu(x) once
@@ -106,6 +106,7 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     d.weight = cw.w.data_ptr()
     d.weight_tc = cw.w_tc.data_ptr() if cw.w_tc is not None else None
     d.in_f16, d.out_f16 = int(x.f16), int(out.f16)
+    d.res1_f16 = int(res is not None and res.f16)
     if x.f16:
         if cw.w_tc16 is None:
             cw.w_tc16 = cw.pack16()

@@ -314,3 +314,22 @@ def test_blocks_with_f16_intermediates(block, monkeypatch):
     assert float((out32 - ref).abs().max()) < 6e-3 * scale
     assert float((out16 - out32).abs().max()) < 6e-3 * scale
     assert not torch.equal(out16, out32)          # the binary16 path really ran
+
+
+@pytest.mark.parametrize("res16,out16", [(True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("cin,cout,k,h,w", [(64, 48, 1, 37, 53), (32, 64, 3, 33, 70), (64, 320, 1, 24, 32)])
+def test_tc_conv_f16_residual(cin, cout, k, h, w, res16, out16):
+    """Residual and result of either element size through the one smem tile of the TMA-store
+    epilogue (rows of 64 and 128 bytes overlap, so the warp reads before anyone writes)."""
+    sd = _sd(cin, cout, k, seed=51)
+    x, r1 = _rand(1, cin, h, w, seed=14), _rand(1, cout, h, w, seed=15)
+    q = torch.rand(cout) + 0.5
+    net = layers.Net(sd, dev())
+    res = ops.copy(to_act(r1), f16=True) if res16 else to_act(r1)
+    rr = r1.half().float() if res16 else r1
+    ref = (F.leaky_relu(F.conv2d(x, sd["c.weight"], sd["c.bias"], 1, k // 2), 0.1) + rr) * q.view(1, -1, 1, 1)
+    out = Act.new(h, w, cout, dev(), f16=out16)
+    ops.conv(to_act(x), net.cw("c"), act=0.1, res=res, scale=q.to(dev()), out=out)
+    got = out.buf[:, :, :cout].float().permute(2, 0, 1).unsqueeze(0).cpu()
+    bound = 4 * (4e-3 * 0.58 * 0.58 + 1e-5) * 1.5 + (float(ref.abs().max()) * 2 ** -11 if out16 else 0.0)
+    assert float((got - ref).abs().max()) < bound, float((got - ref).abs().max())
