@@ -41,6 +41,7 @@ struct TcArgs {
   // halo mode (stride-1 k>1 convs): A stage = whole input window, B ring per tap
   int halo, halo_sa, halo_sb, halo_pw, halo_bg;   // halo_bg: taps per B stage
   uint32_t halo_sbo;
+  int bres;       // halo mode with the whole weight matrix resident in smem (loaded once per CTA)
   int tma_epi;    // 1: TMA-store epilogue (stage_off region = 8 KB per warp, vec_off = bias/scale)
   uint32_t vec_off;
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
@@ -358,6 +359,51 @@ __device__ __forceinline__ void fast_chunk(const TcArgs &a, const float *stg, in
   float *const o2 = a.out2.data ? a.out2.data + a.out2.coff + c : nullptr;
   const int tw_mask = a.tw - 1, tw_shift = 31 - __clz(a.tw);
   const float *src = stg + (lane >> vshift) * STG_PITCH + 4 * c4;
+  if (MODE == 0 && (r1 || r2)) {
+    // residual epilogue: the loads of four rows are issued before any of them is consumed (the
+    // stores may alias the residual views as far as the compiler knows, so it will not hoist
+    // them itself, and one dependent global load per row leaves the warp latency-bound)
+    for (int r = lane >> vshift; r < 32; r += 4 * rstep, src += 4 * rstep * STG_PITCH) {
+      float4 u1[4], u2[4];
+      int pix[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int row = q * 32 + r + j * rstep;
+        const int oy = oy0 + (row >> tw_shift), ox = ox0 + (row & tw_mask);
+        pix[j] = (oy < a.hout && ox < a.wout) ? oy * a.wout + ox : -1;
+        u1[j] = u2[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pix[j] >= 0 && r1)
+          u1[j] = __ldg(reinterpret_cast<const float4 *>(r1 + (size_t)pix[j] * a.res1.cstride));
+        if (pix[j] >= 0 && r2)
+          u2[j] = __ldg(reinterpret_cast<const float4 *>(r2 + (size_t)pix[j] * a.res2.cstride));
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (pix[j] < 0) continue;
+        float4 t = *reinterpret_cast<const float4 *>(src + j * rstep * STG_PITCH);
+        t.x += b.x; t.y += b.y; t.z += b.z; t.w += b.w;
+        if (a.out_slope != 1.f) {
+          t.x = lrelu01(t.x, a.out_slope); t.y = lrelu01(t.y, a.out_slope);
+          t.z = lrelu01(t.z, a.out_slope); t.w = lrelu01(t.w, a.out_slope);
+        }
+        // same order as the generic path: (v + res1) + res2
+        t.x += u1[j].x; t.y += u1[j].y; t.z += u1[j].z; t.w += u1[j].w;
+        if (r2) { t.x += u2[j].x; t.y += u2[j].y; t.z += u2[j].z; t.w += u2[j].w; }
+        if (a.scale) { t.x *= sc.x; t.y *= sc.y; t.z *= sc.z; t.w *= sc.w; }
+        if (a.clamp01) {
+          t.x = fminf(fmaxf(t.x, 0.f), 1.f); t.y = fminf(fmaxf(t.y, 0.f), 1.f);
+          t.z = fminf(fmaxf(t.z, 0.f), 1.f); t.w = fminf(fmaxf(t.w, 0.f), 1.f);
+        }
+        *reinterpret_cast<float4 *>(o + (size_t)pix[j] * a.out.cstride) = t;
+        if (o2) {
+          t.x = lrelu01(t.x, a.out2_slope); t.y = lrelu01(t.y, a.out2_slope);
+          t.z = lrelu01(t.z, a.out2_slope); t.w = lrelu01(t.w, a.out2_slope);
+          *reinterpret_cast<float4 *>(o2 + (size_t)pix[j] * a.out2.cstride) = t;
+        }
+      }
+    }
+    return;
+  }
 #pragma unroll 2
   for (int r = lane >> vshift; r < 32; r += rstep, src += rstep * STG_PITCH) {
     const int row = q * 32 + r;
@@ -503,7 +549,29 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                      tx_b = (uint32_t)(n_tile * a.kcb), b_base = base + sa_n * unit_a;
       int sa = 0, sb = 0;
       uint32_t pha = 0, phb = 0;
-      int a_tile = blockIdx.x, a_ch = 0;             // iterator of the A loads
+      if (a.bres) {
+        // ----- resident weights: every tap's B tile is loaded once and stays; the ring carries
+        // input windows only, one TMA load per tile
+        if (leader) {
+          mbar_expect_tx(full_bar(sa_n), no_tma ? 0u : (uint32_t)taps * tx_b);
+          if (!no_tma)
+            for (int g = 0; g < taps; ++g)
+              tma_load_2d(b_base + g * unit_b, &map_b, full_bar(sa_n), g * kc, 0);
+        }
+        for (int tile = blockIdx.x; tile < total; tile += step) {
+          int mt, nt, ty, tx;
+          tile_coords(a, tile, mt, nt, ty, tx);
+          mbar_wait(empty_bar(sa), pha ^ 1u);
+          if (leader) {
+            mbar_expect_tx(full_bar(sa), no_tma ? 0u : tx_a);
+            if (!no_tma)
+              tma_load_4d(base + sa * unit_a, &map_a, full_bar(sa), 0, tx * a.tw - pad,
+                          ty * a.th - pad, 0);
+          }
+          if (++sa == sa_n) { sa = 0; pha ^= 1u; }
+        }
+      }
+      int a_tile = a.bres ? total : blockIdx.x, a_ch = 0;   // iterator of the A loads
       auto issue_a = [&]() {
         if (a_tile >= total) return;
         int mt, nt, ty, tx;
@@ -519,7 +587,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if (++a_ch == chunks) { a_ch = 0; a_tile += step; }
       };
       issue_a();
-      for (int tile = blockIdx.x; tile < total; tile += step) {
+      for (int tile = a.bres ? total : (int)blockIdx.x; tile < total; tile += step) {
         int mt, nt, ty, tx;
         tile_coords(a, tile, mt, nt, ty, tx);
         const int n_base = nt * n_tile;
@@ -602,7 +670,41 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       const uint32_t b_base = keep((uint32_t)(base + sa_n * unit_a)), pitch = keep((uint32_t)a.kcb);
       int sa = 0, sb = 0;
       uint32_t pha = 0, phb = 0;
-      for (int tile = blockIdx.x; tile < total; tile += step) {
+      if (a.bres) {
+        mbar_wait(full_bar(sa_n), 0u);               // the weights, once
+        tc_fence_after();
+        for (int tile = blockIdx.x; tile < total; tile += step) {
+          mbar_wait(tempty_bar(as), aph ^ 1u);
+          tc_fence_after();
+          const uint32_t tacc = tmem_base + as * acc_stride;
+          mbar_wait(full_bar(sa), pha);
+          tc_fence_after();
+          uint32_t row = base + sa * unit_a, b_addr = b_base, t = 0;
+          for (int dy = 0; dy < ksize; ++dy, row += (uint32_t)pw * pitch) {
+            uint32_t start = row;
+            for (int dx = 0; dx < ksize; ++dx, start += pitch, b_addr += unit_b, ++t) {
+              const uint64_t da = desc_a_hi | (uint64_t)(start >> 4);
+              const uint64_t db = desc_hi | (uint64_t)(b_addr >> 4);
+              const uint32_t tp = tacc, first = t;
+              if (leader) {
+                if (f16)
+                  for (int kk = 0; kk < kk_last; ++kk)
+                    umma_f16(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
+                else
+                  for (int kk = 0; kk < kk_last; ++kk)
+                    umma_tf32(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
+              }
+            }
+          }
+          if (leader) {
+            umma_commit(empty_bar(sa));
+            umma_commit(tfull_bar(as));
+          }
+          if (++sa == sa_n) { sa = 0; pha ^= 1u; }
+          if ((as ^= 1u) == 0) aph ^= 1u;
+        }
+      }
+      for (int tile = a.bres ? total : (int)blockIdx.x; tile < total; tile += step) {
         mbar_wait(tempty_bar(as), aph ^ 1u);
         tc_fence_after();
         const uint32_t tacc = tmem_base + as * acc_stride;
@@ -620,13 +722,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
               const uint32_t start = a_addr + (uint32_t)(dy * pw + dx) * pitch;
               const uint64_t da = desc_a_hi | (uint64_t)(start >> 4);
               const uint64_t db = desc_hi | (uint64_t)((b_base + sb * stage_b + g * unit_b) >> 4);
+              const uint32_t t = (uint32_t)(t0 + g);
+              const uint32_t tp = tacc, first = (uint32_t)ch | t;
               if (leader) {
                 if (f16)
                   for (int kk = 0; kk < kn; ++kk)
-                    umma_f16(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
+                    umma_f16(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
                 else
                   for (int kk = 0; kk < kn; ++kk)
-                    umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (ch | (t0 + g) | kk) ? 1u : 0u);
+                    umma_tf32(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
               }
               if (++dx == ksize) { dx = 0; ++dy; }
             }
@@ -658,13 +762,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const uint64_t da = desc_hi | (uint64_t)(sa >> 4);
             const uint64_t db = desc_hi | (uint64_t)((sa + unit_a) >> 4);
             const int kn = ch == last_ch ? kk_last : kk_n;
+            const uint32_t tp = tacc, first = (uint32_t)u;
             if (leader) {                        // +32 bytes along K per MMA: +2 in the >>4 field
               if (f16)
                 for (int kk = 0; kk < kn; ++kk)
-                  umma_f16(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
+                  umma_f16(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
               else
                 for (int kk = 0; kk < kn; ++kk)
-                  umma_tf32(tacc, da + 2u * kk, db + 2u * kk, idesc, (u | kk) ? 1u : 0u);
+                  umma_tf32(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
             }
             ch = ch == last_ch ? 0 : ch + 1;
           }
@@ -1149,6 +1254,17 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
            a.kcb >= (f16 ? 32 : 64) && d->pad == d->ksize / 2;
   if (a.halo && halo_on == 1)
     a.halo = d->ksize == 3 && !d->shuffle && (a.kcb == 64 || a.n_tile >= 96);
+  // resident weights: one channel chunk, one N tile and all taps' B tiles within 72 KB.  One CTA
+  // per SM then issues every MMA back to back (~130 cycles each for M = 128 whatever N <= 192):
+  // 3x3 48->48 f16 at 1080p 0.254 -> 0.206 ms = 27 MMAs x 110 tiles per SM, the issue floor of
+  // this GEMM orientation; 7x7 only where a tap is a single MMA (16->2: 0.525 -> 0.40 ms)
+  static const int bres_on = getenv("DCVC_TC_BRES") ? atoi(getenv("DCVC_TC_BRES")) : 1;
+  const uint32_t bres_bytes = (uint32_t)(d->ksize * d->ksize) * (uint32_t)ru(a.n_tile * a.kcb, 1024);
+  a.bres = bres_on && halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 7 &&
+           d->pad == d->ksize / 2 && a.kcb >= (f16 ? 32 : 64) && a.chunks_per_tap == 1 &&
+           tiles_n == 1 && bres_bytes <= 72u * 1024u && !d->res2.data && !d->out2.data &&
+           (bres_on == 2 || (d->ksize == 3 && !d->shuffle) || (a.kk_last == 1 && a.n_tile <= 32));
+  if (a.bres) a.halo = 1;
   const int halo_ph = TILE_M / 8 + d->ksize - 1;
   static const int halo_pw16 = getenv("DCVC_TC_HALO_PW16") ? atoi(getenv("DCVC_TC_HALO_PW16")) : 0;
   if (a.halo) { a.tw = 8; a.th = TILE_M / 8; a.halo_pw = halo_pw16 ? 16 : 8 + d->ksize - 1; }
@@ -1182,6 +1298,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.rcp_tiles_n = ((1ull << 40) + (uint64_t)tiles_n - 1) / (uint64_t)tiles_n;
   a.rcp_tiles_x = ((1ull << 40) + (uint64_t)a.tiles_x - 1) / (uint64_t)a.tiles_x;
   // two TMEM accumulators (epilogue of tile i overlaps the MMAs of tile i+1)
+  // (splitting K over two partial accumulators so that consecutive MMAs are independent was
+  // measured: no change on any shape -- the MMA queue is not serialised by the accumulator)
   a.acc_stride = (uint32_t)a.n_tile;
   a.tmem_cols = 32;
   while ((int)a.tmem_cols < 2 * a.n_tile) a.tmem_cols *= 2;
@@ -1199,6 +1317,10 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   if (ctas < 1) ctas = 1;
   static const int halo_ctas = getenv("DCVC_TC_HALO_CTAS") ? atoi(getenv("DCVC_TC_HALO_CTAS")) : 2;
   if (a.halo && ctas > halo_ctas) ctas = halo_ctas;
+  if (a.bres) {   // weights + two windows + ~40 KB of epilogue/barrier space per CTA
+    const int fit = (int)(227u * 1024u / (bres_bytes + 2u * a.unit_a + 40u * 1024u));
+    ctas = fit < 1 ? 1 : (fit < ctas ? fit : ctas);
+  }
   // epilogue warps: 4 per 32-column chunk group; a lone CTA on the SM gets 16 so that enough
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
@@ -1224,7 +1346,18 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.layout_type = a.kcb == 128 ? 2u : a.kcb == 64 ? 4u : 6u;
   // smem: [stages x stage][barriers (1 KB)][epi_warps epilogue tiles][bias, scale vectors]
   a.stage_off = (uint32_t)stages * stage + 1024u;
-  if (a.halo) {
+  if (a.bres) {
+    // [SA x window][all taps' weights][barriers]...
+    const uint32_t room = (227u * 1024u / ctas) - 1024u - fixed;
+    if (room < bres_bytes + 2u * a.unit_a)
+      return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: resident weights do not fit shared memory");
+    int sa = (int)((room - bres_bytes) / a.unit_a);
+    a.halo_sa = sa > 6 ? 6 : sa;
+    a.halo_sb = 1;
+    a.halo_bg = a.ksize * a.ksize;
+    a.stages = a.halo_sa + 1;
+    a.stage_off = (uint32_t)a.halo_sa * a.unit_a + bres_bytes + 1024u;
+  } else if (a.halo) {
     // [SA x window][SB x (bg weight taps)][barriers]...: a B stage carries a group of taps (about
     // 24 KB, at most one kernel row) so that one barrier round trip covers several MMAs
     static const int bg_kb = getenv("DCVC_TC_HALO_BKB") ? atoi(getenv("DCVC_TC_HALO_BKB")) : 24;

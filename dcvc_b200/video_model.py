@@ -65,6 +65,8 @@ class DMC(CompressionModel):
             up = ops.resize_bilinear(flow, h, w, mul=2.0, out=inp.slice(6, 2))
             ops.flow_warp(p2[k], up, out=inp.slice(3, 3))
             p = f"optic_flow.moduleBasic.{lv}"
+            if ops.f16_ok(h, w, 8):
+                inp = ops.copy(inp, f16=True)      # 7x7 on 8 channels: one K=16 MMA per tap
             t = ops.conv(inp, net.cw(p + ".conv1"), act=0.0, f16_out=True)
             t = ops.conv(t, net.cw(p + ".conv2"), act=0.0, f16_out=True)
             t = ops.conv(t, net.cw(p + ".conv3"), act=0.0, f16_out=True)

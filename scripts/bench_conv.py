@@ -25,7 +25,7 @@ if os.environ.get("SHAPES"):   # "cin,cout,k,stride,h,w;..."
     SHAPES = [tuple(int(v) for v in t.split(",")) + ({},) for t in os.environ["SHAPES"].split(";")]
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 for cin, cout, k, s, h, w, kw in SHAPES:
-    name = f"conv{k}x{k}s{s} {cin}->{cout} @{h}x{w} {kw}"
+    name = f"conv{k}x{k}s{s} {cin}->{cout} @{h}x{w}" + (" shuffle" if kw.get("shuffle") else "")
     if flt and flt not in name:
         continue
     g = torch.Generator().manual_seed(0)
@@ -38,11 +38,17 @@ for cin, cout, k, s, h, w, kw in SHAPES:
     if "o" in f16 and cout % 8 == 0 and not kw.get("shuffle"):
         kw = dict(kw, f16_out=True)
     cw = net.cw("c", shuffle=bool(kw.get("shuffle")))
+    if os.environ.get("BENCH_RES") and not kw.get("shuffle"):      # fp32 residual (res_block conv2)
+        ho_, wo_ = (h + 2 * (k // 2) - k) // s + 1, (w + 2 * (k // 2) - k) // s + 1
+        kw = dict(kw, res=Act(torch.randn(ho_, wo_, (cout + 3) // 4 * 4, device=dev), 0, cout))
+        if os.environ.get("BENCH_RES") == "2":
+            kw["res2"] = Act(torch.randn(ho_, wo_, (cout + 3) // 4 * 4, device=dev), 0, cout)
     out = ops.conv(x, cw, stride=s, **kw)
     torch.cuda.synchronize()
     ms = 0.0
     for _ in range(iters):
-        flush.zero_()
+        if not os.environ.get("BENCH_NOFLUSH"):
+            flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         ops.conv(x, cw, stride=s, out=out, **kw)
@@ -53,5 +59,7 @@ for cin, cout, k, s, h, w, kw in SHAPES:
     ho, wo = (h + 2 * (k // 2) - k) // s + 1, (w + 2 * (k // 2) - k) // s + 1
     fl = 2.0 * ho * wo * cout * cin * k * k
     by = (2.0 if x.f16 else 4.0) * h * w * cin + (2.0 if out.f16 else 4.0) * ho * wo * cout + 4.0 * cout * cin * k * k
-    name += (" f16in" if x.f16 else "") + (" f16out" if out.f16 else "")
+    name += (" f16in" if x.f16 else "") + (" f16out" if out.f16 else "") + (" +res" if "res" in kw else "")
+    if "res" in kw:
+        by += 4.0 * ho * wo * cout
     print(f"{name:72s} {ms:8.3f} ms {fl / ms / 1e9:8.1f} TFLOP/s {by / ms / 1e6:8.0f} GB/s", flush=True)

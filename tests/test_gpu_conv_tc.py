@@ -50,6 +50,7 @@ SHAPES = [
     (16, 2, 7, 1, 32, 32), (48, 3, 3, 1, 32, 48), (80, 48, 3, 1, 30, 50), (96, 96, 3, 1, 17, 67),
     (3, 48, 3, 1, 32, 32), (384, 384, 1, 1, 20, 28), (20, 24, 3, 1, 33, 47),
     (128, 512, 1, 1, 24, 32), (384, 1024, 1, 1, 17, 31), (64, 320, 3, 1, 24, 24),
+    (32, 128, 3, 1, 40, 40),    # halo window mode with one channel chunk and streamed weights
 ]
 
 
