@@ -112,6 +112,29 @@ __global__ void pool2_kernel(dcvc_view src, dcvc_view dst, int mode) {
   dst.data[vidx(dst, y, x) + c] = v;
 }
 
+// float4 path of pool2: one thread per (output pixel, 4 channels)
+__global__ void pool2_v4_kernel(dcvc_view src, dcvc_view dst, int mode, uint32_t c4n, uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t p = t / c4n, cq = t - p * c4n;
+  const uint32_t y = p / (uint32_t)dst.w, x = p - y * (uint32_t)dst.w;
+  const float *sp = src.data + ((size_t)(2 * y) * src.w + 2 * x) * src.cstride + src.coff + 4 * cq;
+  const size_t row = (size_t)src.w * src.cstride;
+  const float4 a = *reinterpret_cast<const float4 *>(sp);
+  const float4 b = *reinterpret_cast<const float4 *>(sp + src.cstride);
+  const float4 d = *reinterpret_cast<const float4 *>(sp + row);
+  const float4 e = *reinterpret_cast<const float4 *>(sp + row + src.cstride);
+  float4 v;
+  if (mode == 0) {
+    v = make_float4((a.x + b.x + d.x + e.x) * 0.25f, (a.y + b.y + d.y + e.y) * 0.25f,
+                    (a.z + b.z + d.z + e.z) * 0.25f, (a.w + b.w + d.w + e.w) * 0.25f);
+  } else {
+    v = make_float4(fmaxf(fmaxf(a.x, b.x), fmaxf(d.x, e.x)), fmaxf(fmaxf(a.y, b.y), fmaxf(d.y, e.y)),
+                    fmaxf(fmaxf(a.z, b.z), fmaxf(d.z, e.z)), fmaxf(fmaxf(a.w, b.w), fmaxf(d.w, e.w)));
+  }
+  *reinterpret_cast<float4 *>(dst.data + (size_t)p * dst.cstride + dst.coff + 4 * cq) = v;
+}
+
 // ATen upsample_bilinear2d, align_corners=False: src = scale*(dst+0.5)-0.5 clamped at 0
 __device__ __forceinline__ void src_index(float scale, int dst, int in_size, int &i0, int &i1,
                                           float &l0, float &l1) {
@@ -268,6 +291,69 @@ __global__ void offset_diversity_kernel(dcvc_view x, dcvc_view offs, dcvc_view f
   }
 }
 
+// the same with the offset / mask channels of a sample pair fetched as one float4 / float2 per
+// corner of the x2 resize (offs view 16-byte aligned), corner addresses computed once, 32-bit
+// indices.  Every value is produced by the same expression as above: results are bit-identical.
+__global__ void __launch_bounds__(256)
+offset_diversity_v4_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
+                           const float *__restrict__ fw, const float *__restrict__ fb,
+                           dcvc_view out, uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int q = (int)(t & 15u);
+  const uint32_t p = t >> 4;
+  const int py = (int)(p / (uint32_t)out.w), px = (int)(p - (uint32_t)py * (uint32_t)out.w);
+  int y0, y1, x0, x1;
+  float hl0, hl1, wl0, wl1;
+  src_index((float)offs.h / (float)out.h, py, offs.h, y0, y1, hl0, hl1);
+  src_index((float)offs.w / (float)out.w, px, offs.w, x0, x1, wl0, wl1);
+  const float *o00 = offs.data + vidx(offs, y0, x0), *o01 = offs.data + vidx(offs, y0, x1);
+  const float *o10 = offs.data + vidx(offs, y1, x0), *o11 = offs.data + vidx(offs, y1, x1);
+  const float4 a00 = __ldg(reinterpret_cast<const float4 *>(o00 + 4 * q));
+  const float4 a01 = __ldg(reinterpret_cast<const float4 *>(o01 + 4 * q));
+  const float4 a10 = __ldg(reinterpret_cast<const float4 *>(o10 + 4 * q));
+  const float4 a11 = __ldg(reinterpret_cast<const float4 *>(o11 + 4 * q));
+  const float2 m00 = __ldg(reinterpret_cast<const float2 *>(o00 + 64 + 2 * q));
+  const float2 m01 = __ldg(reinterpret_cast<const float2 *>(o01 + 64 + 2 * q));
+  const float2 m10 = __ldg(reinterpret_cast<const float2 *>(o10 + 64 + 2 * q));
+  const float2 m11 = __ldg(reinterpret_cast<const float2 *>(o11 + 64 + 2 * q));
+  const float2 fl = __ldg(reinterpret_cast<const float2 *>(flow.data + vidx(flow, py, px)));
+  auto bil = [&](float v00, float v01, float v10, float v11) {
+    return hl0 * (wl0 * v00 + wl1 * v01) + hl1 * (wl0 * v10 + wl1 * v11);
+  };
+  const float oxs[2] = {bil(a00.x, a01.x, a10.x, a11.x), bil(a00.z, a01.z, a10.z, a11.z)};
+  const float oys[2] = {bil(a00.y, a01.y, a10.y, a11.y), bil(a00.w, a01.w, a10.w, a11.w)};
+  const float mks[2] = {bil(m00.x, m01.x, m10.x, m11.x), bil(m00.y, m01.y, m10.y, m11.y)};
+  float v[6];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int n = 2 * q + k;
+    const float mask = 1.0f / (1.0f + expf(-mks[k]));
+    const Bilin b = warp_coords(px, py, 40.0f * tanhf(oxs[k]) + fl.x, 40.0f * tanhf(oys[k]) + fl.y,
+                                x.w, x.h);
+    const int c = (n & 15) * 3;
+    const float *c00 = x.data + vidx(x, b.y0, b.x0) + c, *c01 = x.data + vidx(x, b.y0, b.x1) + c;
+    const float *c10 = x.data + vidx(x, b.y1, b.x0) + c, *c11 = x.data + vidx(x, b.y1, b.x1) + c;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      float s = b.nw * __ldg(c00 + j);
+      if (b.vx1) s += b.ne * __ldg(c01 + j);
+      if (b.vy1) s += b.sw * __ldg(c10 + j);
+      if (b.vx1 && b.vy1) s += b.se * __ldg(c11 + j);
+      v[k * 3 + j] = s * mask;
+    }
+  }
+  float *op = out.data + vidx(out, py, px) + 3 * q;
+#pragma unroll
+  for (int o = 0; o < 3; ++o) {
+    const float *wr = fw + (3 * q + o) * 6;
+    float acc = fb ? fb[3 * q + o] : 0.f;
+#pragma unroll
+    for (int r = 0; r < 6; ++r) acc = fmaf(v[r], wr[r], acc);
+    op[o] = acc;
+  }
+}
+
 }  // namespace
 
 #define LAUNCH_1D(kernel, total, stream, ...)                                              \
@@ -329,6 +415,12 @@ extern "C" int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, 
   if (!view_ok(src) || !view_ok(dst) || src->c != dst->c || dst->h != src->h / 2 ||
       dst->w != src->w / 2)
     return dcvc_fail(DCVC_ERR_ARG, "pool2: bad args");
+  const int64_t total4 = (int64_t)dst->h * dst->w * (dst->c / 4);
+  if (view_al16(src) && view_al16(dst) && total4 < (1ll << 31)) {
+    LAUNCH_1D(pool2_v4_kernel, total4, stream, *src, *dst, mode, (uint32_t)(dst->c / 4),
+              (uint32_t)total4);
+    return DCVC_OK;
+  }
   LAUNCH_1D(pool2_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *src, *dst, mode);
   return DCVC_OK;
 }
@@ -366,7 +458,17 @@ extern "C" int dcvc_offset_diversity(const dcvc_view *x, const dcvc_view *offs_h
       x->c != 48 || offs_half->c != 96 || flow->c != 2 || out->c != 48 || out->h != x->h ||
       out->w != x->w || flow->h != x->h || flow->w != x->w)
     return dcvc_fail(DCVC_ERR_ARG, "offset_diversity: bad args");
-  LAUNCH_1D(offset_diversity_kernel, (int64_t)out->h * out->w * 16, stream, *x, *offs_half, *flow,
-            fusion_w, fusion_b, *out);
+  const int64_t total = (int64_t)out->h * out->w * 16;
+  const bool vec = ((offs_half->cstride | offs_half->coff) & 3) == 0 &&
+                   (reinterpret_cast<uintptr_t>(offs_half->data) & 15) == 0 &&
+                   ((flow->cstride | flow->coff) & 1) == 0 &&
+                   (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total < (1ll << 31);
+  if (vec) {
+    offset_diversity_v4_kernel<<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
+    DCVC_LAUNCHED();
+    return DCVC_OK;
+  }
+  LAUNCH_1D(offset_diversity_kernel, total, stream, *x, *offs_half, *flow, fusion_w, fusion_b, *out);
   return DCVC_OK;
 }

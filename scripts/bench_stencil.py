@@ -48,3 +48,12 @@ for h, w, c in [(1088, 1920, 48), (1088, 1920, 32), (544, 960, 64), (272, 480, 1
     timeit(f"copy {h}x{w}x{c} ->f16", lambda: ops.copy(x, out=o16, slope=0.1), 6 * h * w * c)
     p = Act.new(h // 2, w // 2, c, dev)
     timeit(f"max_pool2 {h}x{w}x{c}", lambda: ops.max_pool2(x, out=p), 5 * h * w * c)
+
+h, w = 1088, 1920
+x = Act.new(h, w, 48, dev); x.buf.normal_()
+offs = Act.new(h // 2, w // 2, 96, dev); offs.buf.normal_()
+flow = Act.new(h, w, 2, dev); flow.buf.normal_()
+fw, fb = torch.randn(48, 6, device=dev), torch.randn(48, device=dev)
+o = Act.new(h, w, 48, dev)
+timeit("offset_diversity 1088x1920", lambda: ops.offset_diversity(x, offs, flow, fw, fb, out=o),
+       4 * (2 * h * w * 48 + h * w * 24 + h * w * 2))
