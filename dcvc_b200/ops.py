@@ -123,7 +123,9 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
         _lib.check(_lib.lib().dcvc_conv2d(ctypes.byref(d), _stream(stream)))
         return out
     path = "tcgen05" if _lib.lib().dcvc_conv_tc_eligible(ctypes.byref(d)) else "fma"
-    name = f"conv{k}x{k}s{stride} {cw.cin}->{cw.cout_w} @{ho}x{wo} [{path}]"
+    tags = ("i" if x.f16 else "I") + ("o" if out.f16 else "O") + \
+        ("" if res is None else "r" if res.f16 else "R") + ("2" if res2 is not None else "")
+    name = f"conv{k}x{k}s{stride} {cw.cin}->{cw.cout_w} @{ho}x{wo} [{path}] {tags}"
     flops = 2 * ho * wo * cw.cout_w * cw.cin * k * k
     nbytes = _nb(x, out, res, res2, out2) + 4 * cw.w.numel()
     with _Prof(name, flops, nbytes):
