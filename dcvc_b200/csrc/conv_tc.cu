@@ -468,6 +468,220 @@ __device__ __forceinline__ void tile_coords(const TcArgs &a, int tile, int &mt, 
   tx = mt - ty * a.tiles_x;
 }
 
+// ------------------------------------------------------------------ MMA issue
+// The issuing warp's loops are written so that every operand of tcgen05.mma is provably
+// warp-uniform (derived from kernel parameters, blockIdx and loop counters only -- no value that
+// went through an inline-asm "+r" or shared memory) and so that stepping a descriptor is ONE
+// 32-bit add on its low word: the matrix descriptor is passed as (low word, constant high word).
+// Measured (scripts/ub/mma_rate.cu): back-to-back UTCHMMA with M = 128 retire one per
+// max(N/2, 32 + N/4) cycles (SS operands: 128 + N rows of 32 bytes through the 128 B/clk smem
+// port), i.e. 45 cycles at N = 48 -- the previous loops spent 110-170 cycles per MMA on
+// vector->uniform register moves (R2UR) and 64-bit descriptor arithmetic.
+template <bool F16>
+__device__ __forceinline__ void umma2(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                      uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  if (F16)
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+        ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\tmov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n\t}"
+        ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// high word of a shared-memory matrix descriptor (8-row group stride, version, swizzle mode);
+// the low word is (address >> 4) | 1 << 16 (LBO = 1, unused for swizzled K-major operands)
+__device__ __forceinline__ uint32_t desc_hi32(uint32_t sbo_bytes, uint32_t layout_type) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | ((layout_type & 7u) << 29);
+}
+__device__ __forceinline__ uint32_t desc_lo32(uint32_t addr) { return (addr >> 4) | 0x10000u; }
+
+struct MmaCtx {
+  uint32_t base, bars, tmem, idesc, a_hi, b_hi;
+  int stages;
+  bool issue;
+  __device__ __forceinline__ uint32_t full_bar(int s) const { return bars + 8u * s; }
+  __device__ __forceinline__ uint32_t empty_bar(int s) const { return bars + 8u * (stages + s); }
+  __device__ __forceinline__ uint32_t tfull_bar(int s) const { return bars + 8u * (2 * stages + s); }
+  __device__ __forceinline__ uint32_t tempty_bar(int s) const { return bars + 8u * (2 * stages + 2 + s); }
+};
+
+// resident weights (halo window per tile, every tap's B tile in place): KS*KS*KK MMAs per tile
+// with compile-time offsets from the window / weight bases
+template <int KS, int KK, bool F16>
+__device__ __forceinline__ void mma_bres(const TcArgs &a, const MmaCtx &c) {
+  const int total = a.total_tiles, step = gridDim.x, sa_n = a.halo_sa;
+  const uint32_t p4 = (uint32_t)a.kcb >> 4, pwp4 = (uint32_t)(a.halo_pw * a.kcb) >> 4,
+                 ub4 = a.unit_b >> 4, ua4 = a.unit_a >> 4, acc_stride = a.acc_stride;
+  const uint32_t a4_0 = desc_lo32(c.base), b4 = desc_lo32(c.base + sa_n * a.unit_a);
+  uint32_t as = 0, aph = 0, pha = 0, a4 = a4_0;
+  int sa = 0;
+  mbar_wait(c.full_bar(sa_n), 0u);               // the weights, once
+  for (int tile = blockIdx.x; tile < total; tile += step) {
+    mbar_wait(c.tempty_bar(as), aph ^ 1u);
+    mbar_wait(c.full_bar(sa), pha);
+    tc_fence_after();
+    const uint32_t tacc = c.tmem + as * acc_stride;
+    if (c.issue) {
+#pragma unroll(KS <= 3 ? KS : 1)
+      for (int dy = 0; dy < KS; ++dy) {
+        const uint32_t ra = a4 + dy * pwp4, rb = b4 + dy * KS * ub4;
+#pragma unroll
+        for (int dx = 0; dx < KS; ++dx)
+#pragma unroll
+          for (int kk = 0; kk < KK; ++kk)
+            umma2<F16>(tacc, ra + dx * p4 + 2 * kk, c.a_hi, rb + dx * ub4 + 2 * kk, c.b_hi, c.idesc,
+                       (dx | kk) ? 1u : (uint32_t)dy);
+      }
+      umma_commit(c.empty_bar(sa));
+      umma_commit(c.tfull_bar(as));
+    }
+    a4 += ua4;
+    if (++sa == sa_n) { sa = 0; pha ^= 1u; a4 = a4_0; }
+    if ((as ^= 1u) == 0) aph ^= 1u;
+  }
+}
+
+// halo windows with streamed weights: per (tile, channel chunk) one window, taps walk it;
+// B stages carry `halo_bg` consecutive taps
+template <int KK, bool F16>
+__device__ __forceinline__ void mma_halo(const TcArgs &a, const MmaCtx &c) {
+  const int total = a.total_tiles, step = gridDim.x, sa_n = a.halo_sa, sb_n = a.halo_sb;
+  const int ks = a.ksize, taps = ks * ks, chunks = a.chunks_per_tap, bg = a.halo_bg;
+  const int kk_last = a.kk_last;
+  const uint32_t p4 = (uint32_t)a.kcb >> 4, row4 = ((uint32_t)(a.halo_pw * a.kcb) >> 4) - ks * p4,
+                 ub4 = a.unit_b >> 4, ua4 = a.unit_a >> 4, sb4 = (uint32_t)(a.halo_bg * a.unit_b) >> 4,
+                 acc_stride = a.acc_stride;
+  const uint32_t a4_0 = desc_lo32(c.base), b4_0 = desc_lo32(c.base + sa_n * a.unit_a);
+  uint32_t as = 0, aph = 0, pha = 0, phb = 0, a4 = a4_0, b4 = b4_0;
+  int sa = 0, sb = 0;
+  for (int tile = blockIdx.x; tile < total; tile += step) {
+    mbar_wait(c.tempty_bar(as), aph ^ 1u);
+    tc_fence_after();
+    const uint32_t tacc = c.tmem + as * acc_stride;
+    uint32_t accf = 0;
+    for (int ch = 0; ch < chunks; ++ch) {
+      mbar_wait(c.full_bar(sa), pha);
+      tc_fence_after();
+      const int kn = ch == chunks - 1 ? kk_last : KK;
+      uint32_t a_t = a4;
+      int dx = 0;
+      for (int t0 = 0; t0 < taps; t0 += bg) {          // one B stage = `bg` consecutive taps
+        const int sbar = sa_n + sb, cnt = min(bg, taps - t0);
+        mbar_wait(c.full_bar(sbar), phb);
+        tc_fence_after();
+        uint32_t b_t = b4;
+        for (int g = 0; g < cnt; ++g) {
+          if (c.issue) {
+#pragma unroll
+            for (int kk = 0; kk < KK; ++kk)
+              if (kk < kn)
+                umma2<F16>(tacc, a_t + 2 * kk, c.a_hi, b_t + 2 * kk, c.b_hi, c.idesc,
+                           kk ? 1u : accf);
+          }
+          accf = 1u;
+          b_t += ub4;
+          a_t += p4;
+          if (++dx == ks) { dx = 0; a_t += row4; }
+        }
+        if (c.issue) umma_commit(c.empty_bar(sbar));
+        b4 += sb4;
+        if (++sb == sb_n) { sb = 0; phb ^= 1u; b4 = b4_0; }
+      }
+      if (c.issue) umma_commit(c.empty_bar(sa));
+      a4 += ua4;
+      if (++sa == sa_n) { sa = 0; pha ^= 1u; a4 = a4_0; }
+    }
+    if (c.issue) umma_commit(c.tfull_bar(as));
+    if ((as ^= 1u) == 0) aph ^= 1u;
+  }
+}
+
+// one stage = `group` (tap, channel-chunk) units of [A tile | B tile]
+template <int KK, bool F16>
+__device__ __forceinline__ void mma_plain(const TcArgs &a, const MmaCtx &c) {
+  const int total = a.total_tiles, step = gridDim.x, stages = a.stages, group = a.group,
+            units = a.units, last_ch = a.chunks_per_tap - 1, kk_last = a.kk_last;
+  const int groups = (units + group - 1) / group;
+  const uint32_t ua4 = a.unit_a >> 4, unit4 = (a.unit_a + a.unit_b) >> 4,
+                 stage4 = (uint32_t)group * unit4, acc_stride = a.acc_stride;
+  const uint32_t a4_0 = desc_lo32(c.base);
+  uint32_t as = 0, aph = 0, ph = 0, s4 = a4_0;
+  int s = 0;
+  for (int tile = blockIdx.x; tile < total; tile += step) {
+    mbar_wait(c.tempty_bar(as), aph ^ 1u);       // epilogue has drained this accumulator
+    tc_fence_after();
+    const uint32_t tacc = c.tmem + as * acc_stride;
+    uint32_t accf = 0;
+    int u = 0, ch = 0;
+    for (int gi = 0; gi < groups; ++gi) {
+      mbar_wait(c.full_bar(s), ph);
+      tc_fence_after();
+      const int cnt = min(group, units - u);
+      uint32_t a_t = s4;
+      for (int g = 0; g < cnt; ++g) {
+        const int kn = ch == last_ch ? kk_last : KK;
+        if (c.issue) {
+#pragma unroll
+          for (int kk = 0; kk < KK; ++kk)
+            if (kk < kn)
+              umma2<F16>(tacc, a_t + 2 * kk, c.a_hi, a_t + ua4 + 2 * kk, c.b_hi, c.idesc,
+                         kk ? 1u : accf);
+        }
+        accf = 1u;
+        a_t += unit4;
+        ch = ch == last_ch ? 0 : ch + 1;
+      }
+      u += cnt;
+      if (c.issue) umma_commit(c.empty_bar(s));   // frees the smem slot when these MMAs retire
+      s4 += stage4;
+      if (++s == stages) { s = 0; ph ^= 1u; s4 = a4_0; }
+    }
+    if (c.issue) umma_commit(c.tfull_bar(as));    // accumulator complete
+    if ((as ^= 1u) == 0) aph ^= 1u;
+  }
+}
+
+template <bool F16>
+__device__ __forceinline__ void mma_role(const TcArgs &a, uint32_t base, uint32_t bars,
+                                         uint32_t tmem, bool issue) {
+  MmaCtx c;
+  c.base = base; c.bars = bars; c.tmem = tmem; c.issue = issue; c.stages = a.stages;
+  // instruction descriptor: D = F32 (bit 4), A/B format (bits 7, 10: 2 = TF32, 0 = F16),
+  // K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+  c.idesc = (1u << 4) | (F16 ? 0u : (2u << 7) | (2u << 10)) | ((uint32_t)(a.n_tile >> 3) << 17) |
+            ((uint32_t)(TILE_M >> 4) << 24);
+  c.b_hi = desc_hi32(a.sbo, a.layout_type);
+  c.a_hi = a.halo ? desc_hi32(a.halo_sbo, a.layout_type) : c.b_hi;
+  const int kk_n = a.kcb >> 5;     // one MMA consumes 32 bytes of K per row: 8 TF32 / 16 binary16
+  if (a.bres) {
+    const int key = a.ksize * 8 + a.kk_last;
+    switch (key) {
+      case 3 * 8 + 1: mma_bres<3, 1, F16>(a, c); break;
+      case 3 * 8 + 2: mma_bres<3, 2, F16>(a, c); break;
+      case 3 * 8 + 3: mma_bres<3, 3, F16>(a, c); break;
+      case 3 * 8 + 4: mma_bres<3, 4, F16>(a, c); break;
+      case 5 * 8 + 1: mma_bres<5, 1, F16>(a, c); break;
+      case 7 * 8 + 1: mma_bres<7, 1, F16>(a, c); break;
+      default: __trap();           // the host only selects resident weights for these shapes
+    }
+  } else if (a.halo) {
+    if (kk_n == 4) mma_halo<4, F16>(a, c);
+    else if (kk_n == 2) mma_halo<2, F16>(a, c);
+    else mma_halo<1, F16>(a, c);
+  } else {
+    if (kk_n == 4) mma_plain<4, F16>(a, c);
+    else if (kk_n == 2) mma_plain<2, F16>(a, c);
+    else mma_plain<1, F16>(a, c);
+  }
+}
+
 // ------------------------------------------------------------------ the kernel
 // Persistent: each CTA walks tiles blockIdx.x, +gridDim.x, ...; the smem ring and the two TMEM
 // accumulators keep the TMA producer, the MMA issuer and the epilogue warps of consecutive
@@ -642,145 +856,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    const bool leader = elect_one();
-    const int total = keep((int)(a.total_tiles)), step = keep((int)(gridDim.x));
-    // instruction descriptor: D = F32 (bit 4), A/B format (bits 7, 10: 2 = TF32, 0 = F16),
-    // K-major both, N >> 3 at bit 17, M >> 4 at bit 24
-    const bool f16 = a.f16_in != 0;
-    const uint32_t idesc = keep((uint32_t)((1u << 4) | (f16 ? 0u : (2u << 7) | (2u << 10)) |
-                           ((uint32_t)(a.n_tile >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24)));
-    // one MMA consumes 32 bytes of K per row: 8 TF32 or 16 binary16 values
-    const int kk_n = keep((int)((a.debug & 2) ? 0 : a.kcb / 32));
-    const int kk_last = keep((int)((a.debug & 2) ? 0 : a.kk_last));
-    // descriptor = constant high word | (smem address >> 4) in the low 14 bits
-    const uint64_t desc_hi = keep((uint64_t)(make_smem_desc(0, a.sbo, a.layout_type)));
-    const uint32_t acc_stride = keep((uint32_t)(a.acc_stride)), unit_a = keep((uint32_t)(a.unit_a)), unit_b = keep((uint32_t)(a.unit_b));
-    uint32_t as = 0, aph = 0;
-    if (a.halo) {
-      // A descriptor of tap (dy, dx): the window shifted by (dy * PW + dx) pixels; 8-row groups
-      // (= image rows of the 16x8 tile) are PW pixels apart (halo_sbo).  The start address is
-      // not aligned to the 1024-byte swizzle pattern: the tensor core swizzles on absolute
-      // shared-memory address bits, exactly as TMA wrote the window, so the base-offset field of
-      // the descriptor stays 0 (any other value reads the wrong 16-byte chunks; measured).
-      const int taps = keep((int)(a.ksize * a.ksize)), chunks = keep((int)(a.chunks_per_tap)), ksize = keep((int)(a.ksize));
-      const int sa_n = keep((int)(a.halo_sa)), sb_n = keep((int)(a.halo_sb)), pw = keep((int)(a.halo_pw));
-      const int bg = keep((int)(a.halo_bg));
-      const uint32_t stage_b = keep((uint32_t)(a.halo_bg * a.unit_b));
-      const uint64_t desc_a_hi = keep((uint64_t)(make_smem_desc(0, a.halo_sbo, a.layout_type)));
-      const uint32_t b_base = keep((uint32_t)(base + sa_n * unit_a)), pitch = keep((uint32_t)a.kcb);
-      int sa = 0, sb = 0;
-      uint32_t pha = 0, phb = 0;
-      if (a.bres) {
-        mbar_wait(full_bar(sa_n), 0u);               // the weights, once
-        tc_fence_after();
-        for (int tile = blockIdx.x; tile < total; tile += step) {
-          mbar_wait(tempty_bar(as), aph ^ 1u);
-          tc_fence_after();
-          const uint32_t tacc = tmem_base + as * acc_stride;
-          mbar_wait(full_bar(sa), pha);
-          tc_fence_after();
-          uint32_t row = base + sa * unit_a, b_addr = b_base, t = 0;
-          for (int dy = 0; dy < ksize; ++dy, row += (uint32_t)pw * pitch) {
-            uint32_t start = row;
-            for (int dx = 0; dx < ksize; ++dx, start += pitch, b_addr += unit_b, ++t) {
-              const uint64_t da = desc_a_hi | (uint64_t)(start >> 4);
-              const uint64_t db = desc_hi | (uint64_t)(b_addr >> 4);
-              const uint32_t tp = tacc, first = t;
-              if (leader) {
-                if (f16)
-                  for (int kk = 0; kk < kk_last; ++kk)
-                    umma_f16(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
-                else
-                  for (int kk = 0; kk < kk_last; ++kk)
-                    umma_tf32(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
-              }
-            }
-          }
-          if (leader) {
-            umma_commit(empty_bar(sa));
-            umma_commit(tfull_bar(as));
-          }
-          if (++sa == sa_n) { sa = 0; pha ^= 1u; }
-          if ((as ^= 1u) == 0) aph ^= 1u;
-        }
-      }
-      for (int tile = a.bres ? total : (int)blockIdx.x; tile < total; tile += step) {
-        mbar_wait(tempty_bar(as), aph ^ 1u);
-        tc_fence_after();
-        const uint32_t tacc = tmem_base + as * acc_stride;
-        for (int ch = 0; ch < chunks; ++ch) {
-          mbar_wait(full_bar(sa), pha);
-          tc_fence_after();
-          const uint32_t a_addr = base + sa * unit_a;
-          const int kn = ch == chunks - 1 ? kk_last : kk_n;
-          int dx = 0, dy = 0;
-          for (int t0 = 0; t0 < taps; t0 += bg) {          // one B stage = `bg` consecutive taps
-            const int sbar = sa_n + sb, cnt = min(bg, taps - t0);
-            mbar_wait(full_bar(sbar), phb);
-            tc_fence_after();
-            for (int g = 0; g < cnt; ++g) {
-              const uint32_t start = a_addr + (uint32_t)(dy * pw + dx) * pitch;
-              const uint64_t da = desc_a_hi | (uint64_t)(start >> 4);
-              const uint64_t db = desc_hi | (uint64_t)((b_base + sb * stage_b + g * unit_b) >> 4);
-              const uint32_t t = (uint32_t)(t0 + g);
-              const uint32_t tp = tacc, first = (uint32_t)ch | t;
-              if (leader) {
-                if (f16)
-                  for (int kk = 0; kk < kn; ++kk)
-                    umma_f16(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
-                else
-                  for (int kk = 0; kk < kn; ++kk)
-                    umma_tf32(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
-              }
-              if (++dx == ksize) { dx = 0; ++dy; }
-            }
-            if (leader) umma_commit(empty_bar(sbar));
-            if (++sb == sb_n) { sb = 0; phb ^= 1u; }
-          }
-          if (leader) umma_commit(empty_bar(sa));
-          if (++sa == sa_n) { sa = 0; pha ^= 1u; }
-        }
-        if (leader) umma_commit(tfull_bar(as));
-        if ((as ^= 1u) == 0) aph ^= 1u;
-      }
-    } else {
-      const int stages = keep((int)(a.stages)), group = keep((int)(a.group)), units = keep((int)(a.units));
-      const int last_ch = keep((int)(a.chunks_per_tap - 1));
-      int s = 0;
-      uint32_t ph = 0, stage_addr = base;
-      for (int tile = blockIdx.x; tile < total; tile += step) {
-        mbar_wait(tempty_bar(as), aph ^ 1u);       // epilogue has drained this accumulator
-        tc_fence_after();
-        const uint32_t tacc = tmem_base + as * acc_stride;
-        int u = 0, ch = 0;
-        for (int gi = 0; gi < groups; ++gi) {
-          mbar_wait(full_bar(s), ph);
-          tc_fence_after();
-          const int cnt = min(group, units - u);
-          uint32_t sa = stage_addr;
-          for (int g = 0; g < cnt; ++g, ++u, sa += unit_bytes) {
-            const uint64_t da = desc_hi | (uint64_t)(sa >> 4);
-            const uint64_t db = desc_hi | (uint64_t)((sa + unit_a) >> 4);
-            const int kn = ch == last_ch ? kk_last : kk_n;
-            const uint32_t tp = tacc, first = (uint32_t)u;
-            if (leader) {                        // +32 bytes along K per MMA: +2 in the >>4 field
-              if (f16)
-                for (int kk = 0; kk < kn; ++kk)
-                  umma_f16(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
-              else
-                for (int kk = 0; kk < kn; ++kk)
-                  umma_tf32(tp, da + 2u * kk, db + 2u * kk, idesc, (first | kk) ? 1u : 0u);
-            }
-            ch = ch == last_ch ? 0 : ch + 1;
-          }
-          if (leader) umma_commit(empty_bar(s));   // frees the smem slot when these MMAs retire
-          stage_addr += stage_bytes;
-          if (++s == stages) { s = 0; ph ^= 1u; stage_addr = base; }
-        }
-        if (leader) umma_commit(tfull_bar(as));    // accumulator complete
-        if ((as ^= 1u) == 0) aph ^= 1u;
-      }
-    }
+    const bool issue = elect_one() && !(a.debug & 2);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);   // provably warp-uniform
+    if (a.f16_in) mma_role<true>(a, base, bars, tb, issue);
+    else mma_role<false>(a, base, bars, tb, issue);
   } else if (a.tma_epi) {
     // ===== epilogue, TMA-store flavour (plain convs): each warp owns TMEM lanes 32q..32q+31 =
     // 32 output pixels, and walks its 32-column chunks.  Thread = pixel row: tcgen05.ld gives it
@@ -1247,9 +1326,11 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   }
   // halo mode: stride-1 k x k convs load the (16+k-1) x 16 pixel input window of a 16x8 tile
   // once per channel chunk and feed all k*k taps from it through shifted smem descriptors
-  // DCVC_TC_HALO: 0 off, 1 where it measured faster (3x3 with 64-byte channel chunks or wide N;
-  // both modes are MMA-issue-bound for small N, so the gain is the saved L2 traffic only), 2 all
-  static const int halo_on = getenv("DCVC_TC_HALO") ? atoi(getenv("DCVC_TC_HALO")) : 1;
+  // DCVC_TC_HALO: 0 off, 1 only 3x3 with 64-byte channel chunks or wide N (the selection made
+  // when the MMA issue loop was the bound), 2 (default) every stride-1 k >= 3 convolution: with
+  // the uniform issue loops the taps' L2 -> smem traffic is what is left, 7x7 64->32 f16 at 1080p
+  // 0.86 -> 0.68 ms, 3x3 48->48 fp32 0.39 -> 0.32 ms
+  static const int halo_on = getenv("DCVC_TC_HALO") ? atoi(getenv("DCVC_TC_HALO")) : 2;
   a.halo = halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 9 &&
            a.kcb >= (f16 ? 32 : 64) && d->pad == d->ksize / 2;
   if (a.halo && halo_on == 1)
@@ -1263,6 +1344,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   a.bres = bres_on && halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 7 &&
            d->pad == d->ksize / 2 && a.kcb >= (f16 ? 32 : 64) && a.chunks_per_tap == 1 &&
            tiles_n == 1 && bres_bytes <= 72u * 1024u && !d->res2.data && !d->out2.data &&
+           (d->ksize == 3 || a.kk_last == 1) &&     // shapes mma_bres<> is instantiated for
            (bres_on == 2 || (d->ksize == 3 && !d->shuffle) || (a.kk_last == 1 && a.n_tile <= 32));
   if (a.bres) a.halo = 1;
   const int halo_ph = TILE_M / 8 + d->ksize - 1;
