@@ -54,6 +54,9 @@ def parse_args():
     p.add_argument("--width", type=int, default=WIDTH)
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--pipeline", type=int, default=1,
+                   help="1: encoder and decoder on two CUDA streams, decoder one frame behind "
+                        "(dcvc_b200.pipeline); 0: the reference's strictly sequential frame loop")
     p.add_argument("--profile-out", default=None, help="write the per-kernel table (json) here")
     return p.parse_args()
 
@@ -243,13 +246,21 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     ops.set_conv_mode(args.conv_mode)
     H, W = args.height, args.width
-    i_net = dcvc_b200.IntraNoAR(stream_part=args.stream_part, coder_mode=args.coder)
-    p_net = dcvc_b200.DMC(stream_part=args.stream_part, coder_mode=args.coder)
-    i_net.load_state_dict(arch.synth_state_dict(arch.intra_spec(), 0))
-    p_net.load_state_dict(arch.synth_state_dict(arch.dmc_spec(), 100))
-    i_net, p_net = i_net.to(dev).eval(), p_net.to(dev).eval()
-    i_net.update(force=True)
-    p_net.update(force=True)
+
+    def make_nets():
+        i = dcvc_b200.IntraNoAR(stream_part=args.stream_part, coder_mode=args.coder)
+        p = dcvc_b200.DMC(stream_part=args.stream_part, coder_mode=args.coder)
+        i.load_state_dict(arch.synth_state_dict(arch.intra_spec(), 0))
+        p.load_state_dict(arch.synth_state_dict(arch.dmc_spec(), 100))
+        i, p = i.to(dev).eval(), p.to(dev).eval()
+        i.update(force=True)
+        p.update(force=True)
+        return i, p
+
+    i_net, p_net = make_nets()
+    # pipelined mode: the decoder is a second model instance (own weights copy, coder context and
+    # dpb), as it would be in a separate process; the two only share the byte stream
+    i_dec, p_dec = make_nets() if args.pipeline else (None, None)
 
     nf = 8
     host = synth.synth_frames(nf, H, W, seed=rank).pin_memory()      # [nf,3,H,W] fp32 in [0,1]
@@ -264,17 +275,29 @@ def main():
         torch.cuda.synchronize(dev)
 
     def timed(loop_body):
-        seq = Sequence(i_net, p_net, H, W)
+        if args.pipeline:
+            from dcvc_b200.pipeline import EncDecPipeline
+            seq = EncDecPipeline(i_net, p_net, i_dec, p_dec, INTRA_PERIOD, Q_IN_CKPT, Q_INDEX, dev)
+            tstream = seq.enc_stream
+        else:
+            seq = Sequence(i_net, p_net, H, W)
+            tstream = torch.cuda.current_stream(dev)
         with torch.no_grad():
             for s in range(args.warmup):
                 loop_body(seq, s)
+            if args.pipeline:
+                seq.flush()                      # the timed region holds K encodes and K decodes
             barrier()
             l0 = _lib.launch_count()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
+            e0.record(tstream)
             for s in range(args.warmup, total):
                 loop_body(seq, s)
-            e1.record()
+            if args.pipeline:
+                last = seq.flush()
+                loop_body(None, last)            # end-of-run hook (pending metric reads)
+                seq.join(tstream)                # the encoder stream waits for the decoder's
+            e1.record(tstream)
             barrier()
         ms = e0.elapsed_time(e1)
         if world > 1:
@@ -283,18 +306,51 @@ def main():
             ms = float(t.item())
         return ms, _lib.launch_count() - l0, seq
 
-    stats = {"sse": 0.0, "n": 0}
+    stats = {"sse": 0.0, "n": 0, "pending": [], "prev_x": None}
 
     def body_resident(seq, s):
-        seq.step(resident[order[s % len(order)]])
+        if seq is None:
+            return
+        if args.pipeline:
+            seq.push(resident[order[s % len(order)]])
+        else:
+            seq.step(resident[order[s % len(order)]])
+
+    def _metric(x, x_hat, dstream):
+        # the step's result read back by the host: MSE of the decoded frame, computed on the
+        # decoder's stream; .item() is deferred by one step so the read never stalls the pipeline
+        with torch.cuda.stream(dstream):
+            x.record_stream(dstream)
+            stats["pending"].append(torch.mean((x - x_hat[:, :, :H, :W]) ** 2))
+
+    def _drain(keep):
+        while len(stats["pending"]) > keep:
+            stats["sse"] += float(stats["pending"].pop(0).item())     # D2H of the step's metric
+            stats["n"] += 1
 
     def body_e2e(seq, s):
+        if seq is None:                           # end of a pipelined run: s = last decoded frame
+            if s is not None and stats["prev_x"] is not None:
+                _metric(stats["prev_x"], s, stats["dstream"])
+            stats["prev_x"] = None
+            _drain(0)
+            return
         k = order[s % len(order)]
-        x = host[k:k + 1].to(dev, non_blocking=True)                 # H2D from pinned memory
-        x_hat, _ = seq.step(pad_frame(x))
-        mse = torch.mean((x - x_hat[:, :, :H, :W]) ** 2)
-        stats["sse"] += float(mse.item())                            # D2H of the step's metric
-        stats["n"] += 1
+        if not args.pipeline:
+            x = host[k:k + 1].to(dev, non_blocking=True)             # H2D from pinned memory
+            x_hat, _ = seq.step(pad_frame(x))
+            stats["pending"].append(torch.mean((x - x_hat[:, :, :H, :W]) ** 2))
+            _drain(0)
+            return
+        with torch.cuda.stream(seq.enc_stream):
+            x = host[k:k + 1].to(dev, non_blocking=True)             # H2D from pinned memory
+            xp = pad_frame(x)
+        stats["dstream"] = seq.dec_stream
+        _, decoded = seq.push(xp)                 # returns with the encoder stream synchronised
+        if decoded is not None and stats["prev_x"] is not None:
+            _metric(stats["prev_x"], decoded, seq.dec_stream)
+        stats["prev_x"] = x
+        _drain(1)
 
     clocks = ClockSampler(local_rank)
     clocks.start()
@@ -318,7 +374,8 @@ def main():
     # per-kernel profile of one P frame (CUDA events per launch, outside the timed region)
     roofline, table = None, None
     if rank == 0:
-        roofline, table = profile_step(seq, resident[order[total % len(order)]], args)
+        pseq = Sequence(i_net, p_net, H, W) if args.pipeline else seq
+        roofline, table = profile_step(pseq, resident[order[total % len(order)]], args)
 
     if rank == 0:
         cpu = None if args.no_cpu_baseline else cpu_oracle_fps()
@@ -328,7 +385,11 @@ def main():
                 "dtype": "tf32" if args.conv_mode == 1 else "f32", "data": "synthetic",
                 "config": {"workload": workload_text(args),
                            "l2": "activations per layer (>=100 MB at 1080p) exceed the 126 MB L2",
-                           "conv_mode": args.conv_mode, "coder": args.coder},
+                           "conv_mode": args.conv_mode, "coder": args.coder,
+                           "schedule": ("encoder and decoder are two model instances on two CUDA "
+                                        "streams, the decoder one frame behind the encoder; every "
+                                        "frame is encoded and decoded inside the timed region")
+                           if args.pipeline else "sequential encode -> decode per frame"},
                 "clocks": clock_info, "gpu_launches": int(launches), "e2e": e2e,
                 "roofline": roofline, "cpu_baseline": cpu,
                 "bits_per_frame": bits_per_frame,

@@ -31,6 +31,12 @@ class Conv(ctypes.Structure):
                 ("res1_f16", c_int32)]
 
 
+class Ffn(ctypes.Structure):
+    _fields_ = [("inp", View), ("out", View), ("w1", c_void_p), ("w2", c_void_p),
+                ("b1", c_void_p), ("b2", c_void_p), ("scale", c_void_p),
+                ("slope1", c_float), ("slope2", c_float), ("out_f16", c_int32)]
+
+
 class Quad(ctypes.Structure):
     _fields_ = [("y", View), ("params", View), ("prior", View), ("y_hat", View), ("y_out", View),
                 ("edges", c_void_p), ("step", c_int32), ("distribution", c_int32)]
@@ -54,6 +60,8 @@ SIGNATURES = {
                                       ctypes.POINTER(c_int)]),
     "dcvc_conv_tc_geometry16": (c_int, [c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
                                         ctypes.POINTER(c_int)]),
+    "dcvc_ffn": (c_int, [ctypes.POINTER(Ffn), c_void_p]),
+    "dcvc_ffn_eligible": (c_int, [c_int, c_int64]),
     "dcvc_dwconv3x3": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p]),
     "dcvc_dwconv3x3_f16": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p]),
     "dcvc_nchw_to_nhwc": (c_int, [c_void_p, VP, c_void_p]),

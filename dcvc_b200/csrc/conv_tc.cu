@@ -877,7 +877,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int nchunks = (a.n_tile + 31) >> 5;
     const int tw_mask = a.tw - 1, tw_shift = 31 - __clz(a.tw);
     const int bx = (q * 32) & tw_mask, by = (q * 32) >> tw_shift;
-    const bool has_res = a.res1.data != nullptr;
+    const bool has_res = a.res1.data != nullptr, has_res2 = a.res2.data != nullptr;
+    const int wb = a.tw < 32 ? a.tw : 32, wb_mask = wb - 1, wb_shift = 31 - __clz(wb);
     const uint32_t res_bytes = a.f16_res ? 2048u : 4096u;
     const bool mixed = has_res && (a.f16_res != a.f16_out);   // residual / result rows differ in pitch
     const uint32_t row_off = (uint32_t)lane * 128u, sw = (uint32_t)(lane & 7);
@@ -949,6 +950,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           }
           // rows of the two element sizes overlap other lanes' rows: everyone reads first
           if (mixed) __syncwarp();
+        }
+        if (has_res2) {
+          // second residual (fp32 view): the thread's own pixel row, eight 16-byte loads; rows
+          // outside the image or the real channels are skipped (their results are clipped by the
+          // tensor-map store anyway)
+          const int px = x0 + (lane & wb_mask), py = y0 + (lane >> wb_shift);
+          if (px < a.wout && py < a.hout) {
+            const float4 *r2 = reinterpret_cast<const float4 *>(
+                a.res2.data + ((size_t)py * a.res2.w + px) * a.res2.cstride + a.res2.coff + c0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (c0 + 4 * j < a.cout_w) {
+                const float4 u = __ldg(r2 + j);
+                v[4 * j] += u.x; v[4 * j + 1] += u.y; v[4 * j + 2] += u.z; v[4 * j + 3] += u.w;
+              }
+          }
         }
         if (a.scale) {
 #pragma unroll
@@ -1284,7 +1301,7 @@ bool conv_tc_ok(const dcvc_conv *d) {
     return false;
   // binary16 output / residual go through the TMA-store epilogue only
   if ((d->out_f16 || (d->res1_f16 && d->res1.data)) &&
-      (tc_fast_mode(d) != 1 || d->res2.data || d->out2.data))
+      (tc_fast_mode(d) != 1 || d->out2.data))
     return false;
   if (d->shuffle == 2 && tc_fast_mode(d) != 3) return false;   // planar packing needs the lean path
   const int ho = (d->in.h + 2 * d->pad - d->ksize) / d->stride + 1;
@@ -1343,7 +1360,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   const uint32_t bres_bytes = (uint32_t)(d->ksize * d->ksize) * (uint32_t)ru(a.n_tile * a.kcb, 1024);
   a.bres = bres_on && halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 7 &&
            d->pad == d->ksize / 2 && a.kcb >= (f16 ? 32 : 64) && a.chunks_per_tap == 1 &&
-           tiles_n == 1 && bres_bytes <= 72u * 1024u && !d->res2.data && !d->out2.data &&
+           tiles_n == 1 && bres_bytes <= 72u * 1024u && !d->out2.data &&
            (d->ksize == 3 || a.kk_last == 1) &&     // shapes mma_bres<> is instantiated for
            (bres_on == 2 || (d->ksize == 3 && !d->shuffle) || (a.kk_last == 1 && a.n_tile <= 32));
   if (a.bres) a.halo = 1;
@@ -1407,7 +1424,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
   // TMA-store epilogue: plain convs with at most one residual, views TMA-addressable
-  a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res) && a.fast == 1 && !d->res2.data && !d->out2.data;
+  a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res) && a.fast == 1 && !d->out2.data &&
+              (!d->res2.data || d->res1.data);      // a second residual rides on direct loads
   int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi
             : a.tma_epi ? (ctas == 1 ? 8 : 4) : (ctas == 1 ? 16 : 8);
   while (epi > 4 && epi / 4 > nchunks) epi >>= 1;

@@ -1,0 +1,449 @@
+// ffn_tc.cu -- fused ConvFFN of a DepthConvBlock (reference DCVC-DC/src/models/layers.py:166-179,
+// called from DepthConvBlock.forward :199-209) as ONE two-GEMM tcgen05 kernel for sm_100a:
+//
+//     out = ( t + lrelu( W2 . lrelu( W1 . t + b1, s1 ) + b2, s2 ) ) * scale
+//
+// t is a binary16 NHWC activation with C in {32, 48, 64} channels, W1 is the 1x1 up-projection
+// (C -> 4C), W2 the 1x1 down-projection (4C -> C).  Unfused this is two HBM-bound kernels that
+// write and re-read the 4C-wide hidden tensor (10C of the 14C..16C bytes per pixel); here the
+// hidden tile never leaves the SM:
+//
+//   TMA:   t tile (128 pixels x 64 K-padded binary16, 128B swizzle) -> smem ring of 2
+//   MMA1:  acc1[128 x 4C] (TMEM, fp32) = t . W1^T        ceil(C/16) x UTCHMMA, N = 4C
+//   EPI1:  8 warps: tcgen05.ld -> + b1 -> LeakyReLU -> binary16 -> smem H in the K-major
+//          128B-swizzled layout an A operand needs (4C/64 chunks of 16 KB)
+//   MMA2:  acc2[128 x C] (TMEM) = H . W2^T               4C/16 x UTCHMMA, N = C
+//   EPI2:  4 warps: tcgen05.ld -> + b2 -> LeakyReLU -> + t (read back from the smem A tile)
+//          -> * scale -> 128-bit global stores (fp32 or binary16 rows)
+//
+// Both weight matrices stay resident in shared memory (<= 64 KB).  Persistent CTAs, one per SM;
+// the MMA warp issues MMA2(i) then MMA1(i+1), so EPI1(i+1) and EPI2(i) overlap.
+// tcgen05.commit tracks every earlier MMA of the issuing thread, which orders the reuse of acc1
+// and H without extra barriers (see the protocol notes at the roles).
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <stdlib.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int TILE_M = 128;
+constexpr int EPI1_WARPS = 8, EPI2_WARPS = 4;
+constexpr int THREADS = 64 + 32 * (EPI1_WARPS + EPI2_WARPS);
+constexpr uint32_t SPIN_LIMIT = 1u << 26;
+constexpr uint32_t A_BYTES = TILE_M * 128;       // one t tile: 128 rows x 64 binary16
+constexpr uint32_t ACC2_COL = 256;               // acc1 at column 0 (<= 256 columns), acc2 here
+
+struct FfnArgs {
+  dcvc_view out;
+  const float *b1, *b2, *scale;
+  float slope1, slope2;
+  int c, n1, pixels, tiles, out_f16, kk1, nch;
+  uint32_t w1_off, w2_off, h_off, vec_off, bar_off;   // from the 1024-aligned base; A ring at 0
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+// bounded waits: a protocol bug must fault, not hang the GPU
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins)
+    if (spins > SPIN_LIMIT) __trap();
+}
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity, int lane) {
+  if (lane == 0) {
+    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
+      __nanosleep(32);
+      if (spins > SPIN_LIMIT) __trap();
+    }
+  }
+  __syncwarp();
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void fence_async_smem() {   // generic-proxy smem writes -> async proxy
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
+                                         uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\tmov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+               ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t *r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_wait_ld() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
+  const __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t *>(&h);
+}
+__device__ __forceinline__ float2 unpack_h2(uint32_t u) {
+  return __half22float2(*reinterpret_cast<const __half2 *>(&u));
+}
+__device__ __forceinline__ float lrelu01(float v, float slope) { return fmaxf(v, v * slope); }
+__device__ __forceinline__ uint32_t desc_lo32(uint32_t addr) { return (addr >> 4) | 0x10000u; }
+
+__global__ void __launch_bounds__(THREADS, 1)
+ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w1,
+              const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ FfnArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t *const base_g = smem_raw + (base - raw);
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t bars = base + a.bar_off;
+  // barriers: 0,1 a_full | 2,3 a_empty | 4 w_full | 5 acc1_full | 6 h_full | 7 acc2_full | 8 acc2_empty
+  auto bar = [&](int i) { return bars + 8u * i; };
+  if (threadIdx.x == 0) {
+    mbar_init(bar(0), 1); mbar_init(bar(1), 1);
+    mbar_init(bar(2), EPI2_WARPS); mbar_init(bar(3), EPI2_WARPS);
+    mbar_init(bar(4), 1); mbar_init(bar(5), 1);
+    mbar_init(bar(6), EPI1_WARPS);
+    mbar_init(bar(7), 1);
+    mbar_init(bar(8), EPI2_WARPS);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  {  // b1 | b2 | scale as smem vectors (broadcast reads in the epilogues)
+    float *vec = reinterpret_cast<float *>(base_g + a.vec_off);
+    for (int i = threadIdx.x; i < a.n1; i += blockDim.x) vec[i] = __ldg(a.b1 + i);
+    for (int i = threadIdx.x; i < 64; i += blockDim.x) {
+      vec[a.n1 + i] = i < a.c ? __ldg(a.b2 + i) : 0.f;
+      vec[a.n1 + 64 + i] = (a.scale && i < a.c) ? __ldg(a.scale + i) : 1.f;
+    }
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32(&tmem_slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int total = a.tiles, step = gridDim.x;
+
+  if (warp == 0) {
+    // ===== TMA producer: weights once, then the t tiles through a ring of two
+    const bool leader = elect_one();
+    if (leader) {
+      mbar_expect_tx(bar(4), (uint32_t)a.n1 * 128u + (uint32_t)a.nch * (uint32_t)a.c * 128u);
+      tma_load_2d(base + a.w1_off, &map_w1, bar(4), 0, 0);
+      for (int j = 0; j < a.nch; ++j)
+        tma_load_2d(base + a.w2_off + (uint32_t)j * (uint32_t)a.c * 128u, &map_w2, bar(4), 0, j * a.c);
+    }
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
+      const uint32_t s = lt & 1u;
+      mbar_wait(bar(2 + s), ((lt >> 1) & 1u) ^ 1u);       // EPI2 has read the residual of tile lt-2
+      if (leader) {
+        mbar_expect_tx(bar(s), A_BYTES);
+        tma_load_2d(base + s * A_BYTES, &map_a, bar(s), 0, tile * TILE_M);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer.  Order: MMA1(0) | MMA2(i), MMA1(i+1) ...
+    //  * MMA1(i+1) overwrites acc1: EPI1(i) has read it (h_full(i) was waited on).
+    //  * EPI1(i+1) overwrites H: it waits acc1_full(i+1), a commit issued after MMA2(i), and a
+    //    commit completes only when every earlier MMA of this thread has -- so MMA2(i) is done.
+    //  * MMA2(i+1) overwrites acc2: waits acc2_empty (EPI2(i) has read it).
+    const bool issue = elect_one();
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);      // SBO 1024 B, 128B swizzle
+    const uint32_t idesc1 = (1u << 4) | ((uint32_t)(a.n1 >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
+    const uint32_t idesc2 = (1u << 4) | ((uint32_t)(a.c >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
+    const uint32_t a_lo0 = desc_lo32(base), w1_lo = desc_lo32(base + a.w1_off),
+                   w2_lo = desc_lo32(base + a.w2_off), h_lo = desc_lo32(base + a.h_off);
+    const uint32_t w2_step = ((uint32_t)a.c * 128u) >> 4, acc2 = tb + ACC2_COL;
+    const int kk1 = a.kk1, nch = a.nch;
+    mbar_wait(bar(4), 0u);
+    auto mma1 = [&](uint32_t lt) {
+      const uint32_t s = lt & 1u;
+      mbar_wait(bar(s), (lt >> 1) & 1u);
+      tc_fence_after();
+      if (issue) {
+        const uint32_t a_lo = a_lo0 + s * (A_BYTES >> 4);
+        for (int kk = 0; kk < kk1; ++kk)
+          umma_f16(tb, a_lo + 2 * kk, w1_lo + 2 * kk, hi, idesc1, kk ? 1u : 0u);
+        umma_commit(bar(5));
+      }
+    };
+    uint32_t lt = 0;
+    if ((int)blockIdx.x < total) mma1(0);
+    for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
+      mbar_wait(bar(6), lt & 1u);                          // H(lt) written
+      mbar_wait(bar(8), (lt & 1u) ^ 1u);                   // acc2 drained by EPI2(lt-1)
+      tc_fence_after();
+      if (issue) {
+        for (int j = 0; j < nch; ++j) {
+          const uint32_t hj = h_lo + (uint32_t)j * (16384u >> 4), wj = w2_lo + (uint32_t)j * w2_step;
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            umma_f16(acc2, hj + 2 * kk, wj + 2 * kk, hi, idesc2, (j | kk) ? 1u : 0u);
+        }
+        umma_commit(bar(7));
+      }
+      if (tile + step < total) mma1(lt + 1);
+    }
+  } else if (warp < 2 + EPI1_WARPS) {
+    // ===== EPI1: acc1 -> + b1 -> LeakyReLU -> binary16 -> H (A operand of MMA2)
+    const int e = warp - 2, q = warp & 3, half = e >> 2;
+    const int ng = a.n1 >> 5;                              // 32-column groups
+    const uint32_t r = (uint32_t)(q * 32 + lane), sw = r & 7u;
+    uint8_t *const hrow = base_g + a.h_off + r * 128u;
+    const float4 *const b1v = reinterpret_cast<const float4 *>(base_g + a.vec_off);
+    const float slope = a.slope1;
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
+      mbar_wait_warp(bar(5), lt & 1u, lane);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
+      for (int g = half; g < ng; g += 2) {
+        uint32_t u[32];
+        tmem_ld16_nowait(trow + (uint32_t)g * 32u, u);
+        tmem_ld16_nowait(trow + (uint32_t)g * 32u + 16u, u + 16);
+        tmem_wait_ld();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 bb = b1v[g * 8 + j];
+          v[4 * j] = lrelu01(__uint_as_float(u[4 * j]) + bb.x, slope);
+          v[4 * j + 1] = lrelu01(__uint_as_float(u[4 * j + 1]) + bb.y, slope);
+          v[4 * j + 2] = lrelu01(__uint_as_float(u[4 * j + 2]) + bb.z, slope);
+          v[4 * j + 3] = lrelu01(__uint_as_float(u[4 * j + 3]) + bb.w, slope);
+        }
+        uint8_t *const chunk = hrow + (uint32_t)(g >> 1) * 16384u;
+        const uint32_t i0 = (uint32_t)(g & 1) * 4u;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          uint4 pk;
+          pk.x = pack_h2(v[8 * i], v[8 * i + 1]);     pk.y = pack_h2(v[8 * i + 2], v[8 * i + 3]);
+          pk.z = pack_h2(v[8 * i + 4], v[8 * i + 5]); pk.w = pack_h2(v[8 * i + 6], v[8 * i + 7]);
+          *reinterpret_cast<uint4 *>(chunk + (((i0 + (uint32_t)i) ^ sw) << 4)) = pk;
+        }
+      }
+      fence_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(6));
+    }
+  } else {
+    // ===== EPI2: acc2 -> + b2 -> LeakyReLU -> + t -> * scale -> global
+    const int q = warp & 3;
+    const uint32_t r = (uint32_t)(q * 32 + lane), sw = r & 7u;
+    const float4 *const b2v = reinterpret_cast<const float4 *>(base_g + a.vec_off) + (a.n1 >> 2);
+    const float4 *const scv = b2v + 16;
+    const float slope = a.slope2;
+    const int c = a.c, ng = (c + 31) >> 5;
+    const bool has_scale = a.scale != nullptr;
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
+      const uint32_t s = lt & 1u;
+      mbar_wait_warp(bar(7), lt & 1u, lane);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + ACC2_COL + ((uint32_t)(q * 32) << 16);
+      uint32_t u[64];
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        if (g * 16 < c) tmem_ld16_nowait(trow + (uint32_t)g * 16u, u + 16 * g);
+      tmem_wait_ld();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(8));                  // acc2 may be overwritten
+      // residual: this pixel's row of the t tile, 16-byte slot i = channels 8i..8i+7 (the TMA
+      // write is made visible to this warp by observing the stage's own barrier; its phase
+      // cannot advance before this warp releases the stage below)
+      mbar_wait_warp(bar(s), (lt >> 1) & 1u, lane);
+      const uint8_t *const arow = base_g + s * A_BYTES + r * 128u;
+      uint4 res[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (i * 8 < c) res[i] = *reinterpret_cast<const uint4 *>(arow + (((uint32_t)i ^ sw) << 4));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(2 + s));              // the A stage may be refilled
+      const int64_t p = (int64_t)tile * TILE_M + r;
+      if (p < a.pixels) {
+        const size_t o = (size_t)p * a.out.cstride + a.out.coff;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (i * 8 >= c) continue;
+          float v[8];
+          const float4 ba = b2v[2 * i], bb = b2v[2 * i + 1];
+          const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+          const uint32_t rw[4] = {res[i].x, res[i].y, res[i].z, res[i].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 t2 = unpack_h2(rw[j]);
+            v[2 * j] = lrelu01(__uint_as_float(u[8 * i + 2 * j]) + bias[2 * j], slope) + t2.x;
+            v[2 * j + 1] = lrelu01(__uint_as_float(u[8 * i + 2 * j + 1]) + bias[2 * j + 1], slope) + t2.y;
+          }
+          if (has_scale) {
+            const float4 sa = scv[2 * i], sb = scv[2 * i + 1];
+            v[0] *= sa.x; v[1] *= sa.y; v[2] *= sa.z; v[3] *= sa.w;
+            v[4] *= sb.x; v[5] *= sb.y; v[6] *= sb.z; v[7] *= sb.w;
+          }
+          if (a.out_f16) {
+            uint4 pk;
+            pk.x = pack_h2(v[0], v[1]); pk.y = pack_h2(v[2], v[3]);
+            pk.z = pack_h2(v[4], v[5]); pk.w = pack_h2(v[6], v[7]);
+            *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(a.out.data) + o + 8 * i) = pk;
+          } else {
+            float4 *dst = reinterpret_cast<float4 *>(a.out.data + o + 8 * i);
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;"
+                 ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  });
+  return fn;
+}
+
+// binary16 matrix [rows][cols] with row pitch `pitch_bytes`, box (64 columns, box_rows), 128B swizzle
+int map_2d(const void *ptr, uint64_t cols, uint64_t rows, uint64_t pitch_bytes, uint32_t box_rows,
+           CUtensorMap *out) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return dcvc_fail(DCVC_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {pitch_bytes};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(ptr), dims, strides,
+                   box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return dcvc_fail(DCVC_ERR_CUDA, "cuTensorMapEncodeTiled(ffn) failed: %d", (int)r);
+  return DCVC_OK;
+}
+
+}  // namespace
+
+extern "C" int dcvc_ffn_eligible(int channels, int64_t pixels) {
+  return (channels == 32 || channels == 48 || channels == 64) && pixels >= 4 * TILE_M;
+}
+
+extern "C" int dcvc_ffn(const dcvc_ffn_desc *d, void *stream) {
+  if (!d || !view_ok(&d->in) || !view_ok(&d->out) || !d->w1 || !d->w2 || !d->b1 || !d->b2)
+    return dcvc_fail(DCVC_ERR_ARG, "ffn: bad arguments");
+  const int c = d->in.c;
+  const int64_t pixels = (int64_t)d->in.h * d->in.w;
+  if (!dcvc_ffn_eligible(c, pixels) || d->out.c != c || d->out.h != d->in.h || d->out.w != d->in.w)
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "ffn: unsupported shape (c %d, %lld pixels)", c, (long long)pixels);
+  auto al = [](const dcvc_view &v, int e) {      // whole 16-byte groups of e-byte elements
+    const int m = 16 / e - 1;
+    return ((v.cstride | v.coff) & m) == 0 && (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0;
+  };
+  if (!al(d->in, 2) || !al(d->out, d->out_f16 ? 2 : 4) ||
+      ((reinterpret_cast<uintptr_t>(d->w1) | reinterpret_cast<uintptr_t>(d->w2)) & 15u))
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "ffn: views / weights must be 16-byte aligned");
+  FfnArgs a{};
+  a.out = d->out; a.b1 = d->b1; a.b2 = d->b2; a.scale = d->scale;
+  a.slope1 = d->slope1; a.slope2 = d->slope2;
+  a.c = c; a.n1 = 4 * c; a.pixels = (int)pixels; a.tiles = cdiv(pixels, TILE_M);
+  a.out_f16 = d->out_f16; a.kk1 = (c + 15) / 16; a.nch = a.n1 / 64;
+  a.w1_off = 2u * A_BYTES;
+  a.w2_off = a.w1_off + (uint32_t)a.n1 * 128u;
+  a.h_off = a.w2_off + (uint32_t)a.nch * (uint32_t)c * 128u;
+  a.vec_off = a.h_off + (uint32_t)a.nch * 16384u;
+  a.bar_off = a.vec_off + ((((uint32_t)(a.n1 + 128) * 4u) + 15u) & ~15u);
+  const size_t smem = 1024 + (size_t)a.bar_off + 128;
+  if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "ffn: smem %zu too large", smem);
+  CUtensorMap ma, m1, m2;
+  const __half *in = reinterpret_cast<const __half *>(d->in.data) + d->in.coff;
+  int rc = map_2d(in, (uint64_t)c, (uint64_t)pixels, (uint64_t)d->in.cstride * 2, TILE_M, &ma);
+  if (rc) return rc;
+  if ((rc = map_2d(d->w1, 64, (uint64_t)a.n1, 128, (uint32_t)a.n1, &m1))) return rc;
+  if ((rc = map_2d(d->w2, 64, (uint64_t)a.nch * c, 128, (uint32_t)c, &m2))) return rc;
+  static bool attr_set = false;
+  static int num_sms = 0;
+  if (!attr_set) {
+    DCVC_CUDA(cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   226 * 1024));
+    int dev = 0;
+    DCVC_CUDA(cudaGetDevice(&dev));
+    DCVC_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+    attr_set = true;
+  }
+  const int grid = a.tiles < num_sms ? a.tiles : num_sms;
+  ffn_tc_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(ma, m1, m2, a);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}

@@ -99,6 +99,22 @@ class Net:
             self._conv[key] = r
         return r
 
+    def ffn(self, p):
+        """Packed weights of the fused ConvFFN (dcvc_ffn) of block prefix p: W1 binary16
+        [4C][64] (K zero-padded), W2 binary16 [4C/64][C][64], fp32 biases."""
+        r = self._misc.get(("ffn", p))
+        if r is None:
+            w1 = self.sd[p + ".conv.0.weight"]          # [4C, C, 1, 1]
+            w2 = self.sd[p + ".conv.2.weight"]          # [C, 4C, 1, 1]
+            n1, c = w1.shape[0], w1.shape[1]
+            p1 = torch.zeros((n1, 64), dtype=torch.float16, device=w1.device)
+            p1[:, :c] = w1.reshape(n1, c).to(torch.float16)
+            p2 = w2.reshape(c, n1 // 64, 64).permute(1, 0, 2).to(torch.float16).contiguous()
+            r = (p1.contiguous(), self.sd[p + ".conv.0.bias"].contiguous(), p2,
+                 self.sd[p + ".conv.2.bias"].contiguous())
+            self._misc[("ffn", p)] = r
+        return r
+
     def dw(self, name):
         r = self._dw.get(name)
         if r is None:
@@ -148,6 +164,9 @@ def dcb(net, p, x, out=None, scale=None, f16_out=False):
     `* q` rides on the last epilogue.  f16_out: the caller is the only reader of the result and
     reads it with a convolution (block chains)."""
     t = depth_conv(net, p + ".block.0", x, f16_out=True)
+    if ops.ffn_ok(t):
+        w1, b1, w2, b2 = net.ffn(p + ".block.1")
+        return ops.ffn(t, w1, b1, w2, b2, 0.1, 0.1, scale=scale, out=out, f16_out=f16_out)
     u = ops.conv(t, net.cw(p + ".block.1.conv.0"), act=0.1, f16_out=True)
     return ops.conv(u, net.cw(p + ".block.1.conv.2"), act=0.1, res=t, scale=scale, out=out,
                     f16_out=f16_out)

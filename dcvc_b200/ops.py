@@ -133,6 +133,33 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     return out
 
 
+# fused ConvFFN (dcvc_ffn): DCVC_FFN=0 keeps the two separate 1x1 convolutions
+FFN = _os.environ.get("DCVC_FFN", "1") != "0"
+
+
+def ffn_ok(x):
+    """May DepthConvBlock's ConvFFN on the binary16 activation x run as the fused kernel?"""
+    return (FFN and CONV_MODE == 1 and x.f16 and
+            bool(_lib.lib().dcvc_ffn_eligible(x.c, x.h * x.w)))
+
+
+def ffn(x, w1, b1, w2, b2, slope1=0.1, slope2=0.1, scale=None, out=None, f16_out=False,
+        stream=None):
+    """out = (x + lrelu(W2 . lrelu(W1 . x + b1) + b2)) * scale in one kernel (dcvc_ffn)."""
+    if out is None:
+        out = Act.new(x.h, x.w, x.c, x.device, f16=f16_out and f16_ok(x.h, x.w, x.c))
+    d = _lib.Ffn()
+    d.inp, d.out = x.view(), out.view()
+    d.w1, d.w2, d.b1, d.b2 = w1.data_ptr(), w2.data_ptr(), b1.data_ptr(), b2.data_ptr()
+    d.scale = scale.data_ptr() if scale is not None else None
+    d.slope1, d.slope2, d.out_f16 = slope1, slope2, int(out.f16)
+    flops = 2 * x.h * x.w * x.c * 4 * x.c * 2
+    with _Prof(f"ffn {x.c}->{4 * x.c}->{x.c} @{x.h}x{x.w} [tcgen05] i" + ("o" if out.f16 else "O"),
+               flops, _nb(x, out) + 2 * (w1.numel() + w2.numel())):
+        _lib.check(_lib.lib().dcvc_ffn(ctypes.byref(d), _stream(stream)))
+    return out
+
+
 def dwconv3x3(x, w, b, out=None, stream=None):
     if out is None:
         out = Act.new(x.h, x.w, x.c, x.device, f16=x.f16)

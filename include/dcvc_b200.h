@@ -107,6 +107,25 @@ int dcvc_conv_tc_geometry(int cout_w, int cin, int *n_pad, int *cin_pad, int *kc
 /* the same for weight_tc16: kc in {64, 32, 16} binary16 elements */
 int dcvc_conv_tc_geometry16(int cout_w, int cin, int *n_pad, int *cin_pad, int *kc);
 
+/* Fused ConvFFN of a DepthConvBlock (reference DCVC-DC/src/models/layers.py:166-179, called from
+ * DepthConvBlock.forward :199-209):
+ *     out = (in + lrelu(W2 . lrelu(W1 . in + b1, slope1) + b2, slope2)) * scale
+ * as one two-GEMM tcgen05 kernel; the 4C-wide hidden activation stays in shared memory.
+ * in: binary16 view, c in {32, 48, 64}, >= 512 pixels (dcvc_ffn_eligible); out: fp32 or binary16
+ * view (out_f16) of the same shape.  w1: binary16 [4c][64] (row n = output channel of the 1x1
+ * up-projection conv.0, K zero-padded to 64); w2: binary16 [4c/64][c][64] (chunk j holds input
+ * channels 64j..64j+63 of the down-projection conv.2, row n = its output channel); b1 [4c],
+ * b2 [c], scale [c] or NULL: fp32.  Replaces the two dcvc_conv2d calls of the unfused block. */
+typedef struct dcvc_ffn_desc {
+  dcvc_view in, out;
+  const void *w1, *w2;
+  const float *b1, *b2, *scale;
+  float slope1, slope2;
+  int32_t out_f16;
+} dcvc_ffn_desc;
+int dcvc_ffn(const dcvc_ffn_desc *d, void *stream);
+int dcvc_ffn_eligible(int channels, int64_t pixels);
+
 /* depthwise 3x3, pad 1, stride 1 (DepthConv.depth_conv, layers.py:148); weight [9][c], bias [c] */
 int dcvc_dwconv3x3(const dcvc_view *in, const dcvc_view *out, const float *weight,
                    const float *bias, void *stream);

@@ -205,3 +205,43 @@ def test_gop_256_vs_oracle(mode, conv_mode):
     assert max(abs(d) for d in dp) < 0.05, dp
     assert abs(sum(dp) / n) < 0.02, dp
     assert abs(bits - rbits) <= 0.005 * rbits, (bits, rbits)
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_pipeline_equals_sequential(mode):
+    """dcvc_b200.pipeline.EncDecPipeline (encoder and decoder instances on two CUDA streams, the
+    decoder one frame behind) yields byte-identical streams and bit-identical decoded frames to
+    the sequential encode -> decode loop of the reference harness (test_video.py:138-165)."""
+    from dcvc_b200 import ops
+    from dcvc_b200.pipeline import EncDecPipeline
+    old = ops.CONV_MODE
+    ops.set_conv_mode(mode)
+    try:
+        h, w, n = 64, 96, 6
+        frames = synth.synth_frames(n, h, w, seed=3)
+        i_net, p_net, _, _ = _models(5, 2, 2, "interleaved")
+        i_dec, p_dec, _, _ = _models(5, 2, 2, "interleaved")
+        # intra period 4: I P P P I P
+        ref = []
+        for g0 in (0, 4):
+            ref += _run_gop(i_net, p_net, frames[g0:g0 + 4], h, w, True, 1)
+        pipe = EncDecPipeline(i_net, p_net, i_dec, p_dec, 4, True, 1, dev())
+        got_streams, got_frames = [], []
+        with torch.no_grad():
+            for k in range(n):
+                with torch.cuda.stream(pipe.enc_stream):
+                    x = frames[k:k + 1].to(dev())
+                stream, decoded = pipe.push(x)
+                got_streams.append(stream)
+                if decoded is not None:
+                    got_frames.append(decoded)
+            got_frames.append(pipe.flush())
+            pipe.join()
+            torch.cuda.synchronize()
+        assert len(got_frames) == n
+        for k in range(n):
+            assert got_streams[k] == ref[k][0], f"frame {k}: stream differs"
+            assert torch.equal(got_frames[k].detach().cpu(), ref[k][1]), f"frame {k}: recon differs"
+        assert torch.equal(pipe.enc_dpb["ref_frame"], pipe.dec_dpb["ref_frame"])
+    finally:
+        ops.set_conv_mode(old)

@@ -334,3 +334,65 @@ def test_tc_conv_f16_residual(cin, cout, k, h, w, res16, out16):
     got = out.buf[:, :, :cout].float().permute(2, 0, 1).unsqueeze(0).cpu()
     bound = 4 * (4e-3 * 0.58 * 0.58 + 1e-5) * 1.5 + (float(ref.abs().max()) * 2 ** -11 if out16 else 0.0)
     assert float((got - ref).abs().max()) < bound, float((got - ref).abs().max())
+
+
+@pytest.mark.parametrize("cin,cout,h,w,f16", [(48, 48, 40, 56, True), (48, 48, 37, 50, False),
+                                               (64, 96, 33, 47, True), (96, 48, 24, 40, False)])
+def test_tc_conv_two_residuals_tma_epilogue(cin, cout, h, w, f16):
+    """res_block(..., res2=...) of the context fusion net: conv + res1 + res2 in the TMA-store
+    epilogue (second residual by direct row loads), ragged tiles, channel-slice views."""
+    sd = _sd(cin, cout, 3, seed=21)
+    x, r1, r2 = _rand(1, cin, h, w, seed=1), _rand(1, cout, h, w, seed=2), _rand(1, cout, h, w, seed=3)
+    net = layers.Net(sd, dev())
+    xa = to_act(x)
+    xr = x
+    if f16:
+        xa = ops.copy(xa, f16=True)
+        xr = x.half().float()
+    wr = sd["c.weight"].half().float() if f16 else sd["c.weight"]
+    conv = F.conv2d(xr, wr, sd["c.bias"], 1, 1)
+    out = to_act(torch.zeros(1, cout, h, w), cstride=cout + 16, coff=8)
+    ops.conv(xa, net.cw("c"), act=0.1, res=to_act(r1), res2=to_act(r2, cout + 20, 4), out=out)
+    torch.cuda.synchronize()
+    _check(from_act(out), F.leaky_relu(conv, 0.1) + r1 + r2, cin, 3)
+
+
+@pytest.mark.parametrize("c,h,w,out_f16,scaled", [(48, 40, 56, False, True), (32, 33, 47, True, False),
+                                                  (64, 64, 96, False, False), (48, 128, 200, True, True)])
+def test_fused_ffn_matches_reference(c, h, w, out_f16, scaled):
+    """dcvc_ffn (ConvFFN of DepthConvBlock, layers.py:166-179 + the block's residual) against
+    torch fp32 on the binary16-rounded operands the kernel multiplies; the hidden activation is
+    rounded to binary16 like the unfused path's private intermediate."""
+    g = torch.Generator().manual_seed(c + h)
+    sd = {"f.conv.0.weight": torch.randn(4 * c, c, 1, 1, generator=g) / c ** 0.5,
+          "f.conv.0.bias": torch.randn(4 * c, generator=g) * 0.1,
+          "f.conv.2.weight": torch.randn(c, 4 * c, 1, 1, generator=g) / (4 * c) ** 0.5,
+          "f.conv.2.bias": torch.randn(c, generator=g) * 0.1}
+    x = _rand(1, c, h, w, seed=7)
+    q = (torch.rand(c, generator=g) + 0.5) if scaled else None
+    net = layers.Net(sd, dev())
+    xa = ops.copy(to_act(x), f16=True)
+    old = ops.CONV_MODE
+    ops.set_conv_mode(1)
+    try:
+        assert ops.ffn_ok(xa)
+        w1, b1, w2, b2 = net.ffn("f")
+        out = None
+        if not out_f16:
+            out = to_act(torch.zeros(1, c, h, w), cstride=c + 16, coff=8)
+        out = ops.ffn(xa, w1, b1, w2, b2, 0.1, 0.1, scale=q.to(dev()) if scaled else None, out=out,
+                      f16_out=out_f16)
+        torch.cuda.synchronize()
+        assert out.f16 == out_f16
+    finally:
+        ops.set_conv_mode(old)
+    xh = x.half().float()
+    hid = F.leaky_relu(F.conv2d(xh, sd["f.conv.0.weight"].half().float(), sd["f.conv.0.bias"]), 0.1)
+    hid = hid.half().float()
+    ref = xh + F.leaky_relu(F.conv2d(hid, sd["f.conv.2.weight"].half().float(), sd["f.conv.2.bias"]), 0.1)
+    if scaled:
+        ref = ref * q.view(1, -1, 1, 1)
+    got = from_act(out)
+    tol = 2e-3 if out_f16 else 2e-4
+    err = float((got - ref).abs().max() / ref.abs().max())
+    assert err < tol, err
