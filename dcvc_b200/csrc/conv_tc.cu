@@ -1306,7 +1306,7 @@ bool conv_tc_ok(const dcvc_conv *d) {
   if (d->shuffle == 2 && tc_fast_mode(d) != 3) return false;   // planar packing needs the lean path
   const int ho = (d->in.h + 2 * d->pad - d->ksize) / d->stride + 1;
   const int wo = (d->in.w + 2 * d->pad - d->ksize) / d->stride + 1;
-  if ((int64_t)ho * wo < 4 * TILE_M) return false;             // tiny layers stay on CUDA cores
+  if ((int64_t)ho * wo < 2 * TILE_M) return false;             // tiny layers stay on CUDA cores
   return true;
 }
 

@@ -10,14 +10,15 @@
 //
 //   TMA:   t tile (128 pixels x 64 K-padded binary16, 128B swizzle) -> smem ring of 2
 //   MMA1:  acc1[128 x 4C] (TMEM, fp32) = t . W1^T        ceil(C/16) x UTCHMMA, N = 4C
-//   EPI1:  8 warps: tcgen05.ld -> + b1 -> LeakyReLU -> binary16 -> smem H in the K-major
+//   EPI1:  16 warps: tcgen05.ld -> + b1 -> LeakyReLU -> binary16 -> smem H in the K-major
 //          128B-swizzled layout an A operand needs (4C/64 chunks of 16 KB)
 //   MMA2:  acc2[128 x C] (TMEM) = H . W2^T               4C/16 x UTCHMMA, N = C
 //   EPI2:  4 warps: tcgen05.ld -> + b2 -> LeakyReLU -> + t (read back from the smem A tile)
 //          -> * scale -> 128-bit global stores (fp32 or binary16 rows)
 //
 // Both weight matrices stay resident in shared memory (<= 64 KB).  Persistent CTAs, one per SM;
-// the MMA warp issues MMA2(i) then MMA1(i+1), so EPI1(i+1) and EPI2(i) overlap.
+// the MMA warp issues MMA1(i+1) before MMA2(i) (H double-buffered; single H and the opposite
+// order at C = 64, where two H buffers do not fit), so EPI1(i+1) overlaps MMA2(i) and EPI2(i).
 // tcgen05.commit tracks every earlier MMA of the issuing thread, which orders the reuse of acc1
 // and H without extra barriers (see the protocol notes at the roles).
 #include <cuda.h>
@@ -31,7 +32,7 @@
 namespace {
 
 constexpr int TILE_M = 128;
-constexpr int EPI1_WARPS = 8, EPI2_WARPS = 4;
+constexpr int EPI1_WARPS = 16, EPI2_WARPS = 4;   // EPI1: four warps per TMEM lane quadrant
 constexpr int THREADS = 64 + 32 * (EPI1_WARPS + EPI2_WARPS);
 constexpr uint32_t SPIN_LIMIT = 1u << 26;
 constexpr uint32_t A_BYTES = TILE_M * 128;       // one t tile: 128 rows x 64 binary16
@@ -41,7 +42,8 @@ struct FfnArgs {
   dcvc_view out;
   const float *b1, *b2, *scale;
   float slope1, slope2;
-  int c, n1, pixels, tiles, out_f16, kk1, nch;
+  int c, n1, pixels, tiles, out_f16, kk1, nch, na;   // na: t-tile ring depth (2..4)
+  int hbufs;                                         // 2: H double-buffered (c <= 48), 1: single
   uint32_t w1_off, w2_off, h_off, vec_off, bar_off;   // from the 1024-aligned base; A ring at 0
 };
 
@@ -79,10 +81,8 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity, int lane) {
   if (lane == 0) {
-    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
-      __nanosleep(32);
+    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins)   // try_wait suspends in hardware
       if (spins > SPIN_LIMIT) __trap();
-    }
   }
   __syncwarp();
 }
@@ -148,11 +148,11 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t bars = base + a.bar_off;
-  // barriers: 0,1 a_full | 2,3 a_empty | 4 w_full | 5 acc1_full | 6 h_full | 7 acc2_full | 8 acc2_empty
+  // barriers: 0..3 a_full | 4 w_full | 5 acc1_full | 6 h_full | 7 acc2_full | 8 acc2_empty |
+  // 9..12 a_empty
   auto bar = [&](int i) { return bars + 8u * i; };
   if (threadIdx.x == 0) {
-    mbar_init(bar(0), 1); mbar_init(bar(1), 1);
-    mbar_init(bar(2), EPI2_WARPS); mbar_init(bar(3), EPI2_WARPS);
+    for (int i = 0; i < 4; ++i) { mbar_init(bar(i), 1); mbar_init(bar(9 + i), EPI2_WARPS); }
     mbar_init(bar(4), 1); mbar_init(bar(5), 1);
     mbar_init(bar(6), EPI1_WARPS);
     mbar_init(bar(7), 1);
@@ -187,20 +187,22 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
       for (int j = 0; j < a.nch; ++j)
         tma_load_2d(base + a.w2_off + (uint32_t)j * (uint32_t)a.c * 128u, &map_w2, bar(4), 0, j * a.c);
     }
-    uint32_t lt = 0;
-    for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
-      const uint32_t s = lt & 1u;
-      mbar_wait(bar(2 + s), ((lt >> 1) & 1u) ^ 1u);       // EPI2 has read the residual of tile lt-2
+    uint32_t s = 0, ph = 0;
+    for (int tile = blockIdx.x; tile < total; tile += step) {
+      mbar_wait(bar(9 + s), ph ^ 1u);                     // EPI2 has read the residual of tile lt-na
       if (leader) {
         mbar_expect_tx(bar(s), A_BYTES);
         tma_load_2d(base + s * A_BYTES, &map_a, bar(s), 0, tile * TILE_M);
       }
+      if (++s == (uint32_t)a.na) { s = 0; ph ^= 1u; }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer.  Order: MMA1(0) | MMA2(i), MMA1(i+1) ...
+    // ===== MMA issuer.  Order: MMA1(0) | MMA1(i+1), MMA2(i) ...
     //  * MMA1(i+1) overwrites acc1: EPI1(i) has read it (h_full(i) was waited on).
-    //  * EPI1(i+1) overwrites H: it waits acc1_full(i+1), a commit issued after MMA2(i), and a
-    //    commit completes only when every earlier MMA of this thread has -- so MMA2(i) is done.
+    //  * H is double-buffered: EPI1(i+1) fills H[(i+1)&1] while MMA2(i) reads H[i&1].  The MMA
+    //    that last read H[(i+1)&1] is MMA2(i-1), issued before MMA1(i+1); EPI1(i+1) waits
+    //    acc1_full(i+1), and a commit completes only when every earlier MMA of this thread
+    //    has -- so MMA2(i-1) is done.
     //  * MMA2(i+1) overwrites acc2: waits acc2_empty (EPI2(i) has read it).
     const bool issue = elect_one();
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
@@ -212,40 +214,49 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
     const uint32_t w2_step = ((uint32_t)a.c * 128u) >> 4, acc2 = tb + ACC2_COL;
     const int kk1 = a.kk1, nch = a.nch;
     mbar_wait(bar(4), 0u);
-    auto mma1 = [&](uint32_t lt) {
-      const uint32_t s = lt & 1u;
-      mbar_wait(bar(s), (lt >> 1) & 1u);
+    uint32_t as = 0, aph = 0;
+    const uint32_t na = (uint32_t)a.na;
+    auto mma1 = [&]() {                                    // next tile of the ring
+      mbar_wait(bar(as), aph);
       tc_fence_after();
       if (issue) {
-        const uint32_t a_lo = a_lo0 + s * (A_BYTES >> 4);
+        const uint32_t a_lo = a_lo0 + as * (A_BYTES >> 4);
         for (int kk = 0; kk < kk1; ++kk)
           umma_f16(tb, a_lo + 2 * kk, w1_lo + 2 * kk, hi, idesc1, kk ? 1u : 0u);
         umma_commit(bar(5));
       }
+      if (++as == na) { as = 0; aph ^= 1u; }
     };
     uint32_t lt = 0;
-    if ((int)blockIdx.x < total) mma1(0);
+    if ((int)blockIdx.x < total) mma1();
+    const uint32_t h_stride = ((uint32_t)nch * 16384u) >> 4;
+    const bool dbl = a.hbufs == 2;
     for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
-      mbar_wait(bar(6), lt & 1u);                          // H(lt) written
+      mbar_wait(bar(6), lt & 1u);                          // H[lt & 1] written, acc1 drained
+      // two H buffers: MMA1(lt+1) first, so that EPI1(lt+1) runs under MMA2(lt); with a single
+      // buffer MMA2(lt) must be issued (and, by commit order, finished) before acc1_full(lt+1)
+      if (dbl && tile + step < total) mma1();
       mbar_wait(bar(8), (lt & 1u) ^ 1u);                   // acc2 drained by EPI2(lt-1)
       tc_fence_after();
       if (issue) {
+        const uint32_t hb = h_lo + (dbl ? (lt & 1u) * h_stride : 0u);
         for (int j = 0; j < nch; ++j) {
-          const uint32_t hj = h_lo + (uint32_t)j * (16384u >> 4), wj = w2_lo + (uint32_t)j * w2_step;
+          const uint32_t hj = hb + (uint32_t)j * (16384u >> 4), wj = w2_lo + (uint32_t)j * w2_step;
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
             umma_f16(acc2, hj + 2 * kk, wj + 2 * kk, hi, idesc2, (j | kk) ? 1u : 0u);
         }
         umma_commit(bar(7));
       }
-      if (tile + step < total) mma1(lt + 1);
+      if (!dbl && tile + step < total) mma1();
     }
   } else if (warp < 2 + EPI1_WARPS) {
     // ===== EPI1: acc1 -> + b1 -> LeakyReLU -> binary16 -> H (A operand of MMA2)
-    const int e = warp - 2, q = warp & 3, half = e >> 2;
+    const int e = warp - 2, q = warp & 3, part = e >> 2;
     const int ng = a.n1 >> 5;                              // 32-column groups
     const uint32_t r = (uint32_t)(q * 32 + lane), sw = r & 7u;
-    uint8_t *const hrow = base_g + a.h_off + r * 128u;
+    uint8_t *const hrow0 = base_g + a.h_off + r * 128u;
+    const uint32_t h_bytes = (uint32_t)a.nch * 16384u;
     const float4 *const b1v = reinterpret_cast<const float4 *>(base_g + a.vec_off);
     const float slope = a.slope1;
     uint32_t lt = 0;
@@ -253,27 +264,23 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
       mbar_wait_warp(bar(5), lt & 1u, lane);
       tc_fence_after();
       const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
-      for (int g = half; g < ng; g += 2) {
+      uint8_t *const hrow = hrow0 + (a.hbufs == 2 ? (lt & 1u) * h_bytes : 0u);
+      for (int g = part; g < ng; g += EPI1_WARPS / 4) {
         uint32_t u[32];
         tmem_ld16_nowait(trow + (uint32_t)g * 32u, u);
         tmem_ld16_nowait(trow + (uint32_t)g * 32u + 16u, u + 16);
         tmem_wait_ld();
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 bb = b1v[g * 8 + j];
-          v[4 * j] = lrelu01(__uint_as_float(u[4 * j]) + bb.x, slope);
-          v[4 * j + 1] = lrelu01(__uint_as_float(u[4 * j + 1]) + bb.y, slope);
-          v[4 * j + 2] = lrelu01(__uint_as_float(u[4 * j + 2]) + bb.z, slope);
-          v[4 * j + 3] = lrelu01(__uint_as_float(u[4 * j + 3]) + bb.w, slope);
-        }
         uint8_t *const chunk = hrow + (uint32_t)(g >> 1) * 16384u;
         const uint32_t i0 = (uint32_t)(g & 1) * 4u;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
+          const float4 ba = b1v[g * 8 + 2 * i], bb = b1v[g * 8 + 2 * i + 1];
+          const uint32_t *w = u + 8 * i;
           uint4 pk;
-          pk.x = pack_h2(v[8 * i], v[8 * i + 1]);     pk.y = pack_h2(v[8 * i + 2], v[8 * i + 3]);
-          pk.z = pack_h2(v[8 * i + 4], v[8 * i + 5]); pk.w = pack_h2(v[8 * i + 6], v[8 * i + 7]);
+          pk.x = pack_h2(lrelu01(__uint_as_float(w[0]) + ba.x, slope), lrelu01(__uint_as_float(w[1]) + ba.y, slope));
+          pk.y = pack_h2(lrelu01(__uint_as_float(w[2]) + ba.z, slope), lrelu01(__uint_as_float(w[3]) + ba.w, slope));
+          pk.z = pack_h2(lrelu01(__uint_as_float(w[4]) + bb.x, slope), lrelu01(__uint_as_float(w[5]) + bb.y, slope));
+          pk.w = pack_h2(lrelu01(__uint_as_float(w[6]) + bb.z, slope), lrelu01(__uint_as_float(w[7]) + bb.w, slope));
           *reinterpret_cast<uint4 *>(chunk + (((i0 + (uint32_t)i) ^ sw) << 4)) = pk;
         }
       }
@@ -289,66 +296,68 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
     const float4 *const b2v = reinterpret_cast<const float4 *>(base_g + a.vec_off) + (a.n1 >> 2);
     const float4 *const scv = b2v + 16;
     const float slope = a.slope2;
-    const int c = a.c, ng = (c + 31) >> 5;
+    const int c = a.c;
     const bool has_scale = a.scale != nullptr;
-    uint32_t lt = 0;
+    uint32_t lt = 0, s = 0, sph = 0;
     for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
-      const uint32_t s = lt & 1u;
       mbar_wait_warp(bar(7), lt & 1u, lane);
       tc_fence_after();
       const uint32_t trow = tmem_base + ACC2_COL + ((uint32_t)(q * 32) << 16);
-      uint32_t u[64];
-#pragma unroll
-      for (int g = 0; g < 4; ++g)
-        if (g * 16 < c) tmem_ld16_nowait(trow + (uint32_t)g * 16u, u + 16 * g);
-      tmem_wait_ld();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(8));                  // acc2 may be overwritten
-      // residual: this pixel's row of the t tile, 16-byte slot i = channels 8i..8i+7 (the TMA
-      // write is made visible to this warp by observing the stage's own barrier; its phase
-      // cannot advance before this warp releases the stage below)
-      mbar_wait_warp(bar(s), (lt >> 1) & 1u, lane);
+      // the TMA write of the t tile is made visible to this warp by observing the stage's own
+      // barrier; its phase cannot advance before this warp releases the stage below
+      mbar_wait_warp(bar(s), sph, lane);
       const uint8_t *const arow = base_g + s * A_BYTES + r * 128u;
-      uint4 res[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-        if (i * 8 < c) res[i] = *reinterpret_cast<const uint4 *>(arow + (((uint32_t)i ^ sw) << 4));
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(2 + s));              // the A stage may be refilled
       const int64_t p = (int64_t)tile * TILE_M + r;
-      if (p < a.pixels) {
-        const size_t o = (size_t)p * a.out.cstride + a.out.coff;
+      const size_t o = (size_t)(p < a.pixels ? p : 0) * a.out.cstride + a.out.coff;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+      for (int hp = 0; hp < 2; ++hp) {                     // columns 32 hp .. 32 hp + 31
+        if (hp * 32 >= c) break;
+        uint32_t u[32];
+        tmem_ld16_nowait(trow + (uint32_t)hp * 32u, u);
+        if (hp * 32 + 16 < c) tmem_ld16_nowait(trow + (uint32_t)hp * 32u + 16u, u + 16);
+        tmem_wait_ld();
+        if ((hp + 1) * 32 >= c) {                          // accumulator fully read
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(8));
+        }
+#pragma unroll
+        for (int ii = 0; ii < 4; ++ii) {
+          const int i = hp * 4 + ii;                       // 16-byte slot: channels 8i..8i+7
           if (i * 8 >= c) continue;
+          const uint4 rs = *reinterpret_cast<const uint4 *>(arow + (((uint32_t)i ^ sw) << 4));
           float v[8];
           const float4 ba = b2v[2 * i], bb = b2v[2 * i + 1];
           const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-          const uint32_t rw[4] = {res[i].x, res[i].y, res[i].z, res[i].w};
+          const uint32_t rw[4] = {rs.x, rs.y, rs.z, rs.w};
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float2 t2 = unpack_h2(rw[j]);
-            v[2 * j] = lrelu01(__uint_as_float(u[8 * i + 2 * j]) + bias[2 * j], slope) + t2.x;
-            v[2 * j + 1] = lrelu01(__uint_as_float(u[8 * i + 2 * j + 1]) + bias[2 * j + 1], slope) + t2.y;
+            v[2 * j] = lrelu01(__uint_as_float(u[8 * ii + 2 * j]) + bias[2 * j], slope) + t2.x;
+            v[2 * j + 1] = lrelu01(__uint_as_float(u[8 * ii + 2 * j + 1]) + bias[2 * j + 1], slope) + t2.y;
           }
           if (has_scale) {
             const float4 sa = scv[2 * i], sb = scv[2 * i + 1];
             v[0] *= sa.x; v[1] *= sa.y; v[2] *= sa.z; v[3] *= sa.w;
             v[4] *= sb.x; v[5] *= sb.y; v[6] *= sb.z; v[7] *= sb.w;
           }
-          if (a.out_f16) {
-            uint4 pk;
-            pk.x = pack_h2(v[0], v[1]); pk.y = pack_h2(v[2], v[3]);
-            pk.z = pack_h2(v[4], v[5]); pk.w = pack_h2(v[6], v[7]);
-            *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(a.out.data) + o + 8 * i) = pk;
-          } else {
-            float4 *dst = reinterpret_cast<float4 *>(a.out.data + o + 8 * i);
-            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+          if (p < a.pixels) {
+            if (a.out_f16) {
+              uint4 pk;
+              pk.x = pack_h2(v[0], v[1]); pk.y = pack_h2(v[2], v[3]);
+              pk.z = pack_h2(v[4], v[5]); pk.w = pack_h2(v[6], v[7]);
+              *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(a.out.data) + o + 8 * i) = pk;
+            } else {
+              float4 *dst = reinterpret_cast<float4 *>(a.out.data + o + 8 * i);
+              dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+              dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+            }
           }
         }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(9 + s));              // the A stage may be refilled
+      if (++s == (uint32_t)a.na) { s = 0; sph ^= 1u; }
     }
   }
   tc_fence_before();
@@ -419,13 +428,16 @@ extern "C" int dcvc_ffn(const dcvc_ffn_desc *d, void *stream) {
   a.slope1 = d->slope1; a.slope2 = d->slope2;
   a.c = c; a.n1 = 4 * c; a.pixels = (int)pixels; a.tiles = cdiv(pixels, TILE_M);
   a.out_f16 = d->out_f16; a.kk1 = (c + 15) / 16; a.nch = a.n1 / 64;
-  a.w1_off = 2u * A_BYTES;
+  static const int na_env = getenv("DCVC_FFN_NA") ? atoi(getenv("DCVC_FFN_NA")) : 4;
+  a.na = na_env < 2 ? 2 : na_env > 4 ? 4 : na_env;
+  a.w1_off = (uint32_t)a.na * A_BYTES;
   a.w2_off = a.w1_off + (uint32_t)a.n1 * 128u;
   a.h_off = a.w2_off + (uint32_t)a.nch * (uint32_t)c * 128u;
-  a.vec_off = a.h_off + (uint32_t)a.nch * 16384u;
+  a.hbufs = c == 64 ? 1 : 2;                     // 64 (A) + 64 (weights) + 64 (H) KB at c = 64
+  a.vec_off = a.h_off + (uint32_t)a.hbufs * (uint32_t)a.nch * 16384u;
   a.bar_off = a.vec_off + ((((uint32_t)(a.n1 + 128) * 4u) + 15u) & ~15u);
-  const size_t smem = 1024 + (size_t)a.bar_off + 128;
-  if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "ffn: smem %zu too large", smem);
+  const size_t smem = 1024 + (size_t)a.bar_off + 128;   // 13 barriers
+  if (smem > 232448 - 64) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "ffn: smem %zu too large", smem);
   CUtensorMap ma, m1, m2;
   const __half *in = reinterpret_cast<const __half *>(d->in.data) + d->in.coff;
   int rc = map_2d(in, (uint64_t)c, (uint64_t)pixels, (uint64_t)d->in.cstride * 2, TILE_M, &ma);
@@ -436,7 +448,7 @@ extern "C" int dcvc_ffn(const dcvc_ffn_desc *d, void *stream) {
   static int num_sms = 0;
   if (!attr_set) {
     DCVC_CUDA(cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   226 * 1024));
+                                   232448 - 64));
     int dev = 0;
     DCVC_CUDA(cudaGetDevice(&dev));
     DCVC_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));

@@ -48,11 +48,16 @@ import os as _os
 F16 = _os.environ.get("DCVC_F16", "1") != "0"
 
 
+# maps with fewer output pixels stay on the CUDA-core kernel (conv_tc_ok in conv_tc.cu): 1/64
+# resolution hyperprior tensors at 1080p are 17x30 = 510 pixels and do go to the tensor cores
+TC_MIN_PIXELS = 256
+
+
 def f16_ok(h, w, c):
     """May an h x w x c activation that only convolutions read be stored as binary16?  Both its
-    producer and its consumers must be on the tensor-core path (>= 512 output pixels) and the
+    producer and its consumers must be on the tensor-core path (>= TC_MIN_PIXELS output pixels) and the
     pixel's channel vector must be whole 16-byte groups."""
-    return F16 and CONV_MODE == 1 and h * w >= 512 and c % 8 == 0
+    return F16 and CONV_MODE == 1 and h * w >= TC_MIN_PIXELS and c % 8 == 0
 
 
 def set_conv_mode(mode):
@@ -92,7 +97,7 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
         f16_out = (f16_out and f16_ok(eh, ew, ec) and cw.w_tc is not None and not shuffle
                    and not cw.gate and res2 is None and out2 is None)
         out = Act.new(eh, ew, ec, x.device, f16=f16_out)
-    if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= 512:
+    if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= TC_MIN_PIXELS:
         # the TMA-fed tensor-core kernel has no input prologue: materialise lrelu(x) once
         # (as binary16 when the copy is private to this conv)
         x = copy(x, slope=in_slope, f16=f16_ok(ho, wo, x.c) and cw.pack16 is not None)
