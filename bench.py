@@ -44,7 +44,7 @@ Q_IN_CKPT, Q_INDEX = False, 32
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=16)
+    p.add_argument("--steps", type=int, default=96)   # BASELINE configs[1]: 96 frames = 3 GOPs of 32
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--coder", default="interleaved", choices=["interleaved", "compat"])

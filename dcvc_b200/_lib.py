@@ -28,7 +28,7 @@ class Conv(ctypes.Structure):
                 ("in_slope", c_float), ("out_slope", c_float), ("gate_slope", c_float),
                 ("out2_slope", c_float), ("mode", c_int32), ("clamp01", c_int32),
                 ("weight_tc16", c_void_p), ("in_f16", c_int32), ("out_f16", c_int32),
-                ("res1_f16", c_int32)]
+                ("res1_f16", c_int32), ("res2_f16", c_int32)]
 
 
 class Ffn(ctypes.Structure):
@@ -68,11 +68,14 @@ SIGNATURES = {
     "dcvc_nhwc_to_nchw": (c_int, [VP, c_void_p, c_int, c_void_p]),
     "dcvc_copy": (c_int, [VP, VP, c_float, c_float, c_void_p]),
     "dcvc_copy_f16": (c_int, [VP, VP, c_float, c_float, c_void_p]),
+    "dcvc_copy_f16_f16": (c_int, [VP, VP, c_float, c_float, c_void_p]),
     "dcvc_fill": (c_int, [VP, c_float, c_void_p]),
     "dcvc_pool2": (c_int, [VP, VP, c_int, c_void_p]),
     "dcvc_resize_bilinear": (c_int, [VP, VP, c_float, c_void_p]),
     "dcvc_flow_warp": (c_int, [VP, VP, VP, c_void_p]),
     "dcvc_offset_diversity": (c_int, [VP, VP, VP, c_void_p, c_void_p, VP, c_void_p]),
+    "dcvc_offset_diversity_f16": (c_int, [VP, VP, VP, c_void_p, c_void_p, VP, c_void_p]),
+    "dcvc_flow_warp_f16": (c_int, [VP, VP, VP, c_void_p]),
     "dcvc_quad_bits_ws_bytes": (c_size_t, [c_int64]),
     "dcvc_quad_step_enc": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p]),

@@ -391,7 +391,7 @@ extern "C" int dcvc_conv2d(const dcvc_conv *d, void *stream) {
   if (rc != DCVC_OK) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   if (d->mode == 1 && d->weight_tc && conv_tc_ok(d)) return conv_tc_launch(d, ho, wo, s);
-  if (d->in_f16 || d->out_f16 || (d->res1_f16 && d->res1.data))
+  if (d->in_f16 || d->out_f16 || (d->res1_f16 && d->res1.data) || (d->res2_f16 && d->res2.data))
     return dcvc_fail(DCVC_ERR_UNSUPPORTED,
                      "conv: binary16 views need the tensor-core path, which this descriptor "
                      "does not qualify for (mode, shape, alignment or epilogue)");

@@ -50,6 +50,7 @@ struct TcArgs {
   int f16_in;     // A/B operands are binary16: kind::f16, K = 16 per instruction
   int f16_out;    // TMA-store epilogue writes binary16 (64-byte rows, 64B swizzle)
   int f16_res;    // res1 holds binary16 (fetched as 64-byte rows, 64B swizzle)
+  int f16_res2;   // res2 holds binary16 (TMA-store epilogue: direct 16-byte row loads)
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
 
@@ -957,14 +958,29 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           // tensor-map store anyway)
           const int px = x0 + (lane & wb_mask), py = y0 + (lane >> wb_shift);
           if (px < a.wout && py < a.hout) {
-            const float4 *r2 = reinterpret_cast<const float4 *>(
-                a.res2.data + ((size_t)py * a.res2.w + px) * a.res2.cstride + a.res2.coff + c0);
+            const size_t off = ((size_t)py * a.res2.w + px) * a.res2.cstride + a.res2.coff + c0;
+            if (a.f16_res2) {
+              const uint4 *r2 = reinterpret_cast<const uint4 *>(
+                  reinterpret_cast<const uint16_t *>(a.res2.data) + off);
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (c0 + 4 * j < a.cout_w) {
-                const float4 u = __ldg(r2 + j);
-                v[4 * j] += u.x; v[4 * j + 1] += u.y; v[4 * j + 2] += u.z; v[4 * j + 3] += u.w;
-              }
+              for (int j = 0; j < 4; ++j)
+                if (c0 + 8 * j < a.cout_w) {
+                  const uint4 u = __ldg(r2 + j);
+                  float2 f;
+                  f = unpack_h2(u.x); v[8 * j] += f.x;     v[8 * j + 1] += f.y;
+                  f = unpack_h2(u.y); v[8 * j + 2] += f.x; v[8 * j + 3] += f.y;
+                  f = unpack_h2(u.z); v[8 * j + 4] += f.x; v[8 * j + 5] += f.y;
+                  f = unpack_h2(u.w); v[8 * j + 6] += f.x; v[8 * j + 7] += f.y;
+                }
+            } else {
+              const float4 *r2 = reinterpret_cast<const float4 *>(a.res2.data + off);
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (c0 + 4 * j < a.cout_w) {
+                  const float4 u = __ldg(r2 + j);
+                  v[4 * j] += u.x; v[4 * j + 1] += u.y; v[4 * j + 2] += u.z; v[4 * j + 3] += u.w;
+                }
+            }
           }
         }
         if (a.scale) {
@@ -1281,7 +1297,8 @@ int tc_fast_mode(const dcvc_conv *d) {
             (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
   };
   const bool ok = d->cout_w % 4 == 0 && (d->out_f16 ? al16h(d->out) : al16(d->out)) &&
-                  (d->res1_f16 ? al16h(d->res1) : al16(d->res1)) && al16(d->res2) &&
+                  (d->res1_f16 ? al16h(d->res1) : al16(d->res1)) &&
+                  (d->res2_f16 && d->res2.data ? al16h(d->res2) && d->cout_w % 8 == 0 : al16(d->res2)) &&
                   al16(d->out2) && (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
                   (reinterpret_cast<uintptr_t>(d->scale) & 15u) == 0 && unit(d->out_slope) &&
                   unit(d->gate_slope) && unit(d->out2_slope);
@@ -1300,9 +1317,10 @@ bool conv_tc_ok(const dcvc_conv *d) {
   if (d->in_f16 && (!d->weight_tc16 || (reinterpret_cast<uintptr_t>(d->weight_tc16) & 15)))
     return false;
   // binary16 output / residual go through the TMA-store epilogue only
-  if ((d->out_f16 || (d->res1_f16 && d->res1.data)) &&
+  if ((d->out_f16 || (d->res1_f16 && d->res1.data) || (d->res2_f16 && d->res2.data)) &&
       (tc_fast_mode(d) != 1 || d->out2.data))
     return false;
+  if (d->res2_f16 && d->res2.data && !d->res1.data) return false;   // f16 res2: TMA-store epilogue only
   if (d->shuffle == 2 && tc_fast_mode(d) != 3) return false;   // planar packing needs the lean path
   const int ho = (d->in.h + 2 * d->pad - d->ksize) / d->stride + 1;
   const int wo = (d->in.w + 2 * d->pad - d->ksize) / d->stride + 1;
@@ -1322,6 +1340,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   int cin_pad, n_pad, tiles_n;
   const bool f16 = d->in_f16 != 0;
   a.f16_in = f16; a.f16_out = d->out_f16 != 0; a.f16_res = d->res1.data && d->res1_f16;
+  a.f16_res2 = d->res2.data && d->res2_f16;
   if (f16) dcvc_conv_tc_geometry16(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
   else dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
   a.kcb = a.kc * (f16 ? 2 : 4);
@@ -1424,7 +1443,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
   // TMA-store epilogue: plain convs with at most one residual, views TMA-addressable
-  a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res) && a.fast == 1 && !d->out2.data &&
+  a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res || a.f16_res2) && a.fast == 1 && !d->out2.data &&
               (!d->res2.data || d->res1.data);      // a second residual rides on direct loads
   int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi
             : a.tma_epi ? (ctas == 1 ? 8 : 4) : (ctas == 1 ? 16 : 8);

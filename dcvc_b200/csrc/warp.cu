@@ -9,6 +9,8 @@
 //   torch.cat / F.pad(replicate) / negative F.pad                               common_model.py:70-86
 // Every kernel maps consecutive threads to consecutive channels (then pixels), i.e. coalesced
 // NHWC access; all are one read + one write of their tensors.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace {
@@ -66,15 +68,29 @@ __global__ void copy_v4_kernel(dcvc_view src, dcvc_view dst, float mul, float sl
   *reinterpret_cast<float4 *>(dst.data + (size_t)p * dst.cstride + dst.coff + 4 * cq) = v;
 }
 
-// fp32 -> binary16 converting copy: one thread per (pixel, 8 channels): two float4 loads, one
-// 16-byte store of four half2 (round to nearest even)
+// fp32 (or binary16, HS) -> binary16 converting copy: one thread per (pixel, 8 channels): two
+// float4 loads (one 16-byte load of eight binary16), one 16-byte store of four half2 (round to
+// nearest even)
+template <bool HS>
 __global__ void copy_f16_kernel(dcvc_view src, dcvc_view dst, float mul, float slope, uint32_t c8n,
                                 uint32_t total) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= total) return;
   const uint32_t p = t / c8n, cq = t - p * c8n;
-  const float4 *sp = reinterpret_cast<const float4 *>(src.data + (size_t)p * src.cstride + src.coff + 8 * cq);
-  const float4 u = sp[0], v = sp[1];
+  float4 u, v;
+  if (HS) {
+    const uint4 h = *reinterpret_cast<const uint4 *>(
+        reinterpret_cast<const uint16_t *>(src.data) + (size_t)p * src.cstride + src.coff + 8 * cq);
+    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&h.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&h.y));
+    const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&h.z));
+    const float2 d = __half22float2(*reinterpret_cast<const __half2 *>(&h.w));
+    u = make_float4(a.x, a.y, b.x, b.y);
+    v = make_float4(c.x, c.y, d.x, d.y);
+  } else {
+    const float4 *sp = reinterpret_cast<const float4 *>(src.data + (size_t)p * src.cstride + src.coff + 8 * cq);
+    u = sp[0]; v = sp[1];
+  }
   auto f = [&](float x) { return mul * lrelu(x, slope); };
   auto pk = [](float lo, float hi) {
     uint32_t r;
@@ -223,6 +239,7 @@ __global__ void flow_warp_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out) 
 }
 
 // float4 path: one thread per (pixel, 4 channels); the four bilinear taps are 16-byte gathers
+template <bool HO>   // HO: out holds binary16 elements
 __global__ void flow_warp_v4_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out, uint32_t c4n,
                                     uint32_t total) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -248,7 +265,16 @@ __global__ void flow_warp_v4_kernel(dcvc_view feat, dcvc_view flow, dcvc_view ou
     a = *reinterpret_cast<const float4 *>(base + (r1 + b.x1) * feat.cstride);
     v.x += b.se * a.x; v.y += b.se * a.y; v.z += b.se * a.z; v.w += b.se * a.w;
   }
-  *reinterpret_cast<float4 *>(out.data + (size_t)p * out.cstride + out.coff + 4 * cq) = v;
+  if (HO) {
+    const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+    uint2 u;
+    u.x = *reinterpret_cast<const uint32_t *>(&lo);
+    u.y = *reinterpret_cast<const uint32_t *>(&hi);
+    *reinterpret_cast<uint2 *>(reinterpret_cast<__half *>(out.data) + (size_t)p * out.cstride +
+                               out.coff + 4 * cq) = u;
+  } else {
+    *reinterpret_cast<float4 *>(out.data + (size_t)p * out.cstride + out.coff + 4 * cq) = v;
+  }
 }
 
 // one thread per (pixel, group q of 16): samples n = 2q, 2q+1
@@ -294,6 +320,7 @@ __global__ void offset_diversity_kernel(dcvc_view x, dcvc_view offs, dcvc_view f
 // the same with the offset / mask channels of a sample pair fetched as one float4 / float2 per
 // corner of the x2 resize (offs view 16-byte aligned), corner addresses computed once, 32-bit
 // indices.  Every value is produced by the same expression as above: results are bit-identical.
+template <bool HO>   // HO: out holds binary16 elements
 __global__ void __launch_bounds__(256)
 offset_diversity_v4_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
                            const float *__restrict__ fw, const float *__restrict__ fb,
@@ -350,7 +377,8 @@ offset_diversity_v4_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
     float acc = fb ? fb[3 * q + o] : 0.f;
 #pragma unroll
     for (int r = 0; r < 6; ++r) acc = fmaf(v[r], wr[r], acc);
-    op[o] = acc;
+    if (HO) reinterpret_cast<__half *>(out.data)[vidx(out, py, px) + 3 * q + o] = __float2half_rn(acc);
+    else op[o] = acc;
   }
 }
 
@@ -400,7 +428,21 @@ extern "C" int dcvc_copy_f16(const dcvc_view *src, const dcvc_view *dst, float m
   if (!view_al16(src) || ((dst->cstride | dst->coff | dst->c) & 7) ||
       (reinterpret_cast<uintptr_t>(dst->data) & 15) || total8 >= (1ll << 31))
     return dcvc_fail(DCVC_ERR_UNSUPPORTED, "copy_f16: views must hold whole 16-byte channel groups");
-  LAUNCH_1D(copy_f16_kernel, total8, stream, *src, *dst, mul, slope, (uint32_t)(dst->c / 8),
+  LAUNCH_1D(copy_f16_kernel<false>, total8, stream, *src, *dst, mul, slope, (uint32_t)(dst->c / 8),
+            (uint32_t)total8);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_copy_f16_f16(const dcvc_view *src, const dcvc_view *dst, float mul, float slope,
+                                 void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || src->c != dst->c || src->h != dst->h || src->w != dst->w)
+    return dcvc_fail(DCVC_ERR_ARG, "copy_f16_f16: bad args");
+  const int64_t total8 = (int64_t)dst->h * dst->w * (dst->c / 8);
+  if (((src->cstride | src->coff | dst->cstride | dst->coff | dst->c) & 7) ||
+      ((reinterpret_cast<uintptr_t>(src->data) | reinterpret_cast<uintptr_t>(dst->data)) & 15) ||
+      total8 >= (1ll << 31))
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "copy_f16_f16: views must hold whole 16-byte channel groups");
+  LAUNCH_1D(copy_f16_kernel<true>, total8, stream, *src, *dst, mul, slope, (uint32_t)(dst->c / 8),
             (uint32_t)total8);
   return DCVC_OK;
 }
@@ -443,7 +485,7 @@ extern "C" int dcvc_flow_warp(const dcvc_view *feat, const dcvc_view *flow, cons
   const int64_t total4 = (int64_t)out->h * out->w * (out->c / 4);
   if (view_al16(feat) && view_al16(out) && ((flow->cstride | flow->coff) & 1) == 0 &&
       (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total4 < (1ll << 31)) {
-    LAUNCH_1D(flow_warp_v4_kernel, total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
+    LAUNCH_1D(flow_warp_v4_kernel<false>, total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
               (uint32_t)total4);
     return DCVC_OK;
   }
@@ -464,11 +506,46 @@ extern "C" int dcvc_offset_diversity(const dcvc_view *x, const dcvc_view *offs_h
                    ((flow->cstride | flow->coff) & 1) == 0 &&
                    (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total < (1ll << 31);
   if (vec) {
-    offset_diversity_v4_kernel<<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+    offset_diversity_v4_kernel<false><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
         *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
     DCVC_LAUNCHED();
     return DCVC_OK;
   }
   LAUNCH_1D(offset_diversity_kernel, total, stream, *x, *offs_half, *flow, fusion_w, fusion_b, *out);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_flow_warp_f16(const dcvc_view *feat, const dcvc_view *flow, const dcvc_view *out,
+                                  void *stream) {
+  if (!view_ok(feat) || !view_ok(flow) || !view_ok(out) || flow->c != 2 || out->c != feat->c ||
+      out->h != flow->h || out->w != flow->w)
+    return dcvc_fail(DCVC_ERR_ARG, "flow_warp_f16: bad args");
+  const int64_t total4 = (int64_t)out->h * out->w * (out->c / 4);
+  const bool ok = view_al16(feat) && ((out->cstride | out->coff | out->c) & 3) == 0 &&
+                  (reinterpret_cast<uintptr_t>(out->data) & 7) == 0 &&
+                  ((flow->cstride | flow->coff) & 1) == 0 &&
+                  (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total4 < (1ll << 31);
+  if (!ok) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "flow_warp_f16: views must hold whole 4-channel groups");
+  LAUNCH_1D(flow_warp_v4_kernel<true>, total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
+            (uint32_t)total4);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_offset_diversity_f16(const dcvc_view *x, const dcvc_view *offs_half,
+                                         const dcvc_view *flow, const float *fusion_w,
+                                         const float *fusion_b, const dcvc_view *out, void *stream) {
+  if (!view_ok(x) || !view_ok(offs_half) || !view_ok(flow) || !view_ok(out) || !fusion_w ||
+      x->c != 48 || offs_half->c != 96 || flow->c != 2 || out->c != 48 || out->h != x->h ||
+      out->w != x->w || flow->h != x->h || flow->w != x->w)
+    return dcvc_fail(DCVC_ERR_ARG, "offset_diversity_f16: bad args");
+  const int64_t total = (int64_t)out->h * out->w * 16;
+  const bool vec = ((offs_half->cstride | offs_half->coff) & 3) == 0 &&
+                   (reinterpret_cast<uintptr_t>(offs_half->data) & 15) == 0 &&
+                   ((flow->cstride | flow->coff) & 1) == 0 &&
+                   (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total < (1ll << 31);
+  if (!vec) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "offset_diversity_f16: unaligned offset/flow views");
+  offset_diversity_v4_kernel<true><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
+  DCVC_LAUNCHED();
   return DCVC_OK;
 }

@@ -100,7 +100,7 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= TC_MIN_PIXELS:
         # the TMA-fed tensor-core kernel has no input prologue: materialise lrelu(x) once
         # (as binary16 when the copy is private to this conv)
-        x = copy(x, slope=in_slope, f16=f16_ok(ho, wo, x.c) and cw.pack16 is not None)
+        x = copy(x, slope=in_slope, f16=x.f16 or (f16_ok(ho, wo, x.c) and cw.pack16 is not None))
         in_slope = 1.0
     d = _lib.Conv()
     d.inp = x.view()
@@ -112,6 +112,7 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     d.weight_tc = cw.w_tc.data_ptr() if cw.w_tc is not None else None
     d.in_f16, d.out_f16 = int(x.f16), int(out.f16)
     d.res1_f16 = int(res is not None and res.f16)
+    d.res2_f16 = int(res2 is not None and res2.f16)
     if x.f16:
         if cw.w_tc16 is None:
             cw.w_tc16 = cw.pack16()
@@ -129,7 +130,8 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
         return out
     path = "tcgen05" if _lib.lib().dcvc_conv_tc_eligible(ctypes.byref(d)) else "fma"
     tags = ("i" if x.f16 else "I") + ("o" if out.f16 else "O") + \
-        ("" if res is None else "r" if res.f16 else "R") + ("2" if res2 is not None else "")
+        ("" if res is None else "r" if res.f16 else "R") + \
+        ("" if res2 is None else "2h" if res2.f16 else "2")
     name = f"conv{k}x{k}s{stride} {cw.cin}->{cw.cout_w} @{ho}x{wo} [{path}] {tags}"
     flops = 2 * ho * wo * cw.cout_w * cw.cin * k * k
     nbytes = _nb(x, out, res, res2, out2) + 4 * cw.w.numel()
@@ -182,7 +184,10 @@ def copy(src, out=None, h=None, w=None, mul=1.0, slope=1.0, stream=None, f16=Fal
     if out is None:
         out = Act.new(src.h if h is None else h, src.w if w is None else w, src.c, src.device,
                       f16=f16)
-    fn = _lib.lib().dcvc_copy_f16 if out.f16 else _lib.lib().dcvc_copy
+    if src.f16 and not out.f16:
+        raise ValueError("copy: binary16 -> fp32 is not provided (binary16 tensors feed convolutions)")
+    fn = (_lib.lib().dcvc_copy_f16_f16 if src.f16 else _lib.lib().dcvc_copy_f16) if out.f16 \
+        else _lib.lib().dcvc_copy
     with _Prof(f"copy {out.c}ch @{out.h}x{out.w}" + (" lrelu" if slope != 1.0 else "") +
                (" f16" if out.f16 else ""), 0, _nb(src, out)):
         _lib.check(fn(src.view(), out.view(), mul, slope, _stream(stream)))
@@ -219,21 +224,22 @@ def resize_bilinear(x, h, w, mul=1.0, out=None, stream=None):
 
 
 def flow_warp(feat, flow, out=None, stream=None):
+    """out may be a binary16 Act (a context only tensor-core convolutions read)."""
     if out is None:
         out = Act.new(flow.h, flow.w, feat.c, feat.device)
-    with _Prof("flow_warp", 0, _nb(feat, flow, out)):
-        _lib.check(_lib.lib().dcvc_flow_warp(feat.view(), flow.view(), out.view(),
-                                             _stream(stream)))
+    fn = _lib.lib().dcvc_flow_warp_f16 if out.f16 else _lib.lib().dcvc_flow_warp
+    with _Prof("flow_warp" + (" f16" if out.f16 else ""), 0, _nb(feat, flow, out)):
+        _lib.check(fn(feat.view(), flow.view(), out.view(), _stream(stream)))
     return out
 
 
 def offset_diversity(x, offs_half, flow, fusion_w, fusion_b, out=None, stream=None):
     if out is None:
         out = Act.new(x.h, x.w, 48, x.device)
-    with _Prof("offset_diversity", 0, _nb(x, offs_half, flow, out)):
-        _lib.check(_lib.lib().dcvc_offset_diversity(x.view(), offs_half.view(), flow.view(),
-                                                    fusion_w.data_ptr(), fusion_b.data_ptr(),
-                                                    out.view(), _stream(stream)))
+    fn = _lib.lib().dcvc_offset_diversity_f16 if out.f16 else _lib.lib().dcvc_offset_diversity
+    with _Prof("offset_diversity" + (" f16" if out.f16 else ""), 0, _nb(x, offs_half, flow, out)):
+        _lib.check(fn(x.view(), offs_half.view(), flow.view(), fusion_w.data_ptr(),
+                      fusion_b.data_ptr(), out.view(), _stream(stream)))
     return out
 
 

@@ -163,23 +163,30 @@ class DMC(CompressionModel):
         mv2 = ops.resize_bilinear(mv, H // 2, W // 2, mul=0.5)
         mv3 = ops.resize_bilinear(mv2, H // 4, W // 4, mul=0.5)
         if dpb["ref_feature"] is None:
-            feat = ops.conv(ref_frame, net.cw("feature_adaptor_I"))
+            feat = ops.conv(ref_frame, net.cw("feature_adaptor_I"), f16_out=True)
         else:
             k = [0, 1, 0, 2][frame_idx % 4]
-            feat = ops.conv(Act.wrap(dpb["ref_feature"]), net.cw(f"feature_adaptor.{k}"))
+            feat = ops.conv(Act.wrap(dpb["ref_feature"]), net.cw(f"feature_adaptor.{k}"),
+                            f16_out=True)
         fe = "feature_extractor"
-        l1 = layers.res_block(net, fe + ".res_block1", ops.conv(feat, net.cw(fe + ".conv1")))
+        # a ResBlock's input is private to the block (LeakyReLU copy + residual): binary16
+        l1 = layers.res_block(net, fe + ".res_block1",
+                              ops.conv(feat, net.cw(fe + ".conv1"), f16_out=True))
         l2 = layers.res_block(net, fe + ".res_block2",
-                              ops.conv(l1, net.cw(fe + ".conv2"), stride=2))
+                              ops.conv(l1, net.cw(fe + ".conv2"), stride=2, f16_out=True))
         l3 = layers.res_block(net, fe + ".res_block3",
-                              ops.conv(l2, net.cw(fe + ".conv3"), stride=2))
+                              ops.conv(l2, net.cw(fe + ".conv3"), stride=2, f16_out=True))
         ops.flow_warp(l1, mv, out=aux.slice(0, 48))
         # OffsetDiversity (align)
         t = ops.conv(aux, net.cw("align.conv_offset.0"), stride=2, act=0.1, f16_out=True)
         t = ops.conv(t, net.cw("align.conv_offset.2"), act=0.1, f16_out=True)
         offs = ops.conv(t, net.cw("align.conv_offset.4"))
-        cat1 = Act.new(H, W, 96, dev)                      # [context2_up 48 | context1 48]
-        cat2 = Act.new(H // 2, W // 2, 128, dev)           # [context3_up 64 | context2 64]
+        # the fusion net's concatenations are read by tensor-core convolutions only (as input
+        # and as the second residual): binary16 in tensor-core mode
+        cat1 = Act.new(H, W, 96, dev,                      # [context2_up 48 | context1 48]
+                       f16=ops.f16_ok(H, W, 96))
+        cat2 = Act.new(H // 2, W // 2, 128, dev,           # [context3_up 64 | context2 64]
+                       f16=ops.f16_ok(H // 2, W // 2, 128))
         fw = net.sd["align.fusion.weight"].reshape(48, 6)
         c1 = ops.offset_diversity(l1, offs, mv, fw, net.sd["align.fusion.bias"],
                                   out=cat1.slice(48, 48))
@@ -189,13 +196,13 @@ class DMC(CompressionModel):
         cf = "context_fusion_net"
         t = layers.subpel(net, cf + ".conv3_up", c3)
         layers.res_block(net, cf + ".res_block3_up", t, out=cat2.slice(0, 64))
-        t = ops.conv(c3, net.cw(cf + ".conv3_out"))
+        t = ops.conv(c3, net.cw(cf + ".conv3_out"), f16_out=True)
         ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3, out=bufs["ctx3"])
         t = layers.subpel(net, cf + ".conv2_up", cat2)
         layers.res_block(net, cf + ".res_block2_up", t, out=cat1.slice(0, 48))
-        t = ops.conv(cat2, net.cw(cf + ".conv2_out"))
+        t = ops.conv(cat2, net.cw(cf + ".conv2_out"), f16_out=True)
         ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2, out=bufs["ctx2"])
-        t = ops.conv(cat1, net.cw(cf + ".conv1_out"))
+        t = ops.conv(cat1, net.cw(cf + ".conv1_out"), f16_out=True)
         ctx1 = layers.res_block(net, cf + ".res_block1_out", t, res2=c1, out=bufs["ctx1"])
         return ctx1, ctx2, ctx3
 

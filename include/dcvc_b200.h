@@ -95,6 +95,7 @@ typedef struct dcvc_conv {
   int32_t in_f16;
   int32_t out_f16;
   int32_t res1_f16;
+  int32_t res2_f16;       /* res2.data points at binary16 elements (TMA-store epilogue only) */
 } dcvc_conv;
 
 int dcvc_conv2d(const dcvc_conv *d, void *stream);
@@ -147,6 +148,9 @@ int dcvc_copy(const dcvc_view *src, const dcvc_view *dst, float mul, float slope
 /* dcvc_copy (equal sizes only) with a binary16 destination: dst->data points at binary16
  * elements, dst->cstride/coff count elements; feeds dcvc_conv.in_f16 */
 int dcvc_copy_f16(const dcvc_view *src, const dcvc_view *dst, float mul, float slope, void *stream);
+/* the same with a binary16 source view (LeakyReLU copies of binary16 ResBlock inputs) */
+int dcvc_copy_f16_f16(const dcvc_view *src, const dcvc_view *dst, float mul, float slope,
+                      void *stream);
 int dcvc_fill(const dcvc_view *dst, float value, void *stream);
 /* 2x2/2 pooling; mode 0 = average (F.avg_pool2d), 1 = max (nn.MaxPool2d) */
 int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream);
@@ -161,6 +165,14 @@ int dcvc_flow_warp(const dcvc_view *feat, const dcvc_view *flow, const dcvc_view
 int dcvc_offset_diversity(const dcvc_view *x, const dcvc_view *offs_half, const dcvc_view *flow,
                           const float *fusion_w, const float *fusion_b, const dcvc_view *out,
                           void *stream);
+/* dcvc_flow_warp / dcvc_offset_diversity writing a binary16 `out` view (fp32 inputs, fp32
+ * arithmetic, result rounded to nearest even): the motion-compensated contexts that only
+ * tensor-core convolutions read (MultiScaleContextFusion's concatenations). */
+int dcvc_flow_warp_f16(const dcvc_view *feat, const dcvc_view *flow, const dcvc_view *out,
+                       void *stream);
+int dcvc_offset_diversity_f16(const dcvc_view *x, const dcvc_view *offs_half,
+                              const dcvc_view *flow, const float *fusion_w, const float *fusion_b,
+                              const dcvc_view *out, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * Quad-part entropy model (reference DCVC-DC/src/models/common_model.py:39-61,92-321,
