@@ -549,6 +549,49 @@ __device__ __forceinline__ void mma_bres(const TcArgs &a, const MmaCtx &c) {
   }
 }
 
+// resident weights with several channel chunks per tap (unit = tap * chunks + chunk): one window
+// per (tile, chunk); KK MMAs per full chunk, kk_last in the last one
+template <int KS, int KK, bool F16>
+__device__ __forceinline__ void mma_bres_mc(const TcArgs &a, const MmaCtx &c) {
+  const int total = a.total_tiles, step = gridDim.x, sa_n = a.halo_sa, chunks = a.chunks_per_tap,
+            kk_last = a.kk_last;
+  const uint32_t p4 = (uint32_t)a.kcb >> 4, pwp4 = (uint32_t)(a.halo_pw * a.kcb) >> 4,
+                 ub4 = a.unit_b >> 4, ua4 = a.unit_a >> 4, acc_stride = a.acc_stride;
+  const uint32_t tap4 = ub4 * (uint32_t)chunks;        // B stride between taps
+  const uint32_t a4_0 = desc_lo32(c.base), b4_0 = desc_lo32(c.base + sa_n * a.unit_a);
+  uint32_t as = 0, aph = 0, pha = 0, a4 = a4_0;
+  int sa = 0;
+  mbar_wait(c.full_bar(sa_n), 0u);               // the weights, once
+  for (int tile = blockIdx.x; tile < total; tile += step) {
+    mbar_wait(c.tempty_bar(as), aph ^ 1u);
+    const uint32_t tacc = c.tmem + as * acc_stride;
+    uint32_t b4 = b4_0;
+    for (int ch = 0; ch < chunks; ++ch, b4 += ub4) {
+      mbar_wait(c.full_bar(sa), pha);
+      tc_fence_after();
+      const int kn = ch == chunks - 1 ? kk_last : KK;
+      if (c.issue) {
+#pragma unroll
+        for (int dy = 0; dy < KS; ++dy) {
+          const uint32_t ra = a4 + dy * pwp4, rb = b4 + dy * KS * tap4;
+#pragma unroll
+          for (int dx = 0; dx < KS; ++dx)
+#pragma unroll
+            for (int kk = 0; kk < KK; ++kk)
+              if (kk < kn)
+                umma2<F16>(tacc, ra + dx * p4 + 2 * kk, c.a_hi, rb + dx * tap4 + 2 * kk, c.b_hi,
+                           c.idesc, (dy | dx | kk) ? 1u : (uint32_t)ch);
+        }
+        umma_commit(c.empty_bar(sa));
+      }
+      a4 += ua4;
+      if (++sa == sa_n) { sa = 0; pha ^= 1u; a4 = a4_0; }
+    }
+    if (c.issue) umma_commit(c.tfull_bar(as));
+    if ((as ^= 1u) == 0) aph ^= 1u;
+  }
+}
+
 // halo windows with streamed weights: per (tile, channel chunk) one window, taps walk it;
 // B stages carry `halo_bg` consecutive taps
 template <int KK, bool F16>
@@ -661,7 +704,11 @@ __device__ __forceinline__ void mma_role(const TcArgs &a, uint32_t base, uint32_
   c.b_hi = desc_hi32(a.sbo, a.layout_type);
   c.a_hi = a.halo ? desc_hi32(a.halo_sbo, a.layout_type) : c.b_hi;
   const int kk_n = a.kcb >> 5;     // one MMA consumes 32 bytes of K per row: 8 TF32 / 16 binary16
-  if (a.bres) {
+  if (a.bres && a.chunks_per_tap > 1) {      // 3x3 only (host)
+    if (kk_n == 4) mma_bres_mc<3, 4, F16>(a, c);
+    else if (kk_n == 2) mma_bres_mc<3, 2, F16>(a, c);
+    else mma_bres_mc<3, 1, F16>(a, c);
+  } else if (a.bres) {
     const int key = a.ksize * 8 + a.kk_last;
     switch (key) {
       case 3 * 8 + 1: mma_bres<3, 1, F16>(a, c); break;
@@ -767,23 +814,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       if (a.bres) {
         // ----- resident weights: every tap's B tile is loaded once and stays; the ring carries
         // input windows only, one TMA load per tile
+        const int units = keep((int)(taps * chunks));
         if (leader) {
-          mbar_expect_tx(full_bar(sa_n), no_tma ? 0u : (uint32_t)taps * tx_b);
+          mbar_expect_tx(full_bar(sa_n), no_tma ? 0u : (uint32_t)units * tx_b);
           if (!no_tma)
-            for (int g = 0; g < taps; ++g)
+            for (int g = 0; g < units; ++g)               // unit g = tap * chunks + chunk
               tma_load_2d(b_base + g * unit_b, &map_b, full_bar(sa_n), g * kc, 0);
         }
         for (int tile = blockIdx.x; tile < total; tile += step) {
           int mt, nt, ty, tx;
           tile_coords(a, tile, mt, nt, ty, tx);
-          mbar_wait(empty_bar(sa), pha ^ 1u);
-          if (leader) {
-            mbar_expect_tx(full_bar(sa), no_tma ? 0u : tx_a);
-            if (!no_tma)
-              tma_load_4d(base + sa * unit_a, &map_a, full_bar(sa), 0, tx * a.tw - pad,
-                          ty * a.th - pad, 0);
+          for (int ch = 0; ch < chunks; ++ch) {
+            mbar_wait(empty_bar(sa), pha ^ 1u);
+            if (leader) {
+              mbar_expect_tx(full_bar(sa), no_tma ? 0u : tx_a);
+              if (!no_tma)
+                tma_load_4d(base + sa * unit_a, &map_a, full_bar(sa), ch * kc, tx * a.tw - pad,
+                            ty * a.th - pad, 0);
+            }
+            if (++sa == sa_n) { sa = 0; pha ^= 1u; }
           }
-          if (++sa == sa_n) { sa = 0; pha ^= 1u; }
         }
       }
       int a_tile = a.bres ? total : blockIdx.x, a_ch = 0;   // iterator of the A loads
@@ -1376,12 +1426,19 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // 3x3 48->48 f16 at 1080p 0.254 -> 0.206 ms = 27 MMAs x 110 tiles per SM, the issue floor of
   // this GEMM orientation; 7x7 only where a tap is a single MMA (16->2: 0.525 -> 0.40 ms)
   static const int bres_on = getenv("DCVC_TC_BRES") ? atoi(getenv("DCVC_TC_BRES")) : 1;
-  const uint32_t bres_bytes = (uint32_t)(d->ksize * d->ksize) * (uint32_t)ru(a.n_tile * a.kcb, 1024);
+  const uint32_t bres_bytes = (uint32_t)(d->ksize * d->ksize * a.chunks_per_tap) *
+                              (uint32_t)ru(a.n_tile * a.kcb, 1024);
+  // one channel chunk: up to 72 KB of weights (two CTAs per SM stay possible); 3x3 with 2-3
+  // chunks: up to 112 KB, one CTA per SM (96->48 f16 0.32 -> , 48->3 fp32 0.40 -> ms at 1080p)
+  static const uint32_t bres_mc_kb = getenv("DCVC_TC_BRES_MC_KB") ? atoi(getenv("DCVC_TC_BRES_MC_KB")) : 112;
+  const bool bres_one = a.chunks_per_tap == 1 && bres_bytes <= 72u * 1024u &&
+                        (d->ksize == 3 || a.kk_last == 1) &&   // shapes mma_bres<> is instantiated for
+                        (bres_on == 2 || (d->ksize == 3 && !d->shuffle) || (a.kk_last == 1 && a.n_tile <= 32));
+  const bool bres_mc = a.chunks_per_tap > 1 && a.chunks_per_tap <= 3 && d->ksize == 3 && !d->shuffle &&
+                       bres_bytes <= bres_mc_kb * 1024u;
   a.bres = bres_on && halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 7 &&
-           d->pad == d->ksize / 2 && a.kcb >= (f16 ? 32 : 64) && a.chunks_per_tap == 1 &&
-           tiles_n == 1 && bres_bytes <= 72u * 1024u && !d->out2.data &&
-           (d->ksize == 3 || a.kk_last == 1) &&     // shapes mma_bres<> is instantiated for
-           (bres_on == 2 || (d->ksize == 3 && !d->shuffle) || (a.kk_last == 1 && a.n_tile <= 32));
+           d->pad == d->ksize / 2 && a.kcb >= (f16 ? 32 : 64) && tiles_n == 1 && !d->out2.data &&
+           (bres_one || bres_mc);
   if (a.bres) a.halo = 1;
   const int halo_ph = TILE_M / 8 + d->ksize - 1;
   static const int halo_pw16 = getenv("DCVC_TC_HALO_PW16") ? atoi(getenv("DCVC_TC_HALO_PW16")) : 0;

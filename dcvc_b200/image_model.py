@@ -82,7 +82,8 @@ class IntraNoAR(CompressionModel):
         t = layers.rbu(net, "dec.dec_1.5", layers.dcb2(net, "dec.dec_1.4", t), scale=q_dec)
         t = layers.rbu(net, "dec.dec_2.1", layers.dcb2(net, "dec.dec_2.0", t))
         t = layers.unet(net, "refine.0", t, layers.dcb2)
-        return ops.conv(t, net.cw("refine.1"), clamp01=clamp)
+        # 3 -> 4 output channels (a zero filter): whole 16-byte pixels take the vectorised epilogue
+        return ops.conv(t, net.cw("refine.1", cout_pad=4), clamp01=clamp).slice(0, 3)
 
     def _encode_side(self, x, q_in_ckpt, q_index, write, bits_y=None, bits_z=None):
         q_enc, q_dec = self.get_q_for_inference(q_in_ckpt, q_index)

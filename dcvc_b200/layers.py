@@ -69,13 +69,15 @@ class Net:
     def has(self, name):
         return (name + ".weight") in self.sd
 
-    def cw(self, name, gate=False, cin_perm=None, shuffle=False):
+    def cw(self, name, gate=False, cin_perm=None, shuffle=False, cout_pad=None):
         """KN-packed conv weights: [kh*kw][cin][cout]; gate=True interleaves the two halves of the
         output channels (ConvFFN2's chunk(2), layers.py:193-195) so the gate pairs are adjacent;
         cin_perm reorders the input channels (new channel i reads reference channel cin_perm[i])
         so a concatenated input can be laid out alignment-friendly; shuffle=True marks a
-        depth-to-space conv: its tensor-core copy is packed planar (see _pack_tc)."""
-        key = (name, gate, cin_perm, shuffle)
+        depth-to-space conv: its tensor-core copy is packed planar (see _pack_tc); cout_pad
+        appends zero filters (and zero biases) up to that many output channels, so that a
+        3-channel image convolution qualifies for the vectorised epilogues."""
+        key = (name, gate, cin_perm, shuffle, cout_pad)
         r = self._conv.get(key)
         if r is None:
             w = self.sd[name + ".weight"]
@@ -84,6 +86,11 @@ class Net:
             assert kh == kw
             if cin_perm is not None:
                 w = w[:, torch.tensor(cin_perm, device=w.device)]
+            if cout_pad is not None and cout_pad > cout:
+                w = torch.cat((w, w.new_zeros((cout_pad - cout, cin, kh, kw))), 0)
+                if b is not None:
+                    b = torch.cat((b, b.new_zeros(cout_pad - cout)), 0)
+                cout = cout_pad
             if gate:
                 half = cout // 2
                 perm = torch.stack((torch.arange(half), torch.arange(half) + half), 1).reshape(-1)

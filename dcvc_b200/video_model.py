@@ -253,8 +253,10 @@ class DMC(CompressionModel):
         t = ops.conv(bufs["R"], net.cw(rg + ".first_conv", cin_perm=perm))
         t = layers.unet(net, rg + ".unet_1", t, layers.dcb)
         feature = layers.unet(net, rg + ".unet_2", t, layers.dcb)
-        x_hat = ops.conv(feature, net.cw(rg + ".recon_conv"), clamp01=True)
-        return x_hat, feature
+        # 3 -> 4 output channels (a zero filter): the image pixel is a 16-byte group either way,
+        # and whole groups take the TMA-store epilogue instead of the scalar one
+        x_hat4 = ops.conv(feature, net.cw(rg + ".recon_conv", cout_pad=4), clamp01=True)
+        return x_hat4.slice(0, 3), feature
 
     # ------------------------------------------------------------------ shared encoder side
     def _encode_side(self, x, dpb, q_in_ckpt, q_index, frame_idx, write, bits=None):
