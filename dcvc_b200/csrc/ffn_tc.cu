@@ -32,20 +32,18 @@
 namespace {
 
 constexpr int TILE_M = 128;
-constexpr int EPI2_WARPS = 4;
-// EPI1 warps: 16 (one CTA per SM) or 8 (two CTAs per SM: two tile chains in flight)
-constexpr int threads_of(int e1) { return 64 + 32 * (e1 + EPI2_WARPS); }
+constexpr int EPI1_WARPS = 16, EPI2_WARPS = 4;   // EPI1: four warps per TMEM lane quadrant
+constexpr int THREADS = 64 + 32 * (EPI1_WARPS + EPI2_WARPS);
 constexpr uint32_t SPIN_LIMIT = 1u << 26;
 constexpr uint32_t A_BYTES = TILE_M * 128;       // one t tile: 128 rows x 64 binary16
+constexpr uint32_t ACC2_COL = 256;               // acc1 at column 0 (<= 256 columns), acc2 here
 
 struct FfnArgs {
   dcvc_view out;
   const float *b1, *b2, *scale;
   float slope1, slope2;
   int c, n1, pixels, tiles, out_f16, kk1, nch, na;   // na: t-tile ring depth (2..4)
-  int hbufs;                                         // 2: H double-buffered, 1: single
-  int tmem_cols, acc2_col;                           // TMEM allocation, first column of acc2
-  dcvc_view in;                                      // t again: EPI2 reads the residual from L2
+  int hbufs;                                         // 2: H double-buffered (c <= 48), 1: single
   uint32_t w1_off, w2_off, h_off, vec_off, bar_off;   // from the 1024-aligned base; A ring at 0
 };
 
@@ -140,8 +138,7 @@ __device__ __forceinline__ float2 unpack_h2(uint32_t u) {
 __device__ __forceinline__ float lrelu01(float v, float slope) { return fmaxf(v, v * slope); }
 __device__ __forceinline__ uint32_t desc_lo32(uint32_t addr) { return (addr >> 4) | 0x10000u; }
 
-template <int EPI1_WARPS>
-__global__ void __launch_bounds__(threads_of(EPI1_WARPS), EPI1_WARPS == 8 ? 2 : 1)
+__global__ void __launch_bounds__(THREADS, 1)
 ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w1,
               const __grid_constant__ CUtensorMap map_w2, const __grid_constant__ FfnArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -155,7 +152,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
   // 9..12 a_empty
   auto bar = [&](int i) { return bars + 8u * i; };
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 4; ++i) { mbar_init(bar(i), 1); mbar_init(bar(9 + i), 1); }
+    for (int i = 0; i < 4; ++i) { mbar_init(bar(i), 1); mbar_init(bar(9 + i), EPI2_WARPS); }
     mbar_init(bar(4), 1); mbar_init(bar(5), 1);
     mbar_init(bar(6), EPI1_WARPS);
     mbar_init(bar(7), 1);
@@ -172,7 +169,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                 ::"r"(smem_u32(&tmem_slot)), "r"((uint32_t)a.tmem_cols) : "memory");
+                 ::"r"(smem_u32(&tmem_slot)), "r"(512u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
@@ -192,7 +189,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
     }
     uint32_t s = 0, ph = 0;
     for (int tile = blockIdx.x; tile < total; tile += step) {
-      mbar_wait(bar(9 + s), ph ^ 1u);                     // MMA1 of tile lt-na has read the stage
+      mbar_wait(bar(9 + s), ph ^ 1u);                     // EPI2 has read the residual of tile lt-na
       if (leader) {
         mbar_expect_tx(bar(s), A_BYTES);
         tma_load_2d(base + s * A_BYTES, &map_a, bar(s), 0, tile * TILE_M);
@@ -214,7 +211,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
     const uint32_t idesc2 = (1u << 4) | ((uint32_t)(a.c >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
     const uint32_t a_lo0 = desc_lo32(base), w1_lo = desc_lo32(base + a.w1_off),
                    w2_lo = desc_lo32(base + a.w2_off), h_lo = desc_lo32(base + a.h_off);
-    const uint32_t w2_step = ((uint32_t)a.c * 128u) >> 4, acc2 = tb + (uint32_t)a.acc2_col;
+    const uint32_t w2_step = ((uint32_t)a.c * 128u) >> 4, acc2 = tb + ACC2_COL;
     const int kk1 = a.kk1, nch = a.nch;
     mbar_wait(bar(4), 0u);
     uint32_t as = 0, aph = 0;
@@ -226,7 +223,6 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
         const uint32_t a_lo = a_lo0 + as * (A_BYTES >> 4);
         for (int kk = 0; kk < kk1; ++kk)
           umma_f16(tb, a_lo + 2 * kk, w1_lo + 2 * kk, hi, idesc1, kk ? 1u : 0u);
-        umma_commit(bar(9 + as));                          // the t stage may be refilled
         umma_commit(bar(5));
       }
       if (++as == na) { as = 0; aph ^= 1u; }
@@ -296,24 +292,23 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
   } else {
     // ===== EPI2: acc2 -> + b2 -> LeakyReLU -> + t -> * scale -> global
     const int q = warp & 3;
-    const uint32_t r = (uint32_t)(q * 32 + lane);
+    const uint32_t r = (uint32_t)(q * 32 + lane), sw = r & 7u;
     const float4 *const b2v = reinterpret_cast<const float4 *>(base_g + a.vec_off) + (a.n1 >> 2);
     const float4 *const scv = b2v + 16;
     const float slope = a.slope2;
     const int c = a.c;
     const bool has_scale = a.scale != nullptr;
-    uint32_t lt = 0;
+    uint32_t lt = 0, s = 0, sph = 0;
     for (int tile = blockIdx.x; tile < total; tile += step, ++lt) {
       mbar_wait_warp(bar(7), lt & 1u, lane);
       tc_fence_after();
-      const uint32_t trow = tmem_base + (uint32_t)a.acc2_col + ((uint32_t)(q * 32) << 16);
+      const uint32_t trow = tmem_base + ACC2_COL + ((uint32_t)(q * 32) << 16);
+      // the TMA write of the t tile is made visible to this warp by observing the stage's own
+      // barrier; its phase cannot advance before this warp releases the stage below
+      mbar_wait_warp(bar(s), sph, lane);
+      const uint8_t *const arow = base_g + s * A_BYTES + r * 128u;
       const int64_t p = (int64_t)tile * TILE_M + r;
-      const size_t pc = (size_t)(p < a.pixels ? p : 0);
-      const size_t o = pc * a.out.cstride + a.out.coff;
-      // residual: the pixel's own t row, read back through L2 (the tile was fetched by TMA a
-      // moment ago); keeps the smem stage free for the next tile as soon as MMA1 has read it
-      const uint4 *const trow_g = reinterpret_cast<const uint4 *>(
-          reinterpret_cast<const __half *>(a.in.data) + pc * a.in.cstride + a.in.coff);
+      const size_t o = (size_t)(p < a.pixels ? p : 0) * a.out.cstride + a.out.coff;
 #pragma unroll
       for (int hp = 0; hp < 2; ++hp) {                     // columns 32 hp .. 32 hp + 31
         if (hp * 32 >= c) break;
@@ -330,7 +325,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
         for (int ii = 0; ii < 4; ++ii) {
           const int i = hp * 4 + ii;                       // 16-byte slot: channels 8i..8i+7
           if (i * 8 >= c) continue;
-          const uint4 rs = __ldg(trow_g + i);
+          const uint4 rs = *reinterpret_cast<const uint4 *>(arow + (((uint32_t)i ^ sw) << 4));
           float v[8];
           const float4 ba = b2v[2 * i], bb = b2v[2 * i + 1];
           const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
@@ -360,6 +355,9 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
           }
         }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(9 + s));              // the A stage may be refilled
+      if (++s == (uint32_t)a.na) { s = 0; sph ^= 1u; }
     }
   }
   tc_fence_before();
@@ -367,7 +365,7 @@ ffn_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;"
-                 ::"r"(tmem_base), "r"((uint32_t)a.tmem_cols) : "memory");
+                 ::"r"(tmem_base), "r"(512u) : "memory");
   }
 }
 
@@ -430,31 +428,13 @@ extern "C" int dcvc_ffn(const dcvc_ffn_desc *d, void *stream) {
   a.slope1 = d->slope1; a.slope2 = d->slope2;
   a.c = c; a.n1 = 4 * c; a.pixels = (int)pixels; a.tiles = cdiv(pixels, TILE_M);
   a.out_f16 = d->out_f16; a.kk1 = (c + 15) / 16; a.nch = a.n1 / 64;
-  a.in = d->in;
-  // Two configurations.  c <= 48: two CTAs per SM (8 EPI1 warps each, <= 72 registers), so two
-  // tile chains MMA1 -> EPI1 -> MMA2 -> EPI2 overlap on every SM; shared memory per CTA =
-  // t ring + weights + one H buffer <= 112 KB, TMEM 256 columns each.  c = 64: one CTA per SM
-  // with 16 EPI1 warps, a 4-deep t ring and the 512-column allocation.
-  static const int two_env = getenv("DCVC_FFN_2CTA") ? atoi(getenv("DCVC_FFN_2CTA")) : 1;
-  const uint32_t w_bytes = (uint32_t)a.n1 * 128u + (uint32_t)a.nch * (uint32_t)c * 128u;
-  const uint32_t h_bytes = (uint32_t)a.nch * 16384u;
-  bool two = two_env && a.n1 + c <= 256;
-  a.na = 4; a.hbufs = c == 64 ? 1 : 2;
-  if (two) {
-    a.hbufs = 1;
-    a.na = (int)((111u * 1024u - w_bytes - h_bytes - 4096u) / A_BYTES);
-    if (a.na > 3) a.na = 3;
-    if (a.na < 1) two = false;
-  }
-  if (!two) { a.na = 4; a.hbufs = c == 64 ? 1 : 2; }
-  static const int na_env = getenv("DCVC_FFN_NA") ? atoi(getenv("DCVC_FFN_NA")) : 0;
-  if (na_env >= 1 && na_env <= 4 && !two) a.na = na_env;
-  a.tmem_cols = two ? 256 : 512;
-  a.acc2_col = two ? a.n1 : 256;
+  static const int na_env = getenv("DCVC_FFN_NA") ? atoi(getenv("DCVC_FFN_NA")) : 4;
+  a.na = na_env < 2 ? 2 : na_env > 4 ? 4 : na_env;
   a.w1_off = (uint32_t)a.na * A_BYTES;
   a.w2_off = a.w1_off + (uint32_t)a.n1 * 128u;
   a.h_off = a.w2_off + (uint32_t)a.nch * (uint32_t)c * 128u;
-  a.vec_off = a.h_off + (uint32_t)a.hbufs * h_bytes;
+  a.hbufs = c == 64 ? 1 : 2;                     // 64 (A) + 64 (weights) + 64 (H) KB at c = 64
+  a.vec_off = a.h_off + (uint32_t)a.hbufs * (uint32_t)a.nch * 16384u;
   a.bar_off = a.vec_off + ((((uint32_t)(a.n1 + 128) * 4u) + 15u) & ~15u);
   const size_t smem = 1024 + (size_t)a.bar_off + 128;   // 13 barriers
   if (smem > 232448 - 64) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "ffn: smem %zu too large", smem);
@@ -467,21 +447,15 @@ extern "C" int dcvc_ffn(const dcvc_ffn_desc *d, void *stream) {
   static bool attr_set = false;
   static int num_sms = 0;
   if (!attr_set) {
-    DCVC_CUDA(cudaFuncSetAttribute(ffn_tc_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   232448 - 64));
-    DCVC_CUDA(cudaFuncSetAttribute(ffn_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    DCVC_CUDA(cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    232448 - 64));
     int dev = 0;
     DCVC_CUDA(cudaGetDevice(&dev));
     DCVC_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
     attr_set = true;
   }
-  const int slots = (two ? 2 : 1) * num_sms;
-  const int grid = a.tiles < slots ? a.tiles : slots;
-  if (two)
-    ffn_tc_kernel<8><<<grid, threads_of(8), smem, (cudaStream_t)stream>>>(ma, m1, m2, a);
-  else
-    ffn_tc_kernel<16><<<grid, threads_of(16), smem, (cudaStream_t)stream>>>(ma, m1, m2, a);
+  const int grid = a.tiles < num_sms ? a.tiles : num_sms;
+  ffn_tc_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(ma, m1, m2, a);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }

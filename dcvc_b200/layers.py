@@ -191,7 +191,7 @@ def dcb2(net, p, x, out=None, scale=None, f16_out=False):
 def rbws(net, p, x, out=None):
     """ResidualBlockWithStride (layers.py:42-73), stride 2."""
     t = ops.conv(x, net.cw(p + ".conv1"), stride=2, act=0.01, f16_out=True)
-    idn = ops.conv(x, net.cw(p + ".downsample"), stride=2, pad=0)
+    idn = ops.conv(x, net.cw(p + ".downsample"), stride=2, pad=0, f16_out=True)
     return ops.conv(t, net.cw(p + ".conv2"), act=0.1, res=idn, out=out)
 
 

@@ -78,28 +78,35 @@ class DMC(CompressionModel):
         """MvEnc.forward (video_model.py:138-146)"""
         net = self.net
         m = "mv_encoder"
-        t = layers.dcb(net, m + ".enc_1.1", layers.rbws(net, m + ".enc_1.0", est_mv), scale=q)
+        # block outputs that only convolutions read are binary16 (f16_out)
+        # (their stride-2 consumers must still be tensor-core sized: half() checks that)
+        def half(a):
+            return ops.f16_ok(a.h // 2, a.w // 2, a.c)
+        t = layers.rbws(net, m + ".enc_1.0", est_mv)
+        t = layers.dcb(net, m + ".enc_1.1", t, scale=q, f16_out=half(t))
         if ref_mv_feature is None:
-            t = layers.dcb(net, m + ".adaptor_0", layers.rbws(net, m + ".enc_2", t))
+            t = layers.rbws(net, m + ".enc_2", t)
+            t = layers.dcb(net, m + ".adaptor_0", t, f16_out=half(t))
         else:
             cat = Act.new(t.h // 2, t.w // 2, 128, t.device)
             layers.rbws(net, m + ".enc_2", t, out=cat.slice(0, 64))
             ops.copy(ref_mv_feature, out=cat.slice(64, 64))
-            t = layers.dcb(net, m + ".adaptor_1", cat)
-        t = layers.dcb(net, m + ".enc_3.1", layers.rbws(net, m + ".enc_3.0", t))
+            t = layers.dcb(net, m + ".adaptor_1", cat, f16_out=half(cat))
+        t = layers.rbws(net, m + ".enc_3.0", t)
+        t = layers.dcb(net, m + ".enc_3.1", t, f16_out=half(t))
         return ops.conv(t, net.cw(m + ".enc_3.2"), stride=2)
 
     def _mv_dec(self, mv_y_hat, q):
         """MvDec.forward (video_model.py:165-170) -> (mv [2], mv_feature [64 @1/4])"""
         net = self.net
         m = "mv_decoder"
-        t = layers.dcb(net, m + ".dec_1.0", mv_y_hat)
+        t = layers.dcb(net, m + ".dec_1.0", mv_y_hat, f16_out=True)
         t = layers.rbu(net, m + ".dec_1.1", t)
-        t = layers.dcb(net, m + ".dec_1.2", t)
+        t = layers.dcb(net, m + ".dec_1.2", t, f16_out=True)
         t = layers.rbu(net, m + ".dec_1.3", t)
         feature = layers.dcb(net, m + ".dec_1.4", t)
         t = layers.rbu(net, m + ".dec_2", feature, scale=q)
-        t = layers.dcb(net, m + ".dec_3.0", t)
+        t = layers.dcb(net, m + ".dec_3.0", t)     # fp32: the 8-filter subpel has no f16 packing
         mv = layers.subpel(net, m + ".dec_3.1", t)
         return mv, feature
 
@@ -112,13 +119,13 @@ class DMC(CompressionModel):
         if ref is None:
             if t.h != catb.h or t.w != catb.w:
                 t = ops.copy(t, h=catb.h, w=catb.w)
-            t = layers.dcb(net, "mv_y_prior_fusion_adaptor_0", t)
+            t = layers.dcb(net, "mv_y_prior_fusion_adaptor_0", t, f16_out=True)
         else:
             cat = Act.new(catb.h, catb.w, 128, catb.device)
             ops.copy(t, out=cat.slice(0, 64))
             ops.copy(Act.wrap(ref), out=cat.slice(64, 64))
-            t = layers.dcb(net, "mv_y_prior_fusion_adaptor_1", cat)
-        t = layers.dcb(net, "mv_y_prior_fusion.0", t)
+            t = layers.dcb(net, "mv_y_prior_fusion_adaptor_1", cat, f16_out=True)
+        t = layers.dcb(net, "mv_y_prior_fusion.0", t, f16_out=True)
         layers.dcb(net, "mv_y_prior_fusion.1", t, out=catb.slice(c, 3 * c))
 
     def _res_params(self, z_hat, dpb, ctx3, catb, c):
@@ -131,20 +138,20 @@ class DMC(CompressionModel):
         hier = layers.hyper_dec(net, "contextual_hyper_prior_decoder", z_hat)
         ops.copy(hier, out=cat.slice(128, 128))
         if ref is None:
-            t = layers.dcb(net, "y_prior_fusion_adaptor_0", cat)
+            t = layers.dcb(net, "y_prior_fusion_adaptor_0", cat, f16_out=True)
         else:
             ops.copy(Act.wrap(ref), out=cat.slice(256, 128))
-            t = layers.dcb(net, "y_prior_fusion_adaptor_1", cat)
-        t = layers.dcb(net, "y_prior_fusion.0", t)
+            t = layers.dcb(net, "y_prior_fusion_adaptor_1", cat, f16_out=True)
+        t = layers.dcb(net, "y_prior_fusion.0", t, f16_out=True)
         layers.dcb(net, "y_prior_fusion.1", t, out=catb.slice(c, 3 * c))
 
     def _prior_fn(self, prefix):
         net = self.net
 
         def fn(step, catb):
-            t = ops.conv(catb, net.cw(f"{prefix}_spatial_prior_adaptor_{step}"))
+            t = ops.conv(catb, net.cw(f"{prefix}_spatial_prior_adaptor_{step}"), f16_out=True)
             for i in range(3):
-                t = layers.dcb(net, f"{prefix}_spatial_prior.{i}", t)
+                t = layers.dcb(net, f"{prefix}_spatial_prior.{i}", t, f16_out=i < 2)
             return t
         return fn
 
