@@ -91,6 +91,8 @@ SIGNATURES = {
                                    ctypes.POINTER(Tables)]),
     "dcvc_rans_enc_flush": (c_int, [c_void_p, c_void_p, c_size_t, ctypes.POINTER(c_size_t),
                                     c_void_p]),
+    "dcvc_rans_enc_flush_begin": (c_int, [c_void_p, c_size_t, c_void_p]),
+    "dcvc_rans_enc_flush_end": (c_int, [c_void_p, c_void_p, c_size_t, ctypes.POINTER(c_size_t)]),
     "dcvc_rans_dec_set_stream": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "dcvc_rans_dec_pull": (c_int, [c_void_p, c_void_p, c_int64, c_int64, ctypes.POINTER(Tables),
                                    c_void_p, c_void_p]),

@@ -443,6 +443,9 @@ struct dcvc_rans {
   int dec_parts = 0;
   cudaEvent_t staged = nullptr;
   bool stage_pending = false;
+  cudaEvent_t flushed = nullptr;   // encoder: after the meta words of flush_begin reached the host
+  cudaStream_t side = nullptr;     // encoder: payload copy of flush_end, not behind later work
+  bool flush_pending = false;
 };
 
 extern "C" void dcvc_rans_destroy(dcvc_rans *r) {
@@ -451,6 +454,8 @@ extern "C" void dcvc_rans_destroy(dcvc_rans *r) {
   cudaFree(r->d_parts);
   cudaFreeHost(r->h_meta); cudaFreeHost(r->h_stage); cudaFreeHost(r->h_parts);
   if (r->staged) cudaEventDestroy(r->staged);
+  if (r->flushed) cudaEventDestroy(r->flushed);
+  if (r->side) cudaStreamDestroy(r->side);
   delete r;
 }
 
@@ -487,6 +492,8 @@ extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t ma
   RANS_TRY(cudaMalloc(&r->d_parts, sizeof(DecPart) * MAX_PARTS));
   RANS_TRY(cudaMallocHost(&r->h_parts, sizeof(DecPart) * MAX_PARTS));
   RANS_TRY(cudaEventCreateWithFlags(&r->staged, cudaEventDisableTiming));
+  RANS_TRY(cudaEventCreateWithFlags(&r->flushed, cudaEventDisableTiming));
+  RANS_TRY(cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking));
   *out = r;
   return DCVC_OK;
 }
@@ -521,9 +528,13 @@ static int rans_errors(uint32_t flags) {
   return dcvc_fail(DCVC_ERR_STREAM, "rans: truncated or corrupt stream (flags %u)", flags);
 }
 
-extern "C" int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_capacity,
-                                   size_t *out_len, void *stream) {
-  if (!r || !out_host || !out_len) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush: bad arguments");
+// flush in two halves: `begin` enqueues the coding kernels and the copy of the meta words on
+// `stream` and records an event; `end` waits for THAT EVENT ONLY, then fetches the payload on a
+// side stream.  Work the caller enqueues on `stream` between the two (the encoder's own
+// reconstruction of the frame) keeps running while the host already holds the bytes.
+extern "C" int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void *stream) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_begin: bad arguments");
+  if (r->flush_pending) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_begin: a flush is already pending");
   cudaStream_t s = (cudaStream_t)stream;
   int64_t off = 0;
   for (int i = 0; i < r->parts; ++i) {
@@ -557,15 +568,34 @@ extern "C" int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_c
                                      r->d_meta, r->d_out, cap);
   DCVC_LAUNCHED();
   DCVC_CUDA(cudaMemcpyAsync(r->h_meta, r->d_meta, META_WORDS * 4, cudaMemcpyDeviceToHost, s));
-  DCVC_CUDA(cudaStreamSynchronize(s));
+  DCVC_CUDA(cudaEventRecord(r->flushed, s));
   r->job.ncalls = 0;
+  r->flush_pending = true;
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_enc_flush_end(dcvc_rans *r, uint8_t *out_host, size_t out_capacity,
+                                       size_t *out_len) {
+  if (!r || !out_host || !out_len) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_end: bad arguments");
+  if (!r->flush_pending) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_end: no flush pending");
+  r->flush_pending = false;
+  DCVC_CUDA(cudaEventSynchronize(r->flushed));
   int rc = rans_errors(r->h_meta[0]);
   if (rc) return rc;
   const size_t len = r->h_meta[1];
-  DCVC_CUDA(cudaMemcpyAsync(out_host, r->d_out, len, cudaMemcpyDeviceToHost, s));
-  DCVC_CUDA(cudaStreamSynchronize(s));
+  if (len > out_capacity) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_end: output buffer too small");
+  DCVC_CUDA(cudaMemcpyAsync(out_host, r->d_out, len, cudaMemcpyDeviceToHost, r->side));
+  DCVC_CUDA(cudaStreamSynchronize(r->side));
   *out_len = len;
   return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_capacity,
+                                   size_t *out_len, void *stream) {
+  if (!r || !out_host || !out_len) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush: bad arguments");
+  int rc = dcvc_rans_enc_flush_begin(r, out_capacity, stream);
+  if (rc) return rc;
+  return dcvc_rans_enc_flush_end(r, out_host, out_capacity, out_len);
 }
 
 extern "C" int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_t len, void *stream) {

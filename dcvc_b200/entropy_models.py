@@ -170,6 +170,7 @@ class EntropyCoder:
         self._cap = self.max_symbols * 4 + 1024
         self._out = torch.empty(self._cap, dtype=torch.uint8).pin_memory()
         self._stream_bytes = b""
+        self._pending = False
         self._keep = []
 
     def __del__(self):
@@ -182,6 +183,8 @@ class EntropyCoder:
             self._h = None
 
     def reset(self):
+        if self._pending:        # an unread flush: finish it so the coder can start a new one
+            self.get_encoded_stream()
         self._keep = []
         _lib.check(_lib.lib().dcvc_rans_enc_reset(self._h))
 
@@ -193,15 +196,22 @@ class EntropyCoder:
             n, plane, ctypes.byref(tables.c)))
 
     def flush(self):
-        n = ctypes.c_size_t(0)
+        """Enqueues the coder kernels (RansEncoder.flush, py_rans.cpp:98-135); the host wait is
+        in get_encoded_stream, so whatever the caller enqueues in between runs behind the coder
+        on the GPU while the host already reads the bytes."""
         with _Prof("rans_enc_flush"):
-            _lib.check(_lib.lib().dcvc_rans_enc_flush(
-                self._h, self._out.data_ptr(), self._cap, ctypes.byref(n),
-                torch.cuda.current_stream().cuda_stream))
+            _lib.check(_lib.lib().dcvc_rans_enc_flush_begin(
+                self._h, self._cap, torch.cuda.current_stream().cuda_stream))
         self._keep = []
-        self._stream_bytes = bytes(self._out[:n.value].numpy().tobytes())
+        self._pending = True
 
     def get_encoded_stream(self):
+        if self._pending:
+            n = ctypes.c_size_t(0)
+            self._pending = False
+            _lib.check(_lib.lib().dcvc_rans_enc_flush_end(
+                self._h, self._out.data_ptr(), self._cap, ctypes.byref(n)))
+            self._stream_bytes = bytes(self._out[:n.value].numpy().tobytes())
         return self._stream_bytes
 
     def set_stream(self, stream):

@@ -266,8 +266,10 @@ class DMC(CompressionModel):
         return x_hat4.slice(0, 3), feature
 
     # ------------------------------------------------------------------ shared encoder side
-    def _encode_side(self, x, dpb, q_in_ckpt, q_index, frame_idx, write, bits=None):
-        """compress (:425-453) / forward_one_frame (:559-585) up to the entropy coder."""
+    def _encode_side(self, x, dpb, q_in_ckpt, q_index, frame_idx, write, bits=None, coder=None):
+        """compress (:425-453) / forward_one_frame (:559-585) up to the entropy coder.
+        `coder(mv_z, z, mv_coded, coded)` is called once every symbol of the frame is known and
+        before the reconstruction is enqueued."""
         mv_q_enc, mv_q_dec, y_q_enc, y_q_dec = self.get_q_for_inference(q_in_ckpt, q_index)
         xa = Act.wrap(x)
         ref = Act.wrap(dpb["ref_frame"])
@@ -291,6 +293,8 @@ class DMC(CompressionModel):
         catb = self.new_prior_buffer(y.h, y.w, y.c)
         self._res_params(z_hat, dpb, ctx3, catb, y.c)
         y_hat, coded = self.forward_four_part_prior(y, catb, self._prior_fn("y"), write, b(0))
+        if coder is not None:
+            coder((mv_z_hat, mv_z_sym), (z_hat, z_sym), mv_coded, coded)
         x_hat, feature = self._recon(y_hat, bufs, y_q_dec)
         if self.taps is not None:
             for k, v in (("est_mv", est_mv), ("mv_y", mv_y), ("mv_z_hat", mv_z_hat),
@@ -307,16 +311,23 @@ class DMC(CompressionModel):
 
     # ------------------------------------------------------------------ reference API
     def compress(self, x, dpb, q_in_ckpt, q_index, frame_idx):
-        """video_model.py:425-481; stream order mv_z, z, mv_y parts 0..3, y parts 0..3."""
-        new_dpb, (mv_z_hat, mv_z_sym), (z_hat, z_sym), mv_coded, coded = self._encode_side(
-            x, dpb, q_in_ckpt, q_index, frame_idx, True)
+        """video_model.py:425-481; stream order mv_z, z, mv_y parts 0..3, y parts 0..3.
+        The coder kernels are enqueued BEFORE the frame's reconstruction (the reference hands the
+        symbols to its encoder thread at the same point, :449-476, and reconstructs after); the
+        host then waits for the coder's event only, so the reconstruction is still running on the
+        GPU when this returns -- whoever reads the dpb next does so in stream order."""
         ec = self.entropy_coder
-        ec.reset()
-        self.encode_z(mv_z_sym, mv_z_hat, "bit_estimator_z_mv")
-        self.encode_z(z_sym, z_hat, "bit_estimator_z")
-        self.encode_y(mv_coded)
-        self.encode_y(coded)
-        ec.flush()
+
+        def coder(mv_zs, zs, mv_coded, coded):
+            ec.reset()
+            self.encode_z(mv_zs[1], mv_zs[0], "bit_estimator_z_mv")
+            self.encode_z(zs[1], zs[0], "bit_estimator_z")
+            self.encode_y(mv_coded)
+            self.encode_y(coded)
+            ec.flush()
+
+        new_dpb, _, _, _, _ = self._encode_side(x, dpb, q_in_ckpt, q_index, frame_idx, True,
+                                                coder=coder)
         return {"dpb": new_dpb, "bit_stream": ec.get_encoded_stream()}
 
     def decompress(self, dpb, string, height, width, q_in_ckpt, q_index, frame_idx):

@@ -263,6 +263,13 @@ int dcvc_rans_enc_push(dcvc_rans *r, const int16_t *symbols, const uint8_t *inde
                        int64_t plane, const dcvc_tables *t);
 int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_capacity, size_t *out_len,
                         void *stream);
+/* The same flush in two halves, for callers that keep enqueuing work on `stream` after the coder
+ * (compress enqueues the frame's reconstruction between the two: py_rans.cpp's encoder thread,
+ * :98-135, plays this role in the reference).  begin: kernels + meta copy + event on `stream`, no
+ * host wait.  end: waits for that event only and copies the container to `out_host` on a private
+ * stream.  One flush may be pending per coder. */
+int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void *stream);
+int dcvc_rans_enc_flush_end(dcvc_rans *r, uint8_t *out_host, size_t out_capacity, size_t *out_len);
 int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_t len, void *stream);
 int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t n, int64_t plane,
                        const dcvc_tables *t, int16_t *symbols_out, void *stream);
