@@ -69,6 +69,7 @@ SIGNATURES = {
     "dcvc_copy": (c_int, [VP, VP, c_float, c_float, c_void_p]),
     "dcvc_copy_f16": (c_int, [VP, VP, c_float, c_float, c_void_p]),
     "dcvc_copy_f16_f16": (c_int, [VP, VP, c_float, c_float, c_void_p]),
+    "dcvc_copy_f16_narrow": (c_int, [VP, VP, c_void_p]),
     "dcvc_fill": (c_int, [VP, c_float, c_void_p]),
     "dcvc_pool2": (c_int, [VP, VP, c_int, c_void_p]),
     "dcvc_resize_bilinear": (c_int, [VP, VP, c_float, c_void_p]),

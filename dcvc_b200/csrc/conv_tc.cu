@@ -449,6 +449,13 @@ __device__ __forceinline__ void fast_chunk(const TcArgs &a, const float *stg, in
         t.x = fminf(fmaxf(t.x, 0.f), 1.f); t.y = fminf(fmaxf(t.y, 0.f), 1.f);
         t.z = fminf(fmaxf(t.z, 0.f), 1.f); t.w = fminf(fmaxf(t.w, 0.f), 1.f);
       }
+      if (SHUF && a.f16_out) {
+        // binary16 destination (no residual / second output on this path: host-checked)
+        *reinterpret_cast<uint2 *>(reinterpret_cast<uint16_t *>(a.out.data) + a.out.coff + c +
+                                   (size_t)pix * a.out.cstride) =
+            make_uint2(pack_h2(t.x, t.y), pack_h2(t.z, t.w));
+        continue;
+      }
       *reinterpret_cast<float4 *>(o + (size_t)pix * a.out.cstride) = t;
       if (o2) {
         t.x = lrelu01(t.x, a.out2_slope); t.y = lrelu01(t.y, a.out2_slope);
@@ -1367,7 +1374,10 @@ bool conv_tc_ok(const dcvc_conv *d) {
   if (d->in_f16 && (!d->weight_tc16 || (reinterpret_cast<uintptr_t>(d->weight_tc16) & 15)))
     return false;
   // binary16 output / residual go through the TMA-store epilogue only
-  if ((d->out_f16 || (d->res1_f16 && d->res1.data) || (d->res2_f16 && d->res2.data)) &&
+  // (or, output only, through the planar depth-to-space epilogue without residuals)
+  const bool shuf16 = d->out_f16 && d->shuffle == 2 && tc_fast_mode(d) == 3 && !d->res1.data &&
+                      !d->res2.data && !d->out2.data;
+  if ((d->out_f16 || (d->res1_f16 && d->res1.data) || (d->res2_f16 && d->res2.data)) && !shuf16 &&
       (tc_fast_mode(d) != 1 || d->out2.data))
     return false;
   if (d->res2_f16 && d->res2.data && !d->res1.data) return false;   // f16 res2: TMA-store epilogue only

@@ -104,6 +104,24 @@ __global__ void copy_f16_kernel(dcvc_view src, dcvc_view dst, float mul, float s
   *reinterpret_cast<uint4 *>(dp) = o;
 }
 
+// fewer than eight fp32 channels into one 16-byte binary16 group, zero-padded (the image next to
+// a binary16 context in a concatenation buffer)
+__global__ void copy_f16_narrow_kernel(dcvc_view src, dcvc_view dst, uint32_t total) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= total) return;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    v[j] = j < src.c ? src.data[(size_t)p * src.cstride + src.coff + j] : 0.f;
+  auto pk = [](float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+  };
+  *reinterpret_cast<uint4 *>(reinterpret_cast<uint16_t *>(dst.data) + (size_t)p * dst.cstride + dst.coff) =
+      make_uint4(pk(v[0], v[1]), pk(v[2], v[3]), pk(v[4], v[5]), pk(v[6], v[7]));
+}
+
 __global__ void fill_kernel(dcvc_view dst, float value) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (int64_t)dst.h * dst.w * dst.c) return;
@@ -430,6 +448,18 @@ extern "C" int dcvc_copy_f16(const dcvc_view *src, const dcvc_view *dst, float m
     return dcvc_fail(DCVC_ERR_UNSUPPORTED, "copy_f16: views must hold whole 16-byte channel groups");
   LAUNCH_1D(copy_f16_kernel<false>, total8, stream, *src, *dst, mul, slope, (uint32_t)(dst->c / 8),
             (uint32_t)total8);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_copy_f16_narrow(const dcvc_view *src, const dcvc_view *dst, void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || src->c != dst->c || src->h != dst->h || src->w != dst->w ||
+      src->c >= 8)
+    return dcvc_fail(DCVC_ERR_ARG, "copy_f16_narrow: bad args");
+  const int64_t total = (int64_t)dst->h * dst->w;
+  if (((dst->cstride | dst->coff) & 7) || dst->coff + 8 > dst->cstride ||
+      (reinterpret_cast<uintptr_t>(dst->data) & 15) || total >= (1ll << 31))
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "copy_f16_narrow: the destination must own a whole 16-byte group");
+  LAUNCH_1D(copy_f16_narrow_kernel, total, stream, *src, *dst, (uint32_t)total);
   return DCVC_OK;
 }
 

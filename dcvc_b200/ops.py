@@ -186,6 +186,11 @@ def copy(src, out=None, h=None, w=None, mul=1.0, slope=1.0, stream=None, f16=Fal
                       f16=f16)
     if src.f16 and not out.f16:
         raise ValueError("copy: binary16 -> fp32 is not provided (binary16 tensors feed convolutions)")
+    if out.f16 and not src.f16 and src.c < 8:
+        assert mul == 1.0 and slope == 1.0
+        with _Prof(f"copy {out.c}ch @{out.h}x{out.w} f16", 0, _nb(src, out)):
+            _lib.check(_lib.lib().dcvc_copy_f16_narrow(src.view(), out.view(), _stream(stream)))
+        return out
     fn = (_lib.lib().dcvc_copy_f16_f16 if src.f16 else _lib.lib().dcvc_copy_f16) if out.f16 \
         else _lib.lib().dcvc_copy
     with _Prof(f"copy {out.c}ch @{out.h}x{out.w}" + (" lrelu" if slope != 1.0 else "") +

@@ -28,7 +28,7 @@ class DMC(CompressionModel):
 
     def _tap(self, name, act):
         if self.taps is not None:
-            self.taps[name] = act.nchw().detach().clone()
+            self.taps[name] = act.nchw().detach().float().clone()
 
     # ------------------------------------------------------------------ q
     @staticmethod
@@ -214,7 +214,9 @@ class DMC(CompressionModel):
         return ctx1, ctx2, ctx3
 
     def _new_bufs(self, H, W, dev):
-        R = Act.new(H, W, 80, dev)                         # recon input [ctx1 48 | res 32]
+        # recon input [ctx1 48 | res 32]: two convolutions write it, two read it -> binary16
+        # (the encoder's stride-2 conv1 reads ctx1 too: its output must be tensor-core sized)
+        R = Act.new(H, W, 80, dev, f16=ops.f16_ok(H // 2, W // 2, 80))
         D2 = Act.new(H // 2, W // 2, 128, dev)             # decoder res2 input [f 64 | ctx2 64]
         D3 = Act.new(H // 4, W // 4, 192, dev)             # decoder res1 input [f 96 | ctx3 96]
         return {"R": R, "D2": D2, "D3": D3, "ctx1": R.slice(0, 48), "ctx2": D2.slice(64, 64),
@@ -226,7 +228,7 @@ class DMC(CompressionModel):
         [ctx1 48 | x 3] (weights permuted accordingly) to keep the 48-channel slice aligned."""
         net = self.net
         dev = x.device
-        e1 = Act.new(x.h, x.w, 51, dev)
+        e1 = Act.new(x.h, x.w, 51, dev, f16=ctx1.f16)
         ops.copy(ctx1, out=e1.slice(0, 48))
         ops.copy(x, out=e1.slice(48, 3))
         perm = tuple(range(3, 51)) + (0, 1, 2)

@@ -151,6 +151,9 @@ int dcvc_copy_f16(const dcvc_view *src, const dcvc_view *dst, float mul, float s
 /* the same with a binary16 source view (LeakyReLU copies of binary16 ResBlock inputs) */
 int dcvc_copy_f16_f16(const dcvc_view *src, const dcvc_view *dst, float mul, float slope,
                       void *stream);
+/* fewer than 8 fp32 channels into ONE 16-byte binary16 group of dst (zero-padded): the image next
+ * to a binary16 context in ContextualEncoder's first concatenation (video_model.py:186) */
+int dcvc_copy_f16_narrow(const dcvc_view *src, const dcvc_view *dst, void *stream);
 int dcvc_fill(const dcvc_view *dst, float value, void *stream);
 /* 2x2/2 pooling; mode 0 = average (F.avg_pool2d), 1 = max (nn.MaxPool2d) */
 int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream);

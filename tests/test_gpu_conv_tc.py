@@ -169,6 +169,39 @@ def test_tc_conv_planar_shuffle(cin, cout, k, h, w):
     assert torch.equal(from_act(out_ref), from_act(out_pl))
 
 
+@pytest.mark.parametrize("cin,cout,k,h,w,in16", [(32, 128, 3, 40, 48, False), (64, 128, 1, 37, 53, True),
+                                                 (64, 256, 1, 24, 32, True)])
+def test_tc_conv_planar_shuffle_f16_output(cin, cout, k, h, w, in16):
+    """Depth-to-space into a binary16 channel slice (the contextual decoder's last upsampling
+    writes the binary16 recon buffer): the fp32 result rounded once, neighbours untouched."""
+    sd = _sd(cin, cout, k, seed=23)
+    x = _rand(1, cin, h, w, seed=9)
+    c4 = cout // 4
+    net = layers.Net(sd, dev())
+    cw = net.cw("c", shuffle=True)
+    xa = to_act(x)
+    if in16:
+        xa = ops.copy(xa, f16=True)
+    ref32 = ops.conv(xa, cw, shuffle=True, act=0.01)
+    wide = torch.full((2 * h, 2 * w, c4 + 24), 7.0, device=dev(), dtype=torch.float16)
+    out = Act(wide, 8, c4)
+    ops.conv(xa, cw, shuffle=True, act=0.01, out=out)
+    torch.cuda.synchronize()
+    assert torch.equal(wide[:, :, 8:8 + c4], ref32.buf[:, :, :c4].half())
+    assert bool((wide[:, :, :8] == 7.0).all()) and bool((wide[:, :, 8 + c4:] == 7.0).all())
+    with pytest.raises(_lib.DcvcError):       # no residual on this path
+        ops.conv(xa, cw, shuffle=True, res=Act.new(2 * h, 2 * w, c4, dev()), out=out)
+
+
+def test_copy_f16_narrow():
+    x = _rand(1, 3, 21, 35, seed=5)
+    wide = torch.full((21, 35, 56), 7.0, device=dev(), dtype=torch.float16)
+    ops.copy(to_act(x), out=Act(wide, 48, 3))
+    torch.cuda.synchronize()
+    assert torch.equal(wide[:, :, 48:51].cpu(), x[0].permute(1, 2, 0).half())
+    assert bool((wide[:, :, 51:] == 0).all()) and bool((wide[:, :, :48] == 7.0).all())
+
+
 @pytest.mark.parametrize("cin,cout,k,h,w", [(64, 48, 1, 40, 48), (48, 192, 1, 37, 53),
                                             (32, 64, 3, 33, 70), (64, 768, 1, 24, 32),
                                             (16, 40, 3, 24, 200), (128, 128, 1, 68, 120)])
