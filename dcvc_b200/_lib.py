@@ -72,6 +72,7 @@ SIGNATURES = {
     "dcvc_copy_f16_narrow": (c_int, [VP, VP, c_void_p]),
     "dcvc_fill": (c_int, [VP, c_float, c_void_p]),
     "dcvc_pool2": (c_int, [VP, VP, c_int, c_void_p]),
+    "dcvc_pool2_f16": (c_int, [VP, VP, c_int, c_void_p]),
     "dcvc_resize_bilinear": (c_int, [VP, VP, c_float, c_void_p]),
     "dcvc_flow_warp": (c_int, [VP, VP, VP, c_void_p]),
     "dcvc_offset_diversity": (c_int, [VP, VP, VP, c_void_p, c_void_p, VP, c_void_p]),

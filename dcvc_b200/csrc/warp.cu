@@ -169,6 +169,39 @@ __global__ void pool2_v4_kernel(dcvc_view src, dcvc_view dst, int mode, uint32_t
   *reinterpret_cast<float4 *>(dst.data + (size_t)p * dst.cstride + dst.coff + 4 * cq) = v;
 }
 
+// binary16 views on both sides: one thread per (output pixel, 8 channels); max is exact, the
+// average is summed in fp32 and rounded once
+__global__ void pool2_f16_kernel(dcvc_view src, dcvc_view dst, int mode, uint32_t c8n, uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t p = t / c8n, cq = t - p * c8n;
+  const uint32_t y = p / (uint32_t)dst.w, x = p - y * (uint32_t)dst.w;
+  const uint16_t *sp = reinterpret_cast<const uint16_t *>(src.data) +
+                       ((size_t)(2 * y) * src.w + 2 * x) * src.cstride + src.coff + 8 * cq;
+  const size_t row = (size_t)src.w * src.cstride;
+  const uint4 q[4] = {*reinterpret_cast<const uint4 *>(sp), *reinterpret_cast<const uint4 *>(sp + src.cstride),
+                      *reinterpret_cast<const uint4 *>(sp + row),
+                      *reinterpret_cast<const uint4 *>(sp + row + src.cstride)};
+  uint32_t o[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float2 f[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      f[k] = __half22float2(*reinterpret_cast<const __half2 *>(reinterpret_cast<const uint32_t *>(&q[k]) + j));
+    float2 v;
+    if (mode == 0) {
+      v = make_float2((f[0].x + f[1].x + f[2].x + f[3].x) * 0.25f, (f[0].y + f[1].y + f[2].y + f[3].y) * 0.25f);
+    } else {
+      v = make_float2(fmaxf(fmaxf(f[0].x, f[1].x), fmaxf(f[2].x, f[3].x)),
+                      fmaxf(fmaxf(f[0].y, f[1].y), fmaxf(f[2].y, f[3].y)));
+    }
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(o[j]) : "f"(v.y), "f"(v.x));
+  }
+  *reinterpret_cast<uint4 *>(reinterpret_cast<uint16_t *>(dst.data) + (size_t)p * dst.cstride + dst.coff + 8 * cq) =
+      make_uint4(o[0], o[1], o[2], o[3]);
+}
+
 // ATen upsample_bilinear2d, align_corners=False: src = scale*(dst+0.5)-0.5 clamped at 0
 __device__ __forceinline__ void src_index(float scale, int dst, int in_size, int &i0, int &i1,
                                           float &l0, float &l1) {
@@ -494,6 +527,19 @@ extern "C" int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, 
     return DCVC_OK;
   }
   LAUNCH_1D(pool2_kernel, (int64_t)dst->h * dst->w * dst->c, stream, *src, *dst, mode);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_pool2_f16(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || src->c != dst->c || dst->h != src->h / 2 ||
+      dst->w != src->w / 2)
+    return dcvc_fail(DCVC_ERR_ARG, "pool2_f16: bad args");
+  const int64_t total8 = (int64_t)dst->h * dst->w * (dst->c / 8);
+  if (((src->cstride | src->coff | dst->cstride | dst->coff | dst->c) & 7) ||
+      ((reinterpret_cast<uintptr_t>(src->data) | reinterpret_cast<uintptr_t>(dst->data)) & 15) ||
+      total8 >= (1ll << 31))
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "pool2_f16: views must hold whole 16-byte channel groups");
+  LAUNCH_1D(pool2_f16_kernel, total8, stream, *src, *dst, mode, (uint32_t)(dst->c / 8), (uint32_t)total8);
   return DCVC_OK;
 }
 

@@ -146,12 +146,13 @@ def subpel(net, p, x, act=1.0, out=None, scale=None, res=None):
                     res=res)
 
 
-def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, scale=None):
+def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, scale=None,
+              f16_out=False):
     """ResBlock (video_net.py:58-76): lrelu(x) is conv1's input prologue, the second activation
     conv1's epilogue, `x +` (and an optional outer residual/scale) conv2's epilogue."""
     t = ops.conv(x, net.cw(p + ".conv1"), in_slope=slope, act=slope, f16_out=True)
     return ops.conv(t, net.cw(p + ".conv2"), act=slope if end_with_relu else 1.0, res=x,
-                    res2=res2, scale=scale, out=out)
+                    res2=res2, scale=scale, out=out, f16_out=f16_out)
 
 
 def depth_conv(net, p, x, out=None, f16_out=False):
@@ -202,20 +203,23 @@ def rbu(net, p, x, out=None, scale=None):
     return ops.conv(t, net.cw(p + ".conv"), act=0.1, res=up, scale=scale, out=out)
 
 
-def unet(net, p, x, block, out=None):
-    """UNet / UNet2 (video_net.py:129-214); the two skip concatenations are shared buffers."""
+def unet(net, p, x, block, out=None, f16_out=False):
+    """UNet / UNet2 (video_net.py:129-214); the two skip concatenations are shared buffers, read
+    and written by convolutions and the max pool only: binary16 when every level down to the
+    quarter-resolution one is tensor-core sized."""
     dev = x.device
-    cat2 = Act.new(x.h, x.w, 64, dev)
-    cat3 = Act.new(x.h // 2, x.w // 2, 128, dev)
+    f16 = ops.f16_ok(x.h // 4, x.w // 4, 64)
+    cat2 = Act.new(x.h, x.w, 64, dev, f16=f16)
+    cat3 = Act.new(x.h // 2, x.w // 2, 128, dev, f16=f16)
     x1 = block(net, p + ".conv1", x, out=cat2.slice(0, 32))
     x2 = block(net, p + ".conv2", ops.max_pool2(x1), out=cat3.slice(0, 64))
     x3 = block(net, p + ".conv3", ops.max_pool2(x2), f16_out=True)
     for i in range(4):
         x3 = block(net, f"{p}.context_refine.{i}", x3, f16_out=True)
     subpel(net, p + ".up3", x3, out=cat3.slice(64, 64))
-    d3 = block(net, p + ".up_conv3", cat3)
+    d3 = block(net, p + ".up_conv3", cat3, f16_out=f16)
     subpel(net, p + ".up2", d3, out=cat2.slice(32, 32))
-    return block(net, p + ".up_conv2", cat2, out=out)
+    return block(net, p + ".up_conv2", cat2, out=out, f16_out=f16_out)
 
 
 def hyper_enc5(net, p, x):

@@ -206,9 +206,11 @@ def fill(dst, value, stream=None):
 
 def pool2(x, mode, out=None, stream=None):
     if out is None:
-        out = Act.new(x.h // 2, x.w // 2, x.c, x.device)
-    with _Prof("pool2", 0, _nb(x, out)):
-        _lib.check(_lib.lib().dcvc_pool2(x.view(), out.view(), mode, _stream(stream)))
+        out = Act.new(x.h // 2, x.w // 2, x.c, x.device, f16=x.f16)
+    assert out.f16 == x.f16
+    fn = _lib.lib().dcvc_pool2_f16 if x.f16 else _lib.lib().dcvc_pool2
+    with _Prof("pool2" + (" f16" if x.f16 else ""), 0, _nb(x, out)):
+        _lib.check(fn(x.view(), out.view(), mode, _stream(stream)))
     return out
 
 

@@ -198,7 +198,9 @@ class DMC(CompressionModel):
         c1 = ops.offset_diversity(l1, offs, mv, fw, net.sd["align.fusion.bias"],
                                   out=cat1.slice(48, 48))
         c2 = ops.flow_warp(l2, mv2, out=cat2.slice(64, 64))
-        c3 = ops.flow_warp(l3, mv3)
+        # c3 is read by two convolutions and as a second residual: binary16
+        c3 = ops.flow_warp(l3, mv3, out=Act.new(H // 4, W // 4, l3.c, dev,
+                                                f16=ops.f16_ok(H // 4, W // 4, l3.c)))
         # MultiScaleContextFusion
         cf = "context_fusion_net"
         t = layers.subpel(net, cf + ".conv3_up", c3)
@@ -251,16 +253,16 @@ class DMC(CompressionModel):
         cd = "contextual_decoder"
         t = layers.subpel(net, cd + ".up1", y_hat)
         layers.subpel(net, cd + ".up2", t, out=bufs["D3"].slice(0, 96))
-        t = layers.res_block(net, cd + ".res1", bufs["D3"], 0.1, True)
+        t = layers.res_block(net, cd + ".res1", bufs["D3"], 0.1, True, f16_out=True)
         layers.subpel(net, cd + ".up3", t, scale=q, out=bufs["D2"].slice(0, 64))
-        t = layers.res_block(net, cd + ".res2", bufs["D2"], 0.1, True)
+        t = layers.res_block(net, cd + ".res2", bufs["D2"], 0.1, True, f16_out=True)
         layers.subpel(net, cd + ".up4", t, out=bufs["R"].slice(48, 32))
         rg = "recon_generation_net"
         # the reference calls recon_generation_net(recon_image_feature, context1) (:403), so
         # first_conv's input channels are [res 32 | ctx1 48]; the buffer is [ctx1 | res]
         perm = tuple(range(32, 80)) + tuple(range(0, 32))
-        t = ops.conv(bufs["R"], net.cw(rg + ".first_conv", cin_perm=perm))
-        t = layers.unet(net, rg + ".unet_1", t, layers.dcb)
+        t = ops.conv(bufs["R"], net.cw(rg + ".first_conv", cin_perm=perm), f16_out=True)
+        t = layers.unet(net, rg + ".unet_1", t, layers.dcb, f16_out=True)
         feature = layers.unet(net, rg + ".unet_2", t, layers.dcb)
         # 3 -> 4 output channels (a zero filter): the image pixel is a 16-byte group either way,
         # and whole groups take the TMA-store epilogue instead of the scalar one

@@ -157,6 +157,8 @@ int dcvc_copy_f16_narrow(const dcvc_view *src, const dcvc_view *dst, void *strea
 int dcvc_fill(const dcvc_view *dst, float value, void *stream);
 /* 2x2/2 pooling; mode 0 = average (F.avg_pool2d), 1 = max (nn.MaxPool2d) */
 int dcvc_pool2(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream);
+/* the same between two binary16 views (the UNet's skip buffers, video_net.py:129-214) */
+int dcvc_pool2_f16(const dcvc_view *src, const dcvc_view *dst, int mode, void *stream);
 /* F.interpolate(mode='bilinear', align_corners=False) to dst's size, times `mul` */
 int dcvc_resize_bilinear(const dcvc_view *src, const dcvc_view *dst, float mul, void *stream);
 /* flow_warp: grid_sample(bilinear, border, align_corners=True) at (x + flow[0], y + flow[1]) */

@@ -193,6 +193,20 @@ def test_tc_conv_planar_shuffle_f16_output(cin, cout, k, h, w, in16):
         ops.conv(xa, cw, shuffle=True, res=Act.new(2 * h, 2 * w, c4, dev()), out=out)
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_pool2_f16(mode):
+    c, h, w = 32, 22, 38
+    x = _rand(1, c, h, w, seed=17)
+    wide = ops.copy(to_act(torch.cat((x, x), 1)), f16=True)          # 64 channels, pool a slice
+    out = Act(torch.full((h // 2, w // 2, 48), 7.0, device=dev(), dtype=torch.float16), 8, c)
+    ops.pool2(Act(wide.buf, 32, c), mode, out=out)
+    torch.cuda.synchronize()
+    xh = x.half().float()
+    ref = (F.avg_pool2d(xh, 2) if mode == 0 else F.max_pool2d(xh, 2)).half()
+    assert torch.equal(out.buf[:, :, 8:8 + c].cpu(), ref[0].permute(1, 2, 0))
+    assert bool((out.buf[:, :, :8] == 7.0).all()) and bool((out.buf[:, :, 8 + c:] == 7.0).all())
+
+
 def test_copy_f16_narrow():
     x = _rand(1, 3, 21, 35, seed=5)
     wide = torch.full((21, 35, 56), 7.0, device=dev(), dtype=torch.float16)
