@@ -140,10 +140,10 @@ class Net:
 
 
 # ------------------------------------------------------------------------------- blocks
-def subpel(net, p, x, act=1.0, out=None, scale=None, res=None):
+def subpel(net, p, x, act=1.0, out=None, scale=None, res=None, f16_out=False):
     """subpel_conv1x1/3x3 (layers.py:23-39): conv to 4C with the depth-to-space store fused."""
     return ops.conv(x, net.cw(p + ".0", shuffle=True), shuffle=True, act=act, out=out, scale=scale,
-                    res=res)
+                    res=res, f16_out=f16_out)
 
 
 def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, scale=None,
@@ -199,7 +199,7 @@ def rbws(net, p, x, out=None):
 def rbu(net, p, x, out=None, scale=None):
     """ResidualBlockUpsample (layers.py:76-101)."""
     up = subpel(net, p + ".upsample", x)
-    t = subpel(net, p + ".subpel_conv", x, act=0.01)
+    t = subpel(net, p + ".subpel_conv", x, act=0.01, f16_out=True)
     return ops.conv(t, net.cw(p + ".conv"), act=0.1, res=up, scale=scale, out=out)
 
 

@@ -94,7 +94,9 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     if cw.gate:
         ec //= 2
     if out is None:
-        f16_out = (f16_out and f16_ok(eh, ew, ec) and cw.w_tc is not None and not shuffle
+        # (depth-to-space: only the planar-packed epilogue writes binary16, without residuals)
+        f16_out = (f16_out and f16_ok(eh, ew, ec) and cw.w_tc is not None
+                   and (not shuffle or (cw.tc_planar and res is None and ho * wo >= TC_MIN_PIXELS))
                    and not cw.gate and res2 is None and out2 is None)
         out = Act.new(eh, ew, ec, x.device, f16=f16_out)
     if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= TC_MIN_PIXELS:

@@ -203,11 +203,11 @@ class DMC(CompressionModel):
                                                 f16=ops.f16_ok(H // 4, W // 4, l3.c)))
         # MultiScaleContextFusion
         cf = "context_fusion_net"
-        t = layers.subpel(net, cf + ".conv3_up", c3)
+        t = layers.subpel(net, cf + ".conv3_up", c3, f16_out=True)
         layers.res_block(net, cf + ".res_block3_up", t, out=cat2.slice(0, 64))
         t = ops.conv(c3, net.cw(cf + ".conv3_out"), f16_out=True)
         ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3, out=bufs["ctx3"])
-        t = layers.subpel(net, cf + ".conv2_up", cat2)
+        t = layers.subpel(net, cf + ".conv2_up", cat2, f16_out=True)
         layers.res_block(net, cf + ".res_block2_up", t, out=cat1.slice(0, 48))
         t = ops.conv(cat2, net.cw(cf + ".conv2_out"), f16_out=True)
         ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2, out=bufs["ctx2"])
