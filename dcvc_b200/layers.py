@@ -72,8 +72,9 @@ class Net:
     def cw(self, name, gate=False, cin_perm=None, shuffle=False, cout_pad=None):
         """KN-packed conv weights: [kh*kw][cin][cout]; gate=True interleaves the two halves of the
         output channels (ConvFFN2's chunk(2), layers.py:193-195) so the gate pairs are adjacent;
-        cin_perm reorders the input channels (new channel i reads reference channel cin_perm[i])
-        so a concatenated input can be laid out alignment-friendly; shuffle=True marks a
+        cin_perm reorders the input channels (new channel i reads reference channel cin_perm[i],
+        -1 = a padding channel with zero weights) so a concatenated input can be laid out
+        alignment-friendly; shuffle=True marks a
         depth-to-space conv: its tensor-core copy is packed planar (see _pack_tc); cout_pad
         appends zero filters (and zero biases) up to that many output channels, so that a
         3-channel image convolution qualifies for the vectorised epilogues."""
@@ -84,8 +85,10 @@ class Net:
             b = self.sd.get(name + ".bias")
             cout, cin, kh, kw = w.shape
             assert kh == kw
-            if cin_perm is not None:
-                w = w[:, torch.tensor(cin_perm, device=w.device)]
+            if cin_perm is not None:       # an entry of -1 is a zero (padding) input channel
+                idx = torch.tensor(cin_perm, device=w.device)
+                w = w[:, idx.clamp(min=0)] * (idx >= 0).to(w.dtype).view(1, -1, 1, 1)
+                cin = len(cin_perm)
             if cout_pad is not None and cout_pad > cout:
                 w = torch.cat((w, w.new_zeros((cout_pad - cout, cin, kh, kw))), 0)
                 if b is not None:

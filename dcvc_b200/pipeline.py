@@ -14,7 +14,12 @@ convolutions.
 `EncDecPipeline.push(x)` enqueues the decode of the previous frame on the decoder stream, then the
 encode of `x` on the encoder stream, and returns when the encoder's stream bytes are on the host.
 """
+import os
+
 import torch
+
+# DCVC_PIPE_ENCODE_FIRST=1: enqueue encode(t) before decode(t-1) inside push()
+ENCODE_FIRST = int(os.environ.get("DCVC_PIPE_ENCODE_FIRST", "0"))
 
 
 class EncDecPipeline:
@@ -49,18 +54,27 @@ class EncDecPipeline:
         """x_padded: [1,3,H,W] on the device, produced on (or synchronised with) `enc_stream`.
         Returns (stream bytes of this frame, decoded frame of the PREVIOUS push or None); the
         decoded frame is still being produced on `dec_stream` when this returns."""
-        decoded = self._decode(self._pending) if self._pending is not None else None
         ph, pw = x_padded.shape[2], x_padded.shape[3]
+        decoded, done = None, False
+        if ENCODE_FIRST == 0 and self._pending is not None:
+            decoded, done = self._decode(self._pending), True
         with torch.cuda.stream(self.enc_stream):
             if self.idx % self.intra_period == 0:
                 enc = self.i_enc.compress(x_padded, self.q_in_ckpt, self.q_index)
                 self.enc_dpb = {"ref_frame": enc["x_hat"], "ref_feature": None,
                                 "ref_mv_feature": None, "ref_y": None, "ref_mv_y": None}
+                stream = enc["bit_stream"]
             else:
                 enc = self.p_enc.compress(x_padded, self.enc_dpb, self.q_in_ckpt, self.q_index,
-                                          self.idx % 4)
+                                          self.idx % 4, defer=True)
                 self.enc_dpb = enc["dpb"]
-        stream = enc["bit_stream"]
+                stream = None
+        if not done and self._pending is not None:
+            # the previous frame's decode is enqueued while the GPU works on this frame's encode;
+            # only then does the host wait for the coder's event
+            decoded = self._decode(self._pending)
+        if stream is None:
+            stream = enc["bit_stream"]()
         self._pending = (self.idx, stream, ph, pw)
         self.idx += 1
         self.bits += len(stream) * 8

@@ -57,21 +57,26 @@ class DMC(CompressionModel):
             p1.append(ops.avg_pool2(p1[lv]))
             p2.append(ops.avg_pool2(p2[lv]))
         flow = Act.new(p2[L - 1].h // 2, p2[L - 1].w // 2, 2, dev, zero=True)
+        # level input, 16 channels [im1 3 | warp 3 | 0 0 | flow_up 2 | 0 0 | 0 0 0 0]: a 7x7 tap is
+        # one K=16 MMA whatever the channel count, and [flow_up | 0 0] is a whole 16-byte group,
+        # so conv5 (padded to 4 filters) takes the vectorised residual epilogue
+        perm = (0, 1, 2, 3, 4, 5, -1, -1, 6, 7, -1, -1, -1, -1, -1, -1)
         for lv in range(L):
             k = L - 1 - lv
             h, w = p1[k].h, p1[k].w
-            inp = Act.new(h, w, 8, dev)
+            inp = Act.new(h, w, 16, dev, zero=True)
             ops.copy(p1[k], out=inp.slice(0, 3))
-            up = ops.resize_bilinear(flow, h, w, mul=2.0, out=inp.slice(6, 2))
+            up = ops.resize_bilinear(flow, h, w, mul=2.0, out=inp.slice(8, 2))
             ops.flow_warp(p2[k], up, out=inp.slice(3, 3))
             p = f"optic_flow.moduleBasic.{lv}"
-            if ops.f16_ok(h, w, 8):
-                inp = ops.copy(inp, f16=True)      # 7x7 on 8 channels: one K=16 MMA per tap
-            t = ops.conv(inp, net.cw(p + ".conv1"), act=0.0, f16_out=True)
+            res = inp.slice(8, 4)
+            if ops.f16_ok(h, w, 16):
+                inp = ops.copy(inp, f16=True)
+            t = ops.conv(inp, net.cw(p + ".conv1", cin_perm=perm), act=0.0, f16_out=True)
             t = ops.conv(t, net.cw(p + ".conv2"), act=0.0, f16_out=True)
             t = ops.conv(t, net.cw(p + ".conv3"), act=0.0, f16_out=True)
             t = ops.conv(t, net.cw(p + ".conv4"), act=0.0, f16_out=True)
-            flow = ops.conv(t, net.cw(p + ".conv5"), res=up)
+            flow = ops.conv(t, net.cw(p + ".conv5", cout_pad=4), res=res).slice(0, 2)
         return flow
 
     def _mv_enc(self, est_mv, ref_mv_feature, q):
@@ -106,9 +111,10 @@ class DMC(CompressionModel):
         t = layers.rbu(net, m + ".dec_1.3", t)
         feature = layers.dcb(net, m + ".dec_1.4", t)
         t = layers.rbu(net, m + ".dec_2", feature, scale=q)
-        t = layers.dcb(net, m + ".dec_3.0", t)     # fp32: the 8-filter subpel has no f16 packing
-        mv = layers.subpel(net, m + ".dec_3.1", t)
-        return mv, feature
+        t = layers.dcb(net, m + ".dec_3.0", t, f16_out=True)
+        # 8 -> 16 filters (two zero channels per pixel): planar packing, vectorised epilogue
+        mv4 = ops.conv(t, net.cw(m + ".dec_3.1.0", shuffle=True, cout_pad=16), shuffle=True)
+        return mv4.slice(0, 2), feature
 
     # ------------------------------------------------------------------ priors
     def _mv_params(self, mv_z_hat, dpb, catb, c):
@@ -314,7 +320,7 @@ class DMC(CompressionModel):
         return new_dpb, (mv_z_hat, mv_z_sym), (z_hat, z_sym), mv_coded, coded
 
     # ------------------------------------------------------------------ reference API
-    def compress(self, x, dpb, q_in_ckpt, q_index, frame_idx):
+    def compress(self, x, dpb, q_in_ckpt, q_index, frame_idx, defer=False):
         """video_model.py:425-481; stream order mv_z, z, mv_y parts 0..3, y parts 0..3.
         The coder kernels are enqueued BEFORE the frame's reconstruction (the reference hands the
         symbols to its encoder thread at the same point, :449-476, and reconstructs after); the
@@ -332,6 +338,8 @@ class DMC(CompressionModel):
 
         new_dpb, _, _, _, _ = self._encode_side(x, dpb, q_in_ckpt, q_index, frame_idx, True,
                                                 coder=coder)
+        if defer:      # (pipeline.py) "bit_stream" is a callable: the host wait happens when called
+            return {"dpb": new_dpb, "bit_stream": ec.get_encoded_stream}
         return {"dpb": new_dpb, "bit_stream": ec.get_encoded_stream()}
 
     def decompress(self, dpb, string, height, width, q_in_ckpt, q_index, frame_idx):
