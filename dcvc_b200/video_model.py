@@ -225,8 +225,11 @@ class DMC(CompressionModel):
         # recon input [ctx1 48 | res 32]: two convolutions write it, two read it -> binary16
         # (the encoder's stride-2 conv1 reads ctx1 too: its output must be tensor-core sized)
         R = Act.new(H, W, 80, dev, f16=ops.f16_ok(H // 2, W // 2, 80))
-        D2 = Act.new(H // 2, W // 2, 128, dev)             # decoder res2 input [f 64 | ctx2 64]
-        D3 = Act.new(H // 4, W // 4, 192, dev)             # decoder res1 input [f 96 | ctx3 96]
+        # decoder res2 / res1 inputs [f 64 | ctx2 64], [f 96 | ctx3 96]: convolutions, LeakyReLU
+        # copies and the encoder's own concatenations read them; ctx3 also feeds a stride-2 conv
+        f16 = ops.f16_ok(H // 8, W // 8, 64)
+        D2 = Act.new(H // 2, W // 2, 128, dev, f16=f16)
+        D3 = Act.new(H // 4, W // 4, 192, dev, f16=f16)
         return {"R": R, "D2": D2, "D3": D3, "ctx1": R.slice(0, 48), "ctx2": D2.slice(64, 64),
                 "ctx3": D3.slice(96, 96)}
 
@@ -240,15 +243,16 @@ class DMC(CompressionModel):
         ops.copy(ctx1, out=e1.slice(0, 48))
         ops.copy(x, out=e1.slice(48, 3))
         perm = tuple(range(3, 51)) + (0, 1, 2)
-        e2 = Act.new(x.h // 2, x.w // 2, 128, dev)
+        e2 = Act.new(x.h // 2, x.w // 2, 128, dev, f16=ctx2.f16)
         ops.conv(e1, net.cw("contextual_encoder.conv1", cin_perm=perm), stride=2,
                  out=e2.slice(0, 64))
         ops.copy(ctx2, out=e2.slice(64, 64))
-        t = layers.res_block(net, "contextual_encoder.res1", e2, 0.1, True, scale=q)
-        e3 = Act.new(x.h // 4, x.w // 4, 192, dev)
+        t = layers.res_block(net, "contextual_encoder.res1", e2, 0.1, True, scale=q,
+                             f16_out=ctx3.f16)
+        e3 = Act.new(x.h // 4, x.w // 4, 192, dev, f16=ctx3.f16)
         ops.conv(t, net.cw("contextual_encoder.conv2"), stride=2, out=e3.slice(0, 96))
         ops.copy(ctx3, out=e3.slice(96, 96))
-        t = layers.res_block(net, "contextual_encoder.res2", e3, 0.1, True)
+        t = layers.res_block(net, "contextual_encoder.res2", e3, 0.1, True, f16_out=ctx3.f16)
         t = ops.conv(t, net.cw("contextual_encoder.conv3"), stride=2)
         return ops.conv(t, net.cw("contextual_encoder.conv4"), stride=2)
 
