@@ -41,6 +41,8 @@ for cin, cout, k, s, h, w, kw in SHAPES:
     if os.environ.get("BENCH_RES") and not kw.get("shuffle"):      # fp32 residual (res_block conv2)
         ho_, wo_ = (h + 2 * (k // 2) - k) // s + 1, (w + 2 * (k // 2) - k) // s + 1
         kw = dict(kw, res=Act(torch.randn(ho_, wo_, (cout + 3) // 4 * 4, device=dev), 0, cout))
+        if os.environ.get("BENCH_RES") == "h":                      # binary16 residual
+            kw["res"] = ops.copy(Act(torch.randn(ho_, wo_, (cout + 7) // 8 * 8, device=dev), 0, cout), f16=True)
         if os.environ.get("BENCH_RES") == "2":
             kw["res2"] = Act(torch.randn(ho_, wo_, (cout + 3) // 4 * 4, device=dev), 0, cout)
     out = ops.conv(x, cw, stride=s, **kw)
@@ -61,5 +63,5 @@ for cin, cout, k, s, h, w, kw in SHAPES:
     by = (2.0 if x.f16 else 4.0) * h * w * cin + (2.0 if out.f16 else 4.0) * ho * wo * cout + 4.0 * cout * cin * k * k
     name += (" f16in" if x.f16 else "") + (" f16out" if out.f16 else "") + (" +res" if "res" in kw else "")
     if "res" in kw:
-        by += 4.0 * ho * wo * cout
+        by += (2.0 if kw["res"].f16 else 4.0) * ho * wo * cout
     print(f"{name:72s} {ms:8.3f} ms {fl / ms / 1e9:8.1f} TFLOP/s {by / ms / 1e6:8.0f} GB/s", flush=True)
