@@ -51,6 +51,8 @@ struct TcArgs {
   int f16_out;    // TMA-store epilogue writes binary16 (64-byte rows, 64B swizzle)
   int f16_res;    // res1 holds binary16 (fetched as 64-byte rows, 64B swizzle)
   int f16_res2;   // res2 holds binary16 (TMA-store epilogue: direct 16-byte row loads)
+  int res_direct; // TMA-store epilogue: binary16 res1 by direct row loads issued ahead of the
+                  // accumulator wait (registers), not by TMA into the outgoing tile
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
 
@@ -935,7 +937,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const int nchunks = (a.n_tile + 31) >> 5;
     const int tw_mask = a.tw - 1, tw_shift = 31 - __clz(a.tw);
     const int bx = (q * 32) & tw_mask, by = (q * 32) >> tw_shift;
-    const bool has_res = a.res1.data != nullptr, has_res2 = a.res2.data != nullptr;
+    const bool direct1 = a.res1.data != nullptr && a.res_direct;
+    const bool has_res = a.res1.data != nullptr && !direct1, has_res2 = a.res2.data != nullptr;
+    const bool pre2 = has_res2 && a.f16_res2;
     const int wb = a.tw < 32 ? a.tw : 32, wb_mask = wb - 1, wb_shift = 31 - __clz(wb);
     const uint32_t res_bytes = a.f16_res ? 2048u : 4096u;
     const bool mixed = has_res && (a.f16_res != a.f16_out);   // residual / result rows differ in pitch
@@ -955,6 +959,27 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       tile_coords(a, tile, mt, nt, ty, tx);
       const int n0 = ci * 32, c0 = nt * a.n_tile + n0, x0 = tx * a.tw + bx, y0 = ty * a.th + by;
       const uint32_t as = lt & 1u, aph = (lt >> 1) & 1u;
+      // binary16 residual rows of this thread's pixel: requested before the accumulator wait, so
+      // their latency hides behind the MMAs of the tile
+      uint4 pr1[4], pr2[4];
+      if (direct1 || pre2) {
+        const int px = x0 + (lane & wb_mask), py = y0 + (lane >> wb_shift);
+        const bool inb = px < a.wout && py < a.hout;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          pr1[j] = pr2[j] = make_uint4(0u, 0u, 0u, 0u);
+          if (inb && c0 + 8 * j < a.cout_w) {
+            if (direct1)
+              pr1[j] = __ldg(reinterpret_cast<const uint4 *>(
+                           reinterpret_cast<const uint16_t *>(a.res1.data) +
+                           ((size_t)py * a.res1.w + px) * a.res1.cstride + a.res1.coff + c0) + j);
+            if (pre2)
+              pr2[j] = __ldg(reinterpret_cast<const uint4 *>(
+                           reinterpret_cast<const uint16_t *>(a.res2.data) +
+                           ((size_t)py * a.res2.w + px) * a.res2.cstride + a.res2.coff + c0) + j);
+          }
+        }
+      }
       if (ci == part) {                                   // first chunk of this tile for the warp
         mbar_wait_warp(tfull_bar(as), aph, lane);
         tc_fence_after();
@@ -985,6 +1010,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if (a.out_slope != 1.f) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = lrelu01(v[j], a.out_slope);
+        }
+        if (direct1) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float2 f;
+            f = unpack_h2(pr1[j].x); v[8 * j] += f.x;     v[8 * j + 1] += f.y;
+            f = unpack_h2(pr1[j].y); v[8 * j + 2] += f.x; v[8 * j + 3] += f.y;
+            f = unpack_h2(pr1[j].z); v[8 * j + 4] += f.x; v[8 * j + 5] += f.y;
+            f = unpack_h2(pr1[j].w); v[8 * j + 6] += f.x; v[8 * j + 7] += f.y;
+          }
         }
         if (has_res) {
           mbar_wait_warp(res_bar(2 * we + b), b ? rph1 : rph0, lane);
@@ -1017,12 +1052,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           if (px < a.wout && py < a.hout) {
             const size_t off = ((size_t)py * a.res2.w + px) * a.res2.cstride + a.res2.coff + c0;
             if (a.f16_res2) {
-              const uint4 *r2 = reinterpret_cast<const uint4 *>(
-                  reinterpret_cast<const uint16_t *>(a.res2.data) + off);
 #pragma unroll
               for (int j = 0; j < 4; ++j)
                 if (c0 + 8 * j < a.cout_w) {
-                  const uint4 u = __ldg(r2 + j);
+                  const uint4 u = pr2[j];
                   float2 f;
                   f = unpack_h2(u.x); v[8 * j] += f.x;     v[8 * j + 1] += f.y;
                   f = unpack_h2(u.y); v[8 * j + 2] += f.x; v[8 * j + 3] += f.y;
@@ -1401,6 +1434,10 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   const bool f16 = d->in_f16 != 0;
   a.f16_in = f16; a.f16_out = d->out_f16 != 0; a.f16_res = d->res1.data && d->res1_f16;
   a.f16_res2 = d->res2.data && d->res2_f16;
+  static const int res_direct_on = getenv("DCVC_TC_RES_DIRECT") ? atoi(getenv("DCVC_TC_RES_DIRECT")) : 1;
+  // measured: helps the full-resolution 3x3 convs with up to 48 filters (0.24 -> 0.21 ms), costs a
+  // few % on wide 1x1 tiles whose TMA residual is already hidden; res_direct_on == 2 forces it
+  a.res_direct = res_direct_on && a.f16_res && (res_direct_on == 2 || (d->ksize >= 3 && d->cout_w <= 48));
   if (f16) dcvc_conv_tc_geometry16(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
   else dcvc_conv_tc_geometry(d->cout_w, d->in.c, &n_pad, &cin_pad, &a.kc);
   a.kcb = a.kc * (f16 ? 2 : 4);
