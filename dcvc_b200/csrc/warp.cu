@@ -371,7 +371,7 @@ __global__ void offset_diversity_kernel(dcvc_view x, dcvc_view offs, dcvc_view f
 // the same with the offset / mask channels of a sample pair fetched as one float4 / float2 per
 // corner of the x2 resize (offs view 16-byte aligned), corner addresses computed once, 32-bit
 // indices.  Every value is produced by the same expression as above: results are bit-identical.
-template <bool HO>   // HO: out holds binary16 elements
+template <bool HO, bool X2>   // HO: out holds binary16 elements; X2: 8-byte loads from x
 __global__ void __launch_bounds__(256)
 offset_diversity_v4_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
                            const float *__restrict__ fw, const float *__restrict__ fb,
@@ -410,14 +410,31 @@ offset_diversity_v4_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
     const Bilin b = warp_coords(px, py, 40.0f * tanhf(oxs[k]) + fl.x, 40.0f * tanhf(oys[k]) + fl.y,
                                 x.w, x.h);
     const int c = (n & 15) * 3;
-    const float *c00 = x.data + vidx(x, b.y0, b.x0) + c, *c01 = x.data + vidx(x, b.y0, b.x1) + c;
-    const float *c10 = x.data + vidx(x, b.y1, b.x0) + c, *c11 = x.data + vidx(x, b.y1, b.x1) + c;
+    // the group's 3 channels (12 bytes at a 4-byte-aligned offset) lie inside the 16-byte window
+    // that starts at the 8-byte boundary below them: two 8-byte loads per corner instead of three
+    // 4-byte ones (the kernel is bound by L1 sector requests); X2: the view allows it
+    const int c2 = c & ~1, odd = c & 1;
+    auto corner = [&](int yy, int xx, float (&o)[3]) {
+      const float *cp = x.data + vidx(x, yy, xx);
+      if (X2) {
+        const float2 lo = __ldg(reinterpret_cast<const float2 *>(cp + c2));
+        const float2 hi = __ldg(reinterpret_cast<const float2 *>(cp + c2 + 2));
+        o[0] = odd ? lo.y : lo.x; o[1] = odd ? hi.x : lo.y; o[2] = odd ? hi.y : hi.x;
+      } else {
+        o[0] = __ldg(cp + c); o[1] = __ldg(cp + c + 1); o[2] = __ldg(cp + c + 2);
+      }
+    };
+    float q00[3], q01[3] = {0.f, 0.f, 0.f}, q10[3] = {0.f, 0.f, 0.f}, q11[3] = {0.f, 0.f, 0.f};
+    corner(b.y0, b.x0, q00);
+    if (b.vx1) corner(b.y0, b.x1, q01);
+    if (b.vy1) corner(b.y1, b.x0, q10);
+    if (b.vx1 && b.vy1) corner(b.y1, b.x1, q11);
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
-      float s = b.nw * __ldg(c00 + j);
-      if (b.vx1) s += b.ne * __ldg(c01 + j);
-      if (b.vy1) s += b.sw * __ldg(c10 + j);
-      if (b.vx1 && b.vy1) s += b.se * __ldg(c11 + j);
+      float s = b.nw * q00[j];
+      if (b.vx1) s += b.ne * q01[j];
+      if (b.vy1) s += b.sw * q10[j];
+      if (b.vx1 && b.vy1) s += b.se * q11[j];
       v[k * 3 + j] = s * mask;
     }
   }
@@ -582,8 +599,13 @@ extern "C" int dcvc_offset_diversity(const dcvc_view *x, const dcvc_view *offs_h
                    ((flow->cstride | flow->coff) & 1) == 0 &&
                    (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total < (1ll << 31);
   if (vec) {
-    offset_diversity_v4_kernel<false><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
-        *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
+    const bool x2 = ((x->cstride | x->coff) & 1) == 0 && (reinterpret_cast<uintptr_t>(x->data) & 7) == 0;
+    if (x2)
+      offset_diversity_v4_kernel<false, true><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+          *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
+    else
+      offset_diversity_v4_kernel<false, false><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+          *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
     DCVC_LAUNCHED();
     return DCVC_OK;
   }
@@ -620,8 +642,13 @@ extern "C" int dcvc_offset_diversity_f16(const dcvc_view *x, const dcvc_view *of
                    ((flow->cstride | flow->coff) & 1) == 0 &&
                    (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total < (1ll << 31);
   if (!vec) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "offset_diversity_f16: unaligned offset/flow views");
-  offset_diversity_v4_kernel<true><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
+  const bool x2 = ((x->cstride | x->coff) & 1) == 0 && (reinterpret_cast<uintptr_t>(x->data) & 7) == 0;
+  if (x2)
+    offset_diversity_v4_kernel<true, true><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
+  else
+    offset_diversity_v4_kernel<true, false><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }
