@@ -77,7 +77,9 @@ SIGNATURES = {
     "dcvc_flow_warp": (c_int, [VP, VP, VP, c_void_p]),
     "dcvc_offset_diversity": (c_int, [VP, VP, VP, c_void_p, c_void_p, VP, c_void_p]),
     "dcvc_offset_diversity_f16": (c_int, [VP, VP, VP, c_void_p, c_void_p, VP, c_void_p]),
+    "dcvc_offset_diversity_f16_f16": (c_int, [VP, VP, VP, c_void_p, c_void_p, VP, c_void_p]),
     "dcvc_flow_warp_f16": (c_int, [VP, VP, VP, c_void_p]),
+    "dcvc_flow_warp_f16_f16": (c_int, [VP, VP, VP, c_void_p]),
     "dcvc_quad_bits_ws_bytes": (c_size_t, [c_int64]),
     "dcvc_quad_step_enc": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p]),

@@ -290,7 +290,14 @@ __global__ void flow_warp_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out) 
 }
 
 // float4 path: one thread per (pixel, 4 channels); the four bilinear taps are 16-byte gathers
-template <bool HO>   // HO: out holds binary16 elements
+__device__ __forceinline__ float4 ld4h(const float *data, size_t off_elems) {   // 4 binary16 -> fp32
+  const uint2 u = *reinterpret_cast<const uint2 *>(reinterpret_cast<const uint16_t *>(data) + off_elems);
+  const float2 lo = __half22float2(*reinterpret_cast<const __half2 *>(&u.x));
+  const float2 hi = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+  return make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+
+template <bool HO, bool HS>   // HO / HS: out / feat hold binary16 elements
 __global__ void flow_warp_v4_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out, uint32_t c4n,
                                     uint32_t total) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -299,21 +306,25 @@ __global__ void flow_warp_v4_kernel(dcvc_view feat, dcvc_view flow, dcvc_view ou
   const uint32_t y = p / (uint32_t)out.w, x = p - y * (uint32_t)out.w;
   const float2 fl = *reinterpret_cast<const float2 *>(flow.data + (size_t)p * flow.cstride + flow.coff);
   const Bilin b = warp_coords((int)x, (int)y, fl.x, fl.y, feat.w, feat.h);
-  const float *base = feat.data + feat.coff + 4 * cq;
+  const size_t cbase = (size_t)feat.coff + 4 * cq;
   const size_t r0 = (size_t)b.y0 * feat.w, r1 = (size_t)b.y1 * feat.w;
+  auto tap = [&](size_t pix) {
+    const size_t off = cbase + pix * feat.cstride;
+    return HS ? ld4h(feat.data, off) : *reinterpret_cast<const float4 *>(feat.data + off);
+  };
   // same accumulation order as warp_sample (dropped corners contribute nothing)
-  float4 a = *reinterpret_cast<const float4 *>(base + (r0 + b.x0) * feat.cstride);
+  float4 a = tap(r0 + b.x0);
   float4 v = make_float4(b.nw * a.x, b.nw * a.y, b.nw * a.z, b.nw * a.w);
   if (b.vx1) {
-    a = *reinterpret_cast<const float4 *>(base + (r0 + b.x1) * feat.cstride);
+    a = tap(r0 + b.x1);
     v.x += b.ne * a.x; v.y += b.ne * a.y; v.z += b.ne * a.z; v.w += b.ne * a.w;
   }
   if (b.vy1) {
-    a = *reinterpret_cast<const float4 *>(base + (r1 + b.x0) * feat.cstride);
+    a = tap(r1 + b.x0);
     v.x += b.sw * a.x; v.y += b.sw * a.y; v.z += b.sw * a.z; v.w += b.sw * a.w;
   }
   if (b.vx1 && b.vy1) {
-    a = *reinterpret_cast<const float4 *>(base + (r1 + b.x1) * feat.cstride);
+    a = tap(r1 + b.x1);
     v.x += b.se * a.x; v.y += b.se * a.y; v.z += b.se * a.z; v.w += b.se * a.w;
   }
   if (HO) {
@@ -371,7 +382,7 @@ __global__ void offset_diversity_kernel(dcvc_view x, dcvc_view offs, dcvc_view f
 // the same with the offset / mask channels of a sample pair fetched as one float4 / float2 per
 // corner of the x2 resize (offs view 16-byte aligned), corner addresses computed once, 32-bit
 // indices.  Every value is produced by the same expression as above: results are bit-identical.
-template <bool HO, bool X2>   // HO: out holds binary16 elements; X2: 8-byte loads from x
+template <bool HO, bool X2, bool HS = false>   // HO: binary16 out; X2: 8-byte loads from x; HS: binary16 x
 __global__ void __launch_bounds__(256)
 offset_diversity_v4_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
                            const float *__restrict__ fw, const float *__restrict__ fb,
@@ -415,6 +426,16 @@ offset_diversity_v4_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
     // 4-byte ones (the kernel is bound by L1 sector requests); X2: the view allows it
     const int c2 = c & ~1, odd = c & 1;
     auto corner = [&](int yy, int xx, float (&o)[3]) {
+      if (HS) {
+        // 3 binary16 channels (6 bytes at a 2-byte-aligned offset) inside two aligned 4-byte words
+        const uint16_t *hp = reinterpret_cast<const uint16_t *>(x.data) + vidx(x, yy, xx);
+        const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t *>(hp + c2));
+        const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t *>(hp + c2 + 2));
+        const float2 lo = __half22float2(*reinterpret_cast<const __half2 *>(&w0));
+        const float2 hi = __half22float2(*reinterpret_cast<const __half2 *>(&w1));
+        o[0] = odd ? lo.y : lo.x; o[1] = odd ? hi.x : lo.y; o[2] = odd ? hi.y : hi.x;
+        return;
+      }
       const float *cp = x.data + vidx(x, yy, xx);
       if (X2) {
         const float2 lo = __ldg(reinterpret_cast<const float2 *>(cp + c2));
@@ -578,7 +599,7 @@ extern "C" int dcvc_flow_warp(const dcvc_view *feat, const dcvc_view *flow, cons
   const int64_t total4 = (int64_t)out->h * out->w * (out->c / 4);
   if (view_al16(feat) && view_al16(out) && ((flow->cstride | flow->coff) & 1) == 0 &&
       (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total4 < (1ll << 31)) {
-    LAUNCH_1D(flow_warp_v4_kernel<false>, total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
+    LAUNCH_1D((flow_warp_v4_kernel<false, false>), total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
               (uint32_t)total4);
     return DCVC_OK;
   }
@@ -624,8 +645,44 @@ extern "C" int dcvc_flow_warp_f16(const dcvc_view *feat, const dcvc_view *flow, 
                   ((flow->cstride | flow->coff) & 1) == 0 &&
                   (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total4 < (1ll << 31);
   if (!ok) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "flow_warp_f16: views must hold whole 4-channel groups");
-  LAUNCH_1D(flow_warp_v4_kernel<true>, total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
+  LAUNCH_1D((flow_warp_v4_kernel<true, false>), total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
             (uint32_t)total4);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_flow_warp_f16_f16(const dcvc_view *feat, const dcvc_view *flow, const dcvc_view *out,
+                                      void *stream) {
+  if (!view_ok(feat) || !view_ok(flow) || !view_ok(out) || flow->c != 2 || out->c != feat->c ||
+      out->h != flow->h || out->w != flow->w)
+    return dcvc_fail(DCVC_ERR_ARG, "flow_warp_f16_f16: bad args");
+  const int64_t total4 = (int64_t)out->h * out->w * (out->c / 4);
+  const bool ok = ((feat->cstride | feat->coff | out->cstride | out->coff | out->c) & 3) == 0 &&
+                  ((reinterpret_cast<uintptr_t>(feat->data) | reinterpret_cast<uintptr_t>(out->data)) & 7) == 0 &&
+                  ((flow->cstride | flow->coff) & 1) == 0 &&
+                  (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total4 < (1ll << 31);
+  if (!ok) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "flow_warp_f16_f16: views must hold whole 4-channel groups");
+  LAUNCH_1D((flow_warp_v4_kernel<true, true>), total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
+            (uint32_t)total4);
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_offset_diversity_f16_f16(const dcvc_view *x, const dcvc_view *offs_half,
+                                             const dcvc_view *flow, const float *fusion_w,
+                                             const float *fusion_b, const dcvc_view *out, void *stream) {
+  if (!view_ok(x) || !view_ok(offs_half) || !view_ok(flow) || !view_ok(out) || !fusion_w ||
+      x->c != 48 || offs_half->c != 96 || flow->c != 2 || out->c != 48 || out->h != x->h ||
+      out->w != x->w || flow->h != x->h || flow->w != x->w)
+    return dcvc_fail(DCVC_ERR_ARG, "offset_diversity_f16_f16: bad args");
+  const int64_t total = (int64_t)out->h * out->w * 16;
+  const bool vec = ((offs_half->cstride | offs_half->coff) & 3) == 0 &&
+                   (reinterpret_cast<uintptr_t>(offs_half->data) & 15) == 0 &&
+                   ((flow->cstride | flow->coff) & 1) == 0 &&
+                   (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total < (1ll << 31) &&
+                   ((x->cstride | x->coff) & 1) == 0 && (reinterpret_cast<uintptr_t>(x->data) & 3) == 0;
+  if (!vec) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "offset_diversity_f16_f16: unaligned views");
+  offset_diversity_v4_kernel<true, true, true><<<(unsigned)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      *x, *offs_half, *flow, fusion_w, fusion_b, *out, (uint32_t)total);
+  DCVC_LAUNCHED();
   return DCVC_OK;
 }
 

@@ -236,8 +236,12 @@ def flow_warp(feat, flow, out=None, stream=None):
     """out may be a binary16 Act (a context only tensor-core convolutions read)."""
     if out is None:
         out = Act.new(flow.h, flow.w, feat.c, feat.device)
-    fn = _lib.lib().dcvc_flow_warp_f16 if out.f16 else _lib.lib().dcvc_flow_warp
-    with _Prof("flow_warp" + (" f16" if out.f16 else ""), 0, _nb(feat, flow, out)):
+    if feat.f16 and not out.f16:
+        raise ValueError("flow_warp: a binary16 source needs a binary16 destination")
+    fn = (_lib.lib().dcvc_flow_warp_f16_f16 if feat.f16 else _lib.lib().dcvc_flow_warp_f16) \
+        if out.f16 else _lib.lib().dcvc_flow_warp
+    with _Prof("flow_warp" + (" f16" if out.f16 else "") + (" f16src" if feat.f16 else ""), 0,
+               _nb(feat, flow, out)):
         _lib.check(fn(feat.view(), flow.view(), out.view(), _stream(stream)))
     return out
 
@@ -245,7 +249,10 @@ def flow_warp(feat, flow, out=None, stream=None):
 def offset_diversity(x, offs_half, flow, fusion_w, fusion_b, out=None, stream=None):
     if out is None:
         out = Act.new(x.h, x.w, 48, x.device)
-    fn = _lib.lib().dcvc_offset_diversity_f16 if out.f16 else _lib.lib().dcvc_offset_diversity
+    if x.f16 and not out.f16:
+        raise ValueError("offset_diversity: a binary16 source needs a binary16 destination")
+    fn = (_lib.lib().dcvc_offset_diversity_f16_f16 if x.f16 else _lib.lib().dcvc_offset_diversity_f16) \
+        if out.f16 else _lib.lib().dcvc_offset_diversity
     with _Prof("offset_diversity" + (" f16" if out.f16 else ""), 0, _nb(x, offs_half, flow, out)):
         _lib.check(fn(x.view(), offs_half.view(), flow.view(), fusion_w.data_ptr(),
                       fusion_b.data_ptr(), out.view(), _stream(stream)))

@@ -170,9 +170,16 @@ class DMC(CompressionModel):
         dev = mv.device
         ref_frame = Act.wrap(dpb["ref_frame"])
         H, W = mv.h, mv.w
-        aux = Act.new(H, W, 53, dev)                       # [context1_init 48 | warpframe 3 | mv 2]
-        ops.flow_warp(ref_frame, mv, out=aux.slice(48, 3))
-        ops.copy(mv, out=aux.slice(51, 2))
+        # [context1_init 48 | warpframe 3 | mv 2]: only align.conv_offset.0 (stride 2) reads it
+        aux = Act.new(H, W, 53, dev, f16=ops.f16_ok(H // 2, W // 2, 56))
+        if aux.f16:      # the five narrow channels go through one fp32 scratch pixel group
+            tmp = Act.new(H, W, 5, dev, cstride=8)
+            ops.flow_warp(ref_frame, mv, out=tmp.slice(0, 3))
+            ops.copy(mv, out=tmp.slice(3, 2))
+            ops.copy(tmp, out=aux.slice(48, 5))
+        else:
+            ops.flow_warp(ref_frame, mv, out=aux.slice(48, 3))
+            ops.copy(mv, out=aux.slice(51, 2))
         mv2 = ops.resize_bilinear(mv, H // 2, W // 2, mul=0.5)
         mv3 = ops.resize_bilinear(mv2, H // 4, W // 4, mul=0.5)
         if dpb["ref_feature"] is None:
@@ -183,12 +190,17 @@ class DMC(CompressionModel):
                             f16_out=True)
         fe = "feature_extractor"
         # a ResBlock's input is private to the block (LeakyReLU copy + residual): binary16
+        # the three feature levels are read by the warps / offset diversity (binary16 -> binary16
+        # gathers) and by stride-2 convolutions only: binary16 when every consumer's buffer is
+        fe16 = aux.f16 and ops.f16_ok(H // 8, W // 8, 96)
         l1 = layers.res_block(net, fe + ".res_block1",
-                              ops.conv(feat, net.cw(fe + ".conv1"), f16_out=True))
+                              ops.conv(feat, net.cw(fe + ".conv1"), f16_out=True), f16_out=fe16)
         l2 = layers.res_block(net, fe + ".res_block2",
-                              ops.conv(l1, net.cw(fe + ".conv2"), stride=2, f16_out=True))
+                              ops.conv(l1, net.cw(fe + ".conv2"), stride=2, f16_out=True),
+                              f16_out=fe16)
         l3 = layers.res_block(net, fe + ".res_block3",
-                              ops.conv(l2, net.cw(fe + ".conv3"), stride=2, f16_out=True))
+                              ops.conv(l2, net.cw(fe + ".conv3"), stride=2, f16_out=True),
+                              f16_out=fe16)
         ops.flow_warp(l1, mv, out=aux.slice(0, 48))
         # OffsetDiversity (align)
         t = ops.conv(aux, net.cw("align.conv_offset.0"), stride=2, act=0.1, f16_out=True)

@@ -178,6 +178,13 @@ int dcvc_flow_warp_f16(const dcvc_view *feat, const dcvc_view *flow, const dcvc_
 int dcvc_offset_diversity_f16(const dcvc_view *x, const dcvc_view *offs_half,
                               const dcvc_view *flow, const float *fusion_w, const float *fusion_b,
                               const dcvc_view *out, void *stream);
+/* the same with a binary16 source view too (FeatureExtractor outputs, video_model.py:66-86, that
+ * only these two gathers and convolutions read); offsets, flow and arithmetic stay fp32 */
+int dcvc_flow_warp_f16_f16(const dcvc_view *feat, const dcvc_view *flow, const dcvc_view *out,
+                           void *stream);
+int dcvc_offset_diversity_f16_f16(const dcvc_view *x, const dcvc_view *offs_half,
+                                  const dcvc_view *flow, const float *fusion_w,
+                                  const float *fusion_b, const dcvc_view *out, void *stream);
 
 /* ------------------------------------------------------------------------------------------
  * Quad-part entropy model (reference DCVC-DC/src/models/common_model.py:39-61,92-321,

@@ -165,6 +165,30 @@ def test_flow_warp_and_resample():
     assert maxdiff(from_act(ops.max_pool2(to_act(feat))), F.max_pool2d(feat, 2, 2)) == 0.0
 
 
+def test_gathers_from_binary16_sources():
+    """flow_warp / offset_diversity with binary16 source AND destination views equal the fp32-
+    source kernels run on the same rounded values, rounded once at the store."""
+    h, w = 36, 52
+    feat = _rand(1, 48, h, w, seed=1)
+    flow = _rand(1, 2, h, w, seed=2, scale=9.0)
+    f16 = ops.copy(to_act(feat), f16=True)
+    feat_r = to_act(feat.half().float())
+    want = ops.flow_warp(feat_r, to_act(flow), out=Act.new(h, w, 48, dev(), f16=True))
+    got = ops.flow_warp(f16, to_act(flow), out=Act.new(h, w, 48, dev(), f16=True))
+    assert torch.equal(want.buf, got.buf)
+    offs = to_act(_rand(1, 96, h // 2, w // 2, seed=4, scale=0.7))
+    fw = _rand(1, 1, 48, 6, seed=5).reshape(48, 6).to(dev()).contiguous()
+    fb = _rand(1, 1, 1, 48, seed=6).reshape(48).to(dev()).contiguous()
+    wide = torch.full((h, w, 96), 7.0, device=dev(), dtype=torch.float16)
+    want = ops.offset_diversity(feat_r, offs, to_act(flow), fw, fb, out=Act.new(h, w, 48, dev(), f16=True))
+    got = ops.offset_diversity(f16, offs, to_act(flow), fw, fb, out=Act(wide, 48, 48))
+    torch.cuda.synchronize()
+    assert torch.equal(want.buf[:, :, :48], wide[:, :, 48:])
+    assert bool((wide[:, :, :48] == 7.0).all())
+    with pytest.raises(ValueError):
+        ops.flow_warp(f16, to_act(flow))                   # binary16 source -> fp32: not provided
+
+
 def test_copy_pad_crop_and_layout():
     y = _rand(1, 8, 6, 7, seed=1)
     padded = ops.copy(to_act(y), h=8, w=8)
