@@ -339,6 +339,43 @@ __global__ void flow_warp_v4_kernel(dcvc_view feat, dcvc_view flow, dcvc_view ou
   }
 }
 
+// binary16 -> binary16, one thread per (pixel, 8 channels): 16-byte gathers; same arithmetic and
+// accumulation order per channel as flow_warp_v4_kernel
+__global__ void flow_warp_v8h_kernel(dcvc_view feat, dcvc_view flow, dcvc_view out, uint32_t c8n,
+                                     uint32_t total) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const uint32_t p = t / c8n, cq = t - p * c8n;
+  const uint32_t y = p / (uint32_t)out.w, x = p - y * (uint32_t)out.w;
+  const float2 fl = *reinterpret_cast<const float2 *>(flow.data + (size_t)p * flow.cstride + flow.coff);
+  const Bilin b = warp_coords((int)x, (int)y, fl.x, fl.y, feat.w, feat.h);
+  const uint16_t *base = reinterpret_cast<const uint16_t *>(feat.data) + feat.coff + 8 * cq;
+  const size_t r0 = (size_t)b.y0 * feat.w, r1 = (size_t)b.y1 * feat.w;
+  float v[8];
+  auto tap = [&](size_t pix, float wgt, bool first) {
+    const uint4 u = *reinterpret_cast<const uint4 *>(base + pix * feat.cstride);
+    const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w4[j]));
+      if (first) { v[2 * j] = wgt * f.x; v[2 * j + 1] = wgt * f.y; }
+      else { v[2 * j] += wgt * f.x; v[2 * j + 1] += wgt * f.y; }
+    }
+  };
+  tap(r0 + b.x0, b.nw, true);
+  if (b.vx1) tap(r0 + b.x1, b.ne, false);
+  if (b.vy1) tap(r1 + b.x0, b.sw, false);
+  if (b.vx1 && b.vy1) tap(r1 + b.x1, b.se, false);
+  uint4 o;
+  uint32_t *ow = reinterpret_cast<uint32_t *>(&o);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const __half2 h = __floats2half2_rn(v[2 * j], v[2 * j + 1]);
+    ow[j] = *reinterpret_cast<const uint32_t *>(&h);
+  }
+  *reinterpret_cast<uint4 *>(reinterpret_cast<uint16_t *>(out.data) + (size_t)p * out.cstride + out.coff + 8 * cq) = o;
+}
+
 // one thread per (pixel, group q of 16): samples n = 2q, 2q+1
 __global__ void offset_diversity_kernel(dcvc_view x, dcvc_view offs, dcvc_view flow,
                                         const float *__restrict__ fw, const float *__restrict__ fb,
@@ -661,6 +698,12 @@ extern "C" int dcvc_flow_warp_f16_f16(const dcvc_view *feat, const dcvc_view *fl
                   ((flow->cstride | flow->coff) & 1) == 0 &&
                   (reinterpret_cast<uintptr_t>(flow->data) & 7) == 0 && total4 < (1ll << 31);
   if (!ok) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "flow_warp_f16_f16: views must hold whole 4-channel groups");
+  if (((feat->cstride | feat->coff | out->cstride | out->coff | out->c) & 7) == 0 &&
+      ((reinterpret_cast<uintptr_t>(feat->data) | reinterpret_cast<uintptr_t>(out->data)) & 15) == 0) {
+    LAUNCH_1D(flow_warp_v8h_kernel, total4 / 2, stream, *feat, *flow, *out, (uint32_t)(out->c / 8),
+              (uint32_t)(total4 / 2));
+    return DCVC_OK;
+  }
   LAUNCH_1D((flow_warp_v4_kernel<true, true>), total4, stream, *feat, *flow, *out, (uint32_t)(out->c / 4),
             (uint32_t)total4);
   return DCVC_OK;
