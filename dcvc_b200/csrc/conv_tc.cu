@@ -51,6 +51,8 @@ struct TcArgs {
   int f16_out;    // TMA-store epilogue writes binary16 (64-byte rows, 64B swizzle)
   int f16_res;    // res1 holds binary16 (fetched as 64-byte rows, 64B swizzle)
   int f16_res2;   // res2 holds binary16 (TMA-store epilogue: direct 16-byte row loads)
+  int shuf_tma;   // TMA-store epilogue of a planar depth-to-space conv: one strided tensor map per
+                  // sub-pixel (map_o, map_r, map_o2, map_o3), 32-column chunks never straddle one
   int res_direct; // TMA-store epilogue: binary16 res1 by direct row loads issued ahead of the
                   // accumulator wait (registers), not by TMA into the outgoing tile
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
@@ -746,6 +748,7 @@ __device__ __forceinline__ void mma_role(const TcArgs &a, uint32_t base, uint32_
 __global__ void __launch_bounds__(MAX_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_o, const __grid_constant__ CUtensorMap map_r,
+               const __grid_constant__ CUtensorMap map_o2, const __grid_constant__ CUtensorMap map_o3,
                const __grid_constant__ TcArgs a) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment for the swizzled tiles
@@ -783,9 +786,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // bias / scale of every GEMM column, padded with 0 / 1, for broadcast reads in the epilogue
     float *vec = reinterpret_cast<float *>(smem_raw + (base - raw) + a.vec_off);
     const int n_all = a.tiles_n * ((a.n_tile + 31) & ~31);   // whole 32-column chunks
+    const int c_sp = a.cout_w >> 2;     // depth-to-space: column = (subpixel, channel), bias[4c+sp]
     for (int i = threadIdx.x; i < n_all; i += blockDim.x) {
-      vec[i] = (a.bias && i < a.cout_w) ? __ldg(a.bias + i) : 0.f;
-      vec[n_all + i] = (a.scale && i < a.cout_w) ? __ldg(a.scale + i) : 1.f;
+      const int sp = a.shuf_tma ? i / c_sp : 0, c = a.shuf_tma ? i - sp * c_sp : i;
+      vec[i] = (a.bias && i < a.cout_w) ? __ldg(a.bias + (a.shuf_tma ? 4 * c + sp : i)) : 0.f;
+      vec[n_all + i] = (a.scale && i < a.cout_w) ? __ldg(a.scale + c) : 1.f;
     }
   }
   if (warp == 1) {
@@ -1103,7 +1108,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         fence_async_smem();
         __syncwarp();
         if (leader) {
-          tma_store_3d(&map_o, buf, c0, x0, y0);
+          if (a.shuf_tma) {
+            const int c_sp = a.cout_w >> 2, sp = c0 / c_sp;
+            if (sp < 4)                                   // (padding columns have no destination)
+              tma_store_3d(sp == 0 ? &map_o : sp == 1 ? &map_r : sp == 2 ? &map_o2 : &map_o3, buf,
+                           c0 - sp * c_sp, x0, y0);
+          } else {
+            tma_store_3d(&map_o, buf, c0, x0, y0);
+          }
           bulk_commit();
         }
       } else if (has_res) {                               // experiment: no stores, still drain loads
@@ -1266,12 +1278,19 @@ int make_map_a(const dcvc_view &in, int kc, int th, int tw, int stride, bool f16
 
 // epilogue map over an output-side view (out / residual): dims (C, W, H), box (32 channels,
 // w_box, 32 / w_box rows) = the 32 pixels one epilogue warp owns, 128B swizzle
-int make_map_epi(const dcvc_view &v, int channels, int w_box, bool f16, CUtensorMap *out) {
+// sub > 0: the view is the OUTPUT of a depth-to-space conv and the map addresses sub-pixel
+// (dy, dx) = ((sub-1) >> 1, (sub-1) & 1) of every 2x2 block: an (h/2, w/2) tensor with doubled strides
+int make_map_epi(const dcvc_view &v, int channels, int w_box, bool f16, CUtensorMap *out, int sub = 0) {
   MapKey k{};
   const uint64_t esz = esz_of(f16);
   k.ptr = (uint64_t)v.data + (uint64_t)v.coff * esz;
   k.d0 = channels; k.d1 = v.w; k.d2 = v.h;
   k.s1 = (uint64_t)v.cstride * esz; k.s2 = (uint64_t)v.cstride * esz * v.w;
+  if (sub > 0) {
+    const int dy = (sub - 1) >> 1, dx = (sub - 1) & 1;
+    k.ptr += ((uint64_t)dy * v.w + dx) * v.cstride * esz;
+    k.d1 = v.w / 2; k.d2 = v.h / 2; k.s1 *= 2; k.s2 *= 2;
+  }
   k.b0 = 32; k.b1 = w_box; k.b2 = 32 / w_box;
   k.e1 = 1; k.e2 = 1; k.swz = swizzle_of(32 * (int)esz); k.rank = 3 | (f16 ? 0x100 : 0);
   std::lock_guard<std::mutex> g(g_maps_mu);
@@ -1553,6 +1572,12 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // TMA-store epilogue: plain convs with at most one residual, views TMA-addressable
   a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res || a.f16_res2) && a.fast == 1 && !d->out2.data &&
               (!d->res2.data || d->res1.data);      // a second residual rides on direct loads
+  // planar depth-to-space without residuals whose sub-pixel channel count is whole 32-column
+  // chunks: the same epilogue, storing through one strided tensor map per sub-pixel
+  static const int shuf_tma_on = getenv("DCVC_TC_SHUF_TMA") ? atoi(getenv("DCVC_TC_SHUF_TMA")) : 1;
+  a.shuf_tma = shuf_tma_on && a.fast == 3 && (d->cout_w >> 2) % 32 == 0 && !d->res1.data &&
+               !d->res2.data && !d->out2.data && (d->out.w & 1) == 0 && (d->out.h & 1) == 0;
+  if (a.shuf_tma) a.tma_epi = 1;
   int epi = dbg_epi == 4 || dbg_epi == 8 || dbg_epi == 16 ? dbg_epi
             : a.tma_epi ? (ctas == 1 || (epi8_odd && a.n_tile % 32 == 16 && nchunks >= 2) ? 8 : 4)
                         : (ctas == 1 ? 16 : 8);
@@ -1609,15 +1634,24 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   const size_t smem = 1024 + (size_t)a.stage_off + epi_bytes;
   if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: smem %zu too large", smem);
 
-  CUtensorMap ma, mb, mo, mr;
+  CUtensorMap ma, mb, mo, mr, mo2, mo3;
   int rc = a.halo ? make_map_a(d->in, a.kc, halo_ph, a.halo_pw, 1, f16, &ma)
                   : make_map_a(d->in, a.kc, a.th, a.tw, d->stride, f16, &ma);
   if (rc) return rc;
   if (a.tma_epi) {
     const int w_box = a.tw < 32 ? a.tw : 32;
+    if (a.shuf_tma) {
+      rc = make_map_epi(d->out, d->cout_w >> 2, w_box, a.f16_out != 0, &mo, 1);
+      if (!rc) rc = make_map_epi(d->out, d->cout_w >> 2, w_box, a.f16_out != 0, &mr, 2);
+      if (!rc) rc = make_map_epi(d->out, d->cout_w >> 2, w_box, a.f16_out != 0, &mo2, 3);
+      if (!rc) rc = make_map_epi(d->out, d->cout_w >> 2, w_box, a.f16_out != 0, &mo3, 4);
+      if (rc) return rc;
+    } else {
     rc = make_map_epi(d->out, d->cout_w, w_box, a.f16_out != 0, &mo);
     if (rc) return rc;
-    if (d->res1.data) {
+    }
+    if (a.shuf_tma) {
+    } else if (d->res1.data) {
       rc = make_map_epi(d->res1, d->cout_w, w_box, a.f16_res != 0, &mr);
       if (rc) return rc;
     } else {
@@ -1636,7 +1670,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
     attr_set = true;
   }
   const int grid = a.total_tiles < ctas * num_sms ? a.total_tiles : ctas * num_sms;
-  conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, mo, mr, a);
+  if (!a.shuf_tma) { mo2 = mo; mo3 = mo; }
+  conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, mo, mr, mo2, mo3, a);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }
