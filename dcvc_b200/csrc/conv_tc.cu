@@ -53,6 +53,7 @@ struct TcArgs {
   int f16_res2;   // res2 holds binary16 (TMA-store epilogue: direct 16-byte row loads)
   int shuf_tma;   // TMA-store epilogue of a planar depth-to-space conv: one strided tensor map per
                   // sub-pixel (map_o, map_r, map_o2, map_o3), 32-column chunks never straddle one
+  int out2_tma;   // TMA-store epilogue also stores out2 = lrelu(out) (element type of out) via map_o2
   int res_direct; // TMA-store epilogue: binary16 res1 by direct row loads issued ahead of the
                   // accumulator wait (registers), not by TMA into the outgoing tile
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
@@ -1089,22 +1090,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fminf(fmaxf(v[j], 0.f), 1.f);
         }
-        if (a.f16_out) {
-          // binary16 rows of 64 bytes, 64B swizzle: 16-byte chunk j of row r sits at
-          // j ^ ((r >> 1) & 3) (address bits [4,6) ^= bits [7,9))
+        auto park = [&](uint8_t *dst) {
+          if (a.f16_out) {
+            // binary16 rows of 64 bytes, 64B swizzle: 16-byte chunk j of row r sits at
+            // j ^ ((r >> 1) & 3) (address bits [4,6) ^= bits [7,9))
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 pk;
-            pk.x = pack_h2(v[8 * j], v[8 * j + 1]);     pk.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
-            pk.z = pack_h2(v[8 * j + 4], v[8 * j + 5]); pk.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
-            *reinterpret_cast<uint4 *>(buf_g + row16 + (((uint32_t)j ^ sw4) << 4)) = pk;
+            for (int j = 0; j < 4; ++j) {
+              uint4 pk;
+              pk.x = pack_h2(v[8 * j], v[8 * j + 1]);     pk.y = pack_h2(v[8 * j + 2], v[8 * j + 3]);
+              pk.z = pack_h2(v[8 * j + 4], v[8 * j + 5]); pk.w = pack_h2(v[8 * j + 6], v[8 * j + 7]);
+              *reinterpret_cast<uint4 *>(dst + row16 + (((uint32_t)j ^ sw4) << 4)) = pk;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              *reinterpret_cast<float4 *>(dst + row_off + (((uint32_t)j ^ sw) << 4)) =
+                  make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4 *>(buf_g + row_off + (((uint32_t)j ^ sw) << 4)) =
-                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        }
+        };
+        park(buf_g);
         fence_async_smem();
         __syncwarp();
         if (leader) {
@@ -1117,6 +1121,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             tma_store_3d(&map_o, buf, c0, x0, y0);
           }
           bulk_commit();
+        }
+        if (a.out2_tma) {
+          // second output lrelu(out) (the next ResBlock's activated input) from the warp's OTHER
+          // tile buffer; this mode never toggles `b`, so buffer b carries out, b^1 carries out2
+          if (leader) bulk_wait_read<1>();                // out2 store of the previous chunk has left
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = lrelu01(v[j], a.out2_slope);
+          park(buf0_g + (b ^ 1u) * 4096u);
+          fence_async_smem();
+          __syncwarp();
+          if (leader) {
+            tma_store_3d(&map_o2, buf0 + (b ^ 1u) * 4096u, c0, x0, y0);
+            bulk_commit();
+          }
         }
       } else if (has_res) {                               // experiment: no stores, still drain loads
         mbar_wait_warp(res_bar(2 * we + b), b ? rph1 : rph0, lane);
@@ -1133,7 +1152,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
       }
       __syncwarp();
-      b ^= 1u;
+      if (!a.out2_tma) b ^= 1u;
       tile = ntile;
       ci = nci;
     }
@@ -1402,18 +1421,25 @@ int tc_fast_mode(const dcvc_conv *d) {
   };
   auto unit = [](float s) { return s >= 0.f && s <= 1.f; };
   auto al16h = [](const dcvc_view &v) {     // binary16 view: 8 elements per 16 bytes
-    return ((((unsigned)v.cstride | (unsigned)v.coff) & 7u) == 0 &&
-            (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
+    return !v.data || ((((unsigned)v.cstride | (unsigned)v.coff) & 7u) == 0 &&
+                       (reinterpret_cast<uintptr_t>(v.data) & 15u) == 0);
   };
   const bool ok = d->cout_w % 4 == 0 && (d->out_f16 ? al16h(d->out) : al16(d->out)) &&
                   (d->res1_f16 ? al16h(d->res1) : al16(d->res1)) &&
                   (d->res2_f16 && d->res2.data ? al16h(d->res2) && d->cout_w % 8 == 0 : al16(d->res2)) &&
-                  al16(d->out2) && (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
+                  (d->out_f16 ? al16h(d->out2) : al16(d->out2)) &&   // out2 has out's element type
+                  (reinterpret_cast<uintptr_t>(d->bias) & 15u) == 0 &&
                   (reinterpret_cast<uintptr_t>(d->scale) & 15u) == 0 && unit(d->out_slope) &&
                   unit(d->gate_slope) && unit(d->out2_slope);
   if (!ok) return 0;
   if (d->shuffle) return d->shuffle == 2 && d->cout_w % 16 == 0 && !d->gate ? 3 : 0;
   return d->gate ? 2 : 1;
+}
+
+// out2 = lrelu(out) through the TMA-store epilogue: plain convs without residuals
+static bool out2_tma_ok(const dcvc_conv *d) {
+  static const int on = getenv("DCVC_TC_OUT2_TMA") ? atoi(getenv("DCVC_TC_OUT2_TMA")) : 1;
+  return on && d->out2.data && !d->res1.data && !d->res2.data && tc_fast_mode(d) == 1;
 }
 
 bool conv_tc_ok(const dcvc_conv *d) {
@@ -1430,7 +1456,7 @@ bool conv_tc_ok(const dcvc_conv *d) {
   const bool shuf16 = d->out_f16 && d->shuffle == 2 && tc_fast_mode(d) == 3 && !d->res1.data &&
                       !d->res2.data && !d->out2.data;
   if ((d->out_f16 || (d->res1_f16 && d->res1.data) || (d->res2_f16 && d->res2.data)) && !shuf16 &&
-      (tc_fast_mode(d) != 1 || d->out2.data))
+      (tc_fast_mode(d) != 1 || (d->out2.data && !out2_tma_ok(d))))
     return false;
   if (d->res2_f16 && d->res2.data && !d->res1.data) return false;   // f16 res2: TMA-store epilogue only
   if (d->shuffle == 2 && tc_fast_mode(d) != 3) return false;   // planar packing needs the lean path
@@ -1503,7 +1529,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   const bool bres_mc = a.chunks_per_tap > 1 && a.chunks_per_tap <= 3 && d->ksize == 3 && !d->shuffle &&
                        bres_bytes <= bres_mc_kb * 1024u;
   a.bres = bres_on && halo_on && d->stride == 1 && d->ksize >= 3 && d->ksize <= 7 &&
-           d->pad == d->ksize / 2 && a.kcb >= (f16 ? 32 : 64) && tiles_n == 1 && !d->out2.data &&
+           d->pad == d->ksize / 2 && a.kcb >= (f16 ? 32 : 64) && tiles_n == 1 &&
+           (!d->out2.data || out2_tma_ok(d)) &&
            (bres_one || bres_mc);
   if (a.bres) a.halo = 1;
   const int halo_ph = TILE_M / 8 + d->ksize - 1;
@@ -1570,8 +1597,11 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // loads/stores are in flight, and the register file (96 regs/thread) caps threads per SM
   const int nchunks = cdiv(a.n_tile, 32);
   // TMA-store epilogue: plain convs with at most one residual, views TMA-addressable
-  a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res || a.f16_res2) && a.fast == 1 && !d->out2.data &&
+  a.out2_tma = out2_tma_ok(d);
+  a.tma_epi = (tma_epi_on || a.f16_out || a.f16_res || a.f16_res2) && a.fast == 1 &&
+              (!d->out2.data || a.out2_tma) &&
               (!d->res2.data || d->res1.data);      // a second residual rides on direct loads
+  if (!a.tma_epi) a.out2_tma = 0;
   // planar depth-to-space without residuals whose sub-pixel channel count is whole 32-column
   // chunks: the same epilogue, storing through one strided tensor map per sub-pixel
   static const int shuf_tma_on = getenv("DCVC_TC_SHUF_TMA") ? atoi(getenv("DCVC_TC_SHUF_TMA")) : 1;
@@ -1650,6 +1680,10 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
     rc = make_map_epi(d->out, d->cout_w, w_box, a.f16_out != 0, &mo);
     if (rc) return rc;
     }
+    if (a.out2_tma) {
+      rc = make_map_epi(d->out2, d->cout_w, w_box, a.f16_out != 0, &mo2);
+      if (rc) return rc;
+    }
     if (a.shuf_tma) {
     } else if (d->res1.data) {
       rc = make_map_epi(d->res1, d->cout_w, w_box, a.f16_res != 0, &mr);
@@ -1670,7 +1704,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
     attr_set = true;
   }
   const int grid = a.total_tiles < ctas * num_sms ? a.total_tiles : ctas * num_sms;
-  if (!a.shuf_tma) { mo2 = mo; mo3 = mo; }
+  if (!a.shuf_tma) { if (!a.out2_tma) mo2 = mo; mo3 = mo; }
   conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, mo, mr, mo2, mo3, a);
   DCVC_LAUNCHED();
   return DCVC_OK;

@@ -149,11 +149,26 @@ def subpel(net, p, x, act=1.0, out=None, scale=None, res=None, f16_out=False):
                     res=res, f16_out=f16_out)
 
 
+def conv_for_res_block(net, name, x, slope, **kw):
+    """A convolution whose only reader is a ResBlock: on the tensor-core path (no input prologue
+    there) it also emits the block's activated input, saving the LeakyReLU copy pass.
+    Returns (out, lrelu(out) or None)."""
+    cw = net.cw(name)
+    k, stride = cw.k, kw.get("stride", 1)
+    ho, wo = (x.h + 2 * (k // 2) - k) // stride + 1, (x.w + 2 * (k // 2) - k) // stride + 1
+    if ops.CONV_MODE == 1 and cw.w_tc is not None and ho * wo >= ops.TC_MIN_PIXELS and ops.ACT_COPY:
+        return ops.conv(x, cw, act_copy=slope, **kw)
+    return ops.conv(x, cw, **kw), None
+
+
 def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, scale=None,
-              f16_out=False):
+              f16_out=False, x_act=None):
     """ResBlock (video_net.py:58-76): lrelu(x) is conv1's input prologue, the second activation
     conv1's epilogue, `x +` (and an optional outer residual/scale) conv2's epilogue."""
-    t = ops.conv(x, net.cw(p + ".conv1"), in_slope=slope, act=slope, f16_out=True)
+    if x_act is not None:          # lrelu(x) already made by x's producer (conv_for_res_block)
+        t = ops.conv(x_act, net.cw(p + ".conv1"), act=slope, f16_out=True)
+    else:
+        t = ops.conv(x, net.cw(p + ".conv1"), in_slope=slope, act=slope, f16_out=True)
     return ops.conv(t, net.cw(p + ".conv2"), act=slope if end_with_relu else 1.0, res=x,
                     res2=res2, scale=scale, out=out, f16_out=f16_out)
 

@@ -80,9 +80,11 @@ class ConvW:
 
 def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, res2=None,
          scale=None, shuffle=False, out2=None, out2_slope=1.0, gate_slope=0.1, clamp01=False,
-         stream=None, f16_out=False):
+         stream=None, f16_out=False, act_copy=None):
     """Fused convolution; see dcvc_conv2d in include/dcvc_b200.h for the exact semantics.
-    f16_out=True asks for a binary16 result (granted when f16_ok() holds for it)."""
+    f16_out=True asks for a binary16 result (granted when f16_ok() holds for it).
+    act_copy=slope: also produce lrelu(out, slope) as a second tensor of out's element type (the
+    activated input of the ResBlock that follows) and return (out, copy)."""
     assert x.c == cw.cin, (x, cw.cin)
     k = cw.k
     pad = k // 2 if pad is None else pad
@@ -99,6 +101,9 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
                    and (not shuffle or (cw.tc_planar and res is None and ho * wo >= TC_MIN_PIXELS))
                    and not cw.gate and res2 is None and out2 is None)
         out = Act.new(eh, ew, ec, x.device, f16=f16_out)
+    if act_copy is not None:
+        assert out2 is None and res is None and res2 is None and not shuffle and not cw.gate
+        out2, out2_slope = Act.new(eh, ew, ec, x.device, f16=out.f16), act_copy
     if CONV_MODE == 1 and in_slope != 1.0 and cw.w_tc is not None and ho * wo >= TC_MIN_PIXELS:
         # the TMA-fed tensor-core kernel has no input prologue: materialise lrelu(x) once
         # (as binary16 when the copy is private to this conv)
@@ -129,7 +134,7 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     d.clamp01 = int(clamp01)
     if PROFILE is None:
         _lib.check(_lib.lib().dcvc_conv2d(ctypes.byref(d), _stream(stream)))
-        return out
+        return (out, out2) if act_copy is not None else out
     path = "tcgen05" if _lib.lib().dcvc_conv_tc_eligible(ctypes.byref(d)) else "fma"
     tags = ("i" if x.f16 else "I") + ("o" if out.f16 else "O") + \
         ("" if res is None else "r" if res.f16 else "R") + \
@@ -137,10 +142,13 @@ def conv(x, cw, stride=1, pad=None, out=None, in_slope=1.0, act=1.0, res=None, r
     name = f"conv{k}x{k}s{stride} {cw.cin}->{cw.cout_w} @{ho}x{wo} [{path}] {tags}"
     flops = 2 * ho * wo * cw.cout_w * cw.cin * k * k
     nbytes = _nb(x, out, res, res2, out2) + 4 * cw.w.numel()
-    with _Prof(name, flops, nbytes):
+    with _Prof(name + ("+a" if act_copy is not None else ""), flops, nbytes):
         _lib.check(_lib.lib().dcvc_conv2d(ctypes.byref(d), _stream(stream)))
-    return out
+    return (out, out2) if act_copy is not None else out
 
+
+# DCVC_ACT_COPY=0: ResBlock inputs are activated by a separate copy pass again
+ACT_COPY = _os.environ.get("DCVC_ACT_COPY", "1") != "0"
 
 # fused ConvFFN (dcvc_ffn): DCVC_FFN=0 keeps the two separate 1x1 convolutions
 FFN = _os.environ.get("DCVC_FFN", "1") != "0"

@@ -193,14 +193,12 @@ class DMC(CompressionModel):
         # the three feature levels are read by the warps / offset diversity (binary16 -> binary16
         # gathers) and by stride-2 convolutions only: binary16 when every consumer's buffer is
         fe16 = aux.f16 and ops.f16_ok(H // 8, W // 8, 96)
-        l1 = layers.res_block(net, fe + ".res_block1",
-                              ops.conv(feat, net.cw(fe + ".conv1"), f16_out=True), f16_out=fe16)
-        l2 = layers.res_block(net, fe + ".res_block2",
-                              ops.conv(l1, net.cw(fe + ".conv2"), stride=2, f16_out=True),
-                              f16_out=fe16)
-        l3 = layers.res_block(net, fe + ".res_block3",
-                              ops.conv(l2, net.cw(fe + ".conv3"), stride=2, f16_out=True),
-                              f16_out=fe16)
+        t, ta = layers.conv_for_res_block(net, fe + ".conv1", feat, 0.01, f16_out=True)
+        l1 = layers.res_block(net, fe + ".res_block1", t, f16_out=fe16, x_act=ta)
+        t, ta = layers.conv_for_res_block(net, fe + ".conv2", l1, 0.01, stride=2, f16_out=True)
+        l2 = layers.res_block(net, fe + ".res_block2", t, f16_out=fe16, x_act=ta)
+        t, ta = layers.conv_for_res_block(net, fe + ".conv3", l2, 0.01, stride=2, f16_out=True)
+        l3 = layers.res_block(net, fe + ".res_block3", t, f16_out=fe16, x_act=ta)
         ops.flow_warp(l1, mv, out=aux.slice(0, 48))
         # OffsetDiversity (align)
         t = ops.conv(aux, net.cw("align.conv_offset.0"), stride=2, act=0.1, f16_out=True)
@@ -223,14 +221,17 @@ class DMC(CompressionModel):
         cf = "context_fusion_net"
         t = layers.subpel(net, cf + ".conv3_up", c3, f16_out=True)
         layers.res_block(net, cf + ".res_block3_up", t, out=cat2.slice(0, 64))
-        t = ops.conv(c3, net.cw(cf + ".conv3_out"), f16_out=True)
-        ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3, out=bufs["ctx3"])
+        t, ta = layers.conv_for_res_block(net, cf + ".conv3_out", c3, 0.01, f16_out=True)
+        ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3, out=bufs["ctx3"],
+                                x_act=ta)
         t = layers.subpel(net, cf + ".conv2_up", cat2, f16_out=True)
         layers.res_block(net, cf + ".res_block2_up", t, out=cat1.slice(0, 48))
-        t = ops.conv(cat2, net.cw(cf + ".conv2_out"), f16_out=True)
-        ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2, out=bufs["ctx2"])
-        t = ops.conv(cat1, net.cw(cf + ".conv1_out"), f16_out=True)
-        ctx1 = layers.res_block(net, cf + ".res_block1_out", t, res2=c1, out=bufs["ctx1"])
+        t, ta = layers.conv_for_res_block(net, cf + ".conv2_out", cat2, 0.01, f16_out=True)
+        ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2, out=bufs["ctx2"],
+                                x_act=ta)
+        t, ta = layers.conv_for_res_block(net, cf + ".conv1_out", cat1, 0.01, f16_out=True)
+        ctx1 = layers.res_block(net, cf + ".res_block1_out", t, res2=c1, out=bufs["ctx1"],
+                                x_act=ta)
         return ctx1, ctx2, ctx3
 
     def _new_bufs(self, H, W, dev):

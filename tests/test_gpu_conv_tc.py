@@ -207,6 +207,28 @@ def test_pool2_f16(mode):
     assert bool((out.buf[:, :, :8] == 7.0).all()) and bool((out.buf[:, :, 8 + c:] == 7.0).all())
 
 
+@pytest.mark.parametrize("cin,cout,k,stride,h,w,f16", [(48, 48, 3, 1, 40, 56, True), (48, 64, 3, 2, 64, 96, True),
+                                                        (96, 48, 3, 1, 33, 47, False), (64, 96, 1, 1, 37, 53, True)])
+def test_tc_conv_activated_copy(cin, cout, k, stride, h, w, f16):
+    """act_copy: the TMA-store epilogue writes out and lrelu(out) (the following ResBlock's
+    activated input) from its two tile buffers; out equals the plain convolution's bits."""
+    sd = _sd(cin, cout, k, seed=61)
+    x = _rand(1, cin, h, w, seed=19)
+    net = layers.Net(sd, dev())
+    xa = ops.copy(to_act(x), f16=True) if f16 else to_act(x)
+    plain = ops.conv(xa, net.cw("c"), stride=stride, act=0.1, f16_out=f16)
+    out, act = ops.conv(xa, net.cw("c"), stride=stride, act=0.1, f16_out=f16, act_copy=0.01)
+    torch.cuda.synchronize()
+    assert out.f16 == plain.f16 == act.f16 == f16
+    assert torch.equal(out.buf, plain.buf)
+    o32 = out.buf[:, :, :cout].float()
+    want = torch.where(o32 >= 0, o32, o32 * 0.01)
+    got = act.buf[:, :, :cout].float()
+    # binary16: lrelu is applied before the one rounding (the copy pass rounds twice)
+    tol = (want.abs() * 2 ** -10 + 1e-7) if f16 else torch.zeros_like(want)
+    assert bool(((got - want).abs() <= tol).all())
+
+
 def test_copy_f16_narrow():
     x = _rand(1, 3, 21, 35, seed=5)
     wide = torch.full((21, 35, 56), 7.0, device=dev(), dtype=torch.float16)
