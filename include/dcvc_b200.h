@@ -89,7 +89,9 @@ typedef struct dcvc_conv {
    *          runs kind::f16 on weight_tc16; both operands then carry the 11-bit significand
    *          kind::tf32 would have read from fp32 storage, accumulation stays fp32 in TMEM.
    * out_f16: out.data points at binary16 elements, written round-to-nearest-even after the
-   *          fused epilogue; plain epilogues only (no gate, shuffle, res2 or out2).
+   *          fused epilogue; no gate; depth-to-space only with planar-packed weights and no
+   *          residual; out2, when present, then holds binary16 elements too (out2 always has
+   *          out's element type) and needs a residual-free plain convolution.
    * res1_f16: res1.data points at binary16 elements (same epilogue restriction). */
   const void *weight_tc16; /* [cout_pad][ksize*ksize][cin_pad16] binary16, dcvc_conv_tc_geometry16 */
   int32_t in_f16;
