@@ -8,6 +8,7 @@ per-frame work (index lookup, quantisation, coding) runs in the CUDA kernels and
 to the host except for the finished byte stream.
 """
 import ctypes
+import os
 import math
 
 import numpy as np
@@ -21,6 +22,10 @@ SCALE_MIN = {"laplace": 0.01, "gaussian": 0.11}
 SCALE_MAX = 64.0
 SCALE_LEVELS = 256
 DIST_ID = {"laplace": 0, "gaussian": 1}
+
+
+# DCVC_RANS_SIDE_STREAM=0: the encoder's coder kernels stay on the caller's stream
+SIDE_STREAM = os.environ.get("DCVC_RANS_SIDE_STREAM", "1") != "0"
 
 
 def pmf_to_quantized_cdf(pmf, precision=16):
@@ -171,6 +176,7 @@ class EntropyCoder:
         self._out = torch.empty(self._cap, dtype=torch.uint8).pin_memory()
         self._stream_bytes = b""
         self._pending = False
+        self._side = None
         self._keep = []
 
     def __del__(self):
@@ -199,10 +205,25 @@ class EntropyCoder:
         """Enqueues the coder kernels (RansEncoder.flush, py_rans.cpp:98-135); the host wait is
         in get_encoded_stream, so whatever the caller enqueues in between runs behind the coder
         on the GPU while the host already reads the bytes."""
+        # The coder kernels occupy a handful of warps for ~1.2 ms: they run on the coder's own
+        # stream, forked from the caller's here, so the caller's stream goes straight on with the
+        # reconstruction.  The borrowed symbol tensors stay referenced until the host has waited
+        # for the coder (get_encoded_stream), since the allocator only orders reuse on the
+        # caller's stream.
+        cur = torch.cuda.current_stream()
+        from . import ops as _ops
+        side = SIDE_STREAM and _ops.PROFILE is None     # (the per-kernel table times `cur`)
+        if side:
+            if self._side is None:
+                self._side = torch.cuda.Stream(self.device)
+            self._side.wait_stream(cur)
+            run = self._side
+        else:
+            run = cur
         with _Prof("rans_enc_flush"):
-            _lib.check(_lib.lib().dcvc_rans_enc_flush_begin(
-                self._h, self._cap, torch.cuda.current_stream().cuda_stream))
-        self._keep = []
+            _lib.check(_lib.lib().dcvc_rans_enc_flush_begin(self._h, self._cap, run.cuda_stream))
+        if not side:
+            self._keep = []
         self._pending = True
 
     def get_encoded_stream(self):
@@ -212,6 +233,7 @@ class EntropyCoder:
             _lib.check(_lib.lib().dcvc_rans_enc_flush_end(
                 self._h, self._out.data_ptr(), self._cap, ctypes.byref(n)))
             self._stream_bytes = bytes(self._out[:n.value].numpy().tobytes())
+            self._keep = []
         return self._stream_bytes
 
     def set_stream(self, stream):
