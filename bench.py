@@ -384,7 +384,7 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "tf32" if args.conv_mode == 1 else "f32", "data": "synthetic",
                 "config": {"workload": workload_text(args),
-                           "l2": "activations per layer (>=100 MB at 1080p) exceed the 126 MB L2",
+                           "l2": "inputs larger than L2: every step streams a new frame through >= 6 GB of activations (full-resolution tensors are 130-400 MB each, the L2 is 126 MB); no explicit flush",
                            "conv_mode": args.conv_mode, "coder": args.coder,
                            "schedule": ("encoder and decoder are two model instances on two CUDA "
                                         "streams, the decoder one frame behind the encoder; every "
