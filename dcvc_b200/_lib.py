@@ -49,7 +49,7 @@ class Tables(ctypes.Structure):
 
 VP = ctypes.POINTER(View)
 
-# name -> (restype, argtypes); this table is also what tests/test_abi.py checks against the header
+# name -> (restype, argtypes); tests/test_host_logic.py holds this table, the header and the .so exports equal
 SIGNATURES = {
     "dcvc_last_error": (ctypes.c_char_p, []),
     "dcvc_version": (c_int, []),
