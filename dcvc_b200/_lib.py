@@ -83,6 +83,9 @@ SIGNATURES = {
     "dcvc_quad_bits_ws_bytes": (c_size_t, [c_int64]),
     "dcvc_quad_step_enc": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p]),
+    "dcvc_quad_step_enc_static_max": (c_int64, []),
+    "dcvc_quad_step_enc_static": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p, c_void_p,
+                                          c_void_p]),
     "dcvc_quad_step_indexes": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p]),
     "dcvc_quad_step_dec": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p]),
     "dcvc_z_quant": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -10,6 +10,8 @@
 // (the reference's table [[0,1,2,3],[3,2,1,0],[2,3,0,1],[1,0,3,2]], common_model.py:168-220).
 #include "common.cuh"
 
+#include <mutex>
+
 namespace {
 
 constexpr int TPB = 256;
@@ -277,5 +279,67 @@ extern "C" int dcvc_z_dequant(const int16_t *symbols, const dcvc_view *z_hat, vo
   const int64_t n = (int64_t)z_hat->h * z_hat->w * z_hat->c;
   z_dequant_kernel<<<cdiv(n, TPB), TPB, 0, (cudaStream_t)stream>>>(symbols, *z_hat);
   DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// dcvc_quad_step_enc_static: dcvc_quad_step_enc without a caller workspace and without any
+// allocation.  The per-block bit partials live in a file-scope device array that every GPU
+// loading the library holds until exit (64 KiB).  Every call shares it: a call overwrites the
+// first cdiv(n, TPB) entries before reading them, so nothing needs clearing, but two calls that
+// overlap on the GPU (different streams) race on it.
+#define DCVC_STATIC_MAX_SYMBOLS (1 << 22)  /* positions of ONE step (C/4 * h * w) */
+static __device__ __align__(256) float g_bits_partials[DCVC_STATIC_MAX_SYMBOLS / 256];
+
+namespace {
+static_assert(TPB == 256, "g_bits_partials is sized for 256-thread blocks");
+constexpr int64_t STATIC_MAX_SYMBOLS = DCVC_STATIC_MAX_SYMBOLS;
+
+constexpr int MAX_DEVICES = 64;
+float *g_partials_addr[MAX_DEVICES];  // device address of g_bits_partials per device (host table)
+std::mutex g_partials_mu;
+
+// In host code `g_bits_partials` is only a stand-in symbol; the device address must be asked for,
+// once per device, with that device current.
+int static_partials(float **out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return dcvc_fail(DCVC_ERR_CUDA, "quad_step_enc_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= MAX_DEVICES) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "quad_step_enc_static: device %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_partials_mu);
+  if (!g_partials_addr[dev]) {
+    void *p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_bits_partials);
+    if (e != cudaSuccess || !p)
+      return dcvc_fail(DCVC_ERR_CUDA, "quad_step_enc_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    g_partials_addr[dev] = (float *)p;
+  }
+  *out = g_partials_addr[dev];
+  return DCVC_OK;
+}
+}  // namespace
+
+extern "C" int64_t dcvc_quad_step_enc_static_max(void) { return STATIC_MAX_SYMBOLS; }
+
+extern "C" int dcvc_quad_step_enc_static(const dcvc_quad *q, int16_t *symbols, uint8_t *indexes,
+                                         float *bits, void *stream) {
+  int rc = quad_check(q, true);
+  if (rc) return rc;
+  if ((symbols == nullptr) != (indexes == nullptr))
+    return dcvc_fail(DCVC_ERR_ARG, "quad_step_enc_static: symbols/indexes arguments inconsistent");
+  const int64_t n = (int64_t)q->params.h * q->params.w * (q->params.c / 12);
+  if (n > STATIC_MAX_SYMBOLS)
+    return dcvc_fail(DCVC_ERR_ARG, "quad_step_enc_static: %lld positions per step exceed the static scratch limit of %lld; "
+                     "use dcvc_quad_step_enc with a caller workspace", (long long)n, (long long)STATIC_MAX_SYMBOLS);
+  float *partials = nullptr;
+  if (bits && (rc = static_partials(&partials))) return rc;
+  const int blocks = cdiv(n, TPB);
+  cudaStream_t s = (cudaStream_t)stream;
+  quad_step_enc_kernel<<<blocks, TPB, 0, s>>>(*q, symbols, indexes, partials);
+  DCVC_LAUNCHED();
+  if (bits) {
+    reduce_partials_kernel<<<1, TPB, 0, s>>>(partials, blocks, bits);
+    DCVC_LAUNCHED();
+  }
   return DCVC_OK;
 }

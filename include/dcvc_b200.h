@@ -220,6 +220,18 @@ typedef struct dcvc_quad {
 size_t dcvc_quad_bits_ws_bytes(int64_t n);
 int dcvc_quad_step_enc(const dcvc_quad *q, int16_t *symbols, uint8_t *indexes, float *bits,
                        void *bits_ws, void *stream);
+/* dcvc_quad_step_enc for callers that cannot allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same inputs, outputs and results as dcvc_quad_step_enc, but the per-block
+ * bit partials live in a static device array inside the library (64 KiB, held by every GPU that
+ * loads the library until exit) instead of a caller workspace; the call allocates nothing.
+ * Limit: C4*h*w <= dcvc_quad_step_enc_static_max() (= 1 << 22 positions per step); larger steps
+ * return DCVC_ERR_ARG.  All calls share the array: calls that overlap on the GPU (two streams)
+ * race on it -- serialise them on one stream.  Nothing has to be cleared between calls (each call
+ * overwrites the partials it later reads); *bits is accumulated into, as in dcvc_quad_step_enc. */
+int64_t dcvc_quad_step_enc_static_max(void);
+int dcvc_quad_step_enc_static(const dcvc_quad *q, int16_t *symbols, uint8_t *indexes, float *bits,
+                              void *stream);
 /* decoder, phase 1: CDF indexes of the step's positions (scales_r -> build_indexes) */
 int dcvc_quad_step_indexes(const dcvc_quad *q, uint8_t *indexes, void *stream);
 /* decoder, phase 2: scatter decoded symbols: y_hat = sym + mean at the step's positions */
