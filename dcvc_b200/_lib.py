@@ -91,7 +91,9 @@ SIGNATURES = {
     "dcvc_z_quant": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dcvc_z_dequant": (c_int, [c_void_p, VP, c_void_p]),
     "dcvc_pmf_to_quantized_cdf": (c_int, [c_void_p, c_int, c_int, c_void_p]),
-    "dcvc_rans_create": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, c_int64]),
+    "dcvc_rans_workspace_bytes": (c_size_t, [c_int, c_int, c_int64]),
+    "dcvc_rans_create": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, c_int64, c_void_p,
+                                 c_size_t, c_void_p]),
     "dcvc_rans_destroy": (None, [c_void_p]),
     "dcvc_rans_enc_reset": (c_int, [c_void_p]),
     "dcvc_rans_enc_push": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64,
@@ -103,6 +105,8 @@ SIGNATURES = {
     "dcvc_rans_dec_set_stream": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "dcvc_rans_dec_pull": (c_int, [c_void_p, c_void_p, c_int64, c_int64, ctypes.POINTER(Tables),
                                    c_void_p, c_void_p]),
+    "dcvc_rans_dec_finish": (c_int, [c_void_p, c_void_p]),
+    "dcvc_rans_dec_check": (c_int, [c_void_p]),
     "dcvc_rans_status": (c_int, [c_void_p, c_void_p]),
 }
 

@@ -70,6 +70,7 @@ class CompressionModel(nn.Module):
         self._tables = {}
         self._edges = None
         self._scratch = {}
+        self.taps = None         # tests: dict receiving named intermediates
 
     # ------------------------------------------------------------------ parameter tree
     def _register(self, name, param):

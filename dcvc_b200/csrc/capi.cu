@@ -3,6 +3,9 @@
 
 thread_local char g_dcvc_err[512] = "";
 std::atomic<int64_t> g_dcvc_launches{0};
+std::atomic<uint32_t> g_dcvc_once[DCVC_MAX_DEVICES];
+int g_dcvc_num_sms[DCVC_MAX_DEVICES];
+std::mutex g_dcvc_once_mu;
 
 extern "C" const char *dcvc_last_error(void) { return g_dcvc_err; }
 extern "C" int dcvc_version(void) { return 100; }

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdarg.h>
 #include <atomic>
+#include <mutex>
 
 #include "../../include/dcvc_b200.h"
 
@@ -54,3 +55,44 @@ __device__ __forceinline__ size_t vidx(const dcvc_view &v, int y, int x) {
 }
 
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+
+// ---- per-device one-time set-up (cudaFuncSetAttribute is per device; one process may drive
+// several GPUs, reference test_video.py:282-294 maps workers to cuda:i).  Thread-safe.
+constexpr int DCVC_MAX_DEVICES = 64;
+enum { DCVC_ONCE_CONV_TC = 0, DCVC_ONCE_FFN_TC = 1, DCVC_ONCE_RANS_DEC = 2, DCVC_ONCE_FFN128 = 3,
+       DCVC_ONCE_DCB = 4, DCVC_ONCE_RANS_DEC2 = 5 };
+extern std::atomic<uint32_t> g_dcvc_once[DCVC_MAX_DEVICES];
+extern int g_dcvc_num_sms[DCVC_MAX_DEVICES];
+extern std::mutex g_dcvc_once_mu;
+
+// current device and its SM count (cached per device)
+static inline int dcvc_device_info(int *dev_out, int *num_sms) {
+  int dev = 0;
+  DCVC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= DCVC_MAX_DEVICES) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "device %d out of range", dev);
+  if (!g_dcvc_num_sms[dev]) {
+    std::lock_guard<std::mutex> lk(g_dcvc_once_mu);
+    int n = 0;
+    DCVC_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    g_dcvc_num_sms[dev] = n;
+  }
+  if (dev_out) *dev_out = dev;
+  if (num_sms) *num_sms = g_dcvc_num_sms[dev];
+  return DCVC_OK;
+}
+
+// runs f() (returning a cudaError_t) once per (device, slot)
+template <class F>
+static inline int dcvc_once_per_device(int slot, F &&f) {
+  int dev = 0;
+  int rc = dcvc_device_info(&dev, nullptr);
+  if (rc) return rc;
+  const uint32_t bit = 1u << slot;
+  if (g_dcvc_once[dev].load(std::memory_order_acquire) & bit) return DCVC_OK;
+  std::lock_guard<std::mutex> lk(g_dcvc_once_mu);
+  if (g_dcvc_once[dev].load(std::memory_order_relaxed) & bit) return DCVC_OK;
+  DCVC_CUDA(f());
+  g_dcvc_once[dev].fetch_or(bit, std::memory_order_release);
+  return DCVC_OK;
+}

@@ -1558,12 +1558,8 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   // quad per chunk (8 warps) even when several CTAs share the SM -- measured 64->48 1x1 + residual
   // 0.179 -> 0.143 ms, 48->48 1x1 0.091 -> 0.076 ms; tiles of whole chunks are faster with 4
   static const int epi8_odd = getenv("DCVC_TC_EPI8_ODD") ? atoi(getenv("DCVC_TC_EPI8_ODD")) : 1;
-  static int num_sms = 0;
-  if (!num_sms) {
-    int dev = 0;
-    DCVC_CUDA(cudaGetDevice(&dev));
-    DCVC_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  int num_sms = 0;
+  { int rc_ = dcvc_device_info(nullptr, &num_sms); if (rc_) return rc_; }
   a.debug = dbg;
   a.tiles_n = tiles_n;
   a.total_tiles = a.tiles_x * tiles_y * tiles_n;
@@ -1697,12 +1693,10 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   rc = make_map_b(f16 ? d->weight_tc16 : (const void *)d->weight_tc, a.ksize * a.ksize * cin_pad,
                   n_pad, a.n_tile, a.kc, f16, &mb);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DCVC_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   226 * 1024));
-    attr_set = true;
-  }
+  rc = dcvc_once_per_device(DCVC_ONCE_CONV_TC, [] {
+    return cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  });
+  if (rc) return rc;
   const int grid = a.total_tiles < ctas * num_sms ? a.total_tiles : ctas * num_sms;
   if (!a.shuf_tma) { if (!a.out2_tma) mo2 = mo; mo3 = mo; }
   conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, mo, mr, mo2, mo3, a);

@@ -444,16 +444,12 @@ extern "C" int dcvc_ffn(const dcvc_ffn_desc *d, void *stream) {
   if (rc) return rc;
   if ((rc = map_2d(d->w1, 64, (uint64_t)a.n1, 128, (uint32_t)a.n1, &m1))) return rc;
   if ((rc = map_2d(d->w2, 64, (uint64_t)a.nch * c, 128, (uint32_t)c, &m2))) return rc;
-  static bool attr_set = false;
-  static int num_sms = 0;
-  if (!attr_set) {
-    DCVC_CUDA(cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   232448 - 64));
-    int dev = 0;
-    DCVC_CUDA(cudaGetDevice(&dev));
-    DCVC_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-    attr_set = true;
-  }
+  int num_sms = 0;
+  if ((rc = dcvc_device_info(nullptr, &num_sms))) return rc;
+  rc = dcvc_once_per_device(DCVC_ONCE_FFN_TC, [] {
+    return cudaFuncSetAttribute(ffn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 64);
+  });
+  if (rc) return rc;
   const int grid = a.tiles < num_sms ? a.tiles : num_sms;
   ffn_tc_kernel<<<grid, THREADS, smem, (cudaStream_t)stream>>>(ma, m1, m2, a);
   DCVC_LAUNCHED();

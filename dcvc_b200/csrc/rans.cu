@@ -12,7 +12,9 @@
 //   compat      : byte 0 = ((parts-1)<<4) | (1 if part sizes are 2-byte else 0); parts-1 LE sizes;
 //                 part streams (py_rans.cpp:74-119).  Byte-identical to the reference.
 //   interleaved : byte 0 = ((warps-1)<<4) | 0xF; warps-1 LE uint32 sizes; per warp: 32 LE uint32
-//                 lane states, then LE uint16 words in decode order.  Symbol k of a warp's chunk
+//                 lane states, then LE uint16 words in decode order.  More than 16 warps (up to
+//                 256) do not fit the nibble: byte 0 = 0x0E, bytes 1-2 = warps-1 (LE uint16),
+//                 then the same sizes and payloads.  Symbol k of a warp's chunk
 //                 belongs to lane k%32, round k/32; within a round, operation slot s (0 = the
 //                 symbol, >=1 = escape nibbles) is processed for all lanes that have it, and the
 //                 lanes that renormalise in that slot take consecutive words in lane order.
@@ -26,7 +28,8 @@
 
 namespace {
 
-constexpr int MAX_PARTS = 16;
+constexpr int MAX_PARTS = 256;         // interleaved warps
+constexpr int MAX_COMPAT_PARTS = 16;   // the reference container keeps parts-1 in one nibble
 constexpr size_t DEC_TAB_SMEM_MAX = 200 * 1024;  // decoder's shared-memory table budget
 constexpr int SLACK_WORDS = 4096;  // per part, 32-bit words beyond one word per symbol
 
@@ -41,12 +44,20 @@ struct CallRec {
 struct EncJob {
   CallRec calls[DCVC_RANS_MAX_CALLS];
   int ncalls, parts;
-  int64_t reg_off[MAX_PARTS + 1];  // region bounds in 32-bit words
+  int64_t each_sum;  // sum over the calls of n / parts (symbols of every part but the last)
+  int64_t total;     // sum over the calls of n
   int64_t op_off[DCVC_RANS_MAX_CALLS + 1];  // first prepared operation of each call
 };
 
+// region bounds of part i inside the encode buffer, in 32-bit words: one word per symbol of the
+// part plus SLACK_WORDS (every part but the last holds each_sum symbols)
+__host__ __device__ __forceinline__ int64_t reg_off(const EncJob &job, int i) {
+  return i < job.parts ? (int64_t)i * (job.each_sum + SLACK_WORDS)
+                       : job.total + (int64_t)job.parts * SLACK_WORDS;
+}
+
 // meta layout (uint32): [0] error flags, [1] container length, [2+i] part length in bytes,
-// [18+i] part start in bytes inside the encode buffer
+// [2+MAX_PARTS+i] part start in bytes inside the encode buffer
 constexpr int META_WORDS = 2 + 2 * MAX_PARTS;
 constexpr uint32_t ERR_ENC_OVERFLOW = 1, ERR_DEC_UNDERFLOW = 2, ERR_OUT_CAPACITY = 4, ERR_ESCAPE = 8;
 
@@ -65,7 +76,7 @@ __global__ void compat_encode_kernel(const EncJob job, uint32_t *buf, uint32_t *
   if (threadIdx.x != 0) return;
   const int i = blockIdx.x;
   rans::Enc64 e;
-  rans::enc64_init(e, buf + job.reg_off[i + 1], buf + job.reg_off[i]);
+  rans::enc64_init(e, buf + reg_off(job, i + 1), buf + reg_off(job, i));
   rans::Op ops[rans::MAX_OPS];
   for (int c = job.ncalls - 1; c >= 0; --c) {
     const CallRec &cr = job.calls[c];
@@ -79,7 +90,7 @@ __global__ void compat_encode_kernel(const EncJob job, uint32_t *buf, uint32_t *
   }
   rans::enc64_flush(e);
   if (e.overflow) atomicOr(meta, ERR_ENC_OVERFLOW);
-  meta[2 + i] = (uint32_t)((buf + job.reg_off[i + 1] - e.ptr) * 4);
+  meta[2 + i] = (uint32_t)((buf + reg_off(job, i + 1) - e.ptr) * 4);
   meta[2 + MAX_PARTS + i] = (uint32_t)((e.ptr - buf) * 4);
 }
 
@@ -157,8 +168,8 @@ constexpr int ENC_BATCH = 8;  // rounds whose operations are fetched before the 
 __global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, const uint2 *ops_all,
                                                         uint32_t *buf, uint32_t *meta) {
   const int w = blockIdx.x, lane = threadIdx.x;
-  uint16_t *base = reinterpret_cast<uint16_t *>(buf + job.reg_off[w]);
-  const int64_t cap = (job.reg_off[w + 1] - job.reg_off[w]) * 2;
+  uint16_t *base = reinterpret_cast<uint16_t *>(buf + reg_off(job, w));
+  const int64_t cap = (reg_off(job, w + 1) - reg_off(job, w)) * 2;
   int64_t wp = cap;
   uint32_t x = rans::L32;
   bool overflow = false;
@@ -238,7 +249,7 @@ __global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, const 
   if (overflow && lane == 0) atomicOr(meta, ERR_ENC_OVERFLOW);
   if (lane == 0) {
     meta[2 + w] = (uint32_t)((cap - wp) * 2);
-    meta[2 + MAX_PARTS + w] = (uint32_t)(job.reg_off[w] * 4 + wp * 2);
+    meta[2 + MAX_PARTS + w] = (uint32_t)(reg_off(job, w) * 4 + wp * 2);
   }
 }
 
@@ -395,32 +406,56 @@ __global__ void __launch_bounds__(DEC_THREADS) ilv_decode_kernel(const CallRec c
 // ------------------------------------------------------------------ container assembly
 __global__ void assemble_kernel(int mode, int parts, const uint8_t *buf, uint32_t *meta,
                                 uint8_t *out, uint32_t out_cap) {
-  uint32_t len[MAX_PARTS], maximum = 0, total = 0;
-  for (int i = 0; i < parts; ++i) {
-    len[i] = meta[2 + i];
-    if (i < parts - 1 && len[i] > maximum) maximum = len[i];
-    total += len[i];
+  __shared__ uint32_t dst_off[MAX_PARTS + 1];
+  __shared__ uint32_t s_per, s_overhead;
+  __shared__ int s_fits;
+  const bool ext = mode != DCVC_RANS_COMPAT && parts > 16;
+  if (threadIdx.x == 0) {
+    uint32_t maximum = 0, total = 0;
+    for (int i = 0; i < parts; ++i) {
+      const uint32_t len = meta[2 + i];
+      if (i < parts - 1 && len > maximum) maximum = len;
+      dst_off[i] = total;
+      total += len;
+    }
+    dst_off[parts] = total;
+    s_per = (mode == DCVC_RANS_COMPAT && maximum <= 65535u) ? 2 : 4;
+    s_overhead = (ext ? 3 : 1) + (uint32_t)(parts - 1) * s_per;
+    s_fits = total + s_overhead <= out_cap;
+    if (blockIdx.x == 0) {
+      meta[1] = total + s_overhead;
+      if (!s_fits) atomicOr(meta, ERR_OUT_CAPACITY);
+    }
   }
-  const int per = (mode == DCVC_RANS_COMPAT && maximum <= 65535u) ? 2 : 4;
-  const uint32_t overhead = 1 + (uint32_t)(parts - 1) * per;
-  const bool fits = total + overhead <= out_cap;
-  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (tid == 0) {
-    meta[1] = total + overhead;
-    if (!fits) atomicOr(meta, ERR_OUT_CAPACITY);
+  __syncthreads();
+  if (!s_fits) return;
+  const uint32_t per = s_per, overhead = s_overhead;
+  if (blockIdx.x == 0) {
+    const uint32_t hdr = ext ? 3 : 1;
+    if (threadIdx.x == 0) {
+      if (ext) {
+        out[0] = 0x0E;
+        out[1] = (uint8_t)((parts - 1) & 0xff);
+        out[2] = (uint8_t)((parts - 1) >> 8);
+      } else {
+        out[0] = (uint8_t)(((parts - 1) << 4) | (mode == DCVC_RANS_COMPAT ? (per == 2 ? 1 : 0) : 0xF));
+      }
+    }
+    for (int i = threadIdx.x; i < parts - 1; i += blockDim.x) {
+      const uint32_t len = dst_off[i + 1] - dst_off[i];
+      for (uint32_t b = 0; b < per; ++b) out[hdr + i * per + b] = (uint8_t)(len >> (8 * b));
+    }
   }
-  if (!fits) return;
-  if (tid == 0) {
-    out[0] = (uint8_t)(((parts - 1) << 4) | (mode == DCVC_RANS_COMPAT ? (per == 2 ? 1 : 0) : 0xF));
-    for (int i = 0; i < parts - 1; ++i)
-      for (int b = 0; b < per; ++b) out[1 + i * per + b] = (uint8_t)(len[i] >> (8 * b));
-  }
-  uint32_t dst = overhead;
-  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
-  for (int i = 0; i < parts; ++i) {
+  // payload copy: block b takes slice b / parts of part b % parts (all blocks busy for few parts);
+  // with more parts than blocks every block walks whole parts
+  const int nslices = (int)gridDim.x / parts > 0 ? (int)gridDim.x / parts : 1;
+  for (int job = blockIdx.x; job < parts * nslices; job += gridDim.x) {
+    const int i = job % parts, sl = job / parts;
+    const uint32_t len = dst_off[i + 1] - dst_off[i];
+    const uint32_t b0 = (uint32_t)((uint64_t)len * sl / nslices), b1 = (uint32_t)((uint64_t)len * (sl + 1) / nslices);
     const uint8_t *src = buf + meta[2 + MAX_PARTS + i];
-    for (int64_t b = tid; b < len[i]; b += nthreads) out[dst + b] = src[b];
-    dst += len[i];
+    uint8_t *dst = out + overhead + dst_off[i];
+    for (uint32_t b = b0 + threadIdx.x; b < b1; b += blockDim.x) dst[b] = src[b];
   }
 }
 
@@ -431,30 +466,64 @@ struct dcvc_rans {
   int mode = 0, parts = 1;
   int64_t max_symbols = 0;
   EncJob job;
+  // device memory: slices of the caller's workspace (dcvc_rans_workspace_bytes)
   uint32_t *d_buf = nullptr;
   uint2 *d_ops = nullptr;          // interleaved: prepared operations, one per symbol
   size_t buf_words = 0;
   uint8_t *d_out = nullptr;
   size_t out_cap = 0;
-  uint32_t *d_meta = nullptr, *h_meta = nullptr;
-  uint8_t *h_stage = nullptr, *d_stream = nullptr;
+  uint32_t *d_meta = nullptr;
+  uint8_t *d_stream = nullptr;
   size_t stream_cap = 0;
-  DecPart *d_parts = nullptr, *h_parts = nullptr;
+  DecPart *d_parts = nullptr;
+  // pinned host staging (host memory, owned by the context)
+  uint32_t *h_meta = nullptr, *h_dec_flag = nullptr;
+  uint8_t *h_stage = nullptr;
+  DecPart *h_parts = nullptr;
   int dec_parts = 0;
   cudaEvent_t staged = nullptr;
   bool stage_pending = false;
   cudaEvent_t flushed = nullptr;   // encoder: after the meta words of flush_begin reached the host
   cudaStream_t side = nullptr;     // encoder: payload copy of flush_end, not behind later work
   bool flush_pending = false;
+  cudaEvent_t dec_done = nullptr;  // decoder: after the error word of dec_finish reached the host
+  bool dec_check_pending = false;
 };
+
+namespace {
+struct WsLayout {
+  size_t buf_words, out_cap, stream_cap;
+  size_t o_buf, o_ops, o_out, o_meta, o_stream, o_parts, total;
+};
+inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
+WsLayout ws_layout(int mode, int parts, int64_t max_symbols) {
+  WsLayout w;
+  w.buf_words = (size_t)max_symbols + (size_t)SLACK_WORDS * parts;
+  w.out_cap = w.buf_words * 4 + 256 + 4 * (size_t)parts;
+  w.stream_cap = w.out_cap + 16 * (size_t)parts;
+  size_t o = 0;
+  w.o_buf = o; o = al256(o + w.buf_words * 4);
+  w.o_ops = o; o = al256(o + (mode == DCVC_RANS_INTERLEAVED ? (size_t)max_symbols * sizeof(uint2) : 0));
+  w.o_out = o; o = al256(o + w.out_cap);
+  w.o_meta = o; o = al256(o + META_WORDS * 4);
+  w.o_stream = o; o = al256(o + w.stream_cap);
+  w.o_parts = o; o = al256(o + sizeof(DecPart) * MAX_PARTS);
+  w.total = o;
+  return w;
+}
+bool create_args_ok(int mode, int parts, int64_t max_symbols) {
+  if (mode != DCVC_RANS_COMPAT && mode != DCVC_RANS_INTERLEAVED) return false;
+  if (parts < 1 || parts > (mode == DCVC_RANS_COMPAT ? MAX_COMPAT_PARTS : MAX_PARTS)) return false;
+  return max_symbols >= 1;
+}
+}  // namespace
 
 extern "C" void dcvc_rans_destroy(dcvc_rans *r) {
   if (!r) return;
-  cudaFree(r->d_buf); cudaFree(r->d_ops); cudaFree(r->d_out); cudaFree(r->d_meta); cudaFree(r->d_stream);
-  cudaFree(r->d_parts);
-  cudaFreeHost(r->h_meta); cudaFreeHost(r->h_stage); cudaFreeHost(r->h_parts);
+  cudaFreeHost(r->h_meta); cudaFreeHost(r->h_dec_flag); cudaFreeHost(r->h_stage); cudaFreeHost(r->h_parts);
   if (r->staged) cudaEventDestroy(r->staged);
   if (r->flushed) cudaEventDestroy(r->flushed);
+  if (r->dec_done) cudaEventDestroy(r->dec_done);
   if (r->side) cudaStreamDestroy(r->side);
   delete r;
 }
@@ -470,29 +539,40 @@ extern "C" void dcvc_rans_destroy(dcvc_rans *r) {
     }                                                                                      \
   } while (0)
 
-extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t max_symbols) {
-  if (!out || (mode != DCVC_RANS_COMPAT && mode != DCVC_RANS_INTERLEAVED) || parts < 1 ||
-      parts > MAX_PARTS || max_symbols < 1)
-    return dcvc_fail(DCVC_ERR_ARG, "rans_create: bad arguments (mode %d parts %d)", mode, parts);
+extern "C" size_t dcvc_rans_workspace_bytes(int mode, int parts, int64_t max_symbols) {
+  if (!create_args_ok(mode, parts, max_symbols)) return 0;
+  return ws_layout(mode, parts, max_symbols).total;
+}
+
+extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t max_symbols,
+                                void *workspace, size_t workspace_bytes, void *stream) {
+  if (!out || !create_args_ok(mode, parts, max_symbols))
+    return dcvc_fail(DCVC_ERR_ARG, "rans_create: bad arguments (mode %d parts %d; compat takes 1..%d parts, "
+                     "interleaved 1..%d warps)", mode, parts, MAX_COMPAT_PARTS, MAX_PARTS);
+  const WsLayout w = ws_layout(mode, parts, max_symbols);
+  if (!workspace || workspace_bytes < w.total || (reinterpret_cast<uintptr_t>(workspace) & 255))
+    return dcvc_fail(DCVC_ERR_ARG, "rans_create: workspace of %zu bytes (256-byte aligned device memory) needed, got %zu",
+                     w.total, workspace_bytes);
   dcvc_rans *r = new (std::nothrow) dcvc_rans();
   if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_create: out of host memory");
   r->mode = mode; r->parts = parts; r->max_symbols = max_symbols;
   r->job.ncalls = 0; r->job.parts = parts;
-  r->buf_words = (size_t)max_symbols + (size_t)SLACK_WORDS * MAX_PARTS;
-  r->out_cap = r->buf_words * 4 + 256;
-  r->stream_cap = r->out_cap + 16 * MAX_PARTS;
-  RANS_TRY(cudaMalloc(&r->d_buf, r->buf_words * 4));
-  if (mode == DCVC_RANS_INTERLEAVED) RANS_TRY(cudaMalloc(&r->d_ops, (size_t)max_symbols * sizeof(uint2)));
-  RANS_TRY(cudaMalloc(&r->d_out, r->out_cap));
-  RANS_TRY(cudaMalloc(&r->d_meta, META_WORDS * 4));
-  RANS_TRY(cudaMemset(r->d_meta, 0, META_WORDS * 4));
+  uint8_t *base = static_cast<uint8_t *>(workspace);
+  r->buf_words = w.buf_words; r->out_cap = w.out_cap; r->stream_cap = w.stream_cap;
+  r->d_buf = reinterpret_cast<uint32_t *>(base + w.o_buf);
+  r->d_ops = mode == DCVC_RANS_INTERLEAVED ? reinterpret_cast<uint2 *>(base + w.o_ops) : nullptr;
+  r->d_out = base + w.o_out;
+  r->d_meta = reinterpret_cast<uint32_t *>(base + w.o_meta);
+  r->d_stream = base + w.o_stream;
+  r->d_parts = reinterpret_cast<DecPart *>(base + w.o_parts);
+  RANS_TRY(cudaMemsetAsync(r->d_meta, 0, META_WORDS * 4, (cudaStream_t)stream));
   RANS_TRY(cudaMallocHost(&r->h_meta, META_WORDS * 4));
+  RANS_TRY(cudaMallocHost(&r->h_dec_flag, 16));
   RANS_TRY(cudaMallocHost(&r->h_stage, r->stream_cap));
-  RANS_TRY(cudaMalloc(&r->d_stream, r->stream_cap));
-  RANS_TRY(cudaMalloc(&r->d_parts, sizeof(DecPart) * MAX_PARTS));
   RANS_TRY(cudaMallocHost(&r->h_parts, sizeof(DecPart) * MAX_PARTS));
   RANS_TRY(cudaEventCreateWithFlags(&r->staged, cudaEventDisableTiming));
   RANS_TRY(cudaEventCreateWithFlags(&r->flushed, cudaEventDisableTiming));
+  RANS_TRY(cudaEventCreateWithFlags(&r->dec_done, cudaEventDisableTiming));
   RANS_TRY(cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking));
   *out = r;
   return DCVC_OK;
@@ -536,18 +616,14 @@ extern "C" int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void
   if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_begin: bad arguments");
   if (r->flush_pending) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_begin: a flush is already pending");
   cudaStream_t s = (cudaStream_t)stream;
-  int64_t off = 0;
-  for (int i = 0; i < r->parts; ++i) {
-    int64_t count = 0;
-    for (int c = 0; c < r->job.ncalls; ++c) {
-      const int64_t n = r->job.calls[c].n, each = n / r->parts;
-      count += i < r->parts - 1 ? each : n - each * (r->parts - 1);
-    }
-    r->job.reg_off[i] = off;
-    off += count + SLACK_WORDS;
+  r->job.each_sum = 0;
+  r->job.total = 0;
+  for (int c = 0; c < r->job.ncalls; ++c) {
+    r->job.each_sum += r->job.calls[c].n / r->parts;
+    r->job.total += r->job.calls[c].n;
   }
-  r->job.reg_off[r->parts] = off;
-  if ((size_t)off > r->buf_words) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush: buffer too small");
+  if ((size_t)reg_off(r->job, r->parts) > r->buf_words)
+    return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush: buffer too small");
   DCVC_CUDA(cudaMemsetAsync(r->d_meta, 0, META_WORDS * 4, s));
   if (r->mode == DCVC_RANS_COMPAT)
     compat_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_buf, r->d_meta);
@@ -567,7 +643,7 @@ extern "C" int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void
   assemble_kernel<<<64, 256, 0, s>>>(r->mode, r->parts, reinterpret_cast<const uint8_t *>(r->d_buf),
                                      r->d_meta, r->d_out, cap);
   DCVC_LAUNCHED();
-  DCVC_CUDA(cudaMemcpyAsync(r->h_meta, r->d_meta, META_WORDS * 4, cudaMemcpyDeviceToHost, s));
+  DCVC_CUDA(cudaMemcpyAsync(r->h_meta, r->d_meta, 8, cudaMemcpyDeviceToHost, s));
   DCVC_CUDA(cudaEventRecord(r->flushed, s));
   r->job.ncalls = 0;
   r->flush_pending = true;
@@ -601,14 +677,25 @@ extern "C" int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_c
 extern "C" int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_t len, void *stream) {
   if (!r || !host || len < 1) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: empty stream");
   cudaStream_t s = (cudaStream_t)stream;
+  if (r->dec_check_pending) {      // the previous frame's error word (dcvc_rans_dec_finish)
+    int rc = dcvc_rans_dec_check(r);
+    if (rc) return rc;
+  }
   const uint8_t flag = host[0];
-  const int n = (flag >> 4) + 1;
+  int n = (flag >> 4) + 1;
   const int low = flag & 0x0f;
-  const int mode = low == 0xF ? DCVC_RANS_INTERLEAVED : DCVC_RANS_COMPAT;
+  size_t hdr = 1;
+  if (flag == 0x0E) {              // extended interleaved header: warp count in two bytes
+    if (len < 3) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: truncated header");
+    n = ((int)host[1] | ((int)host[2] << 8)) + 1;
+    hdr = 3;
+    if (n <= 16 || n > MAX_PARTS) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: bad warp count %d", n);
+  }
+  const int mode = (low == 0xF || flag == 0x0E) ? DCVC_RANS_INTERLEAVED : DCVC_RANS_COMPAT;
   if (mode != r->mode) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: container mode %d, coder mode %d", mode, r->mode);
   if (mode == DCVC_RANS_COMPAT && low > 1) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: bad flag byte");
   const int per = (mode == DCVC_RANS_COMPAT && low == 1) ? 2 : 4;
-  size_t off = 1, total = 0;
+  size_t off = hdr, total = 0;
   size_t sizes[MAX_PARTS];
   for (int i = 0; i < n - 1; ++i) {
     if (off + per > len) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: truncated header");
@@ -618,7 +705,7 @@ extern "C" int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_
   }
   if (off + total > len) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: part sizes exceed stream");
   sizes[n - 1] = len - off - total;
-  if (len + 16 * MAX_PARTS > r->stream_cap) return dcvc_fail(DCVC_ERR_ARG, "rans_dec_set_stream: stream larger than coder capacity");
+  if (len + 16 * (size_t)n > r->stream_cap) return dcvc_fail(DCVC_ERR_ARG, "rans_dec_set_stream: stream larger than coder capacity");
   if (r->stage_pending) { DCVC_CUDA(cudaEventSynchronize(r->staged)); r->stage_pending = false; }
   size_t dst = 0;
   const size_t unit = mode == DCVC_RANS_COMPAT ? 4 : 2;
@@ -660,13 +747,11 @@ extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t 
   else {
     const size_t tab_bytes = ((size_t)cr.t.count * cr.t.stride + 2 * (size_t)cr.t.count) * 4;
     if (cr.t.count > 0 && tab_bytes <= DEC_TAB_SMEM_MAX) {
-      static bool attr_set = false;
-      if (!attr_set) {
-        DCVC_CUDA(cudaFuncSetAttribute(ilv_decode_kernel<true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)DEC_TAB_SMEM_MAX));
-        attr_set = true;
-      }
+      int rc = dcvc_once_per_device(DCVC_ONCE_RANS_DEC, [] {
+        return cudaFuncSetAttribute(ilv_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)DEC_TAB_SMEM_MAX);
+      });
+      if (rc) return rc;
       ilv_decode_kernel<true><<<r->dec_parts, DEC_THREADS, tab_bytes, s>>>(
           cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
     } else {
@@ -676,6 +761,27 @@ extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t 
   }
   DCVC_LAUNCHED();
   return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_dec_finish(dcvc_rans *r, void *stream) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans: null context");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (r->dec_check_pending) {
+    int rc = dcvc_rans_dec_check(r);
+    if (rc) return rc;
+  }
+  DCVC_CUDA(cudaMemcpyAsync(r->h_dec_flag, r->d_meta, 4, cudaMemcpyDeviceToHost, s));
+  DCVC_CUDA(cudaEventRecord(r->dec_done, s));
+  r->dec_check_pending = true;
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_dec_check(dcvc_rans *r) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans: null context");
+  if (!r->dec_check_pending) return DCVC_OK;
+  r->dec_check_pending = false;
+  DCVC_CUDA(cudaEventSynchronize(r->dec_done));
+  return rans_errors(r->h_dec_flag[0]);
 }
 
 extern "C" int dcvc_rans_status(dcvc_rans *r, void *stream) {

@@ -166,20 +166,49 @@ class EntropyCoder:
         del ec_thread  # host threading does not exist here: the coder runs on the GPU
         self.mode = mode
         self.parts = int(stream_part)
-        self.max_symbols = int(max_symbols)
         self.device = torch.device(device)
-        h = ctypes.c_void_p()
-        _lib.check(_lib.lib().dcvc_rans_create(ctypes.byref(h), 0 if mode == "compat" else 1,
-                                               self.parts, self.max_symbols))
-        self._h = h
-        self._cap = self.max_symbols * 4 + 1024
-        self._out = torch.empty(self._cap, dtype=torch.uint8).pin_memory()
+        self._h = None
         self._stream_bytes = b""
         self._pending = False
         self._side = None
         self._keep = []
+        self.lazy_check = False      # pipeline.py: check a frame's decode errors one frame later
+        self._create(int(max_symbols))
 
-    def __del__(self):
+    def _create(self, max_symbols):
+        """(Re)creates the coder context for frames of up to `max_symbols` symbols.  All device
+        memory is a torch tensor owned here and lent to the library as its workspace."""
+        L = _lib.lib()
+        mode = 0 if self.mode == "compat" else 1
+        nbytes = L.dcvc_rans_workspace_bytes(mode, self.parts, max_symbols)
+        if nbytes == 0:
+            raise _lib.DcvcError(
+                f"EntropyCoder: unsupported configuration (mode {self.mode}, stream_part "
+                f"{self.parts}: compat takes 1..16 parts, interleaved 1..256 warps)")
+        with torch.cuda.device(self.device):
+            ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=self.device)
+            off = (-ws.data_ptr()) % 256
+            h = ctypes.c_void_p()
+            _lib.check(L.dcvc_rans_create(ctypes.byref(h), mode, self.parts, max_symbols,
+                                          ws.data_ptr() + off, nbytes,
+                                          torch.cuda.current_stream().cuda_stream))
+        self._destroy()
+        self._h, self._ws = h, ws
+        self.max_symbols = max_symbols
+        self._cap = max_symbols * 4 + 1024 + 4 * self.parts
+        self._out = torch.empty(self._cap, dtype=torch.uint8).pin_memory()
+
+    def reserve(self, symbols):
+        """Makes room for frames of `symbols` symbols (the reference coder has no limit): the
+        context is rebuilt, larger, when a frame size beyond the current capacity shows up."""
+        if symbols > self.max_symbols:
+            if self._pending:
+                self.get_encoded_stream()
+            self.check()
+            torch.cuda.synchronize(self.device)
+            self._create(int(symbols))
+
+    def _destroy(self):
         h = getattr(self, "_h", None)
         if h:
             try:
@@ -187,6 +216,9 @@ class EntropyCoder:
             except Exception:      # interpreter shutdown: modules may already be torn down
                 pass
             self._h = None
+
+    def __del__(self):
+        self._destroy()
 
     def reset(self):
         if self._pending:        # an unread flush: finish it so the coder can start a new one
@@ -247,6 +279,16 @@ class EntropyCoder:
                 self._h, indexes.data_ptr() if indexes is not None else None, n, plane,
                 ctypes.byref(tables.c), out.data_ptr(), torch.cuda.current_stream().cuda_stream))
         return out
+
+    def finish_decode(self):
+        """After the frame's last decode(): enqueue the copy of the decode kernels' error word.
+        The matching check() (or the next set_stream) raises DcvcError for a truncated or
+        corrupt frame; with lazy_check the host does not wait here."""
+        _lib.check(_lib.lib().dcvc_rans_dec_finish(self._h,
+                                                   torch.cuda.current_stream().cuda_stream))
+
+    def check(self):
+        _lib.check(_lib.lib().dcvc_rans_dec_check(self._h))
 
     def status(self):
         _lib.check(_lib.lib().dcvc_rans_status(self._h, torch.cuda.current_stream().cuda_stream))

@@ -94,6 +94,14 @@ class IntraNoAR(CompressionModel):
         catb = self.new_prior_buffer(y.h, y.w, y.c)
         self._params(z_hat, catb, y.c)
         y_hat, coded = self.forward_four_part_prior(y, catb, self._prior_fn(), write, bits_y)
+        if self.taps is not None:
+            for k, v in (("y", y), ("z_hat", z_hat), ("params", catb.slice(y.c, 3 * y.c)),
+                         ("y_hat", y_hat)):
+                self.taps["i_" + k] = v.nchw().detach().float().clone()
+            for st, (sym, idx) in enumerate(coded):
+                shp = (1, y.c // 4, y.h, y.w)
+                self.taps[f"i_y_q_w_{st}"] = sym.view(shp).clone()
+                self.taps[f"i_y_idx_w_{st}"] = idx.view(shp).clone()
         return y_hat, coded, z_hat, z_sym, q_dec
 
     # ------------------------------------------------------------------ reference API
@@ -112,6 +120,8 @@ class IntraNoAR(CompressionModel):
 
     def compress(self, x, q_in_ckpt, q_index):
         """image_model.py:198-229; stream order z, y parts 0..3."""
+        zs = get_downsampled_shape(x.shape[2], x.shape[3], 64)
+        self.entropy_coder.reserve(self.N * (x.shape[2] // 16 * (x.shape[3] // 16) + zs[0] * zs[1]))
         y_hat, coded, z_hat, z_sym, q_dec = self._encode_side(x, q_in_ckpt, q_index, True)
         self.entropy_coder.reset()
         self.encode_z(z_sym, z_hat, "bit_estimator_z")
@@ -123,14 +133,19 @@ class IntraNoAR(CompressionModel):
     def decompress(self, bit_stream, height, width, q_in_ckpt, q_index):
         """image_model.py:231-252"""
         _, q_dec = self.get_q_for_inference(q_in_ckpt, q_index)
-        self.entropy_coder.set_stream(bit_stream)
+        ec = self.entropy_coder
         z_size = get_downsampled_shape(height, width, 64)
         yh, yw = get_downsampled_shape(height, width, 16)
+        ec.reserve(self.N * (yh * yw + z_size[0] * z_size[1]))
+        ec.set_stream(bit_stream)
         z_hat = self.decode_z(self.N, z_size, "bit_estimator_z")
         catb = self.new_prior_buffer(yh, yw, self.N)
         self._params(z_hat, catb, self.N)
         y_hat = self.decompress_four_part_prior(catb, self.N, self._prior_fn())
+        ec.finish_decode()
         x_hat = self._synthesis(y_hat, q_dec, clamp=True)
+        if not ec.lazy_check:       # a truncated / corrupt / wrong-table frame raises here
+            ec.check()
         return {"x_hat": x_hat.nchw()}
 
     def encode_decode(self, x, q_in_ckpt, q_index, output_path=None, pic_width=None,

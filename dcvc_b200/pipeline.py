@@ -35,6 +35,16 @@ class EncDecPipeline:
         self.idx = 0              # frames pushed
         self.bits = 0
         self._pending = None      # (frame index, bytes, padded height, padded width)
+        # decode errors (truncated / corrupt frame) are checked one frame late, at the next
+        # set_stream, so that the host never waits for the decoder stream inside push()
+        self._dec_models = (i_dec, p_dec)
+        self._lazy(True)
+
+    def _lazy(self, on):
+        for m in self._dec_models:
+            ec = getattr(m, "entropy_coder", None)
+            if ec is not None:
+                ec.lazy_check = on
 
     # ------------------------------------------------------------------ decoder stage
     def _decode(self, item):
@@ -84,6 +94,8 @@ class EncDecPipeline:
         """Decodes the last pushed frame; returns its decoded frame (or None)."""
         decoded = self._decode(self._pending) if self._pending is not None else None
         self._pending = None
+        for m in self._dec_models:      # the last frames' deferred error checks
+            m.entropy_coder.check()
         return decoded
 
     def join(self, stream=None):

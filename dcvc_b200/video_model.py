@@ -24,7 +24,6 @@ class DMC(CompressionModel):
         super().__init__(arch.dmc_spec(anchor_num), "laplace",
                          ("bit_estimator_z", "bit_estimator_z_mv"), ec_thread, stream_part,
                          anchor_num, coder_mode)
-        self.taps = None     # tests: dict receiving named intermediates (NCHW clones)
 
     def _tap(self, name, act):
         if self.taps is not None:
@@ -331,6 +330,12 @@ class DMC(CompressionModel):
                          ("y_hat", y_hat), ("x_hat", x_hat), ("feature", feature),
                          ("recon_res", bufs["R"].slice(48, 32))):
                 self._tap("p_" + k, v)
+            if write:       # coded symbols / CDF indexes per step, the reference's [1,C/4,h,w] order
+                for name, cd, lat in (("mv_y", mv_coded, mv_y), ("y", coded, y)):
+                    for st, (sym, idx) in enumerate(cd):
+                        shp = (1, lat.c // 4, lat.h, lat.w)
+                        self.taps[f"p_{name}_q_w_{st}"] = sym.view(shp).clone()
+                        self.taps[f"p_{name}_idx_w_{st}"] = idx.view(shp).clone()
         new_dpb = {"ref_frame": x_hat.nchw(), "ref_feature": feature.nchw(),
                    "ref_mv_feature": mv_feature.nchw(), "ref_y": y_hat.nchw(),
                    "ref_mv_y": mv_y_hat.nchw()}
@@ -344,6 +349,8 @@ class DMC(CompressionModel):
         host then waits for the coder's event only, so the reconstruction is still running on the
         GPU when this returns -- whoever reads the dpb next does so in stream order."""
         ec = self.entropy_coder
+        zs_ = get_downsampled_shape(x.shape[2], x.shape[3], 64)
+        ec.reserve((64 + arch.CH_16X) * (x.shape[2] // 16 * (x.shape[3] // 16) + zs_[0] * zs_[1]))
 
         def coder(mv_zs, zs, mv_coded, coded):
             ec.reset()
@@ -363,9 +370,11 @@ class DMC(CompressionModel):
         """video_model.py:483-520"""
         _, mv_q_dec, _, y_q_dec = self.get_q_for_inference(q_in_ckpt, q_index)
         dev = self.device
-        self.entropy_coder.set_stream(string)
+        ec = self.entropy_coder
         z_size = get_downsampled_shape(height, width, 64)
         yh, yw = get_downsampled_shape(height, width, 16)
+        ec.reserve((64 + arch.CH_16X) * (yh * yw + z_size[0] * z_size[1]))
+        ec.set_stream(string)
         mv_z_hat = self.decode_z(64, z_size, "bit_estimator_z_mv")
         z_hat = self.decode_z(arch.CH_16X, z_size, "bit_estimator_z")
         mv_catb = self.new_prior_buffer(yh, yw, 64)
@@ -377,7 +386,10 @@ class DMC(CompressionModel):
         catb = self.new_prior_buffer(yh, yw, arch.CH_16X)
         self._res_params(z_hat, dpb, ctx3, catb, arch.CH_16X)
         y_hat = self.decompress_four_part_prior(catb, arch.CH_16X, self._prior_fn("y"))
+        ec.finish_decode()
         x_hat, feature = self._recon(y_hat, bufs, y_q_dec)
+        if not ec.lazy_check:       # a truncated / corrupt / wrong-table frame raises here
+            ec.check()
         return {"dpb": {"ref_frame": x_hat.nchw(), "ref_feature": feature.nchw(),
                         "ref_mv_feature": mv_feature.nchw(), "ref_y": y_hat.nchw(),
                         "ref_mv_y": mv_y_hat.nchw()}}

@@ -261,8 +261,8 @@ int dcvc_pmf_to_quantized_cdf(const float *pmf, int n, int precision, uint32_t *
  *   container on the device, and copies it to `out_host` (synchronises the stream).
  * mode DCVC_RANS_COMPAT: byte-identical to the reference container with `parts` in 1..16
  *   (one device thread per part: this mode exists for interoperability, not speed).
- * mode DCVC_RANS_INTERLEAVED: `parts` warps x 32 lanes of 32-bit rANS sharing one word stream
- *   per warp (own container; see DESIGN.md "Interleaved stream").
+ * mode DCVC_RANS_INTERLEAVED: `parts` warps (1..256) x 32 lanes of 32-bit rANS sharing one word
+ *   stream per warp (own container; see DESIGN.md "Interleaved stream").
  * Decoder protocol (mirrors set_stream / decode_stream*): dcvc_rans_dec_set_stream copies the
  *   container to the device and initialises the lanes; each dcvc_rans_dec_pull decodes n symbols
  *   for device-resident indexes into a device int16 array, continuing from the previous call.
@@ -280,7 +280,15 @@ typedef struct dcvc_tables {
   int32_t count, stride;
 } dcvc_tables;
 
-int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t max_symbols_per_frame);
+/* `parts`: 1..16 stream parts in compat mode (the reference container keeps parts-1 in a nibble,
+ * py_rans.cpp:99), 1..256 warps in interleaved mode.  Device memory comes from the caller:
+ * `workspace` is >= dcvc_rans_workspace_bytes(mode, parts, max_symbols_per_frame) bytes of
+ * 256-byte aligned device memory that the context uses until dcvc_rans_destroy (0 = bad
+ * arguments).  The context itself only owns pinned host staging buffers, two events and a copy
+ * stream.  `stream` orders the workspace initialisation. */
+size_t dcvc_rans_workspace_bytes(int mode, int parts, int64_t max_symbols_per_frame);
+int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t max_symbols_per_frame,
+                     void *workspace, size_t workspace_bytes, void *stream);
 void dcvc_rans_destroy(dcvc_rans *r);
 int dcvc_rans_enc_reset(dcvc_rans *r);
 /* index_is_u8: indexes are uint8 table rows (y parts); otherwise NULL indexes means
@@ -299,6 +307,15 @@ int dcvc_rans_enc_flush_end(dcvc_rans *r, uint8_t *out_host, size_t out_capacity
 int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_t len, void *stream);
 int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t n, int64_t plane,
                        const dcvc_tables *t, int16_t *symbols_out, void *stream);
+/* Deferred decoder error check (RansDecoder has none: the reference decodes garbage silently,
+ * rans.cpp:272-331).  dcvc_rans_dec_finish, called after the frame's last dcvc_rans_dec_pull,
+ * enqueues a 4-byte copy of the decode kernels' error word plus an event on `stream`, without a
+ * host wait; dcvc_rans_dec_check waits for THAT event only and returns DCVC_ERR_STREAM when a pull
+ * ran out of words or met a malformed escape (truncated / corrupt / wrong-table frame).  A check
+ * still pending when the next dcvc_rans_dec_set_stream or dcvc_rans_dec_finish arrives is done
+ * there, so an error is never lost. */
+int dcvc_rans_dec_finish(dcvc_rans *r, void *stream);
+int dcvc_rans_dec_check(dcvc_rans *r);
 /* device error flag of the decoder/encoder kernels (0 ok); synchronises the stream */
 int dcvc_rans_status(dcvc_rans *r, void *stream);
 

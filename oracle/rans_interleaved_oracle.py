@@ -8,7 +8,8 @@ interval of cdf[value]; out-of-support values escape through the last table entr
 4-bit bypass nibbles: a unary-in-15s digit count, then the digits of 2*|v| (+1 for negative)),
 shared with the compat coder that IS byte-identical to the reference, and (b) losslessness.
 
-Container: byte 0 = ((W-1) << 4) | 0xF; W-1 little-endian uint32 payload sizes; per warp payload:
+Container: byte 0 = ((W-1) << 4) | 0xF (W <= 16) or byte 0 = 0x0E followed by W-1 as a
+little-endian uint16 (16 < W <= 256); W-1 little-endian uint32 payload sizes; per warp payload:
 32 little-endian uint32 lane states, then uint16 words in decode order.  A call of n symbols is
 cut into W contiguous pieces (n // W each, the last takes the remainder); within a piece symbol k
 belongs to lane k % 32, round k // 32.  Every lane is a 32-bit rANS state in [2^16, 2^32) with
@@ -91,7 +92,10 @@ def encode(calls, tables, warps):
         for ev in reversed(events):
             words.extend(ev)
         payloads.append(struct.pack("<32I", *x) + struct.pack(f"<{len(words)}H", *words))
-    head = bytes([((warps - 1) << 4) | 0xF])
+    if warps > 16:      # the warp count does not fit the nibble: extended header
+        head = bytes([0x0E]) + struct.pack("<H", warps - 1)
+    else:
+        head = bytes([((warps - 1) << 4) | 0xF])
     head += b"".join(struct.pack("<I", len(p)) for p in payloads[:-1])
     return head + b"".join(payloads)
 
@@ -99,9 +103,13 @@ def encode(calls, tables, warps):
 def decode(stream, index_calls, tables):
     """index_calls: [indexes[n]] in pull order -> [int16[n]]."""
     cdf, sizes, offsets = tables
-    warps = (stream[0] >> 4) + 1
-    assert stream[0] & 0xF == 0xF
-    pos = 1
+    if stream[0] == 0x0E:
+        warps = struct.unpack_from("<H", stream, 1)[0] + 1
+        pos = 3
+    else:
+        warps = (stream[0] >> 4) + 1
+        assert stream[0] & 0xF == 0xF
+        pos = 1
     lens = []
     for _ in range(warps - 1):
         lens.append(struct.unpack_from("<I", stream, pos)[0])

@@ -245,3 +245,28 @@ def test_pipeline_equals_sequential(mode):
         assert torch.equal(pipe.enc_dpb["ref_frame"], pipe.dec_dpb["ref_frame"])
     finally:
         ops.set_conv_mode(old)
+
+
+@pytest.mark.parametrize("coder_mode", ["compat", "interleaved"])
+def test_corrupt_frame_raises_in_decompress(coder_mode):
+    """A truncated frame must not decode to garbage silently: IntraNoAR.decompress and
+    DMC.decompress raise (the decode kernels' error word is checked once per frame)."""
+    from dcvc_b200._lib import DcvcError
+    h = w = 64
+    i_net, p_net, _, _ = _models(0, 2, 2, coder_mode)
+    frames = synth.synth_frames(2, h, w, seed=0)
+    with torch.no_grad():
+        enc = i_net.compress(frames[0:1].to(dev()), True, 1)
+        s = enc["bit_stream"]
+        with pytest.raises(DcvcError):
+            i_net.decompress(s[:len(s) - len(s) // 3], h, w, True, 1)
+        dec = i_net.decompress(s, h, w, True, 1)          # the coder recovers for the next frame
+        assert torch.equal(dec["x_hat"], enc["x_hat"])
+        dpb = {"ref_frame": dec["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+               "ref_y": None, "ref_mv_y": None}
+        encp = p_net.compress(frames[1:2].to(dev()), dpb, True, 1, 1)
+        sp = encp["bit_stream"]
+        with pytest.raises(DcvcError):
+            p_net.decompress(dpb, sp[:len(sp) - len(sp) // 3], h, w, True, 1, 1)
+        decp = p_net.decompress(dpb, sp, h, w, True, 1, 1)
+        assert torch.equal(decp["dpb"]["ref_frame"], encp["dpb"]["ref_frame"])
