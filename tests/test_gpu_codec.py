@@ -270,3 +270,85 @@ def test_corrupt_frame_raises_in_decompress(coder_mode):
             p_net.decompress(dpb, sp[:len(sp) - len(sp) // 3], h, w, True, 1, 1)
         decp = p_net.decompress(dpb, sp, h, w, True, 1, 1)
         assert torch.equal(decp["dpb"]["ref_frame"], encp["dpb"]["ref_frame"])
+
+
+@pytest.mark.parametrize("name", ["a64", "b96x128"])
+def test_mode0_compat_stream_bytes_vs_reference_golden(golden_dir, name, conv_mode):
+    """fp32-accumulate mode, compat coder, free-running GOP: every frame's stream against the
+    bytes the UNMODIFIED reference wrote for the same weights and frames (tests/golden).  Equal
+    bytes mean every quantised symbol and every CDF index of the frame equal the reference's."""
+    conv_mode(0)
+    g = np.load(os.path.join(golden_dir, f"dc_gop_{name}.npz"))
+    h, w, n, q_in_ckpt, q_index, part_i, part_p, seed = [int(v) for v in g["meta"]]
+    i_net, p_net, _, _ = _models(seed, part_i, part_p)
+    frames = synth.synth_frames(n, h, w, seed=seed)
+    res = _run_gop(i_net, p_net, frames, h, w, bool(q_in_ckpt), q_index)
+    same = [res[k][0] == g[f"stream_{k}"].tobytes() for k in range(n)]
+    rms = [float((res[k][1] - torch.from_numpy(g[f"x_hat_{k}"])).pow(2).mean().sqrt())
+           for k in range(n)]
+    print(f"golden {name}: streams byte-identical per frame {same}, x_hat RMS vs reference {rms}")
+    assert all(same), (same, [len(res[k][0]) - g[f"stream_{k}"].size for k in range(n)])
+    assert max(rms) < 1e-6, rms
+
+
+STAGES = ("est_mv", "mv_y", "mv_z_hat", "mv_params", "mv_y_hat", "mv_hat", "ctx1", "ctx2", "ctx3",
+          "y", "z_hat", "params", "y_hat", "x_hat")
+# per-stage bound on RMS(product - oracle) / RMS(oracle), teacher-forced on the oracle's dpb.
+# mode 0: fp32 reassociation only.  mode 1: TF32 / binary16 operands; the quantised stages
+# (*_hat, z_hat) inherit symbol flips (one flip changes one latent by 1), hence looser.
+# (measured on a B200: mode 0 <= 9.5e-7 everywhere; mode 1 est_mv 1.3e-4, mv_y 6e-4, contexts
+# 3-5e-4, y 5e-4, x_hat 8e-4, and 2 flipped mv_y symbols of 18 432 = 5e-2 of mv_y_hat's RMS)
+STAGE_BOUND = {0: dict.fromkeys(STAGES, 2e-6),
+               1: {"est_mv": 5e-4, "mv_y": 2e-3, "mv_z_hat": 0.1, "mv_params": 1e-4,
+                   "mv_y_hat": 0.1, "mv_hat": 4e-2, "ctx1": 2e-3, "ctx2": 2e-3, "ctx3": 2e-3,
+                   "y": 2e-3, "z_hat": 0.1, "params": 1e-4, "y_hat": 0.1, "x_hat": 3e-3}}
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_per_stage_taps_vs_oracle(mode, conv_mode):
+    """scripts/debug_taps.py as a test: every named stage of a P frame (motion estimate, mv
+    latents, prior parameters, contexts, latents, reconstruction) against the oracle's, frames
+    teacher-forced on the oracle's dpb.  In mode 0 the coded symbols and CDF indexes of the whole
+    frame must be bit-equal to the oracle's (north_star: bit-exact in the fp32-accumulate mode)."""
+    from oracle import entropy_oracle as eo
+    conv_mode(mode)
+    h, w, n, seed, q = 128, 192, 3, 4, 17
+    i_net, p_net, sd_i, sd_p = _models(seed, 1, 1)
+    o_i, o_p = co.OracleIntra(sd_i, 1), co.OracleDMC(sd_p, 1)
+    o_i.update()
+    o_p.update()
+    frames = synth.synth_frames(n, h, w, seed=seed)
+    torch.set_num_threads(8)
+    worst = {}
+    with torch.no_grad():
+        ref = o_i.compress(frames[0:1], False, q)
+        dpbo = {"ref_frame": ref["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+                "ref_y": None, "ref_mv_y": None}
+        for k in range(1, n):
+            o_p.taps, p_net.taps = {}, {}
+            refp = o_p.compress(frames[k:k + 1], dpbo, False, q, k % 4)
+            p_net.compress(frames[k:k + 1].to(dev()), _to_dev(dpbo), False, q, k % 4)
+            for name in STAGES:
+                a, b = p_net.taps["p_" + name].cpu(), o_p.taps["p_" + name]
+                rel = float((a - b).pow(2).mean().sqrt() / b.pow(2).mean().sqrt().clamp_min(1e-12))
+                worst[name] = max(worst.get(name, 0.0), rel)
+            flips = idx_flips = total = 0
+            for lat, sc in (("p_y", "p_scales"), ("p_mv_y", "p_mv_scales")):
+                for s in range(4):
+                    a = p_net.taps[f"{lat}_q_w_{s}"].cpu().int()
+                    b = o_p.taps[f"{lat}_q_w_{s}"].int()
+                    ia = p_net.taps[f"{lat}_idx_w_{s}"].cpu().int()
+                    ib = eo.build_indexes(o_p.taps[f"{sc}_w_{s}"], "laplace")
+                    flips += int((a != b).sum())
+                    idx_flips += int((ia != ib).sum())
+                    total += a.numel()
+            print(f"mode {mode} frame {k}: symbol flips {flips}/{total}, index flips {idx_flips}")
+            if mode == 0:
+                assert flips == 0 and idx_flips == 0, (k, flips, idx_flips)
+            else:
+                assert flips <= 1e-3 * total, (k, flips, total)
+            dpbo = refp["dpb"]
+            p_net.taps = None
+    print(f"mode {mode} per-stage rel RMS:", {k_: f"{v:.2e}" for k_, v in worst.items()})
+    for name in STAGES:
+        assert worst[name] <= STAGE_BOUND[mode][name], (name, worst[name])
