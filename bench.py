@@ -14,12 +14,18 @@ checkpoints offline).
           the fp32 frame from pinned host memory, pads on the device, codes, decodes, and reads
           the frame's PSNR back to the host.
   roofline     : the convolution group (the dominant kernels), algorithmic FLOPs / CUDA-event time.
-  cpu_baseline : the CPU oracle (torch fp32 + C rANS port of the reference coder) on a bounded
-                 reduced-resolution sample, scaled to 1080p-equivalent frames/s.
+  cpu_baseline : ONE P frame of this very 1080p sequence through the unmodified reference on the
+                 host cores (oracle/_ref; the oracle port when that copy is absent), measured.
+  parity       : symbol flips / x_hat RMS / bits of the benchmarked mode against mode 0, and
+                 encoder == decoder, on the first frames of the sequence (outside the timing).
+  arms         : the sequential (drop-in) schedule and the reference-compatible bitstream, timed
+                 beside the pipelined headline.
+  gpu_reference: the UNMODIFIED reference (PyTorch/cuDNN + host rANS) on this same GPU.
 
 N > 1 (torchrun): every rank codes its own sequence (independent GOPs; weak scaling); the only
 collective is one NCCL all-reduce of the rate/distortion statistics after the timed region.
-`--impl reference` times the reference's CPU implementation of the path (oracle port) instead.
+`--impl reference` times the reference's own CPU implementation of the path instead (1 I + 1 P
+frame at the full 1080p size).
 """
 import argparse
 import json
@@ -53,6 +59,11 @@ def parse_args():
     p.add_argument("--height", type=int, default=HEIGHT)
     p.add_argument("--width", type=int, default=WIDTH)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-gpu-reference", action="store_true",
+                   help="skip timing the unmodified reference (PyTorch/cuDNN) on this GPU")
+    p.add_argument("--no-parity", action="store_true")
+    p.add_argument("--no-extra-arms", action="store_true",
+                   help="skip the sequential / reference-compatible schedules timed beside the headline")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--pipeline", type=int, default=1,
                    help="1: encoder and decoder on two CUDA streams, decoder one frame behind "
@@ -114,44 +125,75 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-# ----------------------------------------------------------------------------- CPU oracle leg
-def cpu_oracle_fps(seconds_budget=25.0):
-    """Times the CPU oracle (test infrastructure; the checker, never the product) on a bounded
-    sample: 1 I + 2 P frames at 480x272 (1/16 of the 1080p pixel count, conv cost is linear in
-    pixels), all host threads; returns 1080p-equivalent frames/s."""
-    from dcvc_b200 import arch, synth
-    from oracle import codec_oracle as co
+# ----------------------------------------------------------------------------- CPU reference leg
+def _synth_weights():
+    from dcvc_b200 import arch
+    return (arch.synth_state_dict(arch.intra_spec(), 0), arch.synth_state_dict(arch.dmc_spec(), 100))
+
+
+NF = 8      # synthetic frames per sequence (played as a ping-pong)
+
+
+def _padded_host_frames(h, w, seed):
+    from dcvc_b200 import synth
+    return pad_frame(synth.synth_frames(NF, h, w, seed=seed))
+
+
+def cpu_reference(args, n_frames, dpb=None, first_idx=0, seed=0):
+    """Times the reference's own CPU implementation of the path at the bench's OWN configuration
+    (1080p frames, same weights, same rate point) on all host threads: `n_frames` frames of
+    compress + decompress, I frame first unless a dpb is given.  kind "reference" = the
+    UNMODIFIED reference Python + its C++ coder (oracle/_ref, built from /root/reference by
+    oracle/build_ref.sh); kind "port" = the oracle restatement when that copy is absent.
+    This is measurement infrastructure: the checker / baseline, never the product."""
+    from oracle import ref_runner
+    sd_i, sd_p = _synth_weights()
+    frames = _padded_host_frames(args.height, args.width, seed)
+    frames = frames[first_idx:first_idx + n_frames]
     cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    h, w = 272, 480
-    scale = (1088 * 1920) / (h * w)
-    sd_i = arch.synth_state_dict(arch.intra_spec(), 0)
-    sd_p = arch.synth_state_dict(arch.dmc_spec(), 100)
-    o_i, o_p = co.OracleIntra(sd_i, 1), co.OracleDMC(sd_p, 1)
-    o_i.update()
-    o_p.update()
-    frames = synth.synth_frames(3, h, w, seed=0)
-    t0 = time.time()
-    n = 0
-    with torch.no_grad():
-        enc = o_i.compress(frames[0:1], Q_IN_CKPT, Q_INDEX)
-        dec = o_i.decompress(enc["bit_stream"], h, w, Q_IN_CKPT, Q_INDEX)
-        dpb = {"ref_frame": dec["x_hat"], "ref_feature": None, "ref_mv_feature": None,
-               "ref_y": None, "ref_mv_y": None}
-        n += 1
-        for k in (1, 2):
-            if time.time() - t0 > seconds_budget:
-                break
-            enc = o_p.compress(frames[k:k + 1], dpb, Q_IN_CKPT, Q_INDEX, k % 4)
-            dpb = o_p.decompress(dpb, enc["bit_stream"], h, w, Q_IN_CKPT, Q_INDEX, k % 4)["dpb"]
-            n += 1
-    dt = time.time() - t0
-    fps_small = n / dt
-    return {"value": fps_small / scale, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} frames (1 I + {n - 1} P) enc+dec at {w}x{h} = 1/{scale:.0f} of the "
-                      f"1080p pixel count in {dt:.1f} s; value = measured {fps_small:.4f} "
-                      f"frames/s / {scale:.0f} (1080p-equivalent); oracle torch fp32 + C rANS "
-                      f"port of the reference coder"}
+    if ref_runner.available():
+        secs, sizes, kinds, cores = ref_runner.cpu_reference_times(
+            sd_i, sd_p, frames, Q_IN_CKPT, Q_INDEX, dpb=dpb, first_idx=first_idx, threads=cores)
+        kind = "reference"
+        what = ("unmodified reference DCVC-DC (IntraNoAR/DMC compress+decompress, torch %s CPU "
+                "fp32 + the reference's C++ rANS)" % torch.__version__)
+    else:
+        from oracle import codec_oracle as co
+        torch.set_num_threads(cores)
+        o_i, o_p = co.OracleIntra(sd_i, 1), co.OracleDMC(sd_p, 1)
+        o_i.update()
+        o_p.update()
+        secs, sizes, kinds = [], [], []
+        h, w = frames.shape[2], frames.shape[3]
+        if dpb is not None:
+            dpb = {k: (v.detach().cpu().contiguous() if v is not None else None)
+                   for k, v in dpb.items()}
+        with torch.no_grad():
+            for k in range(frames.shape[0]):
+                t0 = time.perf_counter()
+                if dpb is None:
+                    enc = o_i.compress(frames[k:k + 1], Q_IN_CKPT, Q_INDEX)
+                    dec = o_i.decompress(enc["bit_stream"], h, w, Q_IN_CKPT, Q_INDEX)
+                    dpb = {"ref_frame": dec["x_hat"], "ref_feature": None,
+                           "ref_mv_feature": None, "ref_y": None, "ref_mv_y": None}
+                    kinds.append("I")
+                else:
+                    fi = (first_idx + k) % 4
+                    enc = o_p.compress(frames[k:k + 1], dpb, Q_IN_CKPT, Q_INDEX, fi)
+                    dpb = o_p.decompress(dpb, enc["bit_stream"], h, w, Q_IN_CKPT, Q_INDEX,
+                                         fi)["dpb"]
+                    kinds.append("P")
+                secs.append(time.perf_counter() - t0)
+                sizes.append(len(enc["bit_stream"]))
+        kind = "port"
+        what = "oracle port (torch fp32 CPU restatement + C port of the reference rANS)"
+    total = sum(secs)
+    return {"value": len(secs) / total, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{len(secs)} frame(s) [{' '.join(kinds)}] of the bench's own "
+                      f"{args.width}x{args.height} sequence, compress+decompress, "
+                      f"{', '.join('%.1f s' % t for t in secs)} per frame on {cores} threads; "
+                      f"{what}",
+            "seconds_per_frame": secs, "bytes_per_frame": sizes}
 
 
 def workload_text(args):
@@ -161,30 +203,25 @@ def workload_text(args):
 
 
 def run_reference(args, rank):
-    """--impl reference: the reference's CPU implementation of the path (the oracle port, all
-    host threads) on this arm's metric / config; each step is one bounded sample (see
-    cpu_baseline.sample); rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path on the box's host
+    cores, at THIS arm's configuration (1080p, same weights / frames / rate point).  A step is one
+    frame's compress + decompress; a 1080p frame costs tens of seconds of CPU, so the run is
+    bounded to 1 I + 1 P frame (no warm-up: nothing to warm), whatever --steps asks; rank 0 only."""
     if rank != 0:
         return
     t0 = time.time()
-    for _ in range(min(args.warmup, 1)):
-        cpu_oracle_fps()
-    res = []
-    while len(res) < max(1, args.steps) and (not res or time.time() - t0 < 150.0):
-        res.append(cpu_oracle_fps())
-    value = sum(r["value"] for r in res) / len(res)
-    best = dict(res[-1])
-    best["value"] = value
-    best["sample"] += f"; mean of {len(res)} timed sample(s)"
+    res = cpu_reference(args, 2)
+    secs = res["seconds_per_frame"]
+    value = res["value"]
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": len(res), "warmup": min(args.warmup, 1), "ms_per_step": 1000.0 / value,
+            "steps": len(secs), "warmup": 0, "ms_per_step": 1000.0 * sum(secs) / len(secs),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "reference",
             "config": {"workload": workload_text(args),
-                       "note": "CPU sample at reduced resolution, scaled to 1080p-equivalent "
-                               "frames/s (see cpu_baseline.sample); coder: the reference's "
-                               "sequential rANS, 1 stream"},
-            "cpu_baseline": best,
+                       "note": "CPU arm: the reference's sequential frame loop, 1 process, all host "
+                               "threads, coder = the reference's single-stream rANS; bounded to "
+                               "1 I + 1 P frame at the full 1080p size (measured, not scaled)"},
+            "cpu_baseline": {k: v for k, v in res.items()},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0},
             "wall_s": time.time() - t0}
@@ -262,7 +299,7 @@ def main():
     # dpb), as it would be in a separate process; the two only share the byte stream
     i_dec, p_dec = make_nets() if args.pipeline else (None, None)
 
-    nf = 8
+    nf = NF
     host = synth.synth_frames(nf, H, W, seed=rank).pin_memory()      # [nf,3,H,W] fp32 in [0,1]
     order = list(range(nf)) + list(range(nf - 2, 0, -1))              # ping-pong: small motion
     resident = [pad_frame(host[k:k + 1].to(dev)) for k in range(nf)]
@@ -274,18 +311,21 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed(loop_body):
-        if args.pipeline:
+    def timed(loop_body, pipeline=None, nets=None, steps=None):
+        pipeline = args.pipeline if pipeline is None else pipeline
+        ni, np_ = nets if nets is not None else (i_net, p_net)
+        total = args.warmup + (args.steps if steps is None else steps)
+        if pipeline:
             from dcvc_b200.pipeline import EncDecPipeline
-            seq = EncDecPipeline(i_net, p_net, i_dec, p_dec, INTRA_PERIOD, Q_IN_CKPT, Q_INDEX, dev)
+            seq = EncDecPipeline(ni, np_, i_dec, p_dec, INTRA_PERIOD, Q_IN_CKPT, Q_INDEX, dev)
             tstream = seq.enc_stream
         else:
-            seq = Sequence(i_net, p_net, H, W)
+            seq = Sequence(ni, np_, H, W)
             tstream = torch.cuda.current_stream(dev)
         with torch.no_grad():
             for s in range(args.warmup):
                 loop_body(seq, s)
-            if args.pipeline:
+            if pipeline:
                 seq.flush()                      # the timed region holds K encodes and K decodes
             barrier()
             l0 = _lib.launch_count()
@@ -293,7 +333,7 @@ def main():
             e0.record(tstream)
             for s in range(args.warmup, total):
                 loop_body(seq, s)
-            if args.pipeline:
+            if pipeline:
                 last = seq.flush()
                 loop_body(None, last)            # end-of-run hook (pending metric reads)
                 seq.join(tstream)                # the encoder stream waits for the decoder's
@@ -311,7 +351,7 @@ def main():
     def body_resident(seq, s):
         if seq is None:
             return
-        if args.pipeline:
+        if hasattr(seq, "push"):
             seq.push(resident[order[s % len(order)]])
         else:
             seq.step(resident[order[s % len(order)]])
@@ -377,21 +417,80 @@ def main():
         pseq = Sequence(i_net, p_net, H, W) if args.pipeline else seq
         roofline, table = profile_step(pseq, resident[order[total % len(order)]], args)
 
+    # the same workload in the schedules a reference user would compare with (1 GPU only; short)
+    arms = None
+    if world == 1 and not args.no_extra_arms:
+        arms = {}
+        k = min(args.steps, 24)
+        ms_s, _, seq_s = timed(body_resident, pipeline=0, steps=k)
+        arms["sequential"] = {
+            "value": k / (ms_s / 1000.0), "unit": UNIT, "ms_per_step": ms_s / k, "steps": k,
+            "what": "the drop-in call order of DMC.encode_decode / test_video.py: encode a frame, "
+                    "then decode it, one model instance, one stream; same coder as the headline"}
+        ci = dcvc_b200.IntraNoAR(stream_part=16, coder_mode="compat")
+        cp = dcvc_b200.DMC(stream_part=16, coder_mode="compat")
+        ci.load_state_dict(arch.synth_state_dict(arch.intra_spec(), 0))
+        cp.load_state_dict(arch.synth_state_dict(arch.dmc_spec(), 100))
+        ci, cp = ci.to(dev).eval(), cp.to(dev).eval()
+        ci.update(force=True)
+        cp.update(force=True)
+        kc = min(args.steps, 8)
+        ms_c, _, seq_c = timed(body_resident, pipeline=0, nets=(ci, cp), steps=kc)
+        arms["reference_compatible"] = {
+            "value": kc / (ms_c / 1000.0), "unit": UNIT, "ms_per_step": ms_c / kc, "steps": kc,
+            "bits_per_frame": seq_c.bits / max(seq_c.idx, 1),
+            "what": "bitstream interchangeable with the reference: compat container "
+                    "(--stream_part_i/p 16, py_rans.cpp:66-119; one device thread per part), "
+                    "sequential encode -> decode"}
+        del ci, cp, seq_c
+
+    parity = None
+    if rank == 0 and not args.no_parity:
+        parity = parity_block(i_net, p_net, resident, order, args)
+
+    gpu_ref = None
+    if rank == 0 and world == 1 and not args.no_gpu_reference:
+        try:
+            from oracle import ref_runner
+            if ref_runner.available():
+                sd_i, sd_p = _synth_weights()
+                gpu_ref = ref_runner.gpu_reference_fps(sd_i, sd_p, _padded_host_frames(H, W, rank),
+                                                       Q_IN_CKPT, Q_INDEX, dev)
+            else:
+                gpu_ref = {"unavailable": "oracle/_ref/DCVC-DC (staged reference Python) absent"}
+        except Exception as e:      # measurement aid only: never takes the bench line down
+            gpu_ref = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+
     if rank == 0:
-        cpu = None if args.no_cpu_baseline else cpu_oracle_fps()
+        cpu = None
+        if not args.no_cpu_baseline:
+            # one P frame of this very sequence through the reference on the host cores, starting
+            # from the decoded I frame (a P frame is ~97 % of a GOP-32; ~20-40 s of CPU)
+            with torch.no_grad():
+                enc = i_net.compress(resident[0], Q_IN_CKPT, Q_INDEX)
+                dec = i_net.decompress(enc["bit_stream"], resident[0].shape[2],
+                                       resident[0].shape[3], Q_IN_CKPT, Q_INDEX)
+            dpb0 = {"ref_frame": dec["x_hat"].contiguous(), "ref_feature": None,
+                    "ref_mv_feature": None, "ref_y": None, "ref_mv_y": None}
+            cpu = cpu_reference(args, 1, dpb=dpb0, first_idx=1, seed=rank)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "tf32" if args.conv_mode == 1 else "f32", "data": "synthetic",
+                "dtype": ("tf32 + binary16 storage of conv-to-conv activations, fp32 accumulate"
+                          if ops.F16 else "tf32, fp32 accumulate")
+                if args.conv_mode == 1 else "f32", "data": "synthetic",
                 "config": {"workload": workload_text(args),
                            "l2": "inputs larger than L2: every step streams a new frame through >= 6 GB of activations (full-resolution tensors are 130-400 MB each, the L2 is 126 MB); no explicit flush",
                            "conv_mode": args.conv_mode, "coder": args.coder,
-                           "schedule": ("encoder and decoder are two model instances on two CUDA "
-                                        "streams, the decoder one frame behind the encoder; every "
-                                        "frame is encoded and decoded inside the timed region")
+                           "schedule": ("PIPELINED (dcvc_b200.pipeline.EncDecPipeline, an API the "
+                                        "reference does not have): encoder and decoder are two model "
+                                        "instances on two CUDA streams, the decoder one frame behind "
+                                        "the encoder; every frame is encoded and decoded inside the "
+                                        "timed region; `arms.sequential` is the reference's call order")
                            if args.pipeline else "sequential encode -> decode per frame"},
                 "clocks": clock_info, "gpu_launches": int(launches), "e2e": e2e,
-                "roofline": roofline, "cpu_baseline": cpu,
+                "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "arms": arms,
+                "gpu_reference": gpu_ref,
                 "bits_per_frame": bits_per_frame,
                 "psnr_db": (10 * math.log10(rd[2] / max(rd[1], 1e-12)) if rd[2] else None)}
         print(json.dumps(line), flush=True)
@@ -400,6 +499,80 @@ def main():
                 json.dump(table, f, indent=1)
     if world > 1:
         dist.destroy_process_group()
+
+
+def parity_block(i_net, p_net, resident, order, args):
+    """Parity figures printed beside the timing, computed on the first
+    frames of the bench's own sequence, outside the timed region: 1 I + 2 P frames coded in the
+    benchmarked conv mode and in mode 0 (fp32 FMA, which tests/test_gpu_1080p.py holds bit-equal
+    in symbols to the CPU oracle at this size) FROM THE SAME dpb, so the figures are per-frame
+    kernel error.  enc_dec_equal: the encoder's reconstruction (every dpb entry) equals the
+    decoder's bit for bit in the benchmarked mode."""
+    from dcvc_b200 import ops
+    keys = ("ref_frame", "ref_feature", "ref_mv_feature", "ref_y", "ref_mv_y")
+    prev = ops.CONV_MODE
+
+    def code(kind, x, dpb, fi, mode):
+        ops.set_conv_mode(mode)
+        net = i_net if kind == "I" else p_net
+        net.taps = {}
+        ph, pw = x.shape[2], x.shape[3]
+        if kind == "I":
+            enc = net.compress(x, Q_IN_CKPT, Q_INDEX)
+            dec = net.decompress(enc["bit_stream"], ph, pw, Q_IN_CKPT, Q_INDEX)
+            equal = bool(torch.equal(enc["x_hat"], dec["x_hat"]))
+            new = {"ref_frame": dec["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+                   "ref_y": None, "ref_mv_y": None}
+        else:
+            enc = net.compress(x, dpb, Q_IN_CKPT, Q_INDEX, fi)
+            dec = net.decompress(dpb, enc["bit_stream"], ph, pw, Q_IN_CKPT, Q_INDEX, fi)
+            equal = all(bool(torch.equal(enc["dpb"][k], dec["dpb"][k])) for k in keys)
+            new = dec["dpb"]
+        taps, net.taps = net.taps, None
+        return len(enc["bit_stream"]), new, taps, equal
+
+    def flips(ta, tb, prefixes):
+        n = d = 0
+        for pre in prefixes:
+            for st in range(4):
+                a, b = ta[f"{pre}_q_w_{st}"], tb[f"{pre}_q_w_{st}"]
+                n += a.numel()
+                d += int((a != b).sum())
+        return d, n
+
+    out = {"frames": "1 I + 2 P of this sequence, benchmarked mode vs mode 0 (fp32 FMA) from the same dpb",
+           "enc_dec_equal": True, "symbol_flips": 0, "symbols": 0}
+    bits_m, bits_0, sq, npx = 0, 0, 0.0, 0
+    try:
+        with torch.no_grad():
+            dpb = None
+            for k in range(3):
+                x = resident[order[k]]
+                kind = "I" if k == 0 else "P"
+                b0, dpb0, t0, eq0 = code(kind, x, dpb, k % 4, 0)
+                if args.conv_mode != 0:
+                    b1, dpb1, t1, eq1 = code(kind, x, dpb, k % 4, args.conv_mode)
+                else:
+                    b1, dpb1, t1, eq1 = b0, dpb0, t0, eq0
+                out["enc_dec_equal"] = out["enc_dec_equal"] and eq0 and eq1
+                d, n = flips(t1, t0, ("i_y",) if kind == "I" else ("p_y", "p_mv_y"))
+                out["symbol_flips"] += d
+                out["symbols"] += n
+                bits_m += b1
+                bits_0 += b0
+                diff = dpb1["ref_frame"] - dpb0["ref_frame"]
+                sq += float(diff.pow(2).sum())
+                npx += diff.numel()
+                dpb = dpb0
+    finally:
+        ops.set_conv_mode(prev)
+        i_net.taps = p_net.taps = None
+    out["x_hat_rms_vs_mode0"] = (sq / max(npx, 1)) ** 0.5
+    out["d_bits_pct"] = 100.0 * (bits_m - bits_0) / max(bits_0, 1)
+    out["symbol_flip_frac"] = out["symbol_flips"] / max(out["symbols"], 1)
+    out["oracle_link"] = ("mode 0 vs the CPU oracle at 1080p: symbols bit-equal, x_hat RMS 4e-8 "
+                          "(tests/test_gpu_1080p.py, profiles/r02_parity_1080p.json)")
+    return out
 
 
 def profile_step(seq, x, args):

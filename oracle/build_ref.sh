@@ -46,4 +46,26 @@ if [ -f "$HEM/rans/rans_interface.cpp" ]; then
   INCS=(-I"$HEM/rans")
   build "$OUT/hem/MLCodec_rans$SUF" "$HEM/rans/rans_interface.cpp"
 fi
+# A runnable copy of the reference's Python for the boxes that have no /root/reference (the GPU
+# box): bench.py's CPU reference arm and its "unmodified reference on the same B200" figure import
+# it from here (oracle/ref_loader.py).  oracle/_ref/ is git-ignored build output, never committed.
+stage() { # project, subdirs...
+  local proj="$1"; shift
+  local dst="$OUT/$proj"
+  mkdir -p "$dst/src"
+  for d in "$@"; do
+    rm -rf "$dst/src/$d"
+    cp -r "$REF/$proj/src/$d" "$dst/src/$d"
+  done
+  cp "$REF/$proj/test_video.py" "$dst/test_video.py"
+  chmod -R u+w "$dst"
+  find "$dst" -name __pycache__ -type d -prune -exec rm -rf {} +
+}
+stage DCVC-DC models utils transforms
+cp "$OUT/MLCodec_CXX$SUF" "$OUT/MLCodec_rans$SUF" "$OUT/DCVC-DC/src/models/"
+if [ -d "$REF/DCVC-HEM/src/models" ]; then
+  stage DCVC-HEM models layers entropy_models utils
+  cp "$OUT/MLCodec_CXX$SUF" "$OUT/DCVC-HEM/src/entropy_models/"
+  cp "$OUT/hem/MLCodec_rans$SUF" "$OUT/DCVC-HEM/src/entropy_models/"
+fi
 echo "oracle/_ref ready"

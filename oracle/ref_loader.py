@@ -1,8 +1,10 @@
-"""TEST INFRASTRUCTURE -- import the UNMODIFIED reference from /root/reference.
+"""TEST INFRASTRUCTURE -- import the UNMODIFIED reference from /root/reference, or, on a box
+without it (the GPU box), from the staged copy oracle/build_ref.sh left in oracle/_ref/.
 
-Only usable in the build container (the GPU box has no /root/reference).  It is used by
-tests/golden/make_golden.py to generate the committed golden vectors and by the CPU tests
-that pin oracle/ against the reference when the reference tree is present.
+It is used by tests/golden/make_golden.py to generate the committed golden vectors, by the CPU
+tests that pin oracle/ against the reference when the reference tree is present, and by
+bench.py's reference arms (the reference's own CPU path, and the unmodified reference on the
+same GPU) -- never by the product.
 
 No reference source is copied: the reference's Python is imported in place, and the two
 native modules it lazily imports with a relative import
@@ -20,10 +22,20 @@ import types
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_ROOT = os.environ.get("DCVC_REFERENCE_ROOT", "/root/reference")
 _SUF = sysconfig.get_config_var("EXT_SUFFIX")
+# where /root/reference does not exist (the GPU box) the staged copy made by build_ref.sh in the
+# build container (oracle/_ref/<project>/, git-ignored, travels with gpurun) is imported instead
+STAGED_ROOT = os.path.join(HERE, "_ref")
+
+
+def project_root(project="DCVC-DC"):
+    for root in (REF_ROOT, STAGED_ROOT):
+        if os.path.isdir(os.path.join(root, project, "src", "models")):
+            return os.path.join(root, project)
+    return None
 
 
 def reference_available(project="DCVC-DC"):
-    return os.path.isdir(os.path.join(REF_ROOT, project, "src")) and \
+    return project_root(project) is not None and \
         os.path.isfile(os.path.join(HERE, "_ref", "MLCodec_rans" + _SUF))
 
 
@@ -86,7 +98,7 @@ def import_reference(project="DCVC-DC"):
     """
     if not reference_available(project):
         raise RuntimeError("reference tree or oracle/_ref not available")
-    root = os.path.join(REF_ROOT, project)
+    root = project_root(project)
     if "src" in sys.modules:
         cur = getattr(sys.modules["src"], "__path__", [""])
         if not any(os.path.abspath(p).startswith(root) for p in cur):
