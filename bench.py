@@ -69,6 +69,10 @@ def parse_args():
                    help="1: encoder and decoder on two CUDA streams, decoder one frame behind "
                         "(dcvc_b200.pipeline); 0: the reference's strictly sequential frame loop")
     p.add_argument("--profile-out", default=None, help="write the per-kernel table (json) here")
+    p.add_argument("--workload", default="rgb1080p", choices=["rgb1080p", "entropy", "yuv420x8"],
+                   help="rgb1080p: BASELINE configs[1] (the headline); entropy: configs[4] "
+                        "microbench (bench_entropy.py); yuv420x8: configs[2], 8 YUV420 sequences "
+                        "dealt by GOP over the ranks (bench_yuv.py)")
     return p.parse_args()
 
 
@@ -265,11 +269,47 @@ class Sequence:
         return self.dpb["ref_frame"], len(stream)
 
 
+class ApiSequence:
+    """The reference harness's own calls (test_video.py:141-143,155-158): `encode_decode` with an
+    output_path, i.e. frame header + bytes written to a file and read back (here on tmpfs), the
+    three device synchronisations DMC.encode_decode makes for its encoding/decoding times."""
+
+    def __init__(self, i_net, p_net, h, w, tmpdir):
+        self.i_net, self.p_net, self.h, self.w = i_net, p_net, h, w
+        self.dpb, self.idx, self.bits = None, 0, 0
+        self.path = os.path.join(tmpdir, f"dcvc_bench_{os.getpid()}.bin")
+
+    def step(self, x_padded):
+        if self.idx % INTRA_PERIOD == 0:
+            r = self.i_net.encode_decode(x_padded, Q_IN_CKPT, Q_INDEX, self.path,
+                                         pic_width=self.w, pic_height=self.h)
+            self.dpb = {"ref_frame": r["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+                        "ref_y": None, "ref_mv_y": None}
+        else:
+            r = self.p_net.encode_decode(x_padded, self.dpb, Q_IN_CKPT, Q_INDEX, self.path,
+                                         pic_width=self.w, pic_height=self.h,
+                                         frame_idx=self.idx % 4)
+            self.dpb = r["dpb"]
+        self.idx += 1
+        self.bits += r["bit"]
+        return self.dpb["ref_frame"], r["bit"] // 8
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.workload == "entropy" and args.impl == "b200":
+        import bench_entropy
+        bench_entropy.run(bench_entropy.parse_args(
+            ["--gpus", str(args.gpus), "--steps", str(min(args.steps, 20)),
+             "--warmup", str(args.warmup)]))
+        return
+    if args.workload == "yuv420x8" and args.impl == "b200":
+        import bench_yuv
+        bench_yuv.run(args)
+        return
     if args.impl == "reference":
         run_reference(args, rank)
         return
@@ -311,7 +351,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def timed(loop_body, pipeline=None, nets=None, steps=None):
+    def timed(loop_body, pipeline=None, nets=None, steps=None, api=False):
         pipeline = args.pipeline if pipeline is None else pipeline
         ni, np_ = nets if nets is not None else (i_net, p_net)
         total = args.warmup + (args.steps if steps is None else steps)
@@ -319,6 +359,10 @@ def main():
             from dcvc_b200.pipeline import EncDecPipeline
             seq = EncDecPipeline(ni, np_, i_dec, p_dec, INTRA_PERIOD, Q_IN_CKPT, Q_INDEX, dev)
             tstream = seq.enc_stream
+        elif api:
+            tmp = "/dev/shm" if os.path.isdir("/dev/shm") else "/tmp"
+            seq = ApiSequence(ni, np_, resident[0].shape[2], resident[0].shape[3], tmp)
+            tstream = torch.cuda.current_stream(dev)
         else:
             seq = Sequence(ni, np_, H, W)
             tstream = torch.cuda.current_stream(dev)
@@ -427,6 +471,17 @@ def main():
             "value": k / (ms_s / 1000.0), "unit": UNIT, "ms_per_step": ms_s / k, "steps": k,
             "what": "the drop-in call order of DMC.encode_decode / test_video.py: encode a frame, "
                     "then decode it, one model instance, one stream; same coder as the headline"}
+        ms_a, _, seq_a = timed(body_resident, pipeline=0, steps=k, api=True)
+        arms["encode_decode_api"] = {
+            "value": k / (ms_a / 1000.0), "unit": UNIT, "ms_per_step": ms_a / k, "steps": k,
+            "what": "IntraNoAR.encode_decode / DMC.encode_decode with an output_path, exactly as "
+                    "test_video.py:141-143,155-158 calls them: frame file written and read back "
+                    "(tmpfs), the call's own device synchronisations; the frame is reconstructed "
+                    "once, by the decoder (the reference also continues from the decoder's dpb)"}
+        try:
+            os.remove(seq_a.path)
+        except OSError:
+            pass
         ci = dcvc_b200.IntraNoAR(stream_part=16, coder_mode="compat")
         cp = dcvc_b200.DMC(stream_part=16, coder_mode="compat")
         ci.load_state_dict(arch.synth_state_dict(arch.intra_spec(), 0))

@@ -155,10 +155,13 @@ __global__ void ilv_prepare_kernel(const EncJob job, uint2 *ops) {
     const int32_t *cdf = cr.t.cdf + (int64_t)index * cr.t.stride;
     const int32_t max_value = cr.t.sizes[index] - 2;
     int32_t value = (int32_t)cr.sym[pos] - cr.t.offsets[index];
-    uint32_t esc = 0;
-    if (value < 0 || value >= max_value) { value = max_value; esc = 1; }
+    // out of the table's support: the escape interval, and instead of the reciprocal the raw
+    // value whose nibbles follow it (rans.cpp:88-101): word y = (raw << 1) | 1, raw < 2^17
+    uint32_t esc = 0, raw = 0;
+    if (value < 0) { raw = (uint32_t)(-2 * value - 1); value = max_value; esc = 1; }
+    else if (value >= max_value) { raw = (uint32_t)(2 * (value - max_value)); value = max_value; esc = 1; }
     const uint32_t start = (uint32_t)cdf[value], freq = (uint32_t)(cdf[value + 1] - cdf[value]);
-    ops[i] = make_uint2(start | (freq << 16), ((0xffffffffu / freq) & ~1u) | esc);
+    ops[i] = make_uint2(start | (freq << 16), esc ? ((raw << 1) | 1u) : ((0xffffffffu / freq) & ~1u));
   }
 }
 
@@ -213,19 +216,20 @@ __global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, const 
             x = (q << 16) + rem + start;
           }
         } else {
-          // some lane escapes its table's support: expand to (interval, nibbles...) and walk the
-          // operation slots backwards (rans.cpp:76-139)
-          const int64_t k = (r_hi - 1 - j) * 32 + lane;
-          rans::Op full[rans::MAX_OPS];
-          int nops = 0;
-          if (active) {
-            const int64_t pos = off + k;
-            nops = rans::expand_symbol(cr.sym[pos], call_index(cr, pos), cr.t, full);
-          }
+          // some lane escapes its table's support: its operations are the escape interval
+          // (slot 0), the digit count (slot 1; an int16 symbol has at most 5 hex digits, so the
+          // count is one nibble) and the digits of raw, low first (rans.cpp:76-139); walk the
+          // slots backwards, all lanes in step
+          const bool esc = active && (o[j].y & 1u);
+          const uint32_t raw = o[j].y >> 1;
+          const int nb = esc ? (raw ? (35 - __clz(raw)) >> 2 : 0) : 0;
+          const int nops = active ? (esc ? 2 + nb : 1) : 0;
           const int maxops = __reduce_max_sync(0xffffffffu, nops);
           for (int s = maxops - 1; s >= 0; --s) {
             const bool has = s < nops;
-            const bool emit = has && rans::enc32_needs_emit(x, full[has ? s : 0]);
+            const bool bypass = s > 0;
+            const uint32_t x_max = bypass ? (1u << 28) : (freq << 16);
+            const bool emit = has && x >= x_max;
             const uint32_t m = __ballot_sync(0xffffffffu, emit);
             const int cnt = __popc(m);
             if (cnt) {
@@ -237,7 +241,19 @@ __global__ void __launch_bounds__(32) ilv_encode_kernel(const EncJob job, const 
               }
               if (emit) x >>= 16;
             }
-            if (has) x = rans::enc32_update(x, full[s]);
+            if (has) {
+              if (bypass) {
+                const uint32_t nib = s == 1 ? (uint32_t)nb : (raw >> (4 * (s - 2))) & 15u;
+                x = (x << rans::BYPASS_BITS) | nib;
+              } else if (esc) {
+                x = ((x / freq) << 16) + (x % freq) + start;
+              } else {
+                uint32_t q = __umulhi(x, o[j].y & ~1u);
+                uint32_t rem = x - q * freq;
+                while (rem >= freq) { rem -= freq; ++q; }
+                x = (q << 16) + rem + start;
+              }
+            }
           }
         }
       }

@@ -118,8 +118,10 @@ class IntraNoAR(CompressionModel):
         return {"x_hat": x_hat.nchw(), "bit": torch.sum(bpp_y + bpp_z) * pixel_num,
                 "bpp": bpp_y + bpp_z, "bpp_y": bpp_y, "bpp_z": bpp_z}
 
-    def compress(self, x, q_in_ckpt, q_index):
-        """image_model.py:198-229; stream order z, y parts 0..3."""
+    def compress(self, x, q_in_ckpt, q_index, reconstruct=True):
+        """image_model.py:198-229; stream order z, y parts 0..3.  reconstruct=False (used by
+        encode_decode, which returns the decoder's x_hat as the reference does, :187-196) skips the
+        encoder-side synthesis and returns x_hat None."""
         zs = get_downsampled_shape(x.shape[2], x.shape[3], 64)
         self.entropy_coder.reserve(self.N * (x.shape[2] // 16 * (x.shape[3] // 16) + zs[0] * zs[1]))
         y_hat, coded, z_hat, z_sym, q_dec = self._encode_side(x, q_in_ckpt, q_index, True)
@@ -127,6 +129,8 @@ class IntraNoAR(CompressionModel):
         self.encode_z(z_sym, z_hat, "bit_estimator_z")
         self.encode_y(coded)
         self.entropy_coder.flush()
+        if not reconstruct:
+            return {"bit_stream": self.entropy_coder.get_encoded_stream(), "x_hat": None}
         x_hat = self._synthesis(y_hat, q_dec, clamp=True)
         return {"bit_stream": self.entropy_coder.get_encoded_stream(), "x_hat": x_hat.nchw()}
 
@@ -156,7 +160,7 @@ class IntraNoAR(CompressionModel):
             return {"bit": encoded["bit"].item(), "x_hat": encoded["x_hat"]}
         assert pic_height is not None
         assert pic_width is not None
-        compressed = self.compress(x, q_in_ckpt, q_index)
+        compressed = self.compress(x, q_in_ckpt, q_index, reconstruct=False)
         encode_i(pic_height, pic_width, q_in_ckpt, q_index, compressed["bit_stream"], output_path)
         bit = filesize(output_path) * 8
         height, width, q_in_ckpt, q_index, bit_stream = decode_i(output_path)

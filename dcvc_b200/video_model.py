@@ -292,7 +292,8 @@ class DMC(CompressionModel):
         return x_hat4.slice(0, 3), feature
 
     # ------------------------------------------------------------------ shared encoder side
-    def _encode_side(self, x, dpb, q_in_ckpt, q_index, frame_idx, write, bits=None, coder=None):
+    def _encode_side(self, x, dpb, q_in_ckpt, q_index, frame_idx, write, bits=None, coder=None,
+                     reconstruct=True):
         """compress (:425-453) / forward_one_frame (:559-585) up to the entropy coder.
         `coder(mv_z, z, mv_coded, coded)` is called once every symbol of the frame is known and
         before the reconstruction is enqueued."""
@@ -321,6 +322,8 @@ class DMC(CompressionModel):
         y_hat, coded = self.forward_four_part_prior(y, catb, self._prior_fn("y"), write, b(0))
         if coder is not None:
             coder((mv_z_hat, mv_z_sym), (z_hat, z_sym), mv_coded, coded)
+        if not reconstruct:     # encode_decode: the decoder produces the (bit-identical) dpb
+            return None, (mv_z_hat, mv_z_sym), (z_hat, z_sym), mv_coded, coded
         x_hat, feature = self._recon(y_hat, bufs, y_q_dec)
         if self.taps is not None:
             for k, v in (("est_mv", est_mv), ("mv_y", mv_y), ("mv_z_hat", mv_z_hat),
@@ -342,12 +345,15 @@ class DMC(CompressionModel):
         return new_dpb, (mv_z_hat, mv_z_sym), (z_hat, z_sym), mv_coded, coded
 
     # ------------------------------------------------------------------ reference API
-    def compress(self, x, dpb, q_in_ckpt, q_index, frame_idx, defer=False):
+    def compress(self, x, dpb, q_in_ckpt, q_index, frame_idx, defer=False, reconstruct=True):
         """video_model.py:425-481; stream order mv_z, z, mv_y parts 0..3, y parts 0..3.
         The coder kernels are enqueued BEFORE the frame's reconstruction (the reference hands the
         symbols to its encoder thread at the same point, :449-476, and reconstructs after); the
         host then waits for the coder's event only, so the reconstruction is still running on the
-        GPU when this returns -- whoever reads the dpb next does so in stream order."""
+        GPU when this returns -- whoever reads the dpb next does so in stream order.
+        reconstruct=False (used by encode_decode, which takes the dpb from its own decompress
+        call as the reference does, :535-543) skips the encoder-side reconstruction, whose only
+        product is the returned dpb; the stream is unaffected."""
         ec = self.entropy_coder
         zs_ = get_downsampled_shape(x.shape[2], x.shape[3], 64)
         ec.reserve((64 + arch.CH_16X) * (x.shape[2] // 16 * (x.shape[3] // 16) + zs_[0] * zs_[1]))
@@ -361,7 +367,7 @@ class DMC(CompressionModel):
             ec.flush()
 
         new_dpb, _, _, _, _ = self._encode_side(x, dpb, q_in_ckpt, q_index, frame_idx, True,
-                                                coder=coder)
+                                                coder=coder, reconstruct=reconstruct)
         if defer:      # (pipeline.py) "bit_stream" is a callable: the host wait happens when called
             return {"dpb": new_dpb, "bit_stream": ec.get_encoded_stream}
         return {"dpb": new_dpb, "bit_stream": ec.get_encoded_stream()}
@@ -401,7 +407,10 @@ class DMC(CompressionModel):
             device = x.device
             torch.cuda.synchronize(device=device)
             t0 = time.time()
-            encoded = self.compress(x, dpb, q_in_ckpt, q_index, frame_idx)
+            # the reference discards compress()'s dpb here and continues from the decoder's
+            # (:535-543); both are bit-identical, so only the decoder reconstructs the frame
+            encoded = self.compress(x, dpb, q_in_ckpt, q_index, frame_idx,
+                                    reconstruct=self.taps is not None)
             encode_p(encoded["bit_stream"], q_in_ckpt, q_index, frame_idx, output_path)
             bits = filesize(output_path) * 8
             torch.cuda.synchronize(device=device)
