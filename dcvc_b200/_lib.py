@@ -80,6 +80,11 @@ SIGNATURES = {
     "dcvc_offset_diversity_f16_f16": (c_int, [VP, VP, VP, c_void_p, c_void_p, VP, c_void_p]),
     "dcvc_flow_warp_f16": (c_int, [VP, VP, VP, c_void_p]),
     "dcvc_flow_warp_f16_f16": (c_int, [VP, VP, VP, c_void_p]),
+    "dcvc_frame_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "dcvc_frame_u8_to_view": (c_int, [c_void_p, c_int, c_int, c_int, VP, c_void_p]),
+    "dcvc_plane_sse_ws_bytes": (c_size_t, [c_int, c_int]),
+    "dcvc_view_plane_sse": (c_int, [VP, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_void_p]),
     "dcvc_quad_bits_ws_bytes": (c_size_t, [c_int64]),
     "dcvc_quad_step_enc": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p]),

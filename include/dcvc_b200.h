@@ -189,6 +189,31 @@ int dcvc_offset_diversity_f16_f16(const dcvc_view *x, const dcvc_view *offs_half
                                   const float *fusion_b, const dcvc_view *out, void *stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Frame ingest / egress on the device.  Raw 8-bit planes in device memory
+ * (uploaded by the caller, e.g. from pinned host buffers) <-> the fp32 4:4:4 tensor the models
+ * read and write.  Replaces np_image_to_tensor / astype(float32)/255 of the readers
+ * (DCVC-DC/src/utils/video_reader.py:45-161), ycbcr420_to_444(order=0) and ycbcr444_to_420
+ * (src/transforms/functional.py:61-92), the replicate pad of test_video.py:130-135 and the
+ * squared-error sums of calc_psnr (src/utils/metrics.py:81-92, test_video.py:169-195).
+ *   DCVC_FMT_RGB444: planes R, G, B of h*w bytes each.
+ *   DCVC_FMT_YUV420: planes Y (h*w), U, V ((h/2)*(w/2) each), h and w even.
+ */
+#define DCVC_FMT_RGB444 0
+#define DCVC_FMT_YUV420 1
+size_t dcvc_frame_bytes(int fmt, int h, int w);
+/* dst (3 channels, at least h x w; the excess is the replicate pad): plane value / 255, chroma
+ * repeated 2x2 for 4:2:0 (scipy.ndimage.zoom order 0) */
+int dcvc_frame_u8_to_view(const uint8_t *planes, int fmt, int h, int w, const dcvc_view *dst,
+                          void *stream);
+/* sse3[c] = sum over plane c of (clip(rec) - src/255)^2 in float64, rec cropped to h x w; for
+ * 4:2:0 the chroma planes of rec are the clipped 2x2 means.  rec_planes_out (may be NULL):
+ * the same planes rounded to 8 bits (the decoded-frame writers, src/utils/video_writer.py).
+ * ws: >= dcvc_plane_sse_ws_bytes(h, w) bytes; the reduction order is fixed. */
+size_t dcvc_plane_sse_ws_bytes(int h, int w);
+int dcvc_view_plane_sse(const dcvc_view *rec, int fmt, int h, int w, const uint8_t *src_planes,
+                        double *sse3, uint8_t *rec_planes_out, void *ws, void *stream);
+
+/* ------------------------------------------------------------------------------------------
  * Quad-part entropy model (reference DCVC-DC/src/models/common_model.py:39-61,92-321,
  * entropy_models.py:269-273).
  *

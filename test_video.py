@@ -7,8 +7,9 @@ B200-native models.
 
 One process per GPU instead of the reference's process pool: launched plainly it runs every
 (sequence, rate) job on cuda:0 (or --cuda_device); launched under torchrun (RANK / WORLD_SIZE /
-LOCAL_RANK in the environment) the jobs are dealt round-robin to the ranks and rank 0 gathers
-the per-job records and writes the one JSON.  `--worker` is accepted for command-line
+LOCAL_RANK in the environment) the (job, GOP) units are dealt to the ranks (every GOP restarts
+from an intra frame, so GOPs are independent; `--shard job` deals whole jobs instead) and rank 0
+merges the per-frame records and writes the one JSON.  `--worker` is accepted for command-line
 compatibility and ignored; `--cuda 0` is refused (this implementation has no CPU path);
 `--calc_ssim 1` is refused (MS-SSIM is outside the ported path).
 """
@@ -53,6 +54,8 @@ def parse_args(argv=None):
     p.add_argument("--verbose", type=int, default=0)
     # extension: the product's second container (lossless, warp-interleaved)
     p.add_argument("--coder_mode", choices=("compat", "interleaved"), default="compat")
+    # extension: what is dealt to the ranks under torchrun -- GOPs (default) or whole jobs
+    p.add_argument("--shard", choices=("gop", "job"), default="gop")
     return p.parse_args(argv)
 
 
@@ -155,21 +158,36 @@ def main(argv=None):
         p_net.update(force=True)
 
     jobs = build_jobs(args, config, q_in_ckpt, q_indexes)
-    mine = jobs[rank::world]
-    results = []
-    for job in mine:
+    # the unit of multi-GPU work is one GOP of one job (every GOP restarts from an intra frame,
+    # reference test_video.py:140-159): all (job, GOP) units are dealt longest-first over the ranks
+    # by the same deterministic map on every rank; decoded-frame dumps need whole sequences
+    from dcvc_b200 import sharding
+    units = []
+    for ji, job in enumerate(jobs):
+        per = job["frame_num"] if (args.save_decoded_frame or args.shard == "job") \
+            else max(job["gop_size"], 1)
+        units += [sharding.Unit(ji, u.gop, u.first_frame, u.n_frames)
+                  for u in sharding.work_units(1, job["frame_num"], per)]
+    parts = []
+    for u in sharding.assign_units(units, world)[rank]:
+        job = jobs[u.sequence]
         if job["write_stream"]:
             os.makedirs(job["bin_folder"], exist_ok=True)
-        res = harness.run_sequence(p_net, i_net, job)
-        res.update(ds_name=job["ds_name"], video_path=job["video_path"], rate_idx=job["rate_idx"])
-        results.append(res)
+        rec = harness.run_sequence(p_net, i_net, job, u.first_frame, u.n_frames, summary=False)
+        rec["job"] = u.sequence
+        parts.append(rec)
     if world > 1:
         gathered = [None] * world
-        dist.all_gather_object(gathered, results)
-        results = [r for part in gathered for r in part]
+        dist.all_gather_object(gathered, parts)      # per-frame records: a few floats per frame
+        parts = [r for g in gathered for r in g]
         dist.destroy_process_group()
     if rank != 0:
         return
+    results = []
+    for ji, job in enumerate(jobs):
+        res = harness.merge_units([r for r in parts if r["job"] == ji])
+        res.update(ds_name=job["ds_name"], video_path=job["video_path"], rate_idx=job["rate_idx"])
+        results.append(res)
     log = {}
     for ds_name, ds in config["test_classes"].items():
         if ds["test"] == 0:

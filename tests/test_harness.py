@@ -111,6 +111,21 @@ def test_summary_keys_and_arithmetic():
     assert s["ave_all_frame_psnr_y"] == 1.0 and "ave_i_frame_msssim_v" in s
 
 
+def test_merge_units_equals_whole_sequence_summary():
+    """GOP units coded on different ranks merge into the summary one process would write."""
+    ft, bits = [0, 1, 1, 1, 0, 1, 1, 1], [800.0, 90, 80, 70, 810.0, 95, 85, 75]
+    ps = [40.0, 38, 37, 36, 41.0, 39, 38, 37]
+    planes = {f"{m}_{c}": [float(i) for i in range(8)] for m in ("psnr", "msssim") for c in "yuv"}
+    whole = harness.summarise(ft, bits, ps, [0.0] * 8, 100, 2.0, planes)
+
+    def part(a, b, t):
+        return {"first_frame": a, "frame_types": ft[a:b], "bits": bits[a:b], "psnrs": ps[a:b],
+                "msssims": [0.0] * (b - a), "planes": {k: v[a:b] for k, v in planes.items()},
+                "pixels": 100, "test_time": t}
+    merged = harness.merge_units([part(4, 8, 1.25), part(0, 4, 0.75)])
+    assert merged == whole
+
+
 def _checkpoints(tmp_path):
     paths = []
     for name, spec, seed in (("i", arch.intra_spec(), 0), ("p", arch.dmc_spec(), 100)):
@@ -166,24 +181,67 @@ def test_entry_point_png_with_streams_vs_oracle(tmp_path):
 
 
 @pytest.mark.gpu
-def test_entry_point_yuv420_estimate_mode(tmp_path):
-    h, w, n = 64, 64, 2
+def test_entry_point_yuv420_vs_oracle(tmp_path):
+    """--yuv420 1 through the entry point (YUV file -> pinned upload -> device 4:2:0 -> 4:4:4,
+    coding with stream files, device 4:4:4 -> 4:2:0 + per-plane SSE) against the oracle run on the
+    same planes with the reference's own numpy definitions of the colour handling and PSNR
+    (functional.py:61-92, metrics.py:81-92, test_video.py:169-195)."""
+    scipy_ndimage = pytest.importorskip("scipy.ndimage")
+    from oracle import codec_oracle as co
+    h, w, n = 64, 96, 3
     frames = synth.synth_frames(n, h, w, seed=6)
     os.makedirs(tmp_path / "data")
     yw = harness.YUV420Writer(str(tmp_path / "data" / "seqA"), w, h)
     for k in range(n):
-        y, uv = harness.x_to_yuv420(frames[k:k + 1])
+        y, uv = harness.x_to_yuv420(synth.rgb_to_ycbcr444(frames[k:k + 1]))
         yw.write_420(y, uv)
     yw.close()
-    _, cfg_path = _config(tmp_path, "yuv420", h, w, n, 2)
+    _, cfg_path = _config(tmp_path, "yuv420", h, w, n, 4)
     ip, pp = _checkpoints(tmp_path)
     out = str(tmp_path / "out.json")
-    tv.main(["--i_frame_model_path", ip, "--p_frame_model_path", pp, "--rate_num", "4",
-             "--test_config", cfg_path, "--yuv420", "1", "--output_path", out])
-    log = json.load(open(out))
-    rec = log["SYN"]["seqA"]["003"]
-    for key in ("ave_all_frame_psnr_y", "ave_all_frame_psnr_u", "ave_all_frame_psnr_v",
-                "ave_i_frame_bpp", "ave_p_frame_bpp"):
-        assert key in rec and rec[key] == rec[key]
+    tv.main(["--i_frame_model_path", ip, "--p_frame_model_path", pp, "--rate_num", "2",
+             "--i_frame_q_indexes", "20", "40", "--test_config", cfg_path, "--yuv420", "1",
+             "--cuda", "1", "--write_stream", "1", "--stream_path", str(tmp_path / "bins"),
+             "--output_path", out])
+    rec = json.load(open(out))["SYN"]["seqA"]["000"]
     want = (6 * rec["ave_all_frame_psnr_y"] + rec["ave_all_frame_psnr_u"] + rec["ave_all_frame_psnr_v"]) / 8
     assert abs(rec["ave_all_frame_psnr"] - want) < 1e-4
+    # the oracle on the same file
+    reader = harness.YUV420Reader(str(tmp_path / "data" / "seqA"), w, h)
+    sd_i = arch.synth_state_dict(arch.intra_spec(), 0)
+    sd_p = arch.synth_state_dict(arch.dmc_spec(), 100)
+    o_i, o_p = co.OracleIntra(sd_i, 1), co.OracleDMC(sd_p, 1)
+    o_i.update()
+    o_p.update()
+    torch.set_num_threads(8)
+
+    def calc_psnr(a, b):
+        return 10 * np.log10(1.0 / np.mean(np.square(a.astype(np.float64) - b.astype(np.float64))))
+
+    ps = {c: [] for c in "yuv"}
+    bits, dpb = 0, None
+    with torch.no_grad():
+        for k in range(n):
+            y8, uv8 = reader.read()
+            yf, uvf = y8.astype(np.float32) / 255, uv8.astype(np.float32) / 255
+            yuv = np.concatenate((yf[None], scipy_ndimage.zoom(uvf, (1, 2, 2), order=0)), 0)
+            x = torch.from_numpy(yuv)[None]
+            if k == 0:
+                r = o_i.compress(x, False, 20)
+                bits += (len(r["bit_stream"]) + 13) * 8
+                dpb = {"ref_frame": r["x_hat"].clamp(0, 1), "ref_feature": None,
+                       "ref_mv_feature": None, "ref_y": None, "ref_mv_y": None}
+            else:
+                rp = o_p.compress(x, dpb, False, 20, k % 4)
+                bits += (len(rp["bit_stream"]) + 6) * 8
+                dpb = rp["dpb"]
+                dpb["ref_frame"] = dpb["ref_frame"].clamp(0, 1)
+            rec444 = dpb["ref_frame"][0].numpy()
+            u = np.mean(np.reshape(rec444[1:2], (1, h // 2, 2, w // 2, 2)), axis=(-1, -3))
+            v = np.mean(np.reshape(rec444[2:3], (1, h // 2, 2, w // 2, 2)), axis=(-1, -3))
+            ps["y"].append(calc_psnr(yf, np.clip(rec444[0], 0, 1)))
+            ps["u"].append(calc_psnr(uvf[0], np.clip(u[0], 0, 1)))
+            ps["v"].append(calc_psnr(uvf[1], np.clip(v[0], 0, 1)))
+    for c in "yuv":
+        assert abs(rec[f"ave_all_frame_psnr_{c}"] - sum(ps[c]) / n) < 0.02, c
+    assert abs(rec["ave_all_frame_bpp"] - bits / (n * h * w)) <= 0.005 * bits / (n * h * w)
