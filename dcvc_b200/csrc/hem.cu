@@ -1,0 +1,317 @@
+// hem.cu -- the pieces DCVC-HEM needs beyond the DCVC-DC kernel set: the two-step checkerboard
+// ("dual") spatial prior, per-channel scaling / division, and the squeeze-and-excitation gate.
+//
+//   dual prior : DCVC-HEM/src/models/common_model.py:84-188 (get_mask, process_with_mask,
+//                forward_dual_prior, decompress_dual_prior) + GaussianEncoder.build_indexes
+//                (src/entropy_models/entropy_models.py:264-268) + the bit estimates (:53-75)
+//   scaling    : y / curr_q, y_hat * curr_q with q = LowerBound(q_basic, 0.5) * q_scale
+//                (src/models/video_model.py:263-271, image_model.py:61-63)
+//   SE layer   : SELayer (src/models/video_net.py:149-163): mean over H x W, two bias-free
+//                linear layers (ReLU, sigmoid), per-channel gate
+//
+// Dual-prior algebra.  Channels split in halves (half 0 = first C/2 channels); the checkerboard
+// mask_0 is 1 where (y + x) is even.  Step 0 codes half 0 at mask_0 positions and half 1 at
+// mask_1 positions with (scales, means) from the prior fusion; step 1 codes the complement with
+// (scales, means) from y_spatial_prior(cat(y_hat_0_0, y_hat_1_1, means, scales, quant_step)).
+// The coder's symbol tensor of a step is [1, C/2, h, w]: entry (jj, y, x) holds channel
+// jj + (coded half) * C/2, the one channel of the pair that the step codes at that position.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TPB = 256;
+
+__device__ __forceinline__ int scale_index(const float *__restrict__ edges, float s) {
+  s = fmaxf(s, 1e-5f);
+  int lo = 0, hi = 256;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(edges + mid) <= s) lo = mid + 1; else hi = mid;
+  }
+  if (lo < 256 && __ldg(edges + lo) <= s) ++lo;
+  return max(lo - 1, 0);
+}
+__device__ __forceinline__ float laplace_cdf(float x, float b) {
+  const float sg = (x > 0.f) - (x < 0.f);
+  return 0.5f - 0.5f * sg * expm1f(-fabsf(x) / b);
+}
+__device__ __forceinline__ float normal_cdf(float x, float s) {
+  return 0.5f * (1.0f + erff(x * (1.0f / s) / 1.41421356237309504880f));
+}
+__device__ __forceinline__ float probs_to_bits(float p) {
+  return fmaxf(-1.0f * logf(p + 1e-5f) / 0.69314718055994530942f, 0.f);
+}
+__device__ __forceinline__ float block_sum(float v) {
+  __shared__ float sm[TPB / 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = 0.f;
+  if (threadIdx.x == 0)
+    for (int i = 0; i < TPB / 32; ++i) r += sm[i];
+  return r;
+}
+__global__ void reduce_partials_kernel(const float *__restrict__ part, int n, float *bits) {
+  __shared__ float sm[TPB];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < n; i += TPB) acc += part[i];
+  sm[threadIdx.x] = acc;
+  __syncthreads();
+  for (int o = TPB / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *bits += sm[0];
+}
+
+struct DualGeom {
+  int jj, x, y, C, H2, j, jo;   // j = coded channel of the pair, jo = the other one
+  size_t sym_pos;
+};
+
+__device__ __forceinline__ bool dual_geom(const dcvc_dual &q, int64_t t, DualGeom &g) {
+  const int C = q.cat.c / 4, H2 = C / 2;
+  const int64_t total = (int64_t)q.cat.h * q.cat.w * H2;
+  if (t >= total) return false;
+  g.C = C; g.H2 = H2;
+  g.jj = (int)(t % H2);
+  const int64_t p = t / H2;
+  g.x = (int)(p % q.cat.w);
+  g.y = (int)(p / q.cat.w);
+  const bool mask0 = ((g.x + g.y) & 1) == 0;
+  const bool half1 = (q.step == 0) ? !mask0 : mask0;    // which half the step codes here
+  g.j = g.jj + (half1 ? H2 : 0);
+  g.jo = g.jj + (half1 ? 0 : H2);
+  g.sym_pos = ((size_t)g.jj * q.cat.h + g.y) * q.cat.w + g.x;
+  return true;
+}
+
+// (scale, mean, lower-bounded quant step) of channel j at the step's position
+__device__ __forceinline__ void dual_params(const dcvc_dual &q, const DualGeom &g, int j, float &scale,
+                                            float &mean, float &qs) {
+  if (q.step == 0) {
+    const float *f = q.fused.data + vidx(q.fused, g.y, g.x);     // [q_step | scales | means]
+    qs = fmaxf(f[j], 0.5f);
+    scale = f[g.C + j];
+    mean = f[2 * g.C + j];
+  } else {
+    const float *c = q.cat.data + vidx(q.cat, g.y, g.x);         // [.. | means | scales | q_step]
+    const float *p = q.prior.data + vidx(q.prior, g.y, g.x);     // [sc_0 | mean_0 | sc_1 | mean_1]
+    const int half1 = j >= g.H2;
+    qs = c[3 * g.C + j];
+    scale = p[(half1 ? 2 : 0) * g.H2 + g.jj];
+    mean = p[(half1 ? 3 : 1) * g.H2 + g.jj];
+  }
+}
+
+// step 0 also builds the spatial-prior conv input: cat = [y_hat_0_0 | y_hat_1_1 | means | scales |
+// max(q_step, .5)], zeros where the pair's other channel is not coded yet
+__device__ __forceinline__ void dual_fill_cat(const dcvc_dual &q, const DualGeom &g) {
+  const float *f = q.fused.data + vidx(q.fused, g.y, g.x);
+  float *c = q.cat.data + vidx(q.cat, g.y, g.x);
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const int j = k ? g.jo : g.j;
+    c[g.C + j] = f[2 * g.C + j];
+    c[2 * g.C + j] = f[g.C + j];
+    c[3 * g.C + j] = fmaxf(f[j], 0.5f);
+  }
+  c[g.jo] = 0.f;
+}
+
+__global__ void dual_step_enc_kernel(dcvc_dual q, int16_t *__restrict__ symbols,
+                                     uint8_t *__restrict__ indexes, float *__restrict__ partials) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  DualGeom g;
+  float bits = 0.f;
+  if (dual_geom(q, t, g)) {
+    float scale, mean, qs;
+    dual_params(q, g, g.j, scale, mean, qs);
+    if (q.step == 0) dual_fill_cat(q, g);
+    const float yv = q.y.data[vidx(q.y, g.y, g.x) + g.j] / qs;
+    const float yq = rintf(yv - mean);
+    const float yh = yq + mean;
+    if (q.step == 0) q.cat.data[vidx(q.cat, g.y, g.x) + g.j] = yh;
+    float out = yh * qs;
+    if (q.post_scale) out *= q.post_scale[g.j];
+    q.y_out.data[vidx(q.y_out, g.y, g.x) + g.j] = out;
+    if (symbols) {
+      symbols[g.sym_pos] = (int16_t)fminf(fmaxf(yq, -30000.f), 30000.f);
+      indexes[g.sym_pos] = (uint8_t)scale_index(q.edges, scale);
+    }
+    if (partials) {
+      const float sg = q.distribution == 0 ? fminf(fmaxf(scale, 1e-5f), 1e10f)
+                                           : fminf(fmaxf(scale, 0.11f), 1e10f);
+      const float p = q.distribution == 0
+                          ? laplace_cdf(yq + 0.5f, sg) - laplace_cdf(yq - 0.5f, sg)
+                          : normal_cdf(yq + 0.5f, sg) - normal_cdf(yq - 0.5f, sg);
+      bits = probs_to_bits(p);
+    }
+  }
+  if (partials) {
+    const float s = block_sum(bits);
+    if (threadIdx.x == 0) partials[blockIdx.x] = s;
+  }
+}
+
+__global__ void dual_step_indexes_kernel(dcvc_dual q, uint8_t *__restrict__ indexes) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  DualGeom g;
+  if (!dual_geom(q, t, g)) return;
+  float scale, mean, qs;
+  dual_params(q, g, g.j, scale, mean, qs);
+  indexes[g.sym_pos] = (uint8_t)scale_index(q.edges, scale);
+}
+
+__global__ void dual_step_dec_kernel(dcvc_dual q, const int16_t *__restrict__ symbols) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  DualGeom g;
+  if (!dual_geom(q, t, g)) return;
+  float scale, mean, qs;
+  dual_params(q, g, g.j, scale, mean, qs);
+  if (q.step == 0) dual_fill_cat(q, g);
+  const float yh = (float)symbols[g.sym_pos] + mean;
+  if (q.step == 0) q.cat.data[vidx(q.cat, g.y, g.x) + g.j] = yh;
+  float out = yh * qs;
+  if (q.post_scale) out *= q.post_scale[g.j];
+  q.y_out.data[vidx(q.y_out, g.y, g.x) + g.j] = out;
+}
+
+int dual_check(const dcvc_dual *q, bool need_y) {
+  if (!q || !view_ok(&q->cat) || q->cat.c % 8 || !q->edges || q->step < 0 || q->step > 1)
+    return dcvc_fail(DCVC_ERR_ARG, "dual: bad cat buffer / step");
+  const int C = q->cat.c / 4;
+  const int h = q->cat.h, w = q->cat.w;
+  if (!view_ok(&q->y_out) || q->y_out.c != C || q->y_out.h != h || q->y_out.w != w)
+    return dcvc_fail(DCVC_ERR_ARG, "dual: y_out extent mismatch");
+  if (need_y && (!view_ok(&q->y) || q->y.c != C || q->y.h != h || q->y.w != w))
+    return dcvc_fail(DCVC_ERR_ARG, "dual: y extent mismatch");
+  if (q->step == 0 && (!view_ok(&q->fused) || q->fused.c != 3 * C || q->fused.h != h || q->fused.w != w))
+    return dcvc_fail(DCVC_ERR_ARG, "dual: step 0 needs the prior-fusion output (3C channels)");
+  if (q->step == 1 && (!view_ok(&q->prior) || q->prior.c != 2 * C || q->prior.h != h || q->prior.w != w))
+    return dcvc_fail(DCVC_ERR_ARG, "dual: step 1 needs the spatial-prior output (2C channels)");
+  return DCVC_OK;
+}
+
+// ---------------------------------------------------------------- per-channel scale / divide
+__global__ void channel_scale_kernel(dcvc_view src, dcvc_view dst, const float *__restrict__ v, int divide) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t total = (int64_t)src.h * src.w * src.c;
+  if (t >= total) return;
+  const int c = (int)(t % src.c);
+  const int64_t p = t / src.c;
+  const int x = (int)(p % src.w), y = (int)(p / src.w);
+  const float a = src.data[vidx(src, y, x) + c];
+  dst.data[vidx(dst, y, x) + c] = divide ? a / v[c] : a * v[c];
+}
+
+// ---------------------------------------------------------------- squeeze-and-excitation gate
+// stage 1: per (row block, channel) partial sums in double; stage 2: fixed-order sum, the two
+// bias-free linear layers, sigmoid
+constexpr int SE_ROWS = 8;
+__global__ void se_partial_kernel(dcvc_view x, double *__restrict__ part) {
+  // block = (row block, 0); thread = channel lane, loops channels
+  const int rb = blockIdx.x;
+  const int y0 = rb * SE_ROWS, y1 = min(y0 + SE_ROWS, x.h);
+  for (int c = threadIdx.x; c < x.c; c += blockDim.x) {
+    double acc = 0.0;
+    for (int y = y0; y < y1; ++y) {
+      const float *row = x.data + vidx(x, y, 0) + c;
+      for (int xx = 0; xx < x.w; ++xx) acc += (double)row[(size_t)xx * x.cstride];
+    }
+    part[(size_t)rb * x.c + c] = acc;
+  }
+}
+__global__ void se_gate_kernel(const double *__restrict__ part, int nblocks, int c, int64_t pixels,
+                               const float *__restrict__ w1, const float *__restrict__ w2, int hidden,
+                               float *__restrict__ gate) {
+  extern __shared__ float sm[];      // mean[c], hid[hidden]
+  float *mean = sm, *hid = sm + c;
+  for (int i = threadIdx.x; i < c; i += blockDim.x) {
+    double acc = 0.0;
+    for (int b = 0; b < nblocks; ++b) acc += part[(size_t)b * c + i];
+    mean[i] = (float)(acc / (double)pixels);
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < hidden; k += blockDim.x) {
+    float acc = 0.f;
+    for (int i = 0; i < c; ++i) acc += mean[i] * w1[(size_t)k * c + i];     // Linear(c, c/r).weight [c/r][c]
+    hid[k] = fmaxf(acc, 0.f);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < c; i += blockDim.x) {
+    float acc = 0.f;
+    for (int k = 0; k < hidden; ++k) acc += hid[k] * w2[(size_t)i * hidden + k];   // [c][c/r]
+    gate[i] = 1.0f / (1.0f + expf(-acc));
+  }
+}
+
+}  // namespace
+
+extern "C" int dcvc_dual_step_enc(const dcvc_dual *q, int16_t *symbols, uint8_t *indexes, float *bits,
+                                  void *bits_ws, void *stream) {
+  int rc = dual_check(q, true);
+  if (rc) return rc;
+  if ((symbols == nullptr) != (indexes == nullptr) || (bits && !bits_ws))
+    return dcvc_fail(DCVC_ERR_ARG, "dual_step_enc: symbols/indexes/bits arguments inconsistent");
+  const int64_t n = (int64_t)q->cat.h * q->cat.w * (q->cat.c / 8);
+  const int blocks = cdiv(n, TPB);
+  cudaStream_t s = (cudaStream_t)stream;
+  dual_step_enc_kernel<<<blocks, TPB, 0, s>>>(*q, symbols, indexes, bits ? (float *)bits_ws : nullptr);
+  DCVC_LAUNCHED();
+  if (bits) {
+    reduce_partials_kernel<<<1, TPB, 0, s>>>((const float *)bits_ws, blocks, bits);
+    DCVC_LAUNCHED();
+  }
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_dual_step_indexes(const dcvc_dual *q, uint8_t *indexes, void *stream) {
+  int rc = dual_check(q, false);
+  if (rc) return rc;
+  if (!indexes) return dcvc_fail(DCVC_ERR_ARG, "dual_step_indexes: null output");
+  const int64_t n = (int64_t)q->cat.h * q->cat.w * (q->cat.c / 8);
+  dual_step_indexes_kernel<<<cdiv(n, TPB), TPB, 0, (cudaStream_t)stream>>>(*q, indexes);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_dual_step_dec(const dcvc_dual *q, const int16_t *symbols, void *stream) {
+  int rc = dual_check(q, false);
+  if (rc) return rc;
+  if (!symbols) return dcvc_fail(DCVC_ERR_ARG, "dual_step_dec: null symbols");
+  const int64_t n = (int64_t)q->cat.h * q->cat.w * (q->cat.c / 8);
+  dual_step_dec_kernel<<<cdiv(n, TPB), TPB, 0, (cudaStream_t)stream>>>(*q, symbols);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_channel_scale(const dcvc_view *src, const dcvc_view *dst, const float *vec, int divide,
+                                  void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || !vec || src->h != dst->h || src->w != dst->w || src->c != dst->c)
+    return dcvc_fail(DCVC_ERR_ARG, "channel_scale: bad arguments");
+  const int64_t n = (int64_t)src->h * src->w * src->c;
+  channel_scale_kernel<<<cdiv(n, TPB), TPB, 0, (cudaStream_t)stream>>>(*src, *dst, vec, divide);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
+extern "C" size_t dcvc_se_ws_bytes(int h, int c) {
+  return (size_t)cdiv(h, SE_ROWS) * (size_t)c * sizeof(double);
+}
+
+extern "C" int dcvc_se_gate(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
+                            void *ws, void *stream) {
+  if (!view_ok(x) || !w1 || !w2 || hidden < 1 || !gate || !ws)
+    return dcvc_fail(DCVC_ERR_ARG, "se_gate: bad arguments");
+  const int nblocks = cdiv(x->h, SE_ROWS);
+  cudaStream_t s = (cudaStream_t)stream;
+  se_partial_kernel<<<nblocks, 128, 0, s>>>(*x, (double *)ws);
+  DCVC_LAUNCHED();
+  se_gate_kernel<<<1, 128, (size_t)(x->c + hidden) * sizeof(float), s>>>(
+      (const double *)ws, nblocks, x->c, (int64_t)x->h * x->w, w1, w2, hidden, gate);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
