@@ -42,6 +42,12 @@ class Quad(ctypes.Structure):
                 ("edges", c_void_p), ("step", c_int32), ("distribution", c_int32)]
 
 
+class Dual(ctypes.Structure):
+    _fields_ = [("y", View), ("fused", View), ("prior", View), ("cat", View), ("y_out", View),
+                ("edges", c_void_p), ("post_scale", c_void_p), ("step", c_int32),
+                ("distribution", c_int32)]
+
+
 class Tables(ctypes.Structure):
     _fields_ = [("cdf", c_void_p), ("sizes", c_void_p), ("offsets", c_void_p),
                 ("count", c_int32), ("stride", c_int32)]
@@ -93,6 +99,13 @@ SIGNATURES = {
                                           c_void_p]),
     "dcvc_quad_step_indexes": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p]),
     "dcvc_quad_step_dec": (c_int, [ctypes.POINTER(Quad), c_void_p, c_void_p]),
+    "dcvc_dual_step_enc": (c_int, [ctypes.POINTER(Dual), c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_void_p]),
+    "dcvc_dual_step_indexes": (c_int, [ctypes.POINTER(Dual), c_void_p, c_void_p]),
+    "dcvc_dual_step_dec": (c_int, [ctypes.POINTER(Dual), c_void_p, c_void_p]),
+    "dcvc_channel_scale": (c_int, [VP, VP, c_void_p, c_int, c_void_p]),
+    "dcvc_se_ws_bytes": (c_size_t, [c_int, c_int]),
+    "dcvc_se_gate": (c_int, [VP, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "dcvc_z_quant": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dcvc_z_dequant": (c_int, [c_void_p, VP, c_void_p]),
     "dcvc_pmf_to_quantized_cdf": (c_int, [c_void_p, c_int, c_int, c_void_p]),

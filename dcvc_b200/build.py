@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libdcvc_b200.so")
-SOURCES = ["capi.cu", "conv_direct.cu", "conv_tc.cu", "ffn_tc.cu", "warp.cu", "entropy.cu", "rans.cu", "frame_io.cu"]
+SOURCES = ["capi.cu", "conv_direct.cu", "conv_tc.cu", "ffn_tc.cu", "warp.cu", "entropy.cu", "rans.cu", "frame_io.cu", "hem.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -24,8 +24,8 @@ def _default_init(spec, anchor_num):
     sd = {}
     for name, shape in spec.items():
         if name.endswith(".weight"):
-            bound = 1.0 / math.sqrt(shape[1] * shape[2] * shape[3])
-            sd[name] = (torch.rand(shape) * 2 - 1) * bound
+            fan_in = shape[1] * (shape[2] * shape[3] if len(shape) == 4 else 1)
+            sd[name] = (torch.rand(shape) * 2 - 1) * (1.0 / math.sqrt(fan_in))
         elif name.endswith(".bias"):
             w = spec[name[:-5] + ".weight"]
             bound = 1.0 / math.sqrt(w[1] * w[2] * w[3])

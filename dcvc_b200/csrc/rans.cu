@@ -480,6 +480,7 @@ __global__ void assemble_kernel(int mode, int parts, const uint8_t *buf, uint32_
 // ------------------------------------------------------------------ host context
 struct dcvc_rans {
   int mode = 0, parts = 1;
+  bool bare = false;     // DCVC_RANS_COMPAT_BARE: compat, one part, no flag byte on either side
   int64_t max_symbols = 0;
   EncJob job;
   // device memory: slices of the caller's workspace (dcvc_rans_workspace_bytes)
@@ -528,6 +529,7 @@ WsLayout ws_layout(int mode, int parts, int64_t max_symbols) {
   return w;
 }
 bool create_args_ok(int mode, int parts, int64_t max_symbols) {
+  if (mode == DCVC_RANS_COMPAT_BARE) return parts == 1 && max_symbols >= 1;
   if (mode != DCVC_RANS_COMPAT && mode != DCVC_RANS_INTERLEAVED) return false;
   if (parts < 1 || parts > (mode == DCVC_RANS_COMPAT ? MAX_COMPAT_PARTS : MAX_PARTS)) return false;
   return max_symbols >= 1;
@@ -557,7 +559,7 @@ extern "C" void dcvc_rans_destroy(dcvc_rans *r) {
 
 extern "C" size_t dcvc_rans_workspace_bytes(int mode, int parts, int64_t max_symbols) {
   if (!create_args_ok(mode, parts, max_symbols)) return 0;
-  return ws_layout(mode, parts, max_symbols).total;
+  return ws_layout(mode == DCVC_RANS_COMPAT_BARE ? DCVC_RANS_COMPAT : mode, parts, max_symbols).total;
 }
 
 extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t max_symbols,
@@ -565,13 +567,15 @@ extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t ma
   if (!out || !create_args_ok(mode, parts, max_symbols))
     return dcvc_fail(DCVC_ERR_ARG, "rans_create: bad arguments (mode %d parts %d; compat takes 1..%d parts, "
                      "interleaved 1..%d warps)", mode, parts, MAX_COMPAT_PARTS, MAX_PARTS);
+  const bool bare = mode == DCVC_RANS_COMPAT_BARE;
+  if (bare) mode = DCVC_RANS_COMPAT;
   const WsLayout w = ws_layout(mode, parts, max_symbols);
   if (!workspace || workspace_bytes < w.total || (reinterpret_cast<uintptr_t>(workspace) & 255))
     return dcvc_fail(DCVC_ERR_ARG, "rans_create: workspace of %zu bytes (256-byte aligned device memory) needed, got %zu",
                      w.total, workspace_bytes);
   dcvc_rans *r = new (std::nothrow) dcvc_rans();
   if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_create: out of host memory");
-  r->mode = mode; r->parts = parts; r->max_symbols = max_symbols;
+  r->mode = mode; r->parts = parts; r->max_symbols = max_symbols; r->bare = bare;
   r->job.ncalls = 0; r->job.parts = parts;
   uint8_t *base = static_cast<uint8_t *>(workspace);
   r->buf_words = w.buf_words; r->out_cap = w.out_cap; r->stream_cap = w.stream_cap;
@@ -674,9 +678,10 @@ extern "C" int dcvc_rans_enc_flush_end(dcvc_rans *r, uint8_t *out_host, size_t o
   DCVC_CUDA(cudaEventSynchronize(r->flushed));
   int rc = rans_errors(r->h_meta[0]);
   if (rc) return rc;
-  const size_t len = r->h_meta[1];
+  const size_t skip = r->bare ? 1 : 0;     // the bare framing drops the (constant) flag byte
+  const size_t len = r->h_meta[1] - skip;
   if (len > out_capacity) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_end: output buffer too small");
-  DCVC_CUDA(cudaMemcpyAsync(out_host, r->d_out, len, cudaMemcpyDeviceToHost, r->side));
+  DCVC_CUDA(cudaMemcpyAsync(out_host, r->d_out + skip, len, cudaMemcpyDeviceToHost, r->side));
   DCVC_CUDA(cudaStreamSynchronize(r->side));
   *out_len = len;
   return DCVC_OK;
@@ -697,17 +702,17 @@ extern "C" int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_
     int rc = dcvc_rans_dec_check(r);
     if (rc) return rc;
   }
-  const uint8_t flag = host[0];
+  const uint8_t flag = r->bare ? 0x01 : host[0];     // bare: one part, nothing precedes the words
   int n = (flag >> 4) + 1;
   const int low = flag & 0x0f;
-  size_t hdr = 1;
-  if (flag == 0x0E) {              // extended interleaved header: warp count in two bytes
+  size_t hdr = r->bare ? 0 : 1;
+  if (!r->bare && flag == 0x0E) {  // extended interleaved header: warp count in two bytes
     if (len < 3) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: truncated header");
     n = ((int)host[1] | ((int)host[2] << 8)) + 1;
     hdr = 3;
     if (n <= 16 || n > MAX_PARTS) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: bad warp count %d", n);
   }
-  const int mode = (low == 0xF || flag == 0x0E) ? DCVC_RANS_INTERLEAVED : DCVC_RANS_COMPAT;
+  const int mode = (!r->bare && (low == 0xF || flag == 0x0E)) ? DCVC_RANS_INTERLEAVED : DCVC_RANS_COMPAT;
   if (mode != r->mode) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: container mode %d, coder mode %d", mode, r->mode);
   if (mode == DCVC_RANS_COMPAT && low > 1) return dcvc_fail(DCVC_ERR_STREAM, "rans_dec_set_stream: bad flag byte");
   const int per = (mode == DCVC_RANS_COMPAT && low == 1) ? 2 : 4;

@@ -159,6 +159,8 @@ class EntropyCoder:
 
     mode "compat": the reference's container, byte-identical, stream_part in 1..16.
     mode "interleaved": stream_part warps x 32 interleaved lanes (own container).
+    mode "hem": DCVC-HEM's framing (the bare words of one compat stream, no flag byte;
+                DCVC-HEM/src/cpp/rans/rans_interface.cpp:155-172), stream_part must be 1.
     """
 
     def __init__(self, ec_thread=False, stream_part=1, mode="compat", max_symbols=1 << 22,
@@ -179,7 +181,7 @@ class EntropyCoder:
         """(Re)creates the coder context for frames of up to `max_symbols` symbols.  All device
         memory is a torch tensor owned here and lent to the library as its workspace."""
         L = _lib.lib()
-        mode = 0 if self.mode == "compat" else 1
+        mode = {"compat": 0, "interleaved": 1, "hem": 2}[self.mode]
         nbytes = L.dcvc_rans_workspace_bytes(mode, self.parts, max_symbols)
         if nbytes == 0:
             raise _lib.DcvcError(

@@ -325,3 +325,68 @@ def z_quant(z, z_hat, symbols=None, fparams=None, bits=None, bits_ws=None, strea
 def z_dequant(symbols, z_hat, stream=None):
     with _Prof("z_dequant"):
         _lib.check(_lib.lib().dcvc_z_dequant(symbols.data_ptr(), z_hat.view(), _stream(stream)))
+
+
+# ---------------------------------------------------------------------------- DCVC-HEM pieces
+def _dual(y, fused, prior, cat, y_out, edges, step, distribution, post_scale):
+    q = _lib.Dual()
+    q.y = y.view() if y is not None else NULL_VIEW
+    q.fused = fused.view() if fused is not None else NULL_VIEW
+    q.prior = prior.view() if prior is not None else NULL_VIEW
+    q.cat = cat.view()
+    q.y_out = y_out.view()
+    q.edges = edges.data_ptr()
+    q.post_scale = post_scale.data_ptr() if post_scale is not None else None
+    q.step, q.distribution = step, distribution
+    return q
+
+
+def dual_step_enc(y, fused, prior, cat, y_out, edges, step, distribution, post_scale=None,
+                  symbols=None, indexes=None, bits=None, bits_ws=None, stream=None):
+    q = _dual(y, fused, prior, cat, y_out, edges, step, distribution, post_scale)
+    with _Prof("dual_step_enc"):
+        _lib.check(_lib.lib().dcvc_dual_step_enc(
+            ctypes.byref(q), symbols.data_ptr() if symbols is not None else None,
+            indexes.data_ptr() if indexes is not None else None,
+            bits.data_ptr() if bits is not None else None,
+            bits_ws.data_ptr() if bits_ws is not None else None, _stream(stream)))
+
+
+def dual_step_indexes(fused, prior, cat, y_out, edges, step, indexes, stream=None):
+    q = _dual(None, fused, prior, cat, y_out, edges, step, 0, None)
+    with _Prof("dual_step_indexes"):
+        _lib.check(_lib.lib().dcvc_dual_step_indexes(ctypes.byref(q), indexes.data_ptr(),
+                                                     _stream(stream)))
+
+
+def dual_step_dec(fused, prior, cat, y_out, edges, step, symbols, post_scale=None, stream=None):
+    q = _dual(None, fused, prior, cat, y_out, edges, step, 0, post_scale)
+    with _Prof("dual_step_dec"):
+        _lib.check(_lib.lib().dcvc_dual_step_dec(ctypes.byref(q), symbols.data_ptr(),
+                                                 _stream(stream)))
+
+
+def channel_scale(x, vec, divide=False, out=None, stream=None):
+    """out = x * vec[c] (or x / vec[c]); fp32 views."""
+    if x.f16:
+        raise ValueError("channel_scale works on fp32 activations")
+    if out is None:
+        out = Act.new(x.h, x.w, x.c, x.device)
+    with _Prof("channel_scale", 0, _nb(x, out)):
+        _lib.check(_lib.lib().dcvc_channel_scale(x.view(), out.view(), vec.data_ptr(),
+                                                 int(divide), _stream(stream)))
+    return out
+
+
+def se_gate(x, w1, w2, stream=None):
+    """SELayer gate [C] of the fp32 activation x (w1 [C/r][C], w2 [C][C/r])."""
+    if x.f16:
+        raise ValueError("se_gate works on fp32 activations")
+    hidden = w1.shape[0]
+    gate = torch.empty(x.c, dtype=torch.float32, device=x.device)
+    ws = torch.empty(int(_lib.lib().dcvc_se_ws_bytes(x.h, x.c)) // 8 + 1, dtype=torch.float64,
+                     device=x.device)
+    with _Prof("se_gate", 0, _nb(x)):
+        _lib.check(_lib.lib().dcvc_se_gate(x.view(), w1.data_ptr(), w2.data_ptr(), hidden,
+                                           gate.data_ptr(), ws.data_ptr(), _stream(stream)))
+    return gate

@@ -262,6 +262,48 @@ int dcvc_quad_step_indexes(const dcvc_quad *q, uint8_t *indexes, void *stream);
 /* decoder, phase 2: scatter decoded symbols: y_hat = sym + mean at the step's positions */
 int dcvc_quad_step_dec(const dcvc_quad *q, const int16_t *symbols, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * DCVC-HEM: two-step checkerboard ("dual") spatial prior (reference
+ * DCVC-HEM/src/models/common_model.py:84-188: get_mask, process_with_mask, forward_dual_prior,
+ * decompress_dual_prior).  Channels split in halves; mask_0 = 1 where (y + x) is even.  Step 0
+ * codes half 0 at mask_0 and half 1 at mask_1 positions with (scales, means) from the prior
+ * fusion; step 1 codes the complement with y_spatial_prior's output.
+ *   fused : prior-fusion output [q_step | scales | means] (3C; read by step 0)
+ *   cat   : the spatial-prior conv input [y_hat_0_0 | y_hat_1_1 | means | scales | max(q_step,.5)]
+ *           (4C), WRITTEN by step 0 (it replaces torch.cat, :125), read by step 1
+ *   prior : y_spatial_prior output [scales_0 | means_0 | scales_1 | means_1] (2C; step 1)
+ *   y_out : y_hat * q_step (* post_scale[c] when given: the `* curr_q` that follows, e.g.
+ *           video_model.py:288), written at the step's positions
+ *   symbols / indexes: [1, C/2, h, w] order; entry (jj, y, x) is the one channel of the pair
+ *           {jj, jj + C/2} that the step codes at (y, x) -- y_q_w_0 / y_q_w_1 of :148-153.
+ */
+typedef struct dcvc_dual {
+  dcvc_view y;        /* encoder input (C), already divided by curr_q; unused by the decoder */
+  dcvc_view fused;    /* 3C */
+  dcvc_view prior;    /* 2C (step 1) */
+  dcvc_view cat;      /* 4C */
+  dcvc_view y_out;    /* C */
+  const float *edges; /* device, 256 (see dcvc_quad) */
+  const float *post_scale; /* device [C] or NULL */
+  int32_t step;       /* 0 or 1 */
+  int32_t distribution; /* 0 laplace, 1 gaussian (bit estimate: sigma floor 1e-5 / 0.11) */
+} dcvc_dual;
+int dcvc_dual_step_enc(const dcvc_dual *q, int16_t *symbols, uint8_t *indexes, float *bits,
+                       void *bits_ws, void *stream);   /* bits_ws: dcvc_quad_bits_ws_bytes(C/2*h*w) */
+int dcvc_dual_step_indexes(const dcvc_dual *q, uint8_t *indexes, void *stream);
+int dcvc_dual_step_dec(const dcvc_dual *q, const int16_t *symbols, void *stream);
+/* dst = src * vec[c] (divide = 0) or src / vec[c] (divide = 1, IEEE division): y / curr_q and
+ * y_hat * curr_q of DCVC-HEM (video_model.py:263-271,288; image_model.py:61-63,76), x * gate of
+ * SELayer (video_net.py:162) */
+int dcvc_channel_scale(const dcvc_view *src, const dcvc_view *dst, const float *vec, int divide,
+                       void *stream);
+/* SELayer gate (DCVC-HEM/src/models/video_net.py:149-163): gate = sigmoid(W2 relu(W1 mean_hw(x)));
+ * w1 [hidden][c], w2 [c][hidden] (nn.Linear weights, no bias); the mean is accumulated in float64
+ * in a fixed order.  ws: >= dcvc_se_ws_bytes(h, c). */
+size_t dcvc_se_ws_bytes(int h, int c);
+int dcvc_se_gate(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
+                 void *ws, void *stream);
+
 /* hyper latent: z_hat = round(z) (NHWC in place allowed), symbols in [1,C,h,w] order, and
  * (bits != NULL) factorised-prior bit estimate (BitEstimator, entropy_models.py:58-122;
  * fparams = [h1 b1 a1 h2 b2 a2 h3 b3 a3 h4 b4][C] raw parameters) */
@@ -294,6 +336,11 @@ int dcvc_pmf_to_quantized_cdf(const float *pmf, int n, int precision, uint32_t *
  */
 #define DCVC_RANS_COMPAT 0
 #define DCVC_RANS_INTERLEAVED 1
+/* DCVC-HEM's framing (DCVC-HEM/src/cpp/rans/rans_interface.cpp:85-244: BufferedRansEncoder.flush
+ * returns the bare rANS words, RansDecoder.set_stream takes them): the compat coder with one part
+ * and no flag byte.  Same arithmetic, same tables, symbols clamped to +-30000 like DCVC-DC
+ * (HEM itself passes int32 symbols unclamped; such values do not occur with trained weights). */
+#define DCVC_RANS_COMPAT_BARE 2
 #define DCVC_RANS_MAX_CALLS 32
 
 typedef struct dcvc_rans dcvc_rans; /* opaque coder context (encoder + decoder state) */
