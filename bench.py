@@ -69,10 +69,11 @@ def parse_args():
                    help="1: encoder and decoder on two CUDA streams, decoder one frame behind "
                         "(dcvc_b200.pipeline); 0: the reference's strictly sequential frame loop")
     p.add_argument("--profile-out", default=None, help="write the per-kernel table (json) here")
-    p.add_argument("--workload", default="rgb1080p", choices=["rgb1080p", "entropy", "yuv420x8"],
+    p.add_argument("--workload", default="rgb1080p", choices=["rgb1080p", "entropy", "yuv420x8", "hem_sweep"],
                    help="rgb1080p: BASELINE configs[1] (the headline); entropy: configs[4] "
                         "microbench (bench_entropy.py); yuv420x8: configs[2], 8 YUV420 sequences "
-                        "dealt by GOP over the ranks (bench_yuv.py)")
+                        "dealt by GOP over the ranks (bench_yuv.py); hem_sweep: configs[3], DCVC-HEM "
+                        "4-point q_scale sweep (bench_hem.py)")
     return p.parse_args()
 
 
@@ -309,6 +310,10 @@ def main():
     if args.workload == "yuv420x8" and args.impl == "b200":
         import bench_yuv
         bench_yuv.run(args)
+        return
+    if args.workload == "hem_sweep" and args.impl == "b200":
+        import bench_hem
+        bench_hem.run(args)
         return
     if args.impl == "reference":
         run_reference(args, rank)

@@ -206,22 +206,58 @@ __global__ void channel_scale_kernel(dcvc_view src, dcvc_view dst, const float *
   const float a = src.data[vidx(src, y, x) + c];
   dst.data[vidx(dst, y, x) + c] = divide ? a / v[c] : a * v[c];
 }
+// the same, one thread per 4 channels (views whose pixels are whole 16-byte groups)
+__global__ void channel_scale4_kernel(dcvc_view src, dcvc_view dst, const float *__restrict__ v, int divide) {
+  const int c4n = src.c >> 2;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)src.h * src.w * c4n) return;
+  const int c = (int)(t % c4n) * 4;
+  const int64_t p = t / c4n;
+  const float4 a = *reinterpret_cast<const float4 *>(src.data + (size_t)p * src.cstride + src.coff + c);
+  const float4 q = __ldg(reinterpret_cast<const float4 *>(v + c));
+  float4 r;
+  if (divide) { r.x = a.x / q.x; r.y = a.y / q.y; r.z = a.z / q.z; r.w = a.w / q.w; }
+  else { r.x = a.x * q.x; r.y = a.y * q.y; r.z = a.z * q.z; r.w = a.w * q.w; }
+  *reinterpret_cast<float4 *>(dst.data + (size_t)p * dst.cstride + dst.coff + c) = r;
+}
 
 // ---------------------------------------------------------------- squeeze-and-excitation gate
-// stage 1: per (row block, channel) partial sums in double; stage 2: fixed-order sum, the two
-// bias-free linear layers, sigmoid
-constexpr int SE_ROWS = 8;
-__global__ void se_partial_kernel(dcvc_view x, double *__restrict__ part) {
-  // block = (row block, 0); thread = channel lane, loops channels
-  const int rb = blockIdx.x;
-  const int y0 = rb * SE_ROWS, y1 = min(y0 + SE_ROWS, x.h);
-  for (int c = threadIdx.x; c < x.c; c += blockDim.x) {
-    double acc = 0.0;
-    for (int y = y0; y < y1; ++y) {
-      const float *row = x.data + vidx(x, y, 0) + c;
-      for (int xx = 0; xx < x.w; ++xx) acc += (double)row[(size_t)xx * x.cstride];
+// stage 1: each block sums SE_PIX pixels of every channel (float4 loads, coalesced along the
+// channel axis; fp32 runs of 32 pixels folded into float64); stage 2: fixed-order sum over the
+// blocks, the two bias-free linear layers, sigmoid.  Deterministic: no atomics.
+constexpr int SE_PIX = 4096;
+constexpr int SE_TPB = 256;
+__global__ void __launch_bounds__(SE_TPB) se_partial_kernel(dcvc_view x, double *__restrict__ part) {
+  __shared__ double sm[SE_TPB * 4];
+  const int nvec = x.c >> 2;                 // float4 groups per pixel (c % 4 == 0, nvec <= 64)
+  const int lanes = SE_TPB / nvec;           // pixels in flight per iteration
+  const int vec = threadIdx.x % nvec, lane = threadIdx.x / nvec;
+  const int64_t npix = (int64_t)x.h * x.w;
+  const int64_t p0 = (int64_t)blockIdx.x * SE_PIX;
+  const int64_t p1 = p0 + SE_PIX < npix ? p0 + SE_PIX : npix;
+  double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+  if (lane < lanes) {
+    float4 run = make_float4(0.f, 0.f, 0.f, 0.f);
+    int cnt = 0;
+    for (int64_t p = p0 + lane; p < p1; p += lanes) {
+      const float4 v = *reinterpret_cast<const float4 *>(x.data + (size_t)p * x.cstride + x.coff + 4 * vec);
+      run.x += v.x; run.y += v.y; run.z += v.z; run.w += v.w;
+      if (++cnt == 32) {
+        a0 += run.x; a1 += run.y; a2 += run.z; a3 += run.w;
+        run = make_float4(0.f, 0.f, 0.f, 0.f);
+        cnt = 0;
+      }
     }
-    part[(size_t)rb * x.c + c] = acc;
+    a0 += run.x; a1 += run.y; a2 += run.z; a3 += run.w;
+  }
+  sm[threadIdx.x * 4 + 0] = a0; sm[threadIdx.x * 4 + 1] = a1;
+  sm[threadIdx.x * 4 + 2] = a2; sm[threadIdx.x * 4 + 3] = a3;
+  __syncthreads();
+  if (threadIdx.x < x.c) {                   // thread = channel: sum its column over the lanes
+    const int c = threadIdx.x, v = c >> 2, k = c & 3;
+    double s = 0.0;
+    for (int l = 0; l < lanes; ++l) s += sm[(l * nvec + v) * 4 + k];
+    part[(size_t)blockIdx.x * x.c + c] = s;
   }
 }
 __global__ void se_gate_kernel(const double *__restrict__ part, int nblocks, int c, int64_t pixels,
@@ -293,22 +329,27 @@ extern "C" int dcvc_channel_scale(const dcvc_view *src, const dcvc_view *dst, co
   if (!view_ok(src) || !view_ok(dst) || !vec || src->h != dst->h || src->w != dst->w || src->c != dst->c)
     return dcvc_fail(DCVC_ERR_ARG, "channel_scale: bad arguments");
   const int64_t n = (int64_t)src->h * src->w * src->c;
-  channel_scale_kernel<<<cdiv(n, TPB), TPB, 0, (cudaStream_t)stream>>>(*src, *dst, vec, divide);
+  if (view_al16(src) && view_al16(dst) && (reinterpret_cast<uintptr_t>(vec) & 15) == 0)
+    channel_scale4_kernel<<<cdiv(n / 4, TPB), TPB, 0, (cudaStream_t)stream>>>(*src, *dst, vec, divide);
+  else
+    channel_scale_kernel<<<cdiv(n, TPB), TPB, 0, (cudaStream_t)stream>>>(*src, *dst, vec, divide);
   DCVC_LAUNCHED();
   return DCVC_OK;
 }
 
-extern "C" size_t dcvc_se_ws_bytes(int h, int c) {
-  return (size_t)cdiv(h, SE_ROWS) * (size_t)c * sizeof(double);
+extern "C" size_t dcvc_se_ws_bytes(int h, int w, int c) {
+  return (size_t)cdiv((int64_t)h * w, SE_PIX) * (size_t)c * sizeof(double);
 }
 
 extern "C" int dcvc_se_gate(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
                             void *ws, void *stream) {
   if (!view_ok(x) || !w1 || !w2 || hidden < 1 || !gate || !ws)
     return dcvc_fail(DCVC_ERR_ARG, "se_gate: bad arguments");
-  const int nblocks = cdiv(x->h, SE_ROWS);
+  if (!view_al16(x) || x->c > SE_TPB)
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "se_gate: needs a 16-byte aligned view of at most %d channels", SE_TPB);
+  const int nblocks = cdiv((int64_t)x->h * x->w, SE_PIX);
   cudaStream_t s = (cudaStream_t)stream;
-  se_partial_kernel<<<nblocks, 128, 0, s>>>(*x, (double *)ws);
+  se_partial_kernel<<<nblocks, SE_TPB, 0, s>>>(*x, (double *)ws);
   DCVC_LAUNCHED();
   se_gate_kernel<<<1, 128, (size_t)(x->c + hidden) * sizeof(float), s>>>(
       (const double *)ws, nblocks, x->c, (int64_t)x->h * x->w, w1, w2, hidden, gate);

@@ -50,3 +50,19 @@ def decode_p(inputpath):
         mv_y_q_index, y_q_index = struct.unpack(">2H", f.read(4))
         n, = struct.unpack(">I", f.read(4))
         return mv_y_q_index, y_q_index, f.read(n)
+
+
+def interpolate_log(min_val, max_val, num, decending=True):
+    """DCVC-HEM/src/utils/common.py:23-31: `num` log-spaced q_scales between the checkpoint's
+    extreme anchors (the rate sweep of DCVC-HEM/test_video.py:286-320)."""
+    assert max_val > min_val > 0
+    ends = (np.log(max_val), np.log(min_val)) if decending else (np.log(min_val), np.log(max_val))
+    return np.exp(np.linspace(ends[0], ends[1], num))
+
+
+def get_padding_size(height, width, p=64):
+    """stream_helper.py:22-31; the HEM harness pads with ZEROS to a multiple of 64
+    (DCVC-HEM/test_video.py:114-120)"""
+    new_h = (height + p - 1) // p * p
+    new_w = (width + p - 1) // p * p
+    return 0, new_w - width, 0, new_h - height

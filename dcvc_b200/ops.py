@@ -384,7 +384,7 @@ def se_gate(x, w1, w2, stream=None):
         raise ValueError("se_gate works on fp32 activations")
     hidden = w1.shape[0]
     gate = torch.empty(x.c, dtype=torch.float32, device=x.device)
-    ws = torch.empty(int(_lib.lib().dcvc_se_ws_bytes(x.h, x.c)) // 8 + 1, dtype=torch.float64,
+    ws = torch.empty(int(_lib.lib().dcvc_se_ws_bytes(x.h, x.w, x.c)) // 8 + 1, dtype=torch.float64,
                      device=x.device)
     with _Prof("se_gate", 0, _nb(x)):
         _lib.check(_lib.lib().dcvc_se_gate(x.view(), w1.data_ptr(), w2.data_ptr(), hidden,

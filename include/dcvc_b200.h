@@ -299,8 +299,8 @@ int dcvc_channel_scale(const dcvc_view *src, const dcvc_view *dst, const float *
                        void *stream);
 /* SELayer gate (DCVC-HEM/src/models/video_net.py:149-163): gate = sigmoid(W2 relu(W1 mean_hw(x)));
  * w1 [hidden][c], w2 [c][hidden] (nn.Linear weights, no bias); the mean is accumulated in float64
- * in a fixed order.  ws: >= dcvc_se_ws_bytes(h, c). */
-size_t dcvc_se_ws_bytes(int h, int c);
+ * in a fixed order.  x: 16-byte aligned view, c <= 256.  ws: >= dcvc_se_ws_bytes(h, w, c). */
+size_t dcvc_se_ws_bytes(int h, int w, int c);
 int dcvc_se_gate(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
                  void *ws, void *stream);
 
