@@ -72,22 +72,81 @@ __device__ __forceinline__ int call_index(const CallRec &c, int64_t pos) {
 }
 
 // ------------------------------------------------------------------ compat kernels
-__global__ void compat_encode_kernel(const EncJob job, uint32_t *buf, uint32_t *meta) {
-  if (threadIdx.x != 0) return;
-  const int i = blockIdx.x;
+// Pass 1 (whole grid): per symbol {start | freq << 16, escape ? (raw << 1) | 1 : 0, m} with
+// m = floor((2^64 - 1) / freq), so that the sequential pass replaces its 64-bit division by a
+// multiply-high and a short correction and never waits on a table load.
+__global__ void compat_prepare_kernel(const EncJob job, uint4 *ops) {
+  const int64_t total = job.op_off[job.ncalls];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int c = 0;
+    while (c + 1 < job.ncalls && i >= job.op_off[c + 1]) ++c;
+    const CallRec &cr = job.calls[c];
+    const int64_t pos = i - job.op_off[c];
+    const int index = call_index(cr, pos);
+    const int32_t *cdf = cr.t.cdf + (int64_t)index * cr.t.stride;
+    const int32_t max_value = cr.t.sizes[index] - 2;
+    int32_t value = (int32_t)cr.sym[pos] - cr.t.offsets[index];
+    uint32_t esc = 0, raw = 0;
+    if (value < 0) { raw = (uint32_t)(-2 * value - 1); value = max_value; esc = 1; }
+    else if (value >= max_value) { raw = (uint32_t)(2 * (value - max_value)); value = max_value; esc = 1; }
+    const uint32_t start = (uint32_t)cdf[value], freq = (uint32_t)(cdf[value + 1] - cdf[value]);
+    const uint64_t m = freq ? 0xffffffffffffffffull / freq : 0;
+    ops[i] = make_uint4(start | (freq << 16), esc ? ((raw << 1) | 1u) : 0u, (uint32_t)m, (uint32_t)(m >> 32));
+  }
+}
+
+// Pass 2: one warp per stream part.  The warp fetches 32 prepared operations at a time
+// (coalesced, the next batch in flight while lane 0 works); lane 0 runs the dependent rANS chain
+// of rans.cpp:141-168 (LIFO: last symbol first, within an escape the digits before the count
+// before the escape interval).
+__global__ void __launch_bounds__(32) compat_encode_kernel(const EncJob job, const uint4 *ops_all,
+                                                           uint32_t *buf, uint32_t *meta) {
+  __shared__ uint4 sm[32];
+  const int i = blockIdx.x, lane = threadIdx.x;
   rans::Enc64 e;
   rans::enc64_init(e, buf + reg_off(job, i + 1), buf + reg_off(job, i));
-  rans::Op ops[rans::MAX_OPS];
   for (int c = job.ncalls - 1; c >= 0; --c) {
     const CallRec &cr = job.calls[c];
     int64_t off, cur;
     part_range(cr.n, job.parts, i, off, cur);
-    for (int64_t k = cur - 1; k >= 0; --k) {
-      const int64_t pos = off + k;
-      const int nops = rans::expand_symbol(cr.sym[pos], call_index(cr, pos), cr.t, ops);
-      for (int o = nops - 1; o >= 0; --o) rans::enc64_put(e, ops[o]);
+    const uint4 *ops = ops_all + job.op_off[c] + off;
+    // batches of 32 from the top: batch b covers k in [hi - 32, hi)
+    int64_t hi = cur;
+    uint4 nxt = make_uint4(0, 0, 0, 0);
+    if (hi - 32 + lane >= 0 && hi > 0) nxt = __ldg(ops + hi - 32 + lane);
+    while (hi > 0) {
+      sm[lane] = nxt;
+      const int64_t lo = hi - 32 > 0 ? hi - 32 : 0;
+      const int64_t nhi = lo;
+      if (nhi > 0 && nhi - 32 + lane >= 0) nxt = __ldg(ops + nhi - 32 + lane);
+      __syncwarp();
+      if (lane == 0) {
+        for (int64_t k = hi - 1; k >= lo; --k) {
+          const uint4 o = sm[(int)(k - (hi - 32))];
+          const uint32_t freq = o.x >> 16, start = o.x & 0xffffu;
+          if (o.y & 1u) {                                  // escape: digits (high first), count
+            const uint32_t raw = o.y >> 1;
+            const int nb = raw ? (35 - __clz(raw)) >> 2 : 0;
+            for (int j = nb - 1; j >= -1; --j) {
+              const uint32_t nib = j < 0 ? (uint32_t)nb : (raw >> (4 * j)) & 15u;
+              if (e.x >= (1ull << 59)) rans::enc64_emit(e);
+              e.x = (e.x << rans::BYPASS_BITS) | nib;
+            }
+          }
+          if (e.x >= ((uint64_t)freq << 47)) rans::enc64_emit(e);
+          const uint64_t m = (uint64_t)o.z | ((uint64_t)o.w << 32);
+          uint64_t q = __umul64hi(e.x, m);                 // <= x / freq, short by at most 2
+          uint64_t rem = e.x - q * freq;
+          while (rem >= freq) { rem -= freq; ++q; }
+          e.x = (q << rans::PRECISION) + rem + start;
+        }
+      }
+      __syncwarp();
+      hi = lo;
     }
   }
+  if (lane != 0) return;
   rans::enc64_flush(e);
   if (e.overflow) atomicOr(meta, ERR_ENC_OVERFLOW);
   meta[2 + i] = (uint32_t)((buf + reg_off(job, i + 1) - e.ptr) * 4);
@@ -113,20 +172,52 @@ __global__ void compat_dec_init_kernel(const uint8_t *stream, DecPart *parts, ui
   if (d.underflow) atomicOr(meta, ERR_DEC_UNDERFLOW);
 }
 
-__global__ void compat_decode_kernel(const CallRec cr, int nparts, const uint8_t *stream,
-                                     DecPart *parts, int16_t *out, uint32_t *meta) {
-  if (threadIdx.x != 0) return;
-  const int i = blockIdx.x;
+// One block per stream part: all threads stage the call's CDF rows in shared memory (the symbol
+// search of rans.cpp:289-292 is the dependent chain), then warp 0 decodes: the warp fetches 32
+// table indexes at a time, lane 0 runs the sequential rANS state, the warp stores 32 symbols.
+constexpr int CDEC_THREADS = 128;
+template <bool TAB_SMEM>
+__global__ void __launch_bounds__(CDEC_THREADS) compat_decode_kernel(const CallRec cr, int nparts,
+                                                                     const uint8_t *stream,
+                                                                     DecPart *parts, int16_t *out,
+                                                                     uint32_t *meta) {
+  extern __shared__ int32_t tab[];
+  __shared__ int s_idx[32];
+  __shared__ int16_t s_out[32];
+  rans::Tables t = cr.t;
+  if (TAB_SMEM) {
+    const int ncdf = cr.t.count * cr.t.stride;
+    for (int k = threadIdx.x; k < ncdf; k += CDEC_THREADS) tab[k] = cr.t.cdf[k];
+    for (int k = threadIdx.x; k < cr.t.count; k += CDEC_THREADS) {
+      tab[ncdf + k] = cr.t.sizes[k];
+      tab[ncdf + cr.t.count + k] = cr.t.offsets[k];
+    }
+    __syncthreads();
+    t.cdf = tab; t.sizes = tab + ncdf; t.offsets = tab + ncdf + cr.t.count;
+  }
+  if (threadIdx.x >= 32) return;
+  const int i = blockIdx.x, lane = threadIdx.x;
   DecPart &p = parts[i];
   const uint32_t *w = reinterpret_cast<const uint32_t *>(stream + p.base);
   rans::Dec64 d;
   d.x = p.x; d.ptr = w + p.rp; d.end = w + p.end; d.underflow = 0;
   int64_t off, cur;
   part_range(cr.n, nparts, i, off, cur);
-  for (int64_t k = 0; k < cur; ++k) {
-    const int64_t pos = off + k;
-    out[pos] = (int16_t)rans::dec64_symbol(d, call_index(cr, pos), cr.t);
+  int nxt = (lane < cur) ? call_index(cr, off + lane) : -1;
+  for (int64_t k0 = 0; k0 < cur; k0 += 32) {
+    s_idx[lane] = nxt;
+    const int64_t kn = k0 + 32 + lane;
+    nxt = kn < cur ? call_index(cr, off + kn) : -1;
+    __syncwarp();
+    if (lane == 0) {
+      const int nb = cur - k0 < 32 ? (int)(cur - k0) : 32;
+      for (int j = 0; j < nb; ++j) s_out[j] = (int16_t)rans::dec64_symbol(d, s_idx[j], t);
+    }
+    __syncwarp();
+    if (k0 + lane < cur) out[off + k0 + lane] = s_out[lane];
+    __syncwarp();
   }
+  if (lane != 0) return;
   p.x = d.x;
   p.rp = (uint32_t)(d.ptr - w);
   if (d.underflow) atomicOr(meta, ERR_DEC_UNDERFLOW);
@@ -520,7 +611,8 @@ WsLayout ws_layout(int mode, int parts, int64_t max_symbols) {
   w.stream_cap = w.out_cap + 16 * (size_t)parts;
   size_t o = 0;
   w.o_buf = o; o = al256(o + w.buf_words * 4);
-  w.o_ops = o; o = al256(o + (mode == DCVC_RANS_INTERLEAVED ? (size_t)max_symbols * sizeof(uint2) : 0));
+  // prepared operations, one per symbol: 8 bytes (interleaved) or 16 bytes (compat)
+  w.o_ops = o; o = al256(o + (size_t)max_symbols * (mode == DCVC_RANS_INTERLEAVED ? sizeof(uint2) : sizeof(uint4)));
   w.o_out = o; o = al256(o + w.out_cap);
   w.o_meta = o; o = al256(o + META_WORDS * 4);
   w.o_stream = o; o = al256(o + w.stream_cap);
@@ -580,7 +672,7 @@ extern "C" int dcvc_rans_create(dcvc_rans **out, int mode, int parts, int64_t ma
   uint8_t *base = static_cast<uint8_t *>(workspace);
   r->buf_words = w.buf_words; r->out_cap = w.out_cap; r->stream_cap = w.stream_cap;
   r->d_buf = reinterpret_cast<uint32_t *>(base + w.o_buf);
-  r->d_ops = mode == DCVC_RANS_INTERLEAVED ? reinterpret_cast<uint2 *>(base + w.o_ops) : nullptr;
+  r->d_ops = reinterpret_cast<uint2 *>(base + w.o_ops);
   r->d_out = base + w.o_out;
   r->d_meta = reinterpret_cast<uint32_t *>(base + w.o_meta);
   r->d_stream = base + w.o_stream;
@@ -645,15 +737,20 @@ extern "C" int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void
   if ((size_t)reg_off(r->job, r->parts) > r->buf_words)
     return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush: buffer too small");
   DCVC_CUDA(cudaMemsetAsync(r->d_meta, 0, META_WORDS * 4, s));
-  if (r->mode == DCVC_RANS_COMPAT)
-    compat_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_buf, r->d_meta);
-  else {
-    int64_t total = 0;
-    for (int c = 0; c < r->job.ncalls; ++c) { r->job.op_off[c] = total; total += r->job.calls[c].n; }
-    r->job.op_off[r->job.ncalls] = total;
+  int64_t total = 0;
+  for (int c = 0; c < r->job.ncalls; ++c) { r->job.op_off[c] = total; total += r->job.calls[c].n; }
+  r->job.op_off[r->job.ncalls] = total;
+  const int pblocks = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+  if (r->mode == DCVC_RANS_COMPAT) {
     if (total > 0) {
-      const int blocks = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
-      ilv_prepare_kernel<<<blocks, 256, 0, s>>>(r->job, r->d_ops);
+      compat_prepare_kernel<<<pblocks, 256, 0, s>>>(r->job, reinterpret_cast<uint4 *>(r->d_ops));
+      DCVC_LAUNCHED();
+    }
+    compat_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, reinterpret_cast<const uint4 *>(r->d_ops),
+                                                 r->d_buf, r->d_meta);
+  } else {
+    if (total > 0) {
+      ilv_prepare_kernel<<<pblocks, 256, 0, s>>>(r->job, r->d_ops);
       DCVC_LAUNCHED();
     }
     ilv_encode_kernel<<<r->parts, 32, 0, s>>>(r->job, r->d_ops, r->d_buf, r->d_meta);
@@ -763,10 +860,21 @@ extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t 
   cr.t.cdf = t->cdf; cr.t.sizes = t->sizes; cr.t.offsets = t->offsets; cr.t.stride = t->stride;
   cr.t.count = t->count;
   cudaStream_t s = (cudaStream_t)stream;
-  if (r->mode == DCVC_RANS_COMPAT)
-    compat_decode_kernel<<<r->dec_parts, 32, 0, s>>>(cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
-  else {
-    const size_t tab_bytes = ((size_t)cr.t.count * cr.t.stride + 2 * (size_t)cr.t.count) * 4;
+  const size_t tab_bytes = ((size_t)cr.t.count * cr.t.stride + 2 * (size_t)cr.t.count) * 4;
+  if (r->mode == DCVC_RANS_COMPAT) {
+    if (cr.t.count > 0 && tab_bytes <= DEC_TAB_SMEM_MAX) {
+      int rc = dcvc_once_per_device(DCVC_ONCE_RANS_DEC2, [] {
+        return cudaFuncSetAttribute(compat_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)DEC_TAB_SMEM_MAX);
+      });
+      if (rc) return rc;
+      compat_decode_kernel<true><<<r->dec_parts, CDEC_THREADS, tab_bytes, s>>>(
+          cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+    } else {
+      compat_decode_kernel<false><<<r->dec_parts, CDEC_THREADS, 0, s>>>(
+          cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+    }
+  } else {
     if (cr.t.count > 0 && tab_bytes <= DEC_TAB_SMEM_MAX) {
       int rc = dcvc_once_per_device(DCVC_ONCE_RANS_DEC, [] {
         return cudaFuncSetAttribute(ilv_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
