@@ -68,6 +68,9 @@ def parse_args():
     p.add_argument("--pipeline", type=int, default=1,
                    help="1: encoder and decoder on two CUDA streams, decoder one frame behind "
                         "(dcvc_b200.pipeline); 0: the reference's strictly sequential frame loop")
+    p.add_argument("--graphs", type=int, default=1,
+                   help="1: the P-frame encode / decode launches are replayed from CUDA graphs "
+                        "(dcvc_b200.graphs; bit-identical to the eager launch sequence), 0: eager")
     p.add_argument("--profile-out", default=None, help="write the per-kernel table (json) here")
     p.add_argument("--workload", default="rgb1080p", choices=["rgb1080p", "entropy", "yuv420x8", "hem_sweep"],
                    help="rgb1080p: BASELINE configs[1] (the headline); entropy: configs[4] "
@@ -343,6 +346,14 @@ def main():
     # pipelined mode: the decoder is a second model instance (own weights copy, coder context and
     # dpb), as it would be in a separate process; the two only share the byte stream
     i_dec, p_dec = make_nets() if args.pipeline else (None, None)
+    p_eager = p_net
+    if args.graphs:
+        from dcvc_b200.graphs import GraphedDMC
+        p_net = GraphedDMC(p_net)
+        p_dec = GraphedDMC(p_dec) if p_dec is not None else None
+    # every graph variant (three feature-adaptor indexes) is seen twice -- eager, then recorded --
+    # before it replays: ten untimed frames ahead of the warm-up
+    prime = 10 if args.graphs else 0
 
     nf = NF
     host = synth.synth_frames(nf, H, W, seed=rank).pin_memory()      # [nf,3,H,W] fp32 in [0,1]
@@ -372,7 +383,7 @@ def main():
             seq = Sequence(ni, np_, H, W)
             tstream = torch.cuda.current_stream(dev)
         with torch.no_grad():
-            for s in range(args.warmup):
+            for s in range(-prime, args.warmup):
                 loop_body(seq, s)
             if pipeline:
                 seq.flush()                      # the timed region holds K encodes and K decodes

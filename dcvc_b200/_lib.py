@@ -60,6 +60,7 @@ SIGNATURES = {
     "dcvc_last_error": (ctypes.c_char_p, []),
     "dcvc_version": (c_int, []),
     "dcvc_launch_count": (c_int64, []),
+    "dcvc_launch_count_add": (None, [c_int64]),
     "dcvc_conv2d": (c_int, [ctypes.POINTER(Conv), c_void_p]),
     "dcvc_conv_tc_eligible": (c_int, [ctypes.POINTER(Conv)]),
     "dcvc_conv_tc_geometry": (c_int, [c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int),
@@ -119,6 +120,10 @@ SIGNATURES = {
     "dcvc_rans_enc_flush": (c_int, [c_void_p, c_void_p, c_size_t, ctypes.POINTER(c_size_t),
                                     c_void_p]),
     "dcvc_rans_enc_flush_begin": (c_int, [c_void_p, c_size_t, c_void_p]),
+    "dcvc_rans_enc_flush_enqueue": (c_int, [c_void_p, c_size_t, c_void_p]),
+    "dcvc_rans_enc_flush_mark": (c_int, [c_void_p, c_void_p]),
+    "dcvc_rans_enc_flush_mark_captured": (c_int, [c_void_p, c_void_p]),
+    "dcvc_rans_enc_flush_set_pending": (c_int, [c_void_p]),
     "dcvc_rans_enc_flush_end": (c_int, [c_void_p, c_void_p, c_size_t, ctypes.POINTER(c_size_t)]),
     "dcvc_rans_dec_set_stream": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "dcvc_rans_dec_pull": (c_int, [c_void_p, c_void_p, c_int64, c_int64, ctypes.POINTER(Tables),

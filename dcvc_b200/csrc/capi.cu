@@ -10,3 +10,6 @@ std::mutex g_dcvc_once_mu;
 extern "C" const char *dcvc_last_error(void) { return g_dcvc_err; }
 extern "C" int dcvc_version(void) { return 100; }
 extern "C" int64_t dcvc_launch_count(void) { return g_dcvc_launches.load(); }
+// kernels launched by replaying a CUDA graph that was recorded from this library's launches: the
+// recorder (dcvc_b200/graphs.py) reports them, so that the counter keeps meaning "kernels run"
+extern "C" void dcvc_launch_count_add(int64_t n) { g_dcvc_launches.fetch_add(n); }

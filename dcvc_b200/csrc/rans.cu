@@ -725,8 +725,43 @@ static int rans_errors(uint32_t flags) {
 // side stream.  Work the caller enqueues on `stream` between the two (the encoder's own
 // reconstruction of the frame) keeps running while the host already holds the bytes.
 extern "C" int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void *stream) {
-  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_begin: bad arguments");
-  if (r->flush_pending) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_begin: a flush is already pending");
+  int rc = dcvc_rans_enc_flush_enqueue(r, out_capacity, stream);
+  if (rc) return rc;
+  return dcvc_rans_enc_flush_mark(r, stream);
+}
+
+// flush_begin in two steps for callers that record the coder's work into a CUDA graph: `enqueue`
+// is pure stream work (memset, kernels, the copy of the meta words to pinned host memory) and may
+// be captured; `mark` records the event flush_end waits on and must run outside the capture, after
+// the graph launch, on every replay.
+extern "C" int dcvc_rans_enc_flush_mark(dcvc_rans *r, void *stream) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_mark: bad arguments");
+  if (r->flush_pending) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_mark: a flush is already pending");
+  DCVC_CUDA(cudaEventRecord(r->flushed, (cudaStream_t)stream));
+  r->flush_pending = true;
+  return DCVC_OK;
+}
+
+// `mark` for a stream that is being captured into a CUDA graph: the event becomes an event-record
+// NODE of the graph (cudaEventRecordExternal), so that the host can wait on it after every launch
+// of the graph while the graph's later nodes still run; on replays the host side only has to
+// re-arm the pending flag (dcvc_rans_enc_flush_set_pending).
+extern "C" int dcvc_rans_enc_flush_mark_captured(dcvc_rans *r, void *stream) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_mark_captured: bad arguments");
+  DCVC_CUDA(cudaEventRecordWithFlags(r->flushed, (cudaStream_t)stream, cudaEventRecordExternal));
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_enc_flush_set_pending(dcvc_rans *r) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_set_pending: bad arguments");
+  if (r->flush_pending) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_set_pending: a flush is already pending");
+  r->flush_pending = true;
+  return DCVC_OK;
+}
+
+extern "C" int dcvc_rans_enc_flush_enqueue(dcvc_rans *r, size_t out_capacity, void *stream) {
+  if (!r) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_enqueue: bad arguments");
+  if (r->flush_pending) return dcvc_fail(DCVC_ERR_ARG, "rans_enc_flush_enqueue: a flush is already pending");
   cudaStream_t s = (cudaStream_t)stream;
   r->job.each_sum = 0;
   r->job.total = 0;
@@ -761,9 +796,7 @@ extern "C" int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void
                                      r->d_meta, r->d_out, cap);
   DCVC_LAUNCHED();
   DCVC_CUDA(cudaMemcpyAsync(r->h_meta, r->d_meta, 8, cudaMemcpyDeviceToHost, s));
-  DCVC_CUDA(cudaEventRecord(r->flushed, s));
   r->job.ncalls = 0;
-  r->flush_pending = true;
   return DCVC_OK;
 }
 

@@ -235,6 +235,27 @@ class EntropyCoder:
             self._h, symbols.data_ptr(), indexes.data_ptr() if indexes is not None else None,
             n, plane, ctypes.byref(tables.c)))
 
+    def flush_enqueue(self):
+        """flush() as pure stream work on the CURRENT stream, for CUDA-graph capture
+        (dcvc_b200.graphs): no event, no side stream; mark_flushed() completes it per replay."""
+        _lib.check(_lib.lib().dcvc_rans_enc_flush_enqueue(
+            self._h, self._cap, torch.cuda.current_stream().cuda_stream))
+
+    def mark_flushed_captured(self):
+        """inside a stream capture: the coder's event as an event-record node of the graph"""
+        _lib.check(_lib.lib().dcvc_rans_enc_flush_mark_captured(
+            self._h, torch.cuda.current_stream().cuda_stream))
+
+    def set_pending(self):
+        """per graph replay: the recorded flush is in flight, get_encoded_stream() may wait on it"""
+        _lib.check(_lib.lib().dcvc_rans_enc_flush_set_pending(self._h))
+        self._pending = True
+
+    def mark_flushed(self):
+        _lib.check(_lib.lib().dcvc_rans_enc_flush_mark(
+            self._h, torch.cuda.current_stream().cuda_stream))
+        self._pending = True
+
     def flush(self):
         """Enqueues the coder kernels (RansEncoder.flush, py_rans.cpp:98-135); the host wait is
         in get_encoded_stream, so whatever the caller enqueues in between runs behind the coder

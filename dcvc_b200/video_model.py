@@ -355,8 +355,7 @@ class DMC(CompressionModel):
         call as the reference does, :535-543) skips the encoder-side reconstruction, whose only
         product is the returned dpb; the stream is unaffected."""
         ec = self.entropy_coder
-        zs_ = get_downsampled_shape(x.shape[2], x.shape[3], 64)
-        ec.reserve((64 + arch.CH_16X) * (x.shape[2] // 16 * (x.shape[3] // 16) + zs_[0] * zs_[1]))
+        ec.reserve(self._frame_symbols(x.shape[2], x.shape[3]))
 
         def coder(mv_zs, zs, mv_coded, coded):
             ec.reset()
@@ -374,13 +373,34 @@ class DMC(CompressionModel):
 
     def decompress(self, dpb, string, height, width, q_in_ckpt, q_index, frame_idx):
         """video_model.py:483-520"""
+        ec = self.entropy_coder
+        self._decode_begin(string, height, width)
+        out = self._decompress_body(dpb, height, width, q_in_ckpt, q_index, frame_idx, True)
+        if not ec.lazy_check:       # a truncated / corrupt / wrong-table frame raises here
+            ec.check()
+        return out
+
+    @staticmethod
+    def _frame_symbols(height, width):
+        """symbols one P frame hands to the coder: mv_y + y latents and their hyper latents"""
+        zs = get_downsampled_shape(height, width, 64)
+        ys = get_downsampled_shape(height, width, 16)
+        return (64 + arch.CH_16X) * (ys[0] * ys[1] + zs[0] * zs[1])
+
+    def _decode_begin(self, string, height, width):
+        """host part of decompress: stream parsing, upload, decoder state (not graph-capturable)"""
+        ec = self.entropy_coder
+        ec.reserve(self._frame_symbols(height, width))
+        ec.set_stream(string)
+
+    def _decompress_body(self, dpb, height, width, q_in_ckpt, q_index, frame_idx, finish):
+        """every kernel of decompress, in stream order (this is what dcvc_b200.graphs records);
+        finish: enqueue the decoder's error-word copy right after the last entropy decode"""
         _, mv_q_dec, _, y_q_dec = self.get_q_for_inference(q_in_ckpt, q_index)
         dev = self.device
         ec = self.entropy_coder
         z_size = get_downsampled_shape(height, width, 64)
         yh, yw = get_downsampled_shape(height, width, 16)
-        ec.reserve((64 + arch.CH_16X) * (yh * yw + z_size[0] * z_size[1]))
-        ec.set_stream(string)
         mv_z_hat = self.decode_z(64, z_size, "bit_estimator_z_mv")
         z_hat = self.decode_z(arch.CH_16X, z_size, "bit_estimator_z")
         mv_catb = self.new_prior_buffer(yh, yw, 64)
@@ -392,10 +412,9 @@ class DMC(CompressionModel):
         catb = self.new_prior_buffer(yh, yw, arch.CH_16X)
         self._res_params(z_hat, dpb, ctx3, catb, arch.CH_16X)
         y_hat = self.decompress_four_part_prior(catb, arch.CH_16X, self._prior_fn("y"))
-        ec.finish_decode()
+        if finish:
+            ec.finish_decode()
         x_hat, feature = self._recon(y_hat, bufs, y_q_dec)
-        if not ec.lazy_check:       # a truncated / corrupt / wrong-table frame raises here
-            ec.check()
         return {"dpb": {"ref_frame": x_hat.nchw(), "ref_feature": feature.nchw(),
                         "ref_mv_feature": mv_feature.nchw(), "ref_y": y_hat.nchw(),
                         "ref_mv_y": mv_y_hat.nchw()}}
@@ -409,15 +428,16 @@ class DMC(CompressionModel):
             t0 = time.time()
             # the reference discards compress()'s dpb here and continues from the decoder's
             # (:535-543); both are bit-identical, so only the decoder reconstructs the frame
-            encoded = self.compress(x, dpb, q_in_ckpt, q_index, frame_idx,
-                                    reconstruct=self.taps is not None)
+            run = self.__dict__.get("_graph_runner") or self      # dcvc_b200.graphs, when enabled
+            encoded = run.compress(x, dpb, q_in_ckpt, q_index, frame_idx,
+                                   reconstruct=self.taps is not None)
             encode_p(encoded["bit_stream"], q_in_ckpt, q_index, frame_idx, output_path)
             bits = filesize(output_path) * 8
             torch.cuda.synchronize(device=device)
             t1 = time.time()
             q_in_ckpt, q_index, frame_idx, string = decode_p(output_path)
-            decoded = self.decompress(dpb, string, pic_height, pic_width, q_in_ckpt, q_index,
-                                      frame_idx)
+            decoded = run.decompress(dpb, string, pic_height, pic_width, q_in_ckpt, q_index,
+                                     frame_idx)
             torch.cuda.synchronize(device=device)
             t2 = time.time()
             return {"dpb": decoded["dpb"], "bit": bits, "encoding_time": t1 - t0,

@@ -47,6 +47,8 @@ const char *dcvc_last_error(void);
 int dcvc_version(void);
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
 int64_t dcvc_launch_count(void);
+/* a replayed CUDA graph recorded from n of this library's launches adds n (dcvc_b200/graphs.py) */
+void dcvc_launch_count_add(int64_t n);
 
 /* ------------------------------------------------------------------------------------------
  * Convolution with fused prologue/epilogue.  Replaces nn.Conv2d (+ LeakyReLU/ReLU, residual
@@ -375,6 +377,16 @@ int dcvc_rans_enc_flush(dcvc_rans *r, uint8_t *out_host, size_t out_capacity, si
  * host wait.  end: waits for that event only and copies the container to `out_host` on a private
  * stream.  One flush may be pending per coder. */
 int dcvc_rans_enc_flush_begin(dcvc_rans *r, size_t out_capacity, void *stream);
+/* flush_begin = flush_enqueue + flush_mark.  For callers that record a frame's launches into a
+ * CUDA graph: `enqueue` is pure stream work (capturable); `mark` records the event flush_end waits
+ * on and is called outside the capture, after the graph launch, on every replay. */
+int dcvc_rans_enc_flush_enqueue(dcvc_rans *r, size_t out_capacity, void *stream);
+int dcvc_rans_enc_flush_mark(dcvc_rans *r, void *stream);
+/* `mark` inside a stream capture: the coder's event becomes an event-record node of the graph
+ * (cudaEventRecordExternal) that the host can wait on after each launch while later nodes of the
+ * same graph still run; per replay the host then calls dcvc_rans_enc_flush_set_pending. */
+int dcvc_rans_enc_flush_mark_captured(dcvc_rans *r, void *stream);
+int dcvc_rans_enc_flush_set_pending(dcvc_rans *r);
 int dcvc_rans_enc_flush_end(dcvc_rans *r, uint8_t *out_host, size_t out_capacity, size_t *out_len);
 int dcvc_rans_dec_set_stream(dcvc_rans *r, const uint8_t *host, size_t len, void *stream);
 int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t n, int64_t plane,
