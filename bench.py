@@ -68,9 +68,12 @@ def parse_args():
     p.add_argument("--pipeline", type=int, default=1,
                    help="1: encoder and decoder on two CUDA streams, decoder one frame behind "
                         "(dcvc_b200.pipeline); 0: the reference's strictly sequential frame loop")
-    p.add_argument("--graphs", type=int, default=1,
+    p.add_argument("--graphs", type=int, default=-1,
                    help="1: the P-frame encode / decode launches are replayed from CUDA graphs "
-                        "(dcvc_b200.graphs; bit-identical to the eager launch sequence), 0: eager")
+                        "(dcvc_b200.graphs; bit-identical to the eager launch sequence), 0: eager, "
+                        "-1 (default): graphs where they measured faster -- the one-stream schedules "
+                        "(arms.sequential, arms.encode_decode_api); the two-stream pipeline hides "
+                        "the launch time already, at 1 and at 8 ranks per host (DESIGN.md)")
     p.add_argument("--profile-out", default=None, help="write the per-kernel table (json) here")
     p.add_argument("--workload", default="rgb1080p", choices=["rgb1080p", "entropy", "yuv420x8", "hem_sweep"],
                    help="rgb1080p: BASELINE configs[1] (the headline); entropy: configs[4] "
@@ -346,14 +349,15 @@ def main():
     # pipelined mode: the decoder is a second model instance (own weights copy, coder context and
     # dpb), as it would be in a separate process; the two only share the byte stream
     i_dec, p_dec = make_nets() if args.pipeline else (None, None)
-    p_eager = p_net
-    if args.graphs:
+    use_graphs = args.graphs if args.graphs >= 0 else int(not args.pipeline)
+    arm_graphs = args.graphs != 0
+    if use_graphs:
         from dcvc_b200.graphs import GraphedDMC
         p_net = GraphedDMC(p_net)
         p_dec = GraphedDMC(p_dec) if p_dec is not None else None
     # every graph variant (three feature-adaptor indexes) is seen twice -- eager, then recorded --
     # before it replays: ten untimed frames ahead of the warm-up
-    prime = 10 if args.graphs else 0
+    prime = 10 if (use_graphs or arm_graphs) else 0
 
     nf = NF
     host = synth.synth_frames(nf, H, W, seed=rank).pin_memory()      # [nf,3,H,W] fp32 in [0,1]
@@ -497,18 +501,24 @@ def main():
     if world == 1 and not args.no_extra_arms:
         arms = {}
         k = min(args.steps, 24)
-        ms_s, _, seq_s = timed(body_resident, pipeline=0, steps=k)
+        p_arm = p_net
+        if arm_graphs and not use_graphs:
+            from dcvc_b200.graphs import GraphedDMC
+            p_arm = GraphedDMC(p_net)
+        gtxt = ("; P-frame launches replayed from CUDA graphs (dcvc_b200.graphs)"
+                if arm_graphs else "")
+        ms_s, _, seq_s = timed(body_resident, pipeline=0, nets=(i_net, p_arm), steps=k)
         arms["sequential"] = {
             "value": k / (ms_s / 1000.0), "unit": UNIT, "ms_per_step": ms_s / k, "steps": k,
             "what": "the drop-in call order of DMC.encode_decode / test_video.py: encode a frame, "
-                    "then decode it, one model instance, one stream; same coder as the headline"}
-        ms_a, _, seq_a = timed(body_resident, pipeline=0, steps=k, api=True)
+                    "then decode it, one model instance, one stream; same coder as the headline" + gtxt}
+        ms_a, _, seq_a = timed(body_resident, pipeline=0, nets=(i_net, p_arm), steps=k, api=True)
         arms["encode_decode_api"] = {
             "value": k / (ms_a / 1000.0), "unit": UNIT, "ms_per_step": ms_a / k, "steps": k,
             "what": "IntraNoAR.encode_decode / DMC.encode_decode with an output_path, exactly as "
                     "test_video.py:141-143,155-158 calls them: frame file written and read back "
                     "(tmpfs), the call's own device synchronisations; the frame is reconstructed "
-                    "once, by the decoder (the reference also continues from the decoder's dpb)"}
+                    "once, by the decoder (the reference also continues from the decoder's dpb)" + gtxt}
         try:
             os.remove(seq_a.path)
         except OSError:
@@ -568,6 +578,7 @@ def main():
                 "config": {"workload": workload_text(args),
                            "l2": "inputs larger than L2: every step streams a new frame through >= 6 GB of activations (full-resolution tensors are 130-400 MB each, the L2 is 126 MB); no explicit flush",
                            "conv_mode": args.conv_mode, "coder": args.coder,
+                           "cuda_graphs": bool(use_graphs),
                            "schedule": ("PIPELINED (dcvc_b200.pipeline.EncDecPipeline, an API the "
                                         "reference does not have): encoder and decoder are two model "
                                         "instances on two CUDA streams, the decoder one frame behind "
