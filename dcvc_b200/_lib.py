@@ -50,7 +50,7 @@ class Dual(ctypes.Structure):
 
 class Tables(ctypes.Structure):
     _fields_ = [("cdf", c_void_p), ("sizes", c_void_p), ("offsets", c_void_p),
-                ("count", c_int32), ("stride", c_int32)]
+                ("count", c_int32), ("stride", c_int32), ("lut", c_void_p)]
 
 
 VP = ctypes.POINTER(View)

@@ -377,15 +377,51 @@ constexpr int DEC_THREADS = 128;   // warp 0 decodes; all four warps stage the t
 constexpr int DEC_BATCH = 8;       // rounds whose table indexes are fetched ahead of the chain
 
 // One warp per stream.  The CDF rows of this call's table set are staged in shared memory first
-// (TAB_SMEM; the 7-probe symbol search per round is the dependent chain, and a shared-memory
-// probe costs a tenth of an L2 one); table sets larger than the budget are searched in place.
-template <bool TAB_SMEM>
+// (TAB_SMEM; the symbol search per round is the dependent chain, and a shared-memory probe costs a
+// tenth of an L2 one); table sets larger than the budget are searched in place.
+//
+// A stream is decoded by ONE warp, one round of 32 symbols after the other, and every round
+// depends on the previous one through the lanes' states: the kernel is bound by the number of
+// dependent instructions per round (ncu: 6.5 cycles per instruction, one warp per scheduler,
+// "wait" = fixed-latency dependency is the top stall), so the common round is kept short, free of
+// memory waits and with two branches only (search miss, renormalise-or-escape):
+//  * WORD RING: the stream's renormalisation words pass through a 128-word ring in shared memory,
+//    filled one 32-word window at a time; the window loaded at one rotation sits in a register
+//    until the next rotation stores it, so no instruction ever waits for that global load.  A
+//    round consumes at most 32 words: the ring always holds the current and the next window.
+//  * SEARCH LUT (LUT; dcvc_tables.lut, built once per table set by the host): per CDF row,
+//    lut[b] = largest s with cdf[s] <= 256 b; the symbol for cum lies in [lut[cum >> 8],
+//    lut[(cum >> 8) + 1]]: no probe at all for the peaked rows instead of seven.
+//  * table rows are addressed with 32-bit shared-space addresses, {size, offset} of a row share
+//    one word, table indexes are fetched one batch (8 rounds) ahead, whole batches run without
+//    per-round bounds checks; the last rounds of a part go through the checked round.
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds8(uint32_t a) {
+  uint32_t v;
+  asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+
+constexpr int LUT_PITCH = 260;   // bytes per LUT row in shared memory: 256 buckets + the row's last symbol
+
+// words of shared memory in front of the LUT: cdf rows + one {size, offset} word per row, padded
+// to 16 bytes
+__host__ __device__ __forceinline__ size_t dec_tab_words(int count, int stride) {
+  return ((size_t)count * stride + count + 3) & ~(size_t)3;
+}
+
+template <bool TAB_SMEM, bool LUT>
 __global__ void __launch_bounds__(DEC_THREADS) ilv_decode_kernel(const CallRec cr, int nparts,
                                                                  const uint8_t *stream,
                                                                  DecPart *parts, int16_t *out,
                                                                  uint32_t *meta) {
-  extern __shared__ int32_t tab[];     // [count][stride] cdf, [count] sizes, [count] offsets
-  const int32_t *cdf_all = cr.t.cdf, *sizes = cr.t.sizes, *offsets = cr.t.offsets;
+  extern __shared__ __align__(16) int32_t tab[];   // [count][stride] cdf | [count] size<<16|offset | lut
+  __shared__ uint16_t ring[128];
+  uint32_t s_cdf = 0, s_row = 0, s_lut = 0;
   if (TAB_SMEM) {
     const int ncdf = cr.t.count * cr.t.stride;
     if ((ncdf & 3) == 0 && (reinterpret_cast<uintptr_t>(cr.t.cdf) & 15) == 0) {
@@ -396,12 +432,23 @@ __global__ void __launch_bounds__(DEC_THREADS) ilv_decode_kernel(const CallRec c
     } else {
       for (int i = threadIdx.x; i < ncdf; i += DEC_THREADS) tab[i] = cr.t.cdf[i];
     }
-    for (int i = threadIdx.x; i < cr.t.count; i += DEC_THREADS) {
-      tab[ncdf + i] = cr.t.sizes[i];
-      tab[ncdf + cr.t.count + i] = cr.t.offsets[i];
+    for (int i = threadIdx.x; i < cr.t.count; i += DEC_THREADS)
+      tab[ncdf + i] = (cr.t.sizes[i] << 16) | (cr.t.offsets[i] & 0xffff);
+    const size_t lw = dec_tab_words(cr.t.count, cr.t.stride);
+    if (LUT) {
+      const uint32_t *src = reinterpret_cast<const uint32_t *>(cr.t.lut);
+      uint32_t *dst = reinterpret_cast<uint32_t *>(tab + lw);
+#pragma unroll 8
+      for (int i = threadIdx.x; i < cr.t.count * 64; i += DEC_THREADS)
+        dst[(i >> 6) * (LUT_PITCH / 4) + (i & 63)] = __ldg(src + i);
+      for (int i = threadIdx.x; i < cr.t.count; i += DEC_THREADS)
+        dst[i * (LUT_PITCH / 4) + 64] = (uint32_t)(cr.t.sizes[i] - 2);
     }
     __syncthreads();
-    cdf_all = tab; sizes = tab + ncdf; offsets = tab + ncdf + cr.t.count;
+    s_cdf = (uint32_t)__cvta_generic_to_shared(tab);
+    asm volatile("" : "+r"(s_cdf));      // keep the base in a register (else re-derived every round)
+    s_row = s_cdf + 4u * (uint32_t)ncdf;
+    s_lut = s_cdf + 4u * (uint32_t)lw;
   }
   if (threadIdx.x >= 32) return;
   const int wi = blockIdx.x, lane = threadIdx.x;
@@ -412,97 +459,158 @@ __global__ void __launch_bounds__(DEC_THREADS) ilv_decode_kernel(const CallRec c
   const uint32_t end = p.end;
   const uint32_t lt = lanemask_lt();
   uint32_t err = 0;
+  auto fetch = [&](uint32_t pos) -> uint16_t { return pos < end ? w[pos] : (uint16_t)0; };
+  uint32_t cw = rp >> 5;                                  // window of the read position
+  ring[(cw * 32 + lane) & 127] = fetch(cw * 32 + lane);
+  ring[((cw + 1) * 32 + lane) & 127] = fetch((cw + 1) * 32 + lane);
+  uint16_t pend = fetch((cw + 2) * 32 + lane);            // window cw + 2, stored at the next rotation
+  __syncwarp();
+  // renormalisation of the lanes in `need` (ballot m != 0, warp-uniform): 16 bits each, lane order
+  auto refill = [&](bool need, uint32_t m) {
+    const uint32_t pos = rp + __popc(m & lt);
+    if (need) {
+      if (pos >= end) err |= ERR_DEC_UNDERFLOW;
+      x = (x << 16) | ring[pos & 127];
+    }
+    rp += __popc(m);
+    if ((rp >> 5) != cw) {
+      ++cw;
+      __syncwarp();
+      ring[((cw + 1) * 32 + lane) & 127] = pend;
+      pend = fetch((cw + 2) * 32 + lane);
+      __syncwarp();
+    }
+  };
+  // bypass escape of the lanes with phase == 1 (rans.cpp:296-318): count nibbles, then raw nibbles
+  auto escape = [&](int &phase, int &value, int maxv) {
+    int nb = 0, jn = 0;
+    uint32_t raw = 0;
+    do {
+      uint32_t val = 0;
+      if (phase) {
+        val = x & 15u;
+        x >>= 4;
+      }
+      const bool need2 = phase != 0 && x < rans::L32;
+      const uint32_t m2 = __ballot_sync(0xffffffffu, need2);
+      if (m2) refill(need2, m2);
+      bool done = false;
+      if (phase == 1) {
+        nb += (int)val;
+        if (val != 15u) {
+          if (nb == 0) done = true; else phase = 2;
+          if (nb > 8) { err |= ERR_ESCAPE; done = true; }
+        }
+      } else if (phase == 2) {
+        raw |= val << (4 * jn);
+        if (++jn == nb) done = true;
+      }
+      if (done) {
+        value = (int)(raw >> 1);
+        if (raw & 1u) value = -value - 1; else value += maxv;
+        phase = 0;
+      }
+      if (err & ERR_DEC_UNDERFLOW) phase = 0;  // never spin on a truncated stream
+    } while (__any_sync(0xffffffffu, phase != 0));
+  };
   int64_t off, cur;
   part_range(cr.n, nparts, wi, off, cur);
-  const int64_t rounds = (cur + 31) >> 5;
-  for (int64_t r0 = 0; r0 < rounds; r0 += DEC_BATCH) {
-    int idx[DEC_BATCH];
+  const uint32_t n = (uint32_t)cur;                      // < 2^31: dcvc_rans_dec_pull checks
+  const uint8_t *ip = cr.idx ? cr.idx + off : nullptr;
+  int16_t *o = out + off + lane;
+  const uint32_t stride = (uint32_t)cr.t.stride;
+  auto load_idx = [&](uint32_t k) -> int {
+    if (k >= n) return -1;
+    return ip ? (int)ip[k] : (int)((uint64_t)(off + k) / (uint64_t)cr.plane);
+  };
+  const uint32_t rounds = (n + 31) >> 5;
+  uint32_t r0 = 0;
+  if (TAB_SMEM) {
+    const uint32_t full = n >> 5;                        // rounds in which every lane has a symbol
+    int nxt[DEC_BATCH];
 #pragma unroll
-    for (int j = 0; j < DEC_BATCH; ++j) {
-      const int64_t k = (r0 + j) * 32 + lane;
-      idx[j] = k < cur ? call_index(cr, off + k) : -1;
-    }
-    // a batch consumes about 256 words; pull the lines of the batch after next towards L1
-    if (lane < 8) {
-      const uint32_t ahead = rp + 512u + 64u * lane;
-      if (ahead < end) asm volatile("prefetch.global.L1 [%0];" ::"l"(w + ahead));
-    }
+    for (int j = 0; j < DEC_BATCH; ++j) nxt[j] = load_idx((uint32_t)j * 32 + lane);
+    for (; r0 + DEC_BATCH <= full; r0 += DEC_BATCH) {
+      uint32_t rowm[DEC_BATCH], cbase[DEC_BATCH], lbase[DEC_BATCH];
 #pragma unroll
-    for (int j = 0; j < DEC_BATCH; ++j) {
-      if (r0 + j >= rounds) break;                       // warp-uniform
-      const int64_t k = (r0 + j) * 32 + lane;
-      const bool active = idx[j] >= 0;
-      int phase = 0, maxv = 0, offset = 0, value = 0, nb = 0, jn = 0;
-      uint32_t raw = 0;
-      if (active) {
-        const int index = idx[j];
-        const int32_t *cdf = cdf_all + (int64_t)index * cr.t.stride;
-        const int size = sizes[index];
-        maxv = size - 2;
-        offset = offsets[index];
+      for (int j = 0; j < DEC_BATCH; ++j) {
+        const uint32_t index = (uint32_t)nxt[j];
+        rowm[j] = lds32(s_row + 4u * index);
+        cbase[j] = s_cdf + 4u * index * stride;
+        lbase[j] = s_lut + (uint32_t)LUT_PITCH * index;
+      }
+#pragma unroll
+      for (int j = 0; j < DEC_BATCH; ++j) nxt[j] = load_idx((r0 + DEC_BATCH + j) * 32 + lane);
+#pragma unroll
+      for (int j = 0; j < DEC_BATCH; ++j) {
+        const int maxv = (int)(rowm[j] >> 16) - 2;
         const uint32_t cum = x & 0xffffu;
-        // largest s with cdf[s] <= cum (== find_symbol), as seven branch-free probes
-        int sidx = 0;
-        if (size <= 128) {
-#pragma unroll
-          for (int step = 64; step; step >>= 1) {
-            const int mid = sidx + step;
-            if (mid < size && (uint32_t)cdf[mid < size ? mid : 0] <= cum) sidx = mid;
-          }
-        } else {
-          sidx = rans::find_symbol(cdf, size, cum);
+        int lo = 0, hi = maxv;
+        if (LUT) {
+          const uint32_t l = lbase[j] + (cum >> 8);
+          lo = (int)lds8(l);
+          hi = (int)lds8(l + 1);
         }
-        const uint32_t start = (uint32_t)cdf[sidx], freq = (uint32_t)(cdf[sidx + 1] - cdf[sidx]);
-        x = freq * (x >> 16) + cum - start;
-        value = sidx;
-        if (sidx == maxv) phase = 1;
+        while (lo < hi) {                                // largest s with cdf[s] <= cum
+          const int mid = (lo + hi + 1) >> 1;
+          if (lds32(cbase[j] + 4u * mid) <= cum) lo = mid; else hi = mid - 1;
+        }
+        const uint32_t start = lds32(cbase[j] + 4u * lo), next = lds32(cbase[j] + 4u * lo + 4u);
+        x = (next - start) * (x >> 16) + (cum - start);
+        int value = lo;
+        int phase = lo == maxv ? 1 : 0;
+        const bool need = x < rans::L32;
+        if (__any_sync(0xffffffffu, need || phase)) {
+          const uint32_t m = __ballot_sync(0xffffffffu, need);
+          if (m) refill(need, m);
+          if (__any_sync(0xffffffffu, phase != 0)) escape(phase, value, maxv);
+        }
+        *o = (int16_t)(value + (int)(int16_t)(rowm[j] & 0xffffu));
+        o += 32;
       }
-      {
-        const bool need = active && x < rans::L32;
-        const uint32_t m = __ballot_sync(0xffffffffu, need);
-        if (need) {
-          const uint32_t pos = rp + __popc(m & lt);
-          uint32_t word = 0;
-          if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
-          x = (x << 16) | word;
-        }
-        rp += __popc(m);
-      }
-      while (__ballot_sync(0xffffffffu, phase != 0)) {
-        uint32_t val = 0;
-        if (phase) {
-          val = x & 15u;
-          x >>= 4;
-        }
-        const bool need = phase != 0 && x < rans::L32;
-        const uint32_t m = __ballot_sync(0xffffffffu, need);
-        if (need) {
-          const uint32_t pos = rp + __popc(m & lt);
-          uint32_t word = 0;
-          if (pos < end) word = w[pos]; else err |= ERR_DEC_UNDERFLOW;
-          x = (x << 16) | word;
-        }
-        rp += __popc(m);
-        bool done = false;
-        if (phase == 1) {
-          nb += (int)val;
-          if (val != 15u) {
-            if (nb == 0) done = true; else phase = 2;
-            if (nb > 8) { err |= ERR_ESCAPE; done = true; }
-          }
-        } else if (phase == 2) {
-          raw |= val << (4 * jn);
-          if (++jn == nb) done = true;
-        }
-        if (done) {
-          value = (int)(raw >> 1);
-          if (raw & 1u) value = -value - 1; else value += maxv;
-          phase = 0;
-        }
-        if (err & ERR_DEC_UNDERFLOW) phase = 0;  // never spin on a truncated stream
-      }
-      if (active) out[off + k] = (int16_t)(value + offset);
     }
+  }
+  // checked rounds: the tail of a part, or every round when the tables stay in global memory
+  for (; r0 < rounds; ++r0) {
+    const int index = load_idx(r0 * 32 + lane);
+    const bool active = index >= 0;
+    int phase = 0, maxv = 0, offset = 0, value = 0;
+    if (active) {
+      const uint32_t cum = x & 0xffffu;
+      uint32_t start, next;
+      int sidx;
+      if (TAB_SMEM) {
+        const uint32_t row = lds32(s_row + 4u * (uint32_t)index);
+        const uint32_t c = s_cdf + 4u * (uint32_t)index * stride;
+        maxv = (int)(row >> 16) - 2;
+        offset = (int)(int16_t)(row & 0xffffu);
+        int lo = 0, hi = maxv;
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (lds32(c + 4u * mid) <= cum) lo = mid; else hi = mid - 1;
+        }
+        sidx = lo;
+        start = lds32(c + 4u * sidx);
+        next = lds32(c + 4u * sidx + 4u);
+      } else {
+        const int32_t *cdf = cr.t.cdf + (int64_t)index * cr.t.stride;
+        const int size = cr.t.sizes[index];
+        maxv = size - 2;
+        offset = cr.t.offsets[index];
+        sidx = rans::find_symbol(cdf, size, cum);
+        start = (uint32_t)cdf[sidx];
+        next = (uint32_t)cdf[sidx + 1];
+      }
+      x = (next - start) * (x >> 16) + cum - start;
+      value = sidx;
+      if (sidx == maxv) phase = 1;
+    }
+    const bool need = active && x < rans::L32;
+    const uint32_t m = __ballot_sync(0xffffffffu, need);
+    if (m) refill(need, m);
+    if (__any_sync(0xffffffffu, phase != 0)) escape(phase, value, maxv);
+    if (active) *o = (int16_t)(value + offset);
+    o += 32;
   }
   p.lane_x[lane] = x;
   __syncwarp();
@@ -891,7 +999,9 @@ extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t 
   CallRec cr;
   cr.sym = nullptr; cr.idx = indexes; cr.n = n; cr.plane = plane < 1 ? 1 : plane;
   cr.t.cdf = t->cdf; cr.t.sizes = t->sizes; cr.t.offsets = t->offsets; cr.t.stride = t->stride;
-  cr.t.count = t->count;
+  cr.t.count = t->count; cr.t.lut = t->lut;
+  if (n / r->dec_parts + r->dec_parts >= ((int64_t)1 << 31))
+    return dcvc_fail(DCVC_ERR_ARG, "rans_dec_pull: more than 2^31 symbols per stream part");
   cudaStream_t s = (cudaStream_t)stream;
   const size_t tab_bytes = ((size_t)cr.t.count * cr.t.stride + 2 * (size_t)cr.t.count) * 4;
   if (r->mode == DCVC_RANS_COMPAT) {
@@ -908,16 +1018,29 @@ extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t 
           cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
     }
   } else {
-    if (cr.t.count > 0 && tab_bytes <= DEC_TAB_SMEM_MAX) {
+    // decoder's shared-memory image: cdf rows, one {size, offset} word per row [, the search LUT]
+    const size_t base_bytes = dec_tab_words(cr.t.count, cr.t.stride) * 4;
+    const size_t lut_bytes = (size_t)cr.t.count * LUT_PITCH;
+    // the LUT costs 256 bytes per row to stage: only for parts that decode enough rounds
+    const bool lut_ok = t->lut && n / r->dec_parts >= 4096 && cr.t.stride <= 257 && (reinterpret_cast<uintptr_t>(t->lut) & 3) == 0 &&
+                        base_bytes + lut_bytes <= DEC_TAB_SMEM_MAX;
+    if (cr.t.count > 0 && base_bytes <= DEC_TAB_SMEM_MAX && cr.t.stride < 32768) {
       int rc = dcvc_once_per_device(DCVC_ONCE_RANS_DEC, [] {
-        return cudaFuncSetAttribute(ilv_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)DEC_TAB_SMEM_MAX);
+        cudaError_t e = cudaFuncSetAttribute(ilv_decode_kernel<true, true>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_TAB_SMEM_MAX);
+        if (e != cudaSuccess) return e;
+        return cudaFuncSetAttribute(ilv_decode_kernel<true, false>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_TAB_SMEM_MAX);
       });
       if (rc) return rc;
-      ilv_decode_kernel<true><<<r->dec_parts, DEC_THREADS, tab_bytes, s>>>(
-          cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+      if (lut_ok)
+        ilv_decode_kernel<true, true><<<r->dec_parts, DEC_THREADS, base_bytes + lut_bytes, s>>>(
+            cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+      else
+        ilv_decode_kernel<true, false><<<r->dec_parts, DEC_THREADS, base_bytes, s>>>(
+            cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
     } else {
-      ilv_decode_kernel<false><<<r->dec_parts, DEC_THREADS, 0, s>>>(
+      ilv_decode_kernel<false, false><<<r->dec_parts, DEC_THREADS, 0, s>>>(
           cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
     }
   }

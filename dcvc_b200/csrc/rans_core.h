@@ -36,6 +36,7 @@ struct Tables {
   const int32_t *offsets;
   int32_t stride;
   int32_t count;   // rows (table sets of `stride` entries)
+  const uint8_t *lut = nullptr;  // optional [count][256] search LUT (dcvc_tables.lut)
 };
 
 // One coding operation: bits==16 -> (start,freq) interval; bits==4 -> raw nibble `start`.

@@ -146,8 +146,19 @@ class DeviceTables:
         self.cdf = torch.from_numpy(np.ascontiguousarray(cdf, dtype=np.int32)).to(device)
         self.sizes = torch.from_numpy(np.ascontiguousarray(sizes, dtype=np.int32)).to(device)
         self.offsets = torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.int32)).to(device)
+        # search table of the interleaved decoder (dcvc_tables.lut): per row and 256-wide bucket of
+        # the 16-bit cumulative value, the symbol its first value falls in
+        self.lut = None
+        if cdf.shape[1] <= 257:
+            lut = np.zeros((cdf.shape[0], 256), dtype=np.uint8)
+            starts = np.arange(256, dtype=np.int64) * 256
+            for r in range(cdf.shape[0]):
+                row = np.asarray(cdf[r, :max(int(sizes[r]) - 1, 1)], dtype=np.int64)
+                lut[r] = np.clip(np.searchsorted(row, starts, side="right") - 1, 0, 255)
+            self.lut = torch.from_numpy(lut).to(device)
         self.c = _lib.Tables(self.cdf.data_ptr(), self.sizes.data_ptr(), self.offsets.data_ptr(),
-                             cdf.shape[0], cdf.shape[1])
+                             cdf.shape[0], cdf.shape[1],
+                             self.lut.data_ptr() if self.lut is not None else None)
 
     def get_cdf_info(self):
         return self.cdf_np, self.sizes_np, self.offsets_np

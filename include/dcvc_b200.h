@@ -352,6 +352,10 @@ typedef struct dcvc_tables {
   const int32_t *sizes;   /* device [T] */
   const int32_t *offsets; /* device [T] */
   int32_t count, stride;
+  /* optional search table for the interleaved decoder, device [T][256] uint8, 16-byte aligned,
+   * lut[t][b] = largest s with cdf[t][s] <= 256 b (any stride <= 257); NULL = none.  The
+   * reference searches linearly (rans.cpp:289-292); same result. */
+  const uint8_t *lut;
 } dcvc_tables;
 
 /* `parts`: 1..16 stream parts in compat mode (the reference container keeps parts-1 in a nibble,
