@@ -68,12 +68,10 @@ def parse_args():
     p.add_argument("--pipeline", type=int, default=1,
                    help="1: encoder and decoder on two CUDA streams, decoder one frame behind "
                         "(dcvc_b200.pipeline); 0: the reference's strictly sequential frame loop")
-    p.add_argument("--graphs", type=int, default=-1,
-                   help="1: the P-frame encode / decode launches are replayed from CUDA graphs "
-                        "(dcvc_b200.graphs; bit-identical to the eager launch sequence), 0: eager, "
-                        "-1 (default): graphs where they measured faster -- the one-stream schedules "
-                        "(arms.sequential, arms.encode_decode_api); the two-stream pipeline hides "
-                        "the launch time already, at 1 and at 8 ranks per host (DESIGN.md)")
+    p.add_argument("--graphs", type=int, default=1,
+                   help="1 (default): the P-frame encode / decode launches are replayed from CUDA "
+                        "graphs (dcvc_b200.graphs; bit-identical to the eager launch sequence), "
+                        "0: eager launches")
     p.add_argument("--profile-out", default=None, help="write the per-kernel table (json) here")
     p.add_argument("--workload", default="rgb1080p", choices=["rgb1080p", "entropy", "yuv420x8", "hem_sweep"],
                    help="rgb1080p: BASELINE configs[1] (the headline); entropy: configs[4] "
@@ -349,15 +347,16 @@ def main():
     # pipelined mode: the decoder is a second model instance (own weights copy, coder context and
     # dpb), as it would be in a separate process; the two only share the byte stream
     i_dec, p_dec = make_nets() if args.pipeline else (None, None)
-    use_graphs = args.graphs if args.graphs >= 0 else int(not args.pipeline)
-    arm_graphs = args.graphs != 0
+    use_graphs = bool(args.graphs)
+    arm_graphs = use_graphs
     if use_graphs:
         from dcvc_b200.graphs import GraphedDMC
         p_net = GraphedDMC(p_net)
         p_dec = GraphedDMC(p_dec) if p_dec is not None else None
-    # every graph variant (three feature-adaptor indexes) is seen twice -- eager, then recorded --
-    # before it replays: ten untimed frames ahead of the warm-up
-    prime = 10 if (use_graphs or arm_graphs) else 0
+    # every graph variant (four phases of frame_idx % 4) is seen twice -- eager, then recorded --
+    # and replayed once (the first launch uploads the graph) before the timed region: sixteen
+    # untimed frames ahead of the warm-up
+    prime = 16 if use_graphs else 0
 
     nf = NF
     host = synth.synth_frames(nf, H, W, seed=rank).pin_memory()      # [nf,3,H,W] fp32 in [0,1]
@@ -500,11 +499,11 @@ def main():
     arms = None
     if world == 1 and not args.no_extra_arms:
         arms = {}
-        k = min(args.steps, 24)
+        k = min(args.steps, 48)
         p_arm = p_net
-        if arm_graphs and not use_graphs:
+        if arm_graphs:      # own graphs: this schedule continues from the DECODER's dpb
             from dcvc_b200.graphs import GraphedDMC
-            p_arm = GraphedDMC(p_net)
+            p_arm = GraphedDMC(p_net.m if use_graphs else p_net)
         gtxt = ("; P-frame launches replayed from CUDA graphs (dcvc_b200.graphs)"
                 if arm_graphs else "")
         ms_s, _, seq_s = timed(body_resident, pipeline=0, nets=(i_net, p_arm), steps=k)
@@ -579,6 +578,9 @@ def main():
                            "l2": "inputs larger than L2: every step streams a new frame through >= 6 GB of activations (full-resolution tensors are 130-400 MB each, the L2 is 126 MB); no explicit flush",
                            "conv_mode": args.conv_mode, "coder": args.coder,
                            "cuda_graphs": bool(use_graphs),
+                           "graph_calls": ({"replayed": p_net.replays + p_dec.replays,
+                                            "eager": p_net.eager + p_dec.eager}
+                                           if use_graphs and p_dec is not None else None),
                            "schedule": ("PIPELINED (dcvc_b200.pipeline.EncDecPipeline, an API the "
                                         "reference does not have): encoder and decoder are two model "
                                         "instances on two CUDA streams, the decoder one frame behind "

@@ -14,7 +14,7 @@ import torch
 from torch import nn
 
 from . import entropy_models as em
-from . import layers, ops
+from . import layers, ops, tensor
 from .tensor import Act
 
 
@@ -224,7 +224,7 @@ class CompressionModel(nn.Module):
         ops.fill(catb.slice(0, c), 0.0)
         return catb
 
-    def forward_four_part_prior(self, y, catb, prior_fn, write=False, bits=None):
+    def forward_four_part_prior(self, y, catb, prior_fn, write=False, bits=None, tag=None):
         """forward_four_part_prior / compress_four_part_prior (common_model.py:142-259).
         Returns (y_hat Act, [(symbols, indexes)] * 4 when write)."""
         c = y.c
@@ -232,7 +232,7 @@ class CompressionModel(nn.Module):
         dev = y.device
         y_hat_so_far = catb.slice(0, c)
         params = catb.slice(c, 3 * c)
-        y_out = Act.new(y.h, y.w, c, dev)
+        y_out = tensor.placed(tag, y.h, y.w, c) or Act.new(y.h, y.w, c, dev)
         edges = self._ensure_edges()
         dist = em.DIST_ID[self.y_distribution]
         ws = torch.empty((n + 255) // 256, dtype=torch.float32, device=dev) if bits is not None \
@@ -253,7 +253,7 @@ class CompressionModel(nn.Module):
         for sym, idx in coded:
             self.entropy_coder.encode(sym, idx, sym.numel(), 1, self._tables["y"])
 
-    def decompress_four_part_prior(self, catb, c, prior_fn):
+    def decompress_four_part_prior(self, catb, c, prior_fn, tag=None):
         """decompress_four_part_prior (common_model.py:261-321): per step, indexes -> rANS pull ->
         scatter, all on the device."""
         h, w = catb.h, catb.w
@@ -261,7 +261,7 @@ class CompressionModel(nn.Module):
         dev = catb.device
         y_hat_so_far = catb.slice(0, c)
         params = catb.slice(c, 3 * c)
-        y_out = Act.new(h, w, c, dev)
+        y_out = tensor.placed(tag, h, w, c) or Act.new(h, w, c, dev)
         edges = self._ensure_edges()
         idx = torch.empty(n, dtype=torch.uint8, device=dev)
         sym = torch.empty(n, dtype=torch.int16, device=dev)

@@ -223,6 +223,169 @@ __global__ void __launch_bounds__(CDEC_THREADS) compat_decode_kernel(const CallR
   if (d.underflow) atomicOr(meta, ERR_DEC_UNDERFLOW);
 }
 
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds8(uint32_t a) {
+  uint32_t v;
+  asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+
+constexpr int LUT_PITCH = 260;   // bytes per LUT row in shared memory: 256 buckets + the row's last symbol
+
+// words of shared memory in front of the LUT: cdf rows + one {size, offset} word per row, padded
+// to 16 bytes
+__host__ __device__ __forceinline__ size_t dec_tab_words(int count, int stride) {
+  return ((size_t)count * stride + count + 3) & ~(size_t)3;
+}
+
+
+// The decoders' shared-memory image of a call's table set: [count][stride] cdf | [count]
+// size << 16 | (offset & 0xffff) | (LUT) [count][LUT_PITCH] bytes: the 256 buckets of
+// dcvc_tables.lut and, at byte 256, the row's last symbol.  Returns shared-space addresses.
+template <bool LUT, int THREADS>
+__device__ __forceinline__ void stage_tables(const CallRec &cr, int32_t *tab, uint32_t &s_cdf,
+                                             uint32_t &s_row, uint32_t &s_lut) {
+  const int ncdf = cr.t.count * cr.t.stride;
+  if ((ncdf & 3) == 0 && (reinterpret_cast<uintptr_t>(cr.t.cdf) & 15) == 0) {
+    const int4 *src = reinterpret_cast<const int4 *>(cr.t.cdf);
+    int4 *dst = reinterpret_cast<int4 *>(tab);
+#pragma unroll 4
+    for (int i = threadIdx.x; i < (ncdf >> 2); i += THREADS) dst[i] = __ldg(src + i);
+  } else {
+    for (int i = threadIdx.x; i < ncdf; i += THREADS) tab[i] = cr.t.cdf[i];
+  }
+  for (int i = threadIdx.x; i < cr.t.count; i += THREADS)
+    tab[ncdf + i] = (cr.t.sizes[i] << 16) | (cr.t.offsets[i] & 0xffff);
+  const size_t lw = dec_tab_words(cr.t.count, cr.t.stride);
+  if (LUT) {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(cr.t.lut);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(tab + lw);
+#pragma unroll 8
+    for (int i = threadIdx.x; i < cr.t.count * 64; i += THREADS)
+      dst[(i >> 6) * (LUT_PITCH / 4) + (i & 63)] = __ldg(src + i);
+    for (int i = threadIdx.x; i < cr.t.count; i += THREADS)
+      dst[i * (LUT_PITCH / 4) + 64] = (uint32_t)(cr.t.sizes[i] - 2);
+  }
+  __syncthreads();
+  s_cdf = (uint32_t)__cvta_generic_to_shared(tab);
+  asm volatile("" : "+r"(s_cdf));      // keep the base in a register (else re-derived every round)
+  s_row = s_cdf + 4u * (uint32_t)ncdf;
+  s_lut = s_cdf + 4u * (uint32_t)lw;
+}
+
+// Compat decoder with the tables in shared memory.  The reference's stream is ONE sequential
+// rANS state per part (rans.cpp:272-331), so the warp runs that chain redundantly in all 32 lanes
+// (same state, same instructions): a table index comes from the lane that prefetched it by
+// shuffle, lane j keeps symbol j of a group of 32 for the coalesced store, stream words come from
+// a shared-memory ring filled a window ahead (see ilv_decode_kernel), and the symbol search starts
+// from the host-built LUT.  ~120 dependent cycles per symbol instead of ~900 for the generic
+// single-lane loop (compat_decode_kernel, kept for table sets that do not fit).
+template <bool LUT>
+__global__ void __launch_bounds__(CDEC_THREADS) compat_decode_fast_kernel(const CallRec cr, int nparts,
+                                                                          const uint8_t *stream,
+                                                                          DecPart *parts, int16_t *out,
+                                                                          uint32_t *meta) {
+  extern __shared__ __align__(16) int32_t tab[];
+  __shared__ uint32_t ring[128];
+  uint32_t s_cdf, s_row, s_lut;
+  stage_tables<LUT, CDEC_THREADS>(cr, tab, s_cdf, s_row, s_lut);
+  if (threadIdx.x >= 32) return;
+  const int i = blockIdx.x, lane = threadIdx.x;
+  DecPart &p = parts[i];
+  const uint32_t *w = reinterpret_cast<const uint32_t *>(stream + p.base);
+  uint64_t x = p.x;
+  uint32_t rp = p.rp;
+  const uint32_t end = p.end;
+  uint32_t err = 0;
+  auto fetch = [&](uint32_t pos) -> uint32_t { return pos < end ? w[pos] : 0u; };
+  uint32_t cw = rp >> 5;
+  ring[(cw * 32 + lane) & 127] = fetch(cw * 32 + lane);
+  ring[((cw + 1) * 32 + lane) & 127] = fetch((cw + 1) * 32 + lane);
+  uint32_t pend = fetch((cw + 2) * 32 + lane);
+  __syncwarp();
+  auto word = [&]() -> uint32_t {                          // dec64_word, warp-uniform
+    if (rp >= end) { err |= ERR_DEC_UNDERFLOW; return 0u; }
+    const uint32_t v = ring[rp & 127];
+    ++rp;
+    if ((rp >> 5) != cw) {
+      ++cw;
+      __syncwarp();
+      ring[((cw + 1) * 32 + lane) & 127] = pend;
+      pend = fetch((cw + 2) * 32 + lane);
+      __syncwarp();
+    }
+    return v;
+  };
+  auto bits4 = [&]() -> uint32_t {                         // dec64_bits(d, BYPASS_BITS)
+    const uint32_t val = (uint32_t)x & 15u;
+    x >>= 4;
+    if (x < rans::L64) x = (x << 32) | word();
+    return val;
+  };
+  int64_t off, cur;
+  part_range(cr.n, nparts, i, off, cur);
+  const uint32_t n = (uint32_t)cur;
+  const uint8_t *ip = cr.idx ? cr.idx + off : nullptr;
+  int16_t *o = out + off + lane;
+  const uint32_t stride = (uint32_t)cr.t.stride;
+  auto load_idx = [&](uint32_t k) -> int {
+    if (k >= n) return 0;
+    return ip ? (int)ip[k] : (int)((uint64_t)(off + k) / (uint64_t)cr.plane);
+  };
+  int nxt = load_idx(lane);
+  for (uint32_t k0 = 0; k0 < n; k0 += 32) {
+    const int mine_idx = nxt;
+    nxt = load_idx(k0 + 32 + lane);
+    const int nb = n - k0 < 32u ? (int)(n - k0) : 32;
+    int mine = 0;
+#pragma unroll 4
+    for (int j = 0; j < nb; ++j) {
+      const uint32_t index = (uint32_t)__shfl_sync(0xffffffffu, mine_idx, j);
+      const uint32_t row = lds32(s_row + 4u * index);
+      const uint32_t c = s_cdf + 4u * index * stride;
+      const int maxv = (int)(row >> 16) - 2;
+      const uint32_t cum = (uint32_t)x & 0xffffu;
+      int lo = 0, hi = maxv;
+      if (LUT) {
+        const uint32_t l = s_lut + (uint32_t)LUT_PITCH * index + (cum >> 8);
+        lo = (int)lds8(l);
+        hi = (int)lds8(l + 1);
+      }
+      while (lo < hi) {                                    // largest s with cdf[s] <= cum
+        const int mid = (lo + hi + 1) >> 1;
+        if (lds32(c + 4u * mid) <= cum) lo = mid; else hi = mid - 1;
+      }
+      const uint32_t start = lds32(c + 4u * lo), next = lds32(c + 4u * lo + 4u);
+      x = (uint64_t)(next - start) * (x >> 16) + (cum - start);
+      if (x < rans::L64) x = (x << 32) | word();
+      int value = lo;
+      if (lo == maxv) {                                    // bypass escape, rans.cpp:296-318
+        uint32_t val = bits4();
+        int nbv = (int)val;
+        while (val == 15u && !(err & ERR_DEC_UNDERFLOW)) {
+          val = bits4();
+          nbv += (int)val;
+        }
+        uint32_t raw = 0;
+        for (int q = 0; q < nbv && q < 8; ++q) raw |= bits4() << (4 * q);
+        value = (int)(raw >> 1);
+        if (raw & 1u) value = -value - 1; else value += maxv;
+      }
+      if (lane == j) mine = value + (int)(int16_t)(row & 0xffffu);
+    }
+    if (k0 + lane < n) *o = (int16_t)mine;
+    o += 32;
+  }
+  if (lane != 0) return;
+  p.x = x;
+  p.rp = rp;
+  if (err) atomicOr(meta, err);
+}
+
 // ------------------------------------------------------------------ interleaved kernels
 __device__ __forceinline__ uint32_t lanemask_lt() {
   uint32_t m;
@@ -395,25 +558,6 @@ constexpr int DEC_BATCH = 8;       // rounds whose table indexes are fetched ahe
 //  * table rows are addressed with 32-bit shared-space addresses, {size, offset} of a row share
 //    one word, table indexes are fetched one batch (8 rounds) ahead, whole batches run without
 //    per-round bounds checks; the last rounds of a part go through the checked round.
-__device__ __forceinline__ uint32_t lds32(uint32_t a) {
-  uint32_t v;
-  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
-  return v;
-}
-__device__ __forceinline__ uint32_t lds8(uint32_t a) {
-  uint32_t v;
-  asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
-  return v;
-}
-
-constexpr int LUT_PITCH = 260;   // bytes per LUT row in shared memory: 256 buckets + the row's last symbol
-
-// words of shared memory in front of the LUT: cdf rows + one {size, offset} word per row, padded
-// to 16 bytes
-__host__ __device__ __forceinline__ size_t dec_tab_words(int count, int stride) {
-  return ((size_t)count * stride + count + 3) & ~(size_t)3;
-}
-
 template <bool TAB_SMEM, bool LUT>
 __global__ void __launch_bounds__(DEC_THREADS) ilv_decode_kernel(const CallRec cr, int nparts,
                                                                  const uint8_t *stream,
@@ -422,34 +566,7 @@ __global__ void __launch_bounds__(DEC_THREADS) ilv_decode_kernel(const CallRec c
   extern __shared__ __align__(16) int32_t tab[];   // [count][stride] cdf | [count] size<<16|offset | lut
   __shared__ uint16_t ring[128];
   uint32_t s_cdf = 0, s_row = 0, s_lut = 0;
-  if (TAB_SMEM) {
-    const int ncdf = cr.t.count * cr.t.stride;
-    if ((ncdf & 3) == 0 && (reinterpret_cast<uintptr_t>(cr.t.cdf) & 15) == 0) {
-      const int4 *src = reinterpret_cast<const int4 *>(cr.t.cdf);
-      int4 *dst = reinterpret_cast<int4 *>(tab);
-#pragma unroll 4
-      for (int i = threadIdx.x; i < (ncdf >> 2); i += DEC_THREADS) dst[i] = __ldg(src + i);
-    } else {
-      for (int i = threadIdx.x; i < ncdf; i += DEC_THREADS) tab[i] = cr.t.cdf[i];
-    }
-    for (int i = threadIdx.x; i < cr.t.count; i += DEC_THREADS)
-      tab[ncdf + i] = (cr.t.sizes[i] << 16) | (cr.t.offsets[i] & 0xffff);
-    const size_t lw = dec_tab_words(cr.t.count, cr.t.stride);
-    if (LUT) {
-      const uint32_t *src = reinterpret_cast<const uint32_t *>(cr.t.lut);
-      uint32_t *dst = reinterpret_cast<uint32_t *>(tab + lw);
-#pragma unroll 8
-      for (int i = threadIdx.x; i < cr.t.count * 64; i += DEC_THREADS)
-        dst[(i >> 6) * (LUT_PITCH / 4) + (i & 63)] = __ldg(src + i);
-      for (int i = threadIdx.x; i < cr.t.count; i += DEC_THREADS)
-        dst[i * (LUT_PITCH / 4) + 64] = (uint32_t)(cr.t.sizes[i] - 2);
-    }
-    __syncthreads();
-    s_cdf = (uint32_t)__cvta_generic_to_shared(tab);
-    asm volatile("" : "+r"(s_cdf));      // keep the base in a register (else re-derived every round)
-    s_row = s_cdf + 4u * (uint32_t)ncdf;
-    s_lut = s_cdf + 4u * (uint32_t)lw;
-  }
+  if (TAB_SMEM) stage_tables<LUT, DEC_THREADS>(cr, tab, s_cdf, s_row, s_lut);
   if (threadIdx.x >= 32) return;
   const int wi = blockIdx.x, lane = threadIdx.x;
   DecPart &p = parts[wi];
@@ -1003,28 +1120,36 @@ extern "C" int dcvc_rans_dec_pull(dcvc_rans *r, const uint8_t *indexes, int64_t 
   if (n / r->dec_parts + r->dec_parts >= ((int64_t)1 << 31))
     return dcvc_fail(DCVC_ERR_ARG, "rans_dec_pull: more than 2^31 symbols per stream part");
   cudaStream_t s = (cudaStream_t)stream;
-  const size_t tab_bytes = ((size_t)cr.t.count * cr.t.stride + 2 * (size_t)cr.t.count) * 4;
+  // decoder's shared-memory image: cdf rows, one {size, offset} word per row [, the search LUT]
+  const size_t base_bytes = dec_tab_words(cr.t.count, cr.t.stride) * 4;
+  const size_t lut_bytes = (size_t)cr.t.count * LUT_PITCH;
+  const bool smem_ok = cr.t.count > 0 && base_bytes <= DEC_TAB_SMEM_MAX && cr.t.stride < 32768;
+  // the LUT costs 256 bytes per row to stage: only for parts that decode enough symbols
+  const bool lut_ok = t->lut && n / r->dec_parts >= 4096 && cr.t.stride <= 257 &&
+                      (reinterpret_cast<uintptr_t>(t->lut) & 3) == 0 &&
+                      base_bytes + lut_bytes <= DEC_TAB_SMEM_MAX;
   if (r->mode == DCVC_RANS_COMPAT) {
-    if (cr.t.count > 0 && tab_bytes <= DEC_TAB_SMEM_MAX) {
+    if (smem_ok) {
       int rc = dcvc_once_per_device(DCVC_ONCE_RANS_DEC2, [] {
-        return cudaFuncSetAttribute(compat_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)DEC_TAB_SMEM_MAX);
+        cudaError_t e = cudaFuncSetAttribute(compat_decode_fast_kernel<true>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_TAB_SMEM_MAX);
+        if (e != cudaSuccess) return e;
+        return cudaFuncSetAttribute(compat_decode_fast_kernel<false>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_TAB_SMEM_MAX);
       });
       if (rc) return rc;
-      compat_decode_kernel<true><<<r->dec_parts, CDEC_THREADS, tab_bytes, s>>>(
-          cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+      if (lut_ok)
+        compat_decode_fast_kernel<true><<<r->dec_parts, CDEC_THREADS, base_bytes + lut_bytes, s>>>(
+            cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
+      else
+        compat_decode_fast_kernel<false><<<r->dec_parts, CDEC_THREADS, base_bytes, s>>>(
+            cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
     } else {
       compat_decode_kernel<false><<<r->dec_parts, CDEC_THREADS, 0, s>>>(
           cr, r->dec_parts, r->d_stream, r->d_parts, symbols_out, r->d_meta);
     }
   } else {
-    // decoder's shared-memory image: cdf rows, one {size, offset} word per row [, the search LUT]
-    const size_t base_bytes = dec_tab_words(cr.t.count, cr.t.stride) * 4;
-    const size_t lut_bytes = (size_t)cr.t.count * LUT_PITCH;
-    // the LUT costs 256 bytes per row to stage: only for parts that decode enough rounds
-    const bool lut_ok = t->lut && n / r->dec_parts >= 4096 && cr.t.stride <= 257 && (reinterpret_cast<uintptr_t>(t->lut) & 3) == 0 &&
-                        base_bytes + lut_bytes <= DEC_TAB_SMEM_MAX;
-    if (cr.t.count > 0 && base_bytes <= DEC_TAB_SMEM_MAX && cr.t.stride < 32768) {
+    if (smem_ok) {
       int rc = dcvc_once_per_device(DCVC_ONCE_RANS_DEC, [] {
         cudaError_t e = cudaFuncSetAttribute(ilv_decode_kernel<true, true>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_TAB_SMEM_MAX);

@@ -1,43 +1,50 @@
 """CUDA-graph replay of the P-frame encode and decode.
 
 A 1080p P frame is ~785 kernel launches; issued one by one through ctypes they cost ~20 ms of
-host time per frame, which is what limits 8 ranks on one host and any schedule finer than the
-kernels themselves.  The shapes are static per (resolution, frame type), so the launches of
-`DMC.compress` and `DMC.decompress` are recorded once into CUDA graphs and replayed:
+host time per frame, which bounds any schedule that cannot hide it (one stream, encode then
+decode).  The shapes are static per (resolution, frame type), so the launches of `DMC.compress`
+and `DMC.decompress` are recorded once into CUDA graphs and replayed:
 
     compress   = ONE graph: motion, contexts, latents; then two branches -- the entropy-coder
                  kernels + meta words -> host + an event-record node (cudaEventRecordExternal,
                  dcvc_rans_enc_flush_mark_captured), and the encoder's own reconstruction (the next
                  frame's dpb).  The host waits on the coder's event only, as in the eager path.
     decompress = host: parse + upload the stream (dcvc_rans_dec_set_stream)
-                 | graph C (everything else) | host: error-word copy (dcvc_rans_dec_finish)
+                 | graph (everything else) | host: error-word copy (dcvc_rans_dec_finish)
 
-The only host-visible points are the ones the rANS API already has.  Graph inputs (the frame and
-the five dpb tensors) are copied into static buffers before a replay; every graph ends by copying
-its results into static output buffers of its own (outside the memory pool the graphs share), so
-a returned dpb stays valid until the SAME graph replays again (a graph per feature-adaptor index:
-2 to 4 frames later).  That differs from the reference's "new tensors each
-frame" contract, which is why this is opt-in (`GraphedDMC(model)`); results are bit-identical to
-the eager path (tests/test_gpu_graphs.py).
+The only host-visible points are the ones the rANS API already has.
 
-A key (shape, which dpb entries exist, adaptor index, rate point) is run eagerly the first time
-it is seen -- that fills every lazily built cache (packed weights, q vectors, kernel attributes)
--- recorded the second time, replayed from then on.
+Memory.  A frame's results (the five dpb tensors) are written by their producing kernels straight
+into static buffers OUTSIDE the memory pool the graphs share (`tensor.PLACEMENT`), one set per
+PHASE = frame_idx % 4, so no graph's intermediates can overwrite a dpb the caller still holds and
+nothing is copied at the end of a graph.  A returned dpb stays valid until the same phase comes
+round again (4 frames later) -- this differs from the reference's "new tensors each frame"
+contract, which is why the graphs are opt-in (`GraphedDMC(model)`).  Inputs: a graph is recorded
+reading the dpb it was given IN PLACE when those tensors are themselves static results of a
+GraphedDMC (the steady state: phase p always continues from phase p - 1), so nothing is copied at
+the start either; a call whose dpb lives elsewhere (the second P frame of a GOP continues from an
+eager frame) runs eagerly, into the same static results.  Only the frame itself (25 MB) is copied
+into a static input.  Results are bit-identical to the eager path (tests/test_gpu_graphs.py).
+
+A key (shape, which dpb entries exist, phase, rate point) is run eagerly the first time it is
+seen -- that fills every lazily built cache (packed weights, q vectors, kernel attributes) --
+recorded the second time, replayed from then on.
 """
 import torch
 
-from . import _lib
+from . import _lib, tensor
 from .tensor import Act
 
 DPB_KEYS = ("ref_frame", "ref_feature", "ref_mv_feature", "ref_y", "ref_mv_y")
 
 
 class _Static:
-    """Static copies of a graph's inputs: tensors with the exact memory layout of the ones seen at
-    recording time (dpb entries are NCHW views of NHWC buffers: the whole buffer is mirrored)."""
+    """Static tensors with the exact memory layout of the ones given (dpb entries are NCHW views of
+    NHWC buffers: the whole buffer is mirrored).  views[name]: the [1,C,H,W] tensor, acts[name]:
+    the same memory as an Act."""
 
     def __init__(self, tensors):
-        self.bufs, self.views = {}, {}
+        self.bufs, self.views, self.acts = {}, {}, {}
         for name, t in tensors.items():
             if t is None:
                 self.views[name] = None
@@ -46,11 +53,13 @@ class _Static:
             if a is not None:                       # channels-last view of an NHWC buffer
                 buf = torch.empty_like(a.buf)
                 self.bufs[name] = (buf, True)
-                self.views[name] = Act(buf, a.c0, a.c).nchw()
+                self.acts[name] = Act(buf, a.c0, a.c)
+                self.views[name] = self.acts[name].nchw()
             else:
                 buf = torch.empty_like(t)
                 self.bufs[name] = (buf, False)
                 self.views[name] = buf
+            _STATIC_PTRS.add(buf.data_ptr())
 
     def load(self, tensors):
         for name, (buf, nhwc) in self.bufs.items():
@@ -63,6 +72,28 @@ class _Static:
                     buf.copy_(src.buf, non_blocking=True)
             elif t.data_ptr() != buf.data_ptr():
                 buf.copy_(t, non_blocking=True)
+
+
+# data pointers of every static result buffer of every GraphedDMC of this process: a dpb made of
+# these can be read in place by a recorded graph
+_STATIC_PTRS = set()
+
+
+def _is_static(dpb):
+    for n in DPB_KEYS:
+        t = dpb[n]
+        if t is None:
+            continue
+        a = _as_act(t)
+        if (a.buf.data_ptr() if a is not None else t.data_ptr()) not in _STATIC_PTRS:
+            return False
+    return True
+
+
+def _sig(dpb):
+    """identity of a dpb's memory: what a graph recorded on it depends on"""
+    return tuple(None if dpb[n] is None else (dpb[n].data_ptr(), tuple(dpb[n].shape),
+                                              tuple(dpb[n].stride())) for n in DPB_KEYS)
 
 
 def _as_act(t):
@@ -93,20 +124,19 @@ class GraphedDMC:
         self.cap_stream = torch.cuda.Stream(model.device)
         self.side_stream = torch.cuda.Stream(model.device)
         self.enc, self.dec = {}, {}
-        self.replays = 0
+        self.replays = self.eager = 0
 
     @property
     def entropy_coder(self):
         return self.m.entropy_coder
 
     def _key(self, kind, x_like, dpb, q_in_ckpt, q_index, frame_idx, extra=()):
-        k = -1 if dpb["ref_feature"] is None else [0, 1, 0, 2][frame_idx % 4]
+        phase = -1 if dpb["ref_feature"] is None else frame_idx % 4
         pattern = tuple(dpb[n] is None for n in DPB_KEYS)
-        return (kind, tuple(x_like), pattern, k, bool(q_in_ckpt), int(q_index)) + tuple(extra)
+        return (kind, tuple(x_like), pattern, phase, bool(q_in_ckpt), int(q_index)) + tuple(extra)
 
     def _record(self, fn):
-        """runs fn() under stream capture on the private stream; fn gets (begin, end) callables
-        so that it can cut the recording into several graphs"""
+        """runs fn() under stream capture on the private stream; fn gets (begin, end) callables"""
         cur = torch.cuda.current_stream(self.m.device)
         torch.cuda.synchronize(self.m.device)
         self.cap_stream.wait_stream(cur)
@@ -128,6 +158,21 @@ class GraphedDMC:
         _lib.lib().dcvc_launch_count_add(-self._recorded)            # recorded, not run
         return graphs, out
 
+    def _placed(self, outs, fn):
+        """fn() with the frame's results placed in `outs` (None: nowhere special)"""
+        prev = tensor.PLACEMENT
+        tensor.PLACEMENT = outs.acts if outs is not None else None
+        try:
+            return fn()
+        finally:
+            tensor.PLACEMENT = prev
+
+    @staticmethod
+    def _settle(outs, dpb):
+        """the frame's results as static views: already there when placed, copied otherwise"""
+        outs.load(dpb)
+        return dict(outs.views)
+
     # ------------------------------------------------------------------ encoder
     def compress(self, x, dpb, q_in_ckpt, q_index, frame_idx, defer=False, reconstruct=True):
         m, ec = self.m, self.m.entropy_coder
@@ -137,21 +182,38 @@ class GraphedDMC:
         key = self._key("enc", tuple(x.shape) + tuple(x.stride()), dpb, q_in_ckpt, q_index,
                         frame_idx, (bool(reconstruct),))
         ent = self.enc.get(key)
+
+        def eager(outs):
+            res = self._placed(outs, lambda: m.compress(x, dpb, q_in_ckpt, q_index, frame_idx,
+                                                        defer=defer, reconstruct=reconstruct))
+            self.eager += 1
+            if reconstruct:
+                res["dpb"] = self._settle(outs, res["dpb"])
+            return res
+
         if ent is None:                              # first sight: eager (fills the lazy caches)
             res = m.compress(x, dpb, q_in_ckpt, q_index, frame_idx, defer=defer,
                              reconstruct=reconstruct)
-            # output buffers OUTSIDE the graph pool, laid out like the eager results: the recorded
-            # graph ends by copying its results there, so that no other graph's intermediates
-            # (which share the pool) can ever overwrite a dpb the caller still holds
-            self.enc[key] = ("warm", _Static(res["dpb"]) if reconstruct else None)
+            outs = _Static(res["dpb"]) if reconstruct else None
+            self.enc[key] = ["warm", outs, 0]
+            if reconstruct:
+                res["dpb"] = self._settle(outs, res["dpb"])
             return res
         if ent[0] == "warm":
             outs = ent[1]
-            ins = dict(dpb)
-            ins["x"] = x
-            static = _Static(ins)
-            static.load(ins)
-            sdpb = {n: static.views[n] for n in DPB_KEYS}
+            in_place = _is_static(dpb)
+            if not in_place and ent[2] < 2:          # wait for a steady-state dpb before recording
+                ent[2] += 1
+                return eager(outs)
+            xs = _Static({"x": x})
+            xs.load({"x": x})
+            if in_place:
+                sdpb = {n: dpb[n] for n in DPB_KEYS}
+                static = None
+            else:
+                static = _Static(dict(dpb))
+                static.load(dpb)
+                sdpb = {n: static.views[n] for n in DPB_KEYS}
 
             def body(begin, end):
                 def coder(mv_zs, zs, mv_coded, coded):
@@ -167,10 +229,10 @@ class GraphedDMC:
                         ec.flush_enqueue()
                         ec.mark_flushed_captured()
                 begin()
-                new_dpb = m._encode_side(static.views["x"], sdpb, q_in_ckpt, q_index, frame_idx,
+                new_dpb = m._encode_side(xs.views["x"], sdpb, q_in_ckpt, q_index, frame_idx,
                                          True, coder=coder, reconstruct=reconstruct)[0]
                 if reconstruct:
-                    outs.load(new_dpb)               # recorded copies into the static outputs
+                    outs.load(new_dpb)               # no-op for placed results, else recorded copies
                 self.cap_stream.wait_stream(self.side_stream)        # join the coder branch
                 end()
                 return dict(outs.views) if reconstruct else None
@@ -179,16 +241,19 @@ class GraphedDMC:
             ec.reserve(zs_)
             if ec._pending:                          # an unread flush of the previous frame
                 ec.get_encoded_stream()
-            graphs, new_dpb = self._record(body)
-            ent = ("ready", {"static": static, "graphs": graphs, "dpb": new_dpb,
-                             "launches": self._recorded})
+            graphs, new_dpb = self._placed(outs, lambda: self._record(body))
+            ent = ["ready", {"x": xs, "static": static, "sig": _sig(dpb) if in_place else None,
+                             "held": sdpb, "graphs": graphs, "dpb": new_dpb, "outs": outs,
+                             "launches": self._recorded}]
             self.enc[key] = ent
         ent = ent[1]
+        if ent["sig"] is not None and _sig(dpb) != ent["sig"]:
+            return eager(ent["outs"])                # dpb from elsewhere (GOP start): this once eagerly
         if ec._pending:
             ec.get_encoded_stream()
-        ins = dict(dpb)
-        ins["x"] = x
-        ent["static"].load(ins)
+        ent["x"].load({"x": x})
+        if ent["static"] is not None:
+            ent["static"].load(dpb)
         ent["graphs"][0].replay()
         ec.set_pending()
         _lib.lib().dcvc_launch_count_add(ent["launches"])
@@ -203,15 +268,30 @@ class GraphedDMC:
             return m.decompress(dpb, string, height, width, q_in_ckpt, q_index, frame_idx)
         key = self._key("dec", (height, width), dpb, q_in_ckpt, q_index, frame_idx)
         ent = self.dec.get(key)
+
+        def eager(outs):
+            res = self._placed(outs, lambda: m.decompress(dpb, string, height, width, q_in_ckpt,
+                                                          q_index, frame_idx))
+            self.eager += 1
+            return {"dpb": self._settle(outs, res["dpb"])}
+
         if ent is None:
             res = m.decompress(dpb, string, height, width, q_in_ckpt, q_index, frame_idx)
-            self.dec[key] = ("warm", _Static(res["dpb"]))
-            return res
+            outs = _Static(res["dpb"])
+            self.dec[key] = ["warm", outs, 0]
+            return {"dpb": self._settle(outs, res["dpb"])}
         if ent[0] == "warm":
             outs = ent[1]
-            static = _Static(dict(dpb))
-            static.load(dpb)
-            sdpb = {n: static.views[n] for n in DPB_KEYS}
+            in_place = _is_static(dpb)
+            if not in_place and ent[2] < 2:
+                ent[2] += 1
+                return eager(outs)
+            if in_place:
+                sdpb, static = {n: dpb[n] for n in DPB_KEYS}, None
+            else:
+                static = _Static(dict(dpb))
+                static.load(dpb)
+                sdpb = {n: static.views[n] for n in DPB_KEYS}
 
             def body(begin, end):
                 begin()
@@ -221,13 +301,17 @@ class GraphedDMC:
                 return {"dpb": dict(outs.views)}
 
             m._decode_begin(string, height, width)   # sizes the coder before the recording
-            graphs, out = self._record(body)
-            ent = ("ready", {"static": static, "graphs": graphs, "out": out,
-                             "launches": self._recorded})
+            graphs, out = self._placed(outs, lambda: self._record(body))
+            ent = ["ready", {"static": static, "sig": _sig(dpb) if in_place else None,
+                             "held": sdpb, "graphs": graphs, "out": out, "outs": outs,
+                             "launches": self._recorded}]
             self.dec[key] = ent
         ent = ent[1]
+        if ent["sig"] is not None and _sig(dpb) != ent["sig"]:
+            return eager(ent["outs"])
         m._decode_begin(string, height, width)
-        ent["static"].load(dpb)
+        if ent["static"] is not None:
+            ent["static"].load(dpb)
         ent["graphs"][0].replay()
         _lib.lib().dcvc_launch_count_add(ent["launches"])
         ec.finish_decode()

@@ -17,6 +17,21 @@ def _ru4(c):
     return (c + 3) // 4 * 4
 
 
+# Destinations for tagged allocations: {tag: Act}.  dcvc_b200.graphs sets it around a frame so
+# that the tensors a frame returns (the next frame's dpb) are written straight into buffers that
+# outlive the call, instead of being copied there afterwards.  None = allocate as usual.
+PLACEMENT = None
+
+
+def placed(tag, h, w, c, f16=False):
+    """the preassigned Act for `tag`, or None; the layout must be the one asked for"""
+    a = PLACEMENT.get(tag) if PLACEMENT else None
+    if a is None:
+        return None
+    assert (a.h, a.w, a.c, a.f16) == (h, w, c, f16), (tag, (a.h, a.w, a.c, a.f16), (h, w, c, f16))
+    return a
+
+
 class Act:
     __slots__ = ("buf", "c0", "c")
 

@@ -9,7 +9,7 @@ import time
 
 import torch
 
-from . import arch, layers, ops
+from . import arch, layers, ops, tensor
 from .common_model import CompressionModel, get_downsampled_shape
 from .stream_helper import encode_p, decode_p, filesize
 from .tensor import Act
@@ -108,7 +108,8 @@ class DMC(CompressionModel):
         t = layers.rbu(net, m + ".dec_1.1", t)
         t = layers.dcb(net, m + ".dec_1.2", t, f16_out=True)
         t = layers.rbu(net, m + ".dec_1.3", t)
-        feature = layers.dcb(net, m + ".dec_1.4", t)
+        feature = layers.dcb(net, m + ".dec_1.4", t,
+                             out=tensor.placed("ref_mv_feature", t.h, t.w, 64))
         t = layers.rbu(net, m + ".dec_2", feature, scale=q)
         t = layers.dcb(net, m + ".dec_3.0", t, f16_out=True)
         # 8 -> 16 filters (two zero channels per pixel): planar packing, vectorised epilogue
@@ -285,10 +286,13 @@ class DMC(CompressionModel):
         perm = tuple(range(32, 80)) + tuple(range(0, 32))
         t = ops.conv(bufs["R"], net.cw(rg + ".first_conv", cin_perm=perm), f16_out=True)
         t = layers.unet(net, rg + ".unet_1", t, layers.dcb, f16_out=True)
-        feature = layers.unet(net, rg + ".unet_2", t, layers.dcb)
+        feature = layers.unet(net, rg + ".unet_2", t, layers.dcb,
+                              out=tensor.placed("ref_feature", t.h, t.w, 48))
         # 3 -> 4 output channels (a zero filter): the image pixel is a 16-byte group either way,
         # and whole groups take the TMA-store epilogue instead of the scalar one
-        x_hat4 = ops.conv(feature, net.cw(rg + ".recon_conv", cout_pad=4), clamp01=True)
+        xp = tensor.placed("ref_frame", t.h, t.w, 3)
+        x_hat4 = ops.conv(feature, net.cw(rg + ".recon_conv", cout_pad=4), clamp01=True,
+                          out=Act(xp.buf, 0, 4) if xp is not None and xp.cs == 4 else None)
         return x_hat4.slice(0, 3), feature
 
     # ------------------------------------------------------------------ shared encoder side
@@ -310,7 +314,7 @@ class DMC(CompressionModel):
         mv_catb = self.new_prior_buffer(mv_y.h, mv_y.w, mv_y.c)
         self._mv_params(mv_z_hat, dpb, mv_catb, mv_y.c)
         mv_y_hat, mv_coded = self.forward_four_part_prior(mv_y, mv_catb, self._prior_fn("mv_y"),
-                                                          write, b(2))
+                                                          write, b(2), tag="ref_mv_y")
         mv_hat, mv_feature = self._mv_dec(mv_y_hat, mv_q_dec)
         bufs = self._new_bufs(H, W, xa.device)
         ctx1, ctx2, ctx3 = self._motion_compensation(dpb, mv_hat, frame_idx, bufs)
@@ -319,7 +323,8 @@ class DMC(CompressionModel):
         z_hat, z_sym = self.quant_z(z, "bit_estimator_z", write, b(1))
         catb = self.new_prior_buffer(y.h, y.w, y.c)
         self._res_params(z_hat, dpb, ctx3, catb, y.c)
-        y_hat, coded = self.forward_four_part_prior(y, catb, self._prior_fn("y"), write, b(0))
+        y_hat, coded = self.forward_four_part_prior(y, catb, self._prior_fn("y"), write, b(0),
+                                                    tag="ref_y")
         if coder is not None:
             coder((mv_z_hat, mv_z_sym), (z_hat, z_sym), mv_coded, coded)
         if not reconstruct:     # encode_decode: the decoder produces the (bit-identical) dpb
@@ -405,13 +410,15 @@ class DMC(CompressionModel):
         z_hat = self.decode_z(arch.CH_16X, z_size, "bit_estimator_z")
         mv_catb = self.new_prior_buffer(yh, yw, 64)
         self._mv_params(mv_z_hat, dpb, mv_catb, 64)
-        mv_y_hat = self.decompress_four_part_prior(mv_catb, 64, self._prior_fn("mv_y"))
+        mv_y_hat = self.decompress_four_part_prior(mv_catb, 64, self._prior_fn("mv_y"),
+                                                   tag="ref_mv_y")
         mv_hat, mv_feature = self._mv_dec(mv_y_hat, mv_q_dec)
         bufs = self._new_bufs(mv_hat.h, mv_hat.w, dev)
         _, _, ctx3 = self._motion_compensation(dpb, mv_hat, frame_idx, bufs)
         catb = self.new_prior_buffer(yh, yw, arch.CH_16X)
         self._res_params(z_hat, dpb, ctx3, catb, arch.CH_16X)
-        y_hat = self.decompress_four_part_prior(catb, arch.CH_16X, self._prior_fn("y"))
+        y_hat = self.decompress_four_part_prior(catb, arch.CH_16X, self._prior_fn("y"),
+                                                tag="ref_y")
         if finish:
             ec.finish_decode()
         x_hat, feature = self._recon(y_hat, bufs, y_q_dec)
