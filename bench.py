@@ -731,7 +731,7 @@ def profile_step(seq, x, args):
     # ncu pass (dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/)
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_conv_tc_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_conv_tc_traffic.json")) as f:
             traffic = json.load(f)["dram_bytes_per_launch"]
     except (OSError, ValueError, KeyError):
         pass

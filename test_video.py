@@ -56,6 +56,9 @@ def parse_args(argv=None):
     p.add_argument("--coder_mode", choices=("compat", "interleaved"), default="compat")
     # extension: what is dealt to the ranks under torchrun -- GOPs (default) or whole jobs
     p.add_argument("--shard", choices=("gop", "job"), default="gop")
+    # extension: with --write_stream, replay the P frames' launches from CUDA graphs
+    # (dcvc_b200.graphs; bit-identical to the eager launches)
+    p.add_argument("--graphs", type=str2bool, nargs="?", const=True, default=False)
     return p.parse_args(argv)
 
 
@@ -156,6 +159,9 @@ def main(argv=None):
     i_net.update(force=True)
     if p_net is not None:
         p_net.update(force=True)
+        if args.graphs:
+            from dcvc_b200.graphs import GraphedDMC
+            GraphedDMC(p_net)        # registers itself: DMC.encode_decode replays through it
 
     jobs = build_jobs(args, config, q_in_ckpt, q_indexes)
     # the unit of multi-GPU work is one GOP of one job (every GOP restarts from an intra frame,

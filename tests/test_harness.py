@@ -245,3 +245,31 @@ def test_entry_point_yuv420_vs_oracle(tmp_path):
     for c in "yuv":
         assert abs(rec[f"ave_all_frame_psnr_{c}"] - sum(ps[c]) / n) < 0.02, c
     assert abs(rec["ave_all_frame_bpp"] - bits / (n * h * w)) <= 0.005 * bits / (n * h * w)
+
+
+@pytest.mark.gpu
+def test_entry_point_graphs_equal_eager(tmp_path):
+    """test_video.py --graphs 1 (P frames replayed from CUDA graphs) writes the same stream files
+    and the same results as the eager launches; 14 frames so that graphs are recorded and replayed."""
+    h, w, n = 64, 96, 14
+    frames = (synth.synth_frames(n, h, w, seed=7) * 255).round().to(torch.uint8)
+    pw = harness.PNGWriter(str(tmp_path / "data" / "seqA"), w, h)
+    for k in range(n):
+        pw.write_rgb(frames[k:k + 1].float() / 255)
+    _, cfg_path = _config(tmp_path, "png", h, w, n, 32)
+    ip, pp = _checkpoints(tmp_path)
+    recs = []
+    for g in ("0", "1"):
+        out = str(tmp_path / f"res{g}" / "out.json")
+        tv.main(["--i_frame_model_path", ip, "--p_frame_model_path", pp, "--rate_num", "1",
+                 "--i_frame_q_indexes", "30", "--test_config", cfg_path, "--cuda", "1",
+                 "--write_stream", "1", "--stream_path", str(tmp_path / f"bins{g}"),
+                 "--graphs", g, "--output_path", out])
+        recs.append(json.load(open(out))["SYN"]["seqA"]["000"])
+    for k in range(n):
+        a = open(tmp_path / "bins0" / "seqA" / "0" / f"{k}.bin", "rb").read()
+        b = open(tmp_path / "bins1" / "seqA" / "0" / f"{k}.bin", "rb").read()
+        assert a == b, f"frame {k}: stream differs under graphs"
+    for key in ("ave_all_frame_bpp", "ave_all_frame_psnr", "frame_psnr", "frame_bpp"):
+        if key in recs[0]:
+            assert recs[0][key] == recs[1][key], key
