@@ -134,6 +134,21 @@ class Net:
             self._dw[name] = r
         return r
 
+    def dwpw(self, p):
+        """DepthConv's depthwise 3x3 followed by its 1x1 `conv2` (no activation in between,
+        layers.py:150-163) as ONE dense 3x3 convolution: W[co, ci, ky, kx] = conv2[co, ci] *
+        depth_conv[ci, ky, kx], bias = conv2.bias + conv2 @ depth_conv.bias.  Zero padding of the
+        depthwise input is the dense convolution's own padding, so the two are the same function
+        (up to rounding); nine times the 1x1's MMAs, but no depthwise kernel and no intermediate
+        tensor."""
+        name = p + ".__dwpw"
+        if name + ".weight" not in self.sd:
+            dw = self.sd[p + ".depth_conv.weight"]              # [C, 1, 3, 3]
+            w2 = self.sd[p + ".conv2.weight"][:, :, 0, 0]       # [Co, C]
+            self.sd[name + ".weight"] = (w2[:, :, None, None] * dw[:, 0][None]).contiguous()
+            self.sd[name + ".bias"] = self.sd[p + ".conv2.bias"] + w2 @ self.sd[p + ".depth_conv.bias"]
+        return self.cw(name)
+
     def vec(self, name):
         r = self._misc.get(name)
         if r is None:
@@ -173,6 +188,16 @@ def res_block(net, p, x, slope=0.01, end_with_relu=False, out=None, res2=None, s
                     res2=res2, scale=scale, out=out, f16_out=f16_out)
 
 
+import os as _os
+# "cmin,cmax,pxmin": DepthConv blocks whose depthwise + 1x1 pair runs as one dense 3x3 (Net.dwpw)
+_DWPW = [int(v) for v in _os.environ.get("DCVC_DWPW", "64,256,100000").split(",")]
+
+
+def _fuse_dwpw(t):
+    return (ops.CONV_MODE == 1 and t.f16 and _DWPW[0] <= t.c <= _DWPW[1]
+            and t.h * t.w >= _DWPW[2])
+
+
 def depth_conv(net, p, x, out=None, f16_out=False):
     """DepthConv (layers.py:135-163), stride 1.  Everything only the next kernel of the block
     reads (the adaptor's identity, conv1 and depth_conv outputs) is binary16 in tensor-core mode."""
@@ -180,6 +205,8 @@ def depth_conv(net, p, x, out=None, f16_out=False):
     if net.has(p + ".adaptor"):
         identity = ops.conv(x, net.cw(p + ".adaptor"), f16_out=True)
     t = ops.conv(x, net.cw(p + ".conv1.0"), act=0.01, f16_out=True)
+    if _fuse_dwpw(t):
+        return ops.conv(t, net.dwpw(p), res=identity, out=out, f16_out=f16_out)
     w, b = net.dw(p + ".depth_conv")
     t = ops.dwconv3x3(t, w, b)
     return ops.conv(t, net.cw(p + ".conv2"), res=identity, out=out, f16_out=f16_out)
