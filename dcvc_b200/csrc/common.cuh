@@ -61,7 +61,7 @@ static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 // several GPUs, reference test_video.py:282-294 maps workers to cuda:i).  Thread-safe.
 constexpr int DCVC_MAX_DEVICES = 64;
 enum { DCVC_ONCE_CONV_TC = 0, DCVC_ONCE_FFN_TC = 1, DCVC_ONCE_RANS_DEC = 2, DCVC_ONCE_FFN128 = 3,
-       DCVC_ONCE_DCB = 4, DCVC_ONCE_RANS_DEC2 = 5 };
+       DCVC_ONCE_DCB = 4, DCVC_ONCE_RANS_DEC2 = 5, DCVC_ONCE_FFN2_TC = 6 };
 extern std::atomic<uint32_t> g_dcvc_once[DCVC_MAX_DEVICES];
 extern int g_dcvc_num_sms[DCVC_MAX_DEVICES];
 extern std::mutex g_dcvc_once_mu;

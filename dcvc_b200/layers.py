@@ -111,14 +111,19 @@ class Net:
 
     def ffn(self, p):
         """Packed weights of the fused ConvFFN (dcvc_ffn) of block prefix p: W1 binary16
-        [4C][64] (K zero-padded), W2 binary16 [4C/64][C][64], fp32 biases."""
+        [ceil(C/64)][4C][64] (K in atoms of 64, zero-padded), W2 binary16 [4C/64][C][64], fp32
+        biases."""
         r = self._misc.get(("ffn", p))
         if r is None:
             w1 = self.sd[p + ".conv.0.weight"]          # [4C, C, 1, 1]
             w2 = self.sd[p + ".conv.2.weight"]          # [C, 4C, 1, 1]
             n1, c = w1.shape[0], w1.shape[1]
-            p1 = torch.zeros((n1, 64), dtype=torch.float16, device=w1.device)
-            p1[:, :c] = w1.reshape(n1, c).to(torch.float16)
+            ka = (c + 63) // 64                          # K atoms of 64 (C = 128: two)
+            p1 = torch.zeros((ka, n1, 64), dtype=torch.float16, device=w1.device)
+            w1f = w1.reshape(n1, c).to(torch.float16)
+            for a in range(ka):
+                k = min(64, c - 64 * a)
+                p1[a, :, :k] = w1f[:, 64 * a:64 * a + k]
             p2 = w2.reshape(c, n1 // 64, 64).permute(1, 0, 2).to(torch.float16).contiguous()
             r = (p1.contiguous(), self.sd[p + ".conv.0.bias"].contiguous(), p2,
                  self.sd[p + ".conv.2.bias"].contiguous())

@@ -116,9 +116,10 @@ int dcvc_conv_tc_geometry16(int cout_w, int cin, int *n_pad, int *cin_pad, int *
  * DepthConvBlock.forward :199-209):
  *     out = (in + lrelu(W2 . lrelu(W1 . in + b1, slope1) + b2, slope2)) * scale
  * as one two-GEMM tcgen05 kernel; the 4C-wide hidden activation stays in shared memory.
- * in: binary16 view, c in {32, 48, 64}, >= 512 pixels (dcvc_ffn_eligible); out: fp32 or binary16
- * view (out_f16) of the same shape.  w1: binary16 [4c][64] (row n = output channel of the 1x1
- * up-projection conv.0, K zero-padded to 64); w2: binary16 [4c/64][c][64] (chunk j holds input
+ * in: binary16 view, c in {32, 48, 64, 128}, >= 512 pixels (dcvc_ffn_eligible); out: fp32 or
+ * binary16 view (out_f16) of the same shape.  w1: binary16 [ceil(c/64)][4c][64] (atom a holds input
+ * channels 64a..64a+63 zero-padded to 64, row n = output channel of the 1x1 up-projection
+ * conv.0; one atom for c <= 64); w2: binary16 [4c/64][c][64] (chunk j holds input
  * channels 64j..64j+63 of the down-projection conv.2, row n = its output channel); b1 [4c],
  * b2 [c], scale [c] or NULL: fp32.  Replaces the two dcvc_conv2d calls of the unfused block. */
 typedef struct dcvc_ffn_desc {

@@ -26,7 +26,7 @@ def timeit(fn, iters=10):
     return ms / iters
 
 
-for c, h, w in ((48, 1088, 1920), (32, 1088, 1920), (64, 544, 960)):
+for c, h, w in ((48, 1088, 1920), (32, 1088, 1920), (64, 544, 960), (128, 272, 480)):
     g = torch.Generator().manual_seed(0)
     sd = {"f.conv.0.weight": torch.randn(4 * c, c, 1, 1, generator=g) * 0.05,
           "f.conv.0.bias": torch.randn(4 * c, generator=g),
@@ -43,6 +43,13 @@ for c, h, w in ((48, 1088, 1920), (32, 1088, 1920), (64, 544, 960)):
             u = ops.conv(x, net.cw("f.conv.0"), act=0.1, f16_out=True)
             ops.conv(u, net.cw("f.conv.2"), act=0.1, res=x, out=out)
         t_u = timeit(unfused)
+        ref = out.buf.float().clone()
+        out.buf.zero_()
+        ops.ffn(x, w1, b1, w2, b2, out=out)
+        torch.cuda.synchronize()
+        d = (out.buf.float() - ref).abs()
+        print(f"   fused vs unfused: max |d| {float(d.max()):.3e}  mean {float(d.mean()):.3e}  "
+              f"(ref rms {float(ref.pow(2).mean().sqrt()):.3f})")
         nbytes = h * w * c * (2 + (2 if f16_out else 4))
         print(f"ffn {c}->{4*c}->{c} @{h}x{w} out {'f16' if f16_out else 'f32'}: fused {t_f:.3f} ms "
               f"({nbytes / t_f / 1e6:.0f} GB/s algorithmic), unfused {t_u:.3f} ms")

@@ -176,10 +176,11 @@ def test_conv_at_1080p_shape(case):
 
 
 def test_fused_ffn_at_1080p_shapes():
-    """dcvc_ffn (two tcgen05 GEMMs, hidden activation on chip) at the P frame's three shapes
-    against the two-convolution definition on the same binary16 operands; the hidden activation is
+    """dcvc_ffn (two tcgen05 GEMMs, hidden activation on chip) at the P frame's shapes (C = 128:
+    the chunked kernel with streamed weights; 67x119 = a ragged last tile) against the two-convolution definition on the same binary16 operands; the hidden activation is
     rounded to binary16 between the GEMMs, which the reference mirrors."""
-    for c, h, w, out16 in ((48, 1088, 1920, True), (32, 1088, 1920, False), (64, 544, 960, True)):
+    for c, h, w, out16 in ((48, 1088, 1920, True), (32, 1088, 1920, False), (64, 544, 960, True),
+                           (128, 272, 480, True), (128, 272, 480, False), (128, 67, 119, False)):
         g = torch.Generator().manual_seed(c)
         sd = {"b.conv.0.weight": (torch.rand(4 * c, c, 1, 1, generator=g) * 2 - 1) / c ** 0.5,
               "b.conv.0.bias": torch.rand(4 * c, generator=g) * 0.2 - 0.1,
