@@ -24,58 +24,71 @@ from . import stream_helper as sh
 
 
 # ------------------------------------------------------------------------------ blocks
-def residual_block(net, p, x, out=None):
+def residual_block(net, p, x, out=None, f16_out=False):
     """ResidualBlock (layers.py:103-128): conv -> lrelu(.01) -> conv -> lrelu(.01) -> + x"""
     t = ops.conv(x, net.cw(p + ".conv1"), act=0.01, f16_out=True)
-    return ops.conv(t, net.cw(p + ".conv2"), act=0.01, res=x, out=out)
+    return ops.conv(t, net.cw(p + ".conv2"), act=0.01, res=x, out=out, f16_out=f16_out)
 
 
-def conv_block_residual(net, p, x, out=None):
+def conv_block_residual(net, p, x, out=None, f16_out=False):
     """ConvBlockResidual (video_net.py:166-181): up_dim(x) + SE(conv(lrelu(conv(x))))"""
     t = ops.conv(x, net.cw(p + ".conv.0"), act=0.01, f16_out=True)
     t = ops.conv(t, net.cw(p + ".conv.2"))
     gate = ops.se_gate(t, net.sd[p + ".conv.3.fc.0.weight"], net.sd[p + ".conv.3.fc.2.weight"])
     ops.channel_scale(t, gate, out=t)
-    return ops.conv(x, net.cw(p + ".up_dim"), res=t, out=out)
+    return ops.conv(x, net.cw(p + ".up_dim"), res=t, out=out, f16_out=f16_out)
 
 
-def hem_unet(net, p, x, out=None):
-    """UNet (video_net.py:184-223): the two skip concatenations are shared buffers."""
+def hem_unet(net, p, x, out=None, f16_out=False):
+    """UNet (video_net.py:184-223): the two skip concatenations are shared buffers, binary16 in
+    tensor-core mode like every tensor here that only convolutions and the max pool read (the SE
+    branch stays fp32: its global mean and gate are computed on the fp32 convolution result)."""
     dev = x.device
-    cat2 = Act.new(x.h, x.w, 64, dev)                 # [x1 32 | up2 32]
-    cat3 = Act.new(x.h // 2, x.w // 2, 128, dev)      # [x2 64 | up3 64]
+    f16 = ops.f16_ok(x.h // 4, x.w // 4, 64)
+    cat2 = Act.new(x.h, x.w, 64, dev, f16=f16)                 # [x1 32 | up2 32]
+    cat3 = Act.new(x.h // 2, x.w // 2, 128, dev, f16=f16)      # [x2 64 | up3 64]
     x1 = conv_block_residual(net, p + ".conv1", x, out=cat2.slice(0, 32))
     x2 = conv_block_residual(net, p + ".conv2", ops.max_pool2(x1), out=cat3.slice(0, 64))
-    x3 = conv_block_residual(net, p + ".conv3", ops.max_pool2(x2))
+    x3 = conv_block_residual(net, p + ".conv3", ops.max_pool2(x2), f16_out=True)
     for i in range(4):
-        x3 = layers.res_block(net, f"{p}.context_refine.{i}", x3, slope=0.0)
+        x3 = layers.res_block(net, f"{p}.context_refine.{i}", x3, slope=0.0, f16_out=True)
     layers.subpel(net, p + ".up3", x3, out=cat3.slice(64, 64))
-    d3 = conv_block_residual(net, p + ".up_conv3", cat3)
+    d3 = conv_block_residual(net, p + ".up_conv3", cat3, f16_out=True)
     layers.subpel(net, p + ".up2", d3, out=cat2.slice(32, 32))
-    return conv_block_residual(net, p + ".up_conv2", cat2, out=out)
+    return conv_block_residual(net, p + ".up_conv2", cat2, out=out, f16_out=f16_out)
 
 
 def analysis(net, p, x):
     """get_enc_dec_models encoder (video_net.py:226-235)"""
-    t = layers.rbws(net, p + ".0", x)
-    t = residual_block(net, p + ".1", t)
-    t = layers.rbws(net, p + ".2", t)
-    t = residual_block(net, p + ".3", t)
-    t = layers.rbws(net, p + ".4", t)
-    t = residual_block(net, p + ".5", t)
+    # the chain's tensors are read by convolutions only: binary16 in tensor-core mode, as long as
+    # the stride-2 reader's OUTPUT is tensor-core sized too (a binary16 view on the FMA path is an
+    # error, never a reinterpretation)
+    def ok(div):
+        return ops.f16_ok(x.h // div, x.w // div, 8)
+    t = layers.rbws(net, p + ".0", x, f16_out=True)
+    t = residual_block(net, p + ".1", t, f16_out=ok(4))
+    t = layers.rbws(net, p + ".2", t, f16_out=True)
+    t = residual_block(net, p + ".3", t, f16_out=ok(8))
+    t = layers.rbws(net, p + ".4", t, f16_out=True)
+    t = residual_block(net, p + ".5", t, f16_out=ok(16))
     return ops.conv(t, net.cw(p + ".6"), stride=2)
 
 
-def synthesis(net, p, x):
+def synthesis(net, p, x, f16_out=False):
     """get_enc_dec_models decoder (video_net.py:237-247)"""
-    t = residual_block(net, p + ".0", x)
-    t = layers.rbu(net, p + ".1", t)
-    t = residual_block(net, p + ".2", t)
-    t = layers.rbu(net, p + ".3", t)
-    t = residual_block(net, p + ".4", t)
-    t = layers.rbu(net, p + ".5", t)
-    t = residual_block(net, p + ".6", t)
-    return layers.subpel(net, p + ".7", t)
+    t = residual_block(net, p + ".0", x, f16_out=True)
+    t = layers.rbu(net, p + ".1", t, f16_out=True)
+    t = residual_block(net, p + ".2", t, f16_out=True)
+    t = layers.rbu(net, p + ".3", t, f16_out=True)
+    t = residual_block(net, p + ".4", t, f16_out=True)
+    t = layers.rbu(net, p + ".5", t, f16_out=True)
+    t = residual_block(net, p + ".6", t, f16_out=True)
+    cout = net.sd[p + ".7.0.weight"].shape[0]
+    if cout % 16:      # 8 filters (2-channel flow): zero filters up to 16 -> planar packing, which
+        # is what a binary16 input needs (as the DCVC-DC mv decoder does)
+        cw = net.cw(p + ".7.0", shuffle=True, cout_pad=16)
+        return ops.conv(t, cw, shuffle=True).slice(0, cout // 4)
+    return layers.subpel(net, p + ".7", t, f16_out=f16_out)
 
 
 def three_convs(net, p, x, out=None):
@@ -180,7 +193,7 @@ class IntraNoAR(HemCompressionModel):
 
     def _synthesis(self, y_hat, clamp):
         net = self.net
-        t = hem_unet(net, "refine.0", synthesis(net, "dec", y_hat))
+        t = hem_unet(net, "refine.0", synthesis(net, "dec", y_hat, f16_out=True), f16_out=True)
         return ops.conv(t, net.cw("refine.1", cout_pad=4), clamp01=clamp).slice(0, 3)
 
     def forward(self, x, q_scale=None):
@@ -314,71 +327,78 @@ class DMC(HemCompressionModel):
         H, W, dev = mv.h, mv.w, mv.device
         mv2 = ops.resize_bilinear(mv, H // 2, W // 2, mul=0.5)
         mv3 = ops.resize_bilinear(mv2, H // 4, W // 4, mul=0.5)
+        # binary16 for everything only tensor-core convolutions, the warps and copies read (the
+        # same rule as dcvc_b200/video_model.py: feature levels, fusion concatenations, contexts)
+        f16 = ops.f16_ok(H // 8, W // 8, 64)
         if dpb["ref_feature"] is None:
-            feat = ops.conv(Act.wrap(dpb["ref_frame"]), net.cw("feature_adaptor_I"))
+            feat = ops.conv(Act.wrap(dpb["ref_frame"]), net.cw("feature_adaptor_I"), f16_out=True)
         else:
-            feat = ops.conv(Act.wrap(dpb["ref_feature"]), net.cw("feature_adaptor_P"))
+            feat = ops.conv(Act.wrap(dpb["ref_feature"]), net.cw("feature_adaptor_P"), f16_out=True)
         fe = "feature_extractor"
-        l1 = layers.res_block(net, fe + ".res_block1", ops.conv(feat, net.cw(fe + ".conv1")))
-        l2 = layers.res_block(net, fe + ".res_block2", ops.conv(l1, net.cw(fe + ".conv2"), stride=2))
-        l3 = layers.res_block(net, fe + ".res_block3", ops.conv(l2, net.cw(fe + ".conv3"), stride=2))
-        cat1 = Act.new(H, W, 128, dev)                  # [context2_up | context1]
-        cat2 = Act.new(H // 2, W // 2, 128, dev)        # [context3_up | context2]
+        t, ta = layers.conv_for_res_block(net, fe + ".conv1", feat, 0.01, f16_out=True)
+        l1 = layers.res_block(net, fe + ".res_block1", t, f16_out=f16, x_act=ta)
+        t, ta = layers.conv_for_res_block(net, fe + ".conv2", l1, 0.01, stride=2, f16_out=True)
+        l2 = layers.res_block(net, fe + ".res_block2", t, f16_out=f16, x_act=ta)
+        t, ta = layers.conv_for_res_block(net, fe + ".conv3", l2, 0.01, stride=2, f16_out=True)
+        l3 = layers.res_block(net, fe + ".res_block3", t, f16_out=f16, x_act=ta)
+        cat1 = Act.new(H, W, 128, dev, f16=f16)                  # [context2_up | context1]
+        cat2 = Act.new(H // 2, W // 2, 128, dev, f16=f16)        # [context3_up | context2]
         c1 = ops.flow_warp(l1, mv, out=cat1.slice(64, 64))
         c2 = ops.flow_warp(l2, mv2, out=cat2.slice(64, 64))
-        c3 = ops.flow_warp(l3, mv3)
+        c3 = ops.flow_warp(l3, mv3, out=Act.new(H // 4, W // 4, 64, dev, f16=f16))
         cf = "context_fusion_net"
-        t = layers.subpel(net, cf + ".conv3_up", c3)
+        t = layers.subpel(net, cf + ".conv3_up", c3, f16_out=True)
         layers.res_block(net, cf + ".res_block3_up", t, out=cat2.slice(0, 64))
-        t = ops.conv(c3, net.cw(cf + ".conv3_out"))
-        ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3)
-        t = layers.subpel(net, cf + ".conv2_up", cat2)
+        t, ta = layers.conv_for_res_block(net, cf + ".conv3_out", c3, 0.01, f16_out=True)
+        ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3, f16_out=f16, x_act=ta)
+        t = layers.subpel(net, cf + ".conv2_up", cat2, f16_out=True)
         layers.res_block(net, cf + ".res_block2_up", t, out=cat1.slice(0, 64))
-        t = ops.conv(cat2, net.cw(cf + ".conv2_out"))
-        ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2)
-        t = ops.conv(cat1, net.cw(cf + ".conv1_out"))
-        ctx1 = layers.res_block(net, cf + ".res_block1_out", t, res2=c1)
+        t, ta = layers.conv_for_res_block(net, cf + ".conv2_out", cat2, 0.01, f16_out=True)
+        ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2, f16_out=f16, x_act=ta)
+        t, ta = layers.conv_for_res_block(net, cf + ".conv1_out", cat1, 0.01, f16_out=True)
+        ctx1 = layers.res_block(net, cf + ".res_block1_out", t, res2=c1, f16_out=f16, x_act=ta)
         return ctx1, ctx2, ctx3
 
     def _contextual_encoder(self, x, ctx1, ctx2, ctx3):
         """ContextualEncoder (:71-91); conv1's input is laid out [ctx1 64 | x 3]"""
         net, dev = self.net, x.device
-        e1 = Act.new(x.h, x.w, 67, dev)
+        e1 = Act.new(x.h, x.w, 67, dev, f16=ctx1.f16)
         ops.copy(ctx1, out=e1.slice(0, 64))
         ops.copy(x, out=e1.slice(64, 3))
         perm = tuple(range(3, 67)) + (0, 1, 2)
-        e2 = Act.new(x.h // 2, x.w // 2, 128, dev)
+        e2 = Act.new(x.h // 2, x.w // 2, 128, dev, f16=ctx2.f16)
         ops.conv(e1, net.cw("contextual_encoder.conv1", cin_perm=perm), stride=2, out=e2.slice(0, 64))
         ops.copy(ctx2, out=e2.slice(64, 64))
-        t = layers.res_block(net, "contextual_encoder.res1", e2, 0.1, True)
-        e3 = Act.new(x.h // 4, x.w // 4, 128, dev)
+        t = layers.res_block(net, "contextual_encoder.res1", e2, 0.1, True, f16_out=ctx2.f16)
+        e3 = Act.new(x.h // 4, x.w // 4, 128, dev, f16=ctx3.f16)
         ops.conv(t, net.cw("contextual_encoder.conv2"), stride=2, out=e3.slice(0, 64))
         ops.copy(ctx3, out=e3.slice(64, 64))
-        t = layers.res_block(net, "contextual_encoder.res2", e3, 0.1, True)
-        t = ops.conv(t, net.cw("contextual_encoder.conv3"), stride=2)
+        t = layers.res_block(net, "contextual_encoder.res2", e3, 0.1, True, f16_out=ctx3.f16)
+        t = ops.conv(t, net.cw("contextual_encoder.conv3"), stride=2,
+                     f16_out=ops.f16_ok(x.h // 16, x.w // 16, 8))
         return ops.conv(t, net.cw("contextual_encoder.conv4"), stride=2)
 
     def _recon(self, y_hat, ctx1, ctx2, ctx3):
         """ContextualDecoder + ReconGeneration (:94-128, :301-302)"""
         net, dev = self.net, y_hat.device
         cd = "contextual_decoder"
-        t = layers.subpel(net, cd + ".up1", y_hat)
-        d3 = Act.new(ctx3.h, ctx3.w, 128, dev)
+        t = layers.subpel(net, cd + ".up1", y_hat, f16_out=True)
+        d3 = Act.new(ctx3.h, ctx3.w, 128, dev, f16=ctx3.f16)
         layers.subpel(net, cd + ".up2", t, out=d3.slice(0, 64))
         ops.copy(ctx3, out=d3.slice(64, 64))
-        t = layers.res_block(net, cd + ".res1", d3, 0.1, True)
-        d2 = Act.new(ctx2.h, ctx2.w, 128, dev)
+        t = layers.res_block(net, cd + ".res1", d3, 0.1, True, f16_out=True)
+        d2 = Act.new(ctx2.h, ctx2.w, 128, dev, f16=ctx2.f16)
         layers.subpel(net, cd + ".up3", t, out=d2.slice(0, 64))
         ops.copy(ctx2, out=d2.slice(64, 64))
-        t = layers.res_block(net, cd + ".res2", d2, 0.1, True)
+        t = layers.res_block(net, cd + ".res2", d2, 0.1, True, f16_out=True)
         # recon_generation_net(recon_image_feature, context1) (:301): first_conv reads
         # [feature 32 | context1 64]
-        r = Act.new(ctx1.h, ctx1.w, 96, dev)
+        r = Act.new(ctx1.h, ctx1.w, 96, dev, f16=ctx1.f16)
         layers.subpel(net, cd + ".up4", t, out=r.slice(0, 32))
         ops.copy(ctx1, out=r.slice(32, 64))
         rg = "recon_generation_net"
-        t = ops.conv(r, net.cw(rg + ".first_conv"))
-        t = hem_unet(net, rg + ".unet_1", t)
+        t = ops.conv(r, net.cw(rg + ".first_conv"), f16_out=True)
+        t = hem_unet(net, rg + ".unet_1", t, f16_out=True)
         feature = hem_unet(net, rg + ".unet_2", t)
         x_hat4 = ops.conv(feature, net.cw(rg + ".recon_conv", cout_pad=4), clamp01=False)
         return x_hat4.slice(0, 3), feature

@@ -239,18 +239,18 @@ def dcb2(net, p, x, out=None, scale=None, f16_out=False):
                     f16_out=f16_out)
 
 
-def rbws(net, p, x, out=None):
+def rbws(net, p, x, out=None, f16_out=False):
     """ResidualBlockWithStride (layers.py:42-73), stride 2."""
     t = ops.conv(x, net.cw(p + ".conv1"), stride=2, act=0.01, f16_out=True)
     idn = ops.conv(x, net.cw(p + ".downsample"), stride=2, pad=0, f16_out=True)
-    return ops.conv(t, net.cw(p + ".conv2"), act=0.1, res=idn, out=out)
+    return ops.conv(t, net.cw(p + ".conv2"), act=0.1, res=idn, out=out, f16_out=f16_out)
 
 
-def rbu(net, p, x, out=None, scale=None):
+def rbu(net, p, x, out=None, scale=None, f16_out=False):
     """ResidualBlockUpsample (layers.py:76-101)."""
-    up = subpel(net, p + ".upsample", x)
+    up = subpel(net, p + ".upsample", x, f16_out=f16_out)
     t = subpel(net, p + ".subpel_conv", x, act=0.01, f16_out=True)
-    return ops.conv(t, net.cw(p + ".conv"), act=0.1, res=up, scale=scale, out=out)
+    return ops.conv(t, net.cw(p + ".conv"), act=0.1, res=up, scale=scale, out=out, f16_out=f16_out)
 
 
 def unet(net, p, x, block, out=None, f16_out=False):

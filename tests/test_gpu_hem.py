@@ -196,3 +196,28 @@ def test_hem_interleaved_coder_same_recon():
     b = _run_gop(*_models(0, 1.0, "interleaved", 2)[:2], frames, h, w, 1.0, 1.0, 1.0)
     for k in range(2):
         assert torch.equal(a[k][1], b[k][1])
+
+
+def test_hem_1080p_modes_agree_and_enc_equals_dec(conv_mode):
+    """The size the hem_sweep workload runs (1920x1080 zero-padded to 1088): there the tensor-core
+    mode stores most conv-to-conv activations as binary16 (the golden GOPs are too small for
+    that).  I + 2 P, interleaved coder: encoder reconstruction == decoder reconstruction bit for
+    bit in both modes (asserted inside _run_gop), and mode 1 against mode 0 (fp32 FMA, held
+    byte-identical to the unmodified reference by the golden tests): reconstruction RMS and
+    stream size."""
+    import torch.nn.functional as F
+    h, w, n = 1088, 1920, 3
+    frames = F.pad(synth.synth_frames(n, 1080, w, seed=3), (0, 0, 0, 8))
+    res = {}
+    for mode in (0, 1):
+        conv_mode(mode)
+        i_net, p_net, _, _ = _models(0, 1.0, coder_mode="interleaved", parts=8)
+        res[mode] = _run_gop(i_net, p_net, frames, h, w, 1.0, 1.0, 1.0)
+        del i_net, p_net
+        torch.cuda.empty_cache()
+    for k in range(n):
+        rms = float((res[1][k][1] - res[0][k][1]).pow(2).mean().sqrt())
+        b0, b1 = len(res[0][k][0]), len(res[1][k][0])
+        print(f"hem 1080p frame {k}: x_hat RMS mode1 vs mode0 {rms:.3e}, bytes {b1} vs {b0}")
+        assert rms < 2e-3, (k, rms)                       # 0.02 dB at 38 dB
+        assert abs(b1 - b0) <= 0.005 * b0, (k, b0, b1)
