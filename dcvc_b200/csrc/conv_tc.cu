@@ -45,6 +45,9 @@ struct TcArgs {
   int tma_epi;    // 1: TMA-store epilogue (stage_off region = 8 KB per warp, vec_off = bias/scale)
   uint32_t vec_off;
   int epi_warps;  // 4, 8 or 16 epilogue warps (blockDim = 64 + 32 * epi_warps)
+  int epi_sets;   // TMA-store epilogue: 2 = two sets of epi_warps / 2 warps, set s drains the tiles
+                  // whose accumulator is s (every other tile of the CTA); 1 = all warps on every tile
+  uint32_t epi_buf;  // bytes of one epilogue tile buffer (two per warp): 4096, or 2048 for binary16 rows
   int kcb;        // bytes of one K chunk row (128/64/32) = kc * element size
   int kk_last;    // MMAs of a tap's last chunk: its zero-padded tail is not multiplied at all
   int f16_in;     // A/B operands are binary16: kind::f16, K = 16 per instruction
@@ -515,6 +518,13 @@ __device__ __forceinline__ uint32_t desc_hi32(uint32_t sbo_bytes, uint32_t layou
 }
 __device__ __forceinline__ uint32_t desc_lo32(uint32_t addr) { return (addr >> 4) | 0x10000u; }
 
+#ifdef DCVC_TC_TIMELINE
+__device__ unsigned long long g_tl[2][4096][8];
+#define TL(role, idx, k) do { if (blockIdx.x == 0 && (idx) < 4096) g_tl[role][idx][k] = clock64(); } while (0)
+#else
+#define TL(role, idx, k) do {} while (0)
+#endif
+
 struct MmaCtx {
   uint32_t base, bars, tmem, idesc, a_hi, b_hi;
   int stages;
@@ -536,9 +546,13 @@ __device__ __forceinline__ void mma_bres(const TcArgs &a, const MmaCtx &c) {
   uint32_t as = 0, aph = 0, pha = 0, a4 = a4_0;
   int sa = 0;
   mbar_wait(c.full_bar(sa_n), 0u);               // the weights, once
-  for (int tile = blockIdx.x; tile < total; tile += step) {
+  int tli = 0;
+  for (int tile = blockIdx.x; tile < total; tile += step, ++tli) {
+    if (c.issue) TL(0, tli, 0);
     mbar_wait(c.tempty_bar(as), aph ^ 1u);
+    if (c.issue) TL(0, tli, 1);
     mbar_wait(c.full_bar(sa), pha);
+    if (c.issue) TL(0, tli, 2);
     tc_fence_after();
     const uint32_t tacc = c.tmem + as * acc_stride;
     if (c.issue) {
@@ -554,6 +568,7 @@ __device__ __forceinline__ void mma_bres(const TcArgs &a, const MmaCtx &c) {
       }
       umma_commit(c.empty_bar(sa));
       umma_commit(c.tfull_bar(as));
+      TL(0, tli, 3);
     }
     a4 += ua4;
     if (++sa == sa_n) { sa = 0; pha ^= 1u; a4 = a4_0; }
@@ -777,7 +792,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), a.epi_warps);
+      mbar_init(tempty_bar(s), a.epi_warps / a.epi_sets);
     }
     if (a.tma_epi)
       for (int s = 0; s < 2 * a.epi_warps; ++s) mbar_init(res_bar(s), 1);
@@ -935,9 +950,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // residual tile arrives the same way (TMA load into the very buffer the result will leave
     // from), so no per-element address arithmetic or global LD/ST is issued by the warp.
     const bool leader = elect_one();
-    const int we = warp - 2, q = warp & 3, part = we >> 2, parts = a.epi_warps >> 2;
-    const uint32_t buf0 = base + a.stage_off + (uint32_t)we * 8192u;
-    uint8_t *const buf0_g = smem_raw + (base - raw) + a.stage_off + (size_t)we * 8192u;
+    // two sets (epi_sets = 2): the epilogue of a narrow tile is a chain of fixed costs (barrier
+    // waits, tile coordinates, fence, elected store: ~2000 cycles per tile against ~1450 of MMA
+    // issue, scripts/tc_timeline.py), so set s takes the tiles of accumulator s only and each set
+    // has two MMA periods per tile
+    const int we = warp - 2, q = warp & 3, per_set = a.epi_warps / a.epi_sets, eset = we / per_set;
+    const int part = (we - eset * per_set) >> 2, parts = per_set >> 2;
+    const int estep = a.epi_sets * (int)gridDim.x;
+    const uint32_t ebuf = a.epi_buf;
+    const uint32_t buf0 = base + a.stage_off + (uint32_t)we * 2u * ebuf;
+    uint8_t *const buf0_g = smem_raw + (base - raw) + a.stage_off + (size_t)we * 2u * ebuf;
     const float4 *const vec4 = reinterpret_cast<const float4 *>(smem_raw + (base - raw) + a.vec_off);
     const int n_all4 = (a.tiles_n * ((a.n_tile + 31) & ~31)) >> 2;
     const int nchunks = (a.n_tile + 31) >> 5;
@@ -951,8 +973,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     const bool mixed = has_res && (a.f16_res != a.f16_out);   // residual / result rows differ in pitch
     const uint32_t row_off = (uint32_t)lane * 128u, sw = (uint32_t)(lane & 7);
     const uint32_t row16 = (uint32_t)lane * 64u, sw4 = (uint32_t)(lane >> 1) & 3u;
-    uint32_t rph0 = 0, rph1 = 0, b = 0, lt = 0;
-    int tile = blockIdx.x, ci = part;
+    uint32_t rph0 = 0, rph1 = 0, b = 0, lt = (uint32_t)eset;
+    int tile = blockIdx.x + eset * (int)gridDim.x, ci = part;
     if (has_res && leader && tile < a.total_tiles) {
       int mt, nt, ty, tx;
       tile_coords(a, tile, mt, nt, ty, tx);
@@ -986,10 +1008,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           }
         }
       }
+      if (we == 0 && lane == 0) TL(1, (int)lt, 0);
       if (ci == part) {                                   // first chunk of this tile for the warp
         mbar_wait_warp(tfull_bar(as), aph, lane);
         tc_fence_after();
       }
+      const int tl_i = (int)lt;
+      if (we == 0 && lane == 0) TL(1, tl_i, 1);
       const uint32_t trow = tmem_base + as * a.acc_stride + ((uint32_t)(q * 32) << 16);
       float v[32];
       if (!(a.debug & 16)) {
@@ -998,15 +1023,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       }
       // next chunk of this warp (possibly in its next tile)
       int ntile = tile, nci = ci + parts;
-      if (nci >= nchunks) { nci = part; ntile += gridDim.x; }
+      if (nci >= nchunks) { nci = part; ntile += estep; }
       if (nci == part) {                                  // accumulator fully read: hand it back
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty_bar(as));
-        ++lt;
+        lt += (uint32_t)a.epi_sets;
       }
-      const uint32_t buf = buf0 + b * 4096u;
-      uint8_t *const buf_g = buf0_g + b * 4096u;
+      const uint32_t buf = buf0 + b * ebuf;
+      uint8_t *const buf_g = buf0_g + b * ebuf;
+      if (we == 0 && lane == 0) TL(1, tl_i, 2);
       if (!(a.debug & 4)) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -1017,6 +1043,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = lrelu01(v[j], a.out_slope);
         }
+        if (we == 0 && lane == 0) TL(1, tl_i, 4);
         if (direct1) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -1108,9 +1135,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                   make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           }
         };
+        if (we == 0 && lane == 0) TL(1, tl_i, 5);
         park(buf_g);
         fence_async_smem();
         __syncwarp();
+        if (we == 0 && lane == 0) TL(1, tl_i, 6);
         if (leader) {
           if (a.shuf_tma) {
             const int c_sp = a.cout_w >> 2, sp = c0 / c_sp;
@@ -1129,11 +1158,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = lrelu01(v[j], a.out2_slope);
-          park(buf0_g + (b ^ 1u) * 4096u);
+          park(buf0_g + (b ^ 1u) * ebuf);
           fence_async_smem();
           __syncwarp();
           if (leader) {
-            tma_store_3d(&map_o2, buf0 + (b ^ 1u) * 4096u, c0, x0, y0);
+            tma_store_3d(&map_o2, buf0 + (b ^ 1u) * ebuf, c0, x0, y0);
             bulk_commit();
           }
         }
@@ -1141,17 +1170,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         mbar_wait_warp(res_bar(2 * we + b), b ? rph1 : rph0, lane);
         if (b) rph1 ^= 1u; else rph0 ^= 1u;
       }
+      if (we == 0 && lane == 0) TL(1, tl_i, 7);
       if (leader) {
         bulk_wait_read<1>();                              // the store issued a chunk ago has left smem
         if (has_res && ntile < a.total_tiles) {
           int mt2, nt2, ty2, tx2;
           tile_coords(a, ntile, mt2, nt2, ty2, tx2);
           mbar_expect_tx(res_bar(2 * we + (b ^ 1u)), res_bytes);
-          tma_load_3d(buf0 + (b ^ 1u) * 4096u, &map_r, res_bar(2 * we + (b ^ 1u)),
+          tma_load_3d(buf0 + (b ^ 1u) * ebuf, &map_r, res_bar(2 * we + (b ^ 1u)),
                       nt2 * a.n_tile + nci * 32, tx2 * a.tw + bx, ty2 * a.th + by);
         }
       }
       __syncwarp();
+      if (we == 0 && lane == 0) TL(1, tl_i, 3);
       if (!a.out2_tma) b ^= 1u;
       tile = ntile;
       ci = nci;
@@ -1609,8 +1640,19 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
                         : (ctas == 1 ? 16 : 8);
   while (epi > 4 && epi / 4 > nchunks) epi >>= 1;
   while (ctas > 1 && ctas * (64 + 32 * epi) > 680) --ctas;
+  // two epilogue sets (see the kernel): a lone CTA whose tiles need at most 8 warps, binary16
+  // rows everywhere (2 KB tile buffers, so that 16 warps take the shared memory 8 took)
+  static const int sets_on = getenv("DCVC_TC_EPI_SETS") ? atoi(getenv("DCVC_TC_EPI_SETS")) : 2;
+  a.epi_sets = 1;
+  a.epi_buf = 4096u;
+  if (sets_on == 2 && a.tma_epi && ctas == 1 && epi <= 8 && a.f16_out && !a.shuf_tma &&
+      (!d->res1.data || a.f16_res) && a.total_tiles >= 4 * num_sms) {
+    a.epi_sets = 2;
+    a.epi_buf = 2048u;
+    epi *= 2;
+  }
   a.epi_warps = epi;
-  const uint32_t epi_bytes = (uint32_t)epi * (a.tma_epi ? 8192u : STG_WARP_FLOATS * 4u) +
+  const uint32_t epi_bytes = (uint32_t)epi * (a.tma_epi ? 2u * a.epi_buf : STG_WARP_FLOATS * 4u) +
                              (a.tma_epi ? 8u * (uint32_t)(tiles_n * ru(a.n_tile, 32)) : 0u);
   const uint32_t fixed = 1024u /*align*/ + 1024u /*barriers*/ + epi_bytes;
   while (ctas > 1 && (227u * 1024u / ctas) - 1024u < fixed + 2u * stage) --ctas;
@@ -1656,7 +1698,7 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
     a.stages = a.halo_sa + a.halo_sb;
     a.stage_off = (uint32_t)a.halo_sa * a.unit_a + (uint32_t)a.halo_sb * stage_b + 1024u;
   }
-  a.vec_off = a.stage_off + (uint32_t)epi * 8192u;
+  a.vec_off = a.stage_off + (uint32_t)epi * (a.tma_epi ? 2u * a.epi_buf : 8192u);
   const size_t smem = 1024 + (size_t)a.stage_off + epi_bytes;
   if (smem > 226 * 1024) return dcvc_fail(DCVC_ERR_UNSUPPORTED, "conv_tc: smem %zu too large", smem);
 
@@ -1703,3 +1745,9 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   DCVC_LAUNCHED();
   return DCVC_OK;
 }
+
+#ifdef DCVC_TC_TIMELINE
+extern "C" int dcvc_debug_timeline(unsigned long long *host, int bytes) {
+  return (int)cudaMemcpyFromSymbol(host, g_tl, bytes);
+}
+#endif
