@@ -1024,6 +1024,28 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       // next chunk of this warp (possibly in its next tile)
       int ntile = tile, nci = ci + parts;
       if (nci >= nchunks) { nci = part; ntile += estep; }
+      if ((direct1 || pre2) && ntile < a.total_tiles) {
+        // the NEXT chunk's residual rows towards L2 now: their direct loads are issued just
+        // before the next accumulator wait, too late to hide a DRAM round trip behind it
+        int mt2, nt2, ty2, tx2;
+        tile_coords(a, ntile, mt2, nt2, ty2, tx2);
+        const int px2 = tx2 * a.tw + bx + (lane & wb_mask), py2 = ty2 * a.th + by + (lane >> wb_shift);
+        const int cn = nt2 * a.n_tile + nci * 32;
+        if (px2 < a.wout && py2 < a.hout && cn < a.cout_w) {
+          if (direct1) {
+            const uint16_t *rp = reinterpret_cast<const uint16_t *>(a.res1.data) +
+                                 ((size_t)py2 * a.res1.w + px2) * a.res1.cstride + a.res1.coff + cn;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(rp));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + 16));
+          }
+          if (pre2) {
+            const uint16_t *rp = reinterpret_cast<const uint16_t *>(a.res2.data) +
+                                 ((size_t)py2 * a.res2.w + px2) * a.res2.cstride + a.res2.coff + cn;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(rp));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + 16));
+          }
+        }
+      }
       if (nci == part) {                                  // accumulator fully read: hand it back
         tc_fence_before();
         __syncwarp();
