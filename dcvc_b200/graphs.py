@@ -176,7 +176,9 @@ class GraphedDMC:
     # ------------------------------------------------------------------ encoder
     def compress(self, x, dpb, q_in_ckpt, q_index, frame_idx, defer=False, reconstruct=True):
         m, ec = self.m, self.m.entropy_coder
-        if dpb["ref_feature"] is None and not self.first_p:
+        # the first P frame of a GOP, and any frame whose per-stage taps are being collected (a
+        # replay has no host code between its kernels), run as plain launches
+        if (dpb["ref_feature"] is None and not self.first_p) or m.taps is not None:
             return m.compress(x, dpb, q_in_ckpt, q_index, frame_idx, defer=defer,
                               reconstruct=reconstruct)
         key = self._key("enc", tuple(x.shape) + tuple(x.stride()), dpb, q_in_ckpt, q_index,
@@ -264,7 +266,7 @@ class GraphedDMC:
     # ------------------------------------------------------------------ decoder
     def decompress(self, dpb, string, height, width, q_in_ckpt, q_index, frame_idx):
         m, ec = self.m, self.m.entropy_coder
-        if dpb["ref_feature"] is None and not self.first_p:
+        if (dpb["ref_feature"] is None and not self.first_p) or m.taps is not None:
             return m.decompress(dpb, string, height, width, q_in_ckpt, q_index, frame_idx)
         key = self._key("dec", (height, width), dpb, q_in_ckpt, q_index, frame_idx)
         ent = self.dec.get(key)
