@@ -105,8 +105,10 @@ SIGNATURES = {
     "dcvc_dual_step_indexes": (c_int, [ctypes.POINTER(Dual), c_void_p, c_void_p]),
     "dcvc_dual_step_dec": (c_int, [ctypes.POINTER(Dual), c_void_p, c_void_p]),
     "dcvc_channel_scale": (c_int, [VP, VP, c_void_p, c_int, c_void_p]),
+    "dcvc_channel_scale_f16": (c_int, [VP, VP, c_void_p, c_int, c_void_p]),
     "dcvc_se_ws_bytes": (c_size_t, [c_int, c_int, c_int]),
     "dcvc_se_gate": (c_int, [VP, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "dcvc_se_gate_f16": (c_int, [VP, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "dcvc_z_quant": (c_int, [VP, VP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dcvc_z_dequant": (c_int, [c_void_p, VP, c_void_p]),
     "dcvc_pmf_to_quantized_cdf": (c_int, [c_void_p, c_int, c_int, c_void_p]),

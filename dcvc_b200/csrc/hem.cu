@@ -15,6 +15,8 @@
 // (scales, means) from y_spatial_prior(cat(y_hat_0_0, y_hat_1_1, means, scales, quant_step)).
 // The coder's symbol tensor of a step is [1, C/2, h, w]: entry (jj, y, x) holds channel
 // jj + (coded half) * C/2, the one channel of the pair that the step codes at that position.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace {
@@ -221,26 +223,81 @@ __global__ void channel_scale4_kernel(dcvc_view src, dcvc_view dst, const float 
   *reinterpret_cast<float4 *>(dst.data + (size_t)p * dst.cstride + dst.coff + c) = r;
 }
 
+// binary16 views (the SE branch of a ConvBlockResidual in tensor-core mode): 8 channels per thread,
+// fp32 arithmetic, result rounded to nearest even
+__global__ void channel_scale8h_kernel(dcvc_view src, dcvc_view dst, const float *__restrict__ v, int divide) {
+  const int c8n = src.c >> 3;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (int64_t)src.h * src.w * c8n) return;
+  const int c = (int)(t % c8n) * 8;
+  const int64_t p = t / c8n;
+  const uint4 a = *reinterpret_cast<const uint4 *>(reinterpret_cast<const __half *>(src.data) +
+                                                   (size_t)p * src.cstride + src.coff + c);
+  const float4 q0 = __ldg(reinterpret_cast<const float4 *>(v + c)), q1 = __ldg(reinterpret_cast<const float4 *>(v + c + 4));
+  const float q[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+  const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+  uint32_t o[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w[j]));
+    const float lo = divide ? f.x / q[2 * j] : f.x * q[2 * j];
+    const float hi = divide ? f.y / q[2 * j + 1] : f.y * q[2 * j + 1];
+    const __half2 h = __floats2half2_rn(lo, hi);
+    o[j] = *reinterpret_cast<const uint32_t *>(&h);
+  }
+  *reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(dst.data) + (size_t)p * dst.cstride + dst.coff + c) =
+      make_uint4(o[0], o[1], o[2], o[3]);
+}
+
 // ---------------------------------------------------------------- squeeze-and-excitation gate
 // stage 1: each block sums SE_PIX pixels of every channel (float4 loads, coalesced along the
 // channel axis; fp32 runs of 32 pixels folded into float64); stage 2: fixed-order sum over the
 // blocks, the two bias-free linear layers, sigmoid.  Deterministic: no atomics.
 constexpr int SE_PIX = 4096;
 constexpr int SE_TPB = 256;
+constexpr int SE_FIN_TPB = 512;       // threads of the final kernel (>= c)
+template <bool H16>
 __global__ void __launch_bounds__(SE_TPB) se_partial_kernel(dcvc_view x, double *__restrict__ part) {
   __shared__ double sm[SE_TPB * 4];
-  const int nvec = x.c >> 2;                 // float4 groups per pixel (c % 4 == 0, nvec <= 64)
+  const int nvec = x.c >> 2;                 // 4-channel groups per pixel (c % 4 == 0, nvec <= 64)
   const int lanes = SE_TPB / nvec;           // pixels in flight per iteration
   const int vec = threadIdx.x % nvec, lane = threadIdx.x / nvec;
   const int64_t npix = (int64_t)x.h * x.w;
   const int64_t p0 = (int64_t)blockIdx.x * SE_PIX;
   const int64_t p1 = p0 + SE_PIX < npix ? p0 + SE_PIX : npix;
   double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+  auto load = [&](int64_t p) -> float4 {
+    if (H16) {
+      const uint2 u = *reinterpret_cast<const uint2 *>(reinterpret_cast<const __half *>(x.data) +
+                                                       (size_t)p * x.cstride + x.coff + 4 * vec);
+      const float2 lo = __half22float2(*reinterpret_cast<const __half2 *>(&u.x));
+      const float2 hi = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+      return make_float4(lo.x, lo.y, hi.x, hi.y);
+    }
+    return *reinterpret_cast<const float4 *>(x.data + (size_t)p * x.cstride + x.coff + 4 * vec);
+  };
   if (lane < lanes) {
+    // the same summation order as ever (runs of 32 pixels in fp32, folded into float64), with four
+    // loads in flight per thread
     float4 run = make_float4(0.f, 0.f, 0.f, 0.f);
     int cnt = 0;
-    for (int64_t p = p0 + lane; p < p1; p += lanes) {
-      const float4 v = *reinterpret_cast<const float4 *>(x.data + (size_t)p * x.cstride + x.coff + 4 * vec);
+    int64_t p = p0 + lane;
+    for (; p + 3 * (int64_t)lanes < p1; p += 4 * (int64_t)lanes) {
+      const float4 v0 = load(p), v1 = load(p + lanes), v2 = load(p + 2 * (int64_t)lanes),
+                   v3 = load(p + 3 * (int64_t)lanes);
+      const float4 vs[4] = {v0, v1, v2, v3};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        run.x += vs[j].x; run.y += vs[j].y; run.z += vs[j].z; run.w += vs[j].w;
+        if (++cnt == 32) {
+          a0 += run.x; a1 += run.y; a2 += run.z; a3 += run.w;
+          run = make_float4(0.f, 0.f, 0.f, 0.f);
+          cnt = 0;
+        }
+      }
+    }
+    for (; p < p1; p += lanes) {
+      const float4 v = load(p);
       run.x += v.x; run.y += v.y; run.z += v.z; run.w += v.w;
       if (++cnt == 32) {
         a0 += run.x; a1 += run.y; a2 += run.z; a3 += run.w;
@@ -264,10 +321,23 @@ __global__ void se_gate_kernel(const double *__restrict__ part, int nblocks, int
                                const float *__restrict__ w1, const float *__restrict__ w2, int hidden,
                                float *__restrict__ gate) {
   extern __shared__ float sm[];      // mean[c], hid[hidden]
+  __shared__ double psum[SE_FIN_TPB];
   float *mean = sm, *hid = sm + c;
+  // the blocks' partial sums, in a fixed order: thread (g, i) adds the blocks b = g, g + G, ...
+  // of channel i (G = blockDim / c groups, so that the loads of one channel are spread over G
+  // threads instead of one dependent chain), then channel i's G sums are added in order of g
+  const int G = blockDim.x / c;
+  {
+    const int g = threadIdx.x / c, i = threadIdx.x - g * c;
+    double acc = 0.0;
+    if (g < G)
+      for (int b = g; b < nblocks; b += G) acc += part[(size_t)b * c + i];
+    psum[threadIdx.x] = acc;
+  }
+  __syncthreads();
   for (int i = threadIdx.x; i < c; i += blockDim.x) {
     double acc = 0.0;
-    for (int b = 0; b < nblocks; ++b) acc += part[(size_t)b * c + i];
+    for (int g = 0; g < G; ++g) acc += psum[g * c + i];
     mean[i] = (float)(acc / (double)pixels);
   }
   __syncthreads();
@@ -337,22 +407,50 @@ extern "C" int dcvc_channel_scale(const dcvc_view *src, const dcvc_view *dst, co
   return DCVC_OK;
 }
 
+extern "C" int dcvc_channel_scale_f16(const dcvc_view *src, const dcvc_view *dst, const float *vec,
+                                      int divide, void *stream) {
+  if (!view_ok(src) || !view_ok(dst) || !vec || src->h != dst->h || src->w != dst->w || src->c != dst->c)
+    return dcvc_fail(DCVC_ERR_ARG, "channel_scale_f16: bad arguments");
+  auto al = [](const dcvc_view *v) {
+    return ((v->cstride | v->coff | v->c) & 7) == 0 && (reinterpret_cast<uintptr_t>(v->data) & 15) == 0;
+  };
+  if (!al(src) || !al(dst) || (reinterpret_cast<uintptr_t>(vec) & 15))
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "channel_scale_f16: views must hold whole 8-channel groups");
+  const int64_t n = (int64_t)src->h * src->w * (src->c / 8);
+  channel_scale8h_kernel<<<cdiv(n, TPB), TPB, 0, (cudaStream_t)stream>>>(*src, *dst, vec, divide);
+  DCVC_LAUNCHED();
+  return DCVC_OK;
+}
+
 extern "C" size_t dcvc_se_ws_bytes(int h, int w, int c) {
   return (size_t)cdiv((int64_t)h * w, SE_PIX) * (size_t)c * sizeof(double);
 }
 
-extern "C" int dcvc_se_gate(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
-                            void *ws, void *stream) {
+static int se_gate_impl(const dcvc_view *x, bool f16, const float *w1, const float *w2, int hidden,
+                        float *gate, void *ws, void *stream) {
   if (!view_ok(x) || !w1 || !w2 || hidden < 1 || !gate || !ws)
     return dcvc_fail(DCVC_ERR_ARG, "se_gate: bad arguments");
-  if (!view_al16(x) || x->c > SE_TPB)
-    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "se_gate: needs a 16-byte aligned view of at most %d channels", SE_TPB);
+  const bool al = f16 ? ((x->cstride | x->coff | x->c) & 3) == 0 && (reinterpret_cast<uintptr_t>(x->data) & 7) == 0
+                      : view_al16(x);
+  if (!al || x->c > SE_TPB)
+    return dcvc_fail(DCVC_ERR_UNSUPPORTED, "se_gate: needs an aligned view of whole 4-channel groups, at most %d channels", SE_TPB);
   const int nblocks = cdiv((int64_t)x->h * x->w, SE_PIX);
   cudaStream_t s = (cudaStream_t)stream;
-  se_partial_kernel<<<nblocks, SE_TPB, 0, s>>>(*x, (double *)ws);
+  if (f16) se_partial_kernel<true><<<nblocks, SE_TPB, 0, s>>>(*x, (double *)ws);
+  else se_partial_kernel<false><<<nblocks, SE_TPB, 0, s>>>(*x, (double *)ws);
   DCVC_LAUNCHED();
-  se_gate_kernel<<<1, 128, (size_t)(x->c + hidden) * sizeof(float), s>>>(
+  se_gate_kernel<<<1, SE_FIN_TPB, (size_t)(x->c + hidden) * sizeof(float), s>>>(
       (const double *)ws, nblocks, x->c, (int64_t)x->h * x->w, w1, w2, hidden, gate);
   DCVC_LAUNCHED();
   return DCVC_OK;
+}
+
+extern "C" int dcvc_se_gate(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
+                            void *ws, void *stream) {
+  return se_gate_impl(x, false, w1, w2, hidden, gate, ws, stream);
+}
+
+extern "C" int dcvc_se_gate_f16(const dcvc_view *x, const float *w1, const float *w2, int hidden,
+                                float *gate, void *ws, void *stream) {
+  return se_gate_impl(x, true, w1, w2, hidden, gate, ws, stream);
 }

@@ -33,7 +33,7 @@ def residual_block(net, p, x, out=None, f16_out=False):
 def conv_block_residual(net, p, x, out=None, f16_out=False):
     """ConvBlockResidual (video_net.py:166-181): up_dim(x) + SE(conv(lrelu(conv(x))))"""
     t = ops.conv(x, net.cw(p + ".conv.0"), act=0.01, f16_out=True)
-    t = ops.conv(t, net.cw(p + ".conv.2"))
+    t = ops.conv(t, net.cw(p + ".conv.2"), f16_out=True)       # the SE branch: binary16 in tensor-core mode
     gate = ops.se_gate(t, net.sd[p + ".conv.3.fc.0.weight"], net.sd[p + ".conv.3.fc.2.weight"])
     ops.channel_scale(t, gate, out=t)
     return ops.conv(x, net.cw(p + ".up_dim"), res=t, out=out, f16_out=f16_out)
@@ -42,7 +42,7 @@ def conv_block_residual(net, p, x, out=None, f16_out=False):
 def hem_unet(net, p, x, out=None, f16_out=False):
     """UNet (video_net.py:184-223): the two skip concatenations are shared buffers, binary16 in
     tensor-core mode like every tensor here that only convolutions and the max pool read (the SE
-    branch stays fp32: its global mean and gate are computed on the fp32 convolution result)."""
+    branch too: the global mean is accumulated in float64 from the binary16 convolution result)."""
     dev = x.device
     f16 = ops.f16_ok(x.h // 4, x.w // 4, 64)
     cat2 = Act.new(x.h, x.w, 64, dev, f16=f16)                 # [x1 32 | up2 32]

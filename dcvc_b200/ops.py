@@ -367,26 +367,25 @@ def dual_step_dec(fused, prior, cat, y_out, edges, step, symbols, post_scale=Non
 
 
 def channel_scale(x, vec, divide=False, out=None, stream=None):
-    """out = x * vec[c] (or x / vec[c]); fp32 views."""
-    if x.f16:
-        raise ValueError("channel_scale works on fp32 activations")
+    """out = x * vec[c] (or x / vec[c]); fp32 views, or binary16 in and out."""
     if out is None:
-        out = Act.new(x.h, x.w, x.c, x.device)
-    with _Prof("channel_scale", 0, _nb(x, out)):
-        _lib.check(_lib.lib().dcvc_channel_scale(x.view(), out.view(), vec.data_ptr(),
-                                                 int(divide), _stream(stream)))
+        out = Act.new(x.h, x.w, x.c, x.device, f16=x.f16)
+    if out.f16 != x.f16:
+        raise ValueError("channel_scale: source and destination must hold the same element type")
+    fn = _lib.lib().dcvc_channel_scale_f16 if x.f16 else _lib.lib().dcvc_channel_scale
+    with _Prof("channel_scale" + (" f16" if x.f16 else ""), 0, _nb(x, out)):
+        _lib.check(fn(x.view(), out.view(), vec.data_ptr(), int(divide), _stream(stream)))
     return out
 
 
 def se_gate(x, w1, w2, stream=None):
-    """SELayer gate [C] of the fp32 activation x (w1 [C/r][C], w2 [C][C/r])."""
-    if x.f16:
-        raise ValueError("se_gate works on fp32 activations")
+    """SELayer gate [C] of the activation x, fp32 or binary16 (w1 [C/r][C], w2 [C][C/r])."""
     hidden = w1.shape[0]
     gate = torch.empty(x.c, dtype=torch.float32, device=x.device)
     ws = torch.empty(int(_lib.lib().dcvc_se_ws_bytes(x.h, x.w, x.c)) // 8 + 1, dtype=torch.float64,
                      device=x.device)
-    with _Prof("se_gate", 0, _nb(x)):
-        _lib.check(_lib.lib().dcvc_se_gate(x.view(), w1.data_ptr(), w2.data_ptr(), hidden,
-                                           gate.data_ptr(), ws.data_ptr(), _stream(stream)))
+    fn = _lib.lib().dcvc_se_gate_f16 if x.f16 else _lib.lib().dcvc_se_gate
+    with _Prof("se_gate" + (" f16" if x.f16 else ""), 0, _nb(x)):
+        _lib.check(fn(x.view(), w1.data_ptr(), w2.data_ptr(), hidden, gate.data_ptr(), ws.data_ptr(),
+                      _stream(stream)))
     return gate

@@ -300,12 +300,19 @@ int dcvc_dual_step_dec(const dcvc_dual *q, const int16_t *symbols, void *stream)
  * SELayer (video_net.py:162) */
 int dcvc_channel_scale(const dcvc_view *src, const dcvc_view *dst, const float *vec, int divide,
                        void *stream);
+/* the same on binary16 views (whole 8-channel groups; fp32 arithmetic, round to nearest even):
+ * the SE branch of ConvBlockResidual in tensor-core mode */
+int dcvc_channel_scale_f16(const dcvc_view *src, const dcvc_view *dst, const float *vec, int divide,
+                           void *stream);
 /* SELayer gate (DCVC-HEM/src/models/video_net.py:149-163): gate = sigmoid(W2 relu(W1 mean_hw(x)));
  * w1 [hidden][c], w2 [c][hidden] (nn.Linear weights, no bias); the mean is accumulated in float64
  * in a fixed order.  x: 16-byte aligned view, c <= 256.  ws: >= dcvc_se_ws_bytes(h, w, c). */
 size_t dcvc_se_ws_bytes(int h, int w, int c);
 int dcvc_se_gate(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
                  void *ws, void *stream);
+/* the same gate of a binary16 view (whole 4-channel groups) */
+int dcvc_se_gate_f16(const dcvc_view *x, const float *w1, const float *w2, int hidden, float *gate,
+                     void *ws, void *stream);
 
 /* hyper latent: z_hat = round(z) (NHWC in place allowed), symbols in [1,C,h,w] order, and
  * (bits != NULL) factorised-prior bit estimate (BitEstimator, entropy_models.py:58-122;
