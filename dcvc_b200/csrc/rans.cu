@@ -102,47 +102,54 @@ __global__ void compat_prepare_kernel(const EncJob job, uint4 *ops) {
 // before the escape interval).
 __global__ void __launch_bounds__(32) compat_encode_kernel(const EncJob job, const uint4 *ops_all,
                                                            uint32_t *buf, uint32_t *meta) {
-  __shared__ uint4 sm[32];
+  // One sequential 64-bit state per part (rans.cpp:76-168).  The warp runs the chain redundantly
+  // in all 32 lanes (same state, same instructions): lane l holds prepared operation l of the
+  // current group of 32 in registers and every lane fetches operation j by shuffle, off the
+  // state's dependent chain, so there is no shared-memory round trip and no warp barrier per
+  // group; lane 0 alone writes the emitted words.
   const int i = blockIdx.x, lane = threadIdx.x;
   rans::Enc64 e;
   rans::enc64_init(e, buf + reg_off(job, i + 1), buf + reg_off(job, i));
+  auto emit = [&]() {
+    if (e.ptr <= e.limit) e.overflow = 1;
+    else { --e.ptr; if (lane == 0) *e.ptr = (uint32_t)e.x; }
+    e.x >>= 32;
+  };
   for (int c = job.ncalls - 1; c >= 0; --c) {
     const CallRec &cr = job.calls[c];
     int64_t off, cur;
     part_range(cr.n, job.parts, i, off, cur);
     const uint4 *ops = ops_all + job.op_off[c] + off;
-    // batches of 32 from the top: batch b covers k in [hi - 32, hi)
+    // groups of 32 from the top: the group ending at hi covers k in [hi - 32, hi), lane = k - (hi - 32)
     int64_t hi = cur;
     uint4 nxt = make_uint4(0, 0, 0, 0);
     if (hi - 32 + lane >= 0 && hi > 0) nxt = __ldg(ops + hi - 32 + lane);
     while (hi > 0) {
-      sm[lane] = nxt;
+      const uint4 mine = nxt;
       const int64_t lo = hi - 32 > 0 ? hi - 32 : 0;
-      const int64_t nhi = lo;
-      if (nhi > 0 && nhi - 32 + lane >= 0) nxt = __ldg(ops + nhi - 32 + lane);
-      __syncwarp();
-      if (lane == 0) {
-        for (int64_t k = hi - 1; k >= lo; --k) {
-          const uint4 o = sm[(int)(k - (hi - 32))];
-          const uint32_t freq = o.x >> 16, start = o.x & 0xffffu;
-          if (o.y & 1u) {                                  // escape: digits (high first), count
-            const uint32_t raw = o.y >> 1;
-            const int nb = raw ? (35 - __clz(raw)) >> 2 : 0;
-            for (int j = nb - 1; j >= -1; --j) {
-              const uint32_t nib = j < 0 ? (uint32_t)nb : (raw >> (4 * j)) & 15u;
-              if (e.x >= (1ull << 59)) rans::enc64_emit(e);
-              e.x = (e.x << rans::BYPASS_BITS) | nib;
-            }
+      if (lo > 0 && lo - 32 + lane >= 0) nxt = __ldg(ops + lo - 32 + lane);
+      const int jlo = (int)(lo - (hi - 32));               // first valid lane of this group
+#pragma unroll 4
+      for (int j = 31; j >= jlo; --j) {
+        const uint32_t ox = __shfl_sync(0xffffffffu, mine.x, j), oy = __shfl_sync(0xffffffffu, mine.y, j);
+        const uint32_t oz = __shfl_sync(0xffffffffu, mine.z, j), ow = __shfl_sync(0xffffffffu, mine.w, j);
+        const uint32_t freq = ox >> 16, start = ox & 0xffffu;
+        if (oy & 1u) {                                     // escape: digits (high first), count
+          const uint32_t raw = oy >> 1;
+          const int nb = raw ? (35 - __clz(raw)) >> 2 : 0;
+          for (int d = nb - 1; d >= -1; --d) {
+            const uint32_t nib = d < 0 ? (uint32_t)nb : (raw >> (4 * d)) & 15u;
+            if (e.x >= (1ull << 59)) emit();
+            e.x = (e.x << rans::BYPASS_BITS) | nib;
           }
-          if (e.x >= ((uint64_t)freq << 47)) rans::enc64_emit(e);
-          const uint64_t m = (uint64_t)o.z | ((uint64_t)o.w << 32);
-          uint64_t q = __umul64hi(e.x, m);                 // <= x / freq, short by at most 2
-          uint64_t rem = e.x - q * freq;
-          while (rem >= freq) { rem -= freq; ++q; }
-          e.x = (q << rans::PRECISION) + rem + start;
         }
+        if (e.x >= ((uint64_t)freq << 47)) emit();
+        const uint64_t m = (uint64_t)oz | ((uint64_t)ow << 32);
+        uint64_t q = __umul64hi(e.x, m);                   // <= x / freq, short by at most 2
+        uint64_t rem = e.x - q * freq;
+        while (rem >= freq) { rem -= freq; ++q; }
+        e.x = (q << rans::PRECISION) + rem + start;
       }
-      __syncwarp();
       hi = lo;
     }
   }
