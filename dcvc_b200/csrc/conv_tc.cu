@@ -59,6 +59,7 @@ struct TcArgs {
   int out2_tma;   // TMA-store epilogue also stores out2 = lrelu(out) (element type of out) via map_o2
   int res_direct; // TMA-store epilogue: binary16 res1 by direct row loads issued ahead of the
                   // accumulator wait (registers), not by TMA into the outgoing tile
+  int pdl;    // launched with programmatic stream serialisation (griddepcontrol.wait after the prologue)
   int debug;  // experiments: bit0 = no TMA, bit1 = no MMA, bit2 = no epilogue stores
 };
 
@@ -798,6 +799,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       for (int s = 0; s < 2 * a.epi_warps; ++s) mbar_init(res_bar(s), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 ::"r"(smem_u32(&tmem_base_slot)), "r"(a.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // Programmatic dependent launch: the barrier initialisation and the TMEM allocation above may run
+  // while the previous kernel of the stream is still draining; nothing below reads or writes
+  // global memory before that kernel has completed and flushed (the bias / scale vectors
+  // included: they may have been packed by a kernel launched just before this one).  The next
+  // kernel's prologue may start as soon as it finds room.
+  if (a.pdl) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;");
+  }
   if (a.tma_epi) {
     // bias / scale of every GEMM column, padded with 0 / 1, for broadcast reads in the epilogue
     float *vec = reinterpret_cast<float *>(smem_raw + (base - raw) + a.vec_off);
@@ -808,12 +824,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       vec[i] = (a.bias && i < a.cout_w) ? __ldg(a.bias + (a.shuf_tma ? 4 * c + sp : i)) : 0.f;
       vec[n_all + i] = (a.scale && i < a.cout_w) ? __ldg(a.scale + c) : 1.f;
     }
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                 ::"r"(smem_u32(&tmem_base_slot)), "r"(a.tmem_cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -1763,7 +1773,25 @@ int conv_tc_launch(const dcvc_conv *d, int hout, int wout, cudaStream_t s) {
   if (rc) return rc;
   const int grid = a.total_tiles < ctas * num_sms ? a.total_tiles : ctas * num_sms;
   if (!a.shuf_tma) { if (!a.out2_tma) mo2 = mo; mo3 = mo; }
-  conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, mo, mr, mo2, mo3, a);
+  // programmatic dependent launch (DCVC_TC_PDL=1): measured within noise once the bias / scale
+  // vector fill sits behind griddepcontrol.wait, as it must; off by default
+  static const int pdl_on = getenv("DCVC_TC_PDL") ? atoi(getenv("DCVC_TC_PDL")) : 0;
+  a.pdl = pdl_on;
+  if (pdl_on) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)(64 + 32 * epi));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DCVC_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel, ma, mb, mo, mr, mo2, mo3, a));
+  } else {
+    conv_tc_kernel<<<grid, 64 + 32 * epi, smem, s>>>(ma, mb, mo, mr, mo2, mo3, a);
+  }
   DCVC_LAUNCHED();
   return DCVC_OK;
 }
