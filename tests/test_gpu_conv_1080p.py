@@ -136,7 +136,7 @@ def test_conv_at_1080p_shape(case):
         ref = ref + r2.float()
         kw["res2"] = _act(r2)
     if extra == "scale":
-        q = torch.rand(ec, device=dev()) + 0.5
+        q = (torch.rand(ec, generator=torch.Generator().manual_seed(11)) + 0.5).to(dev())
         ref = ref * q.view(1, -1, 1, 1)
         kw["scale"] = q
     if extra == "clamp4":
@@ -188,7 +188,7 @@ def test_fused_ffn_at_1080p_shapes():
               "b.conv.2.bias": torch.rand(c, generator=g) * 0.2 - 0.1}
         net = layers.Net(sd, dev())
         x = _rand((1, c, h, w), 5, True)
-        q = torch.rand(c, device=dev()) + 0.5
+        q = (torch.rand(c, generator=g) + 0.5).to(dev())       # seeded: the bounds below scale with it
         xa = _act(x)
         assert ops.ffn_ok(xa)
         w1, b1, w2, b2 = net.ffn("b")
@@ -204,4 +204,8 @@ def test_fused_ffn_at_1080p_shapes():
         # order): one half-ulp of the hidden tensor times |w2| <= 2^-11 * 4 * (1/sqrt(4c)) ...
         lim = 2e-3 + (2.0 ** -10 if out16 else 0.0) * ref.abs()
         assert not bool((d > lim).any()), (c, float(d.max()))
-        assert float(d.mean()) < 1e-4, (c, float(d.mean()))
+        # mean error: binary16 rounding of the result (2^-12 relative on average) when out16, plus
+        # the hidden tensor's rounding; the unseeded scale vector used to put the 48-channel case
+        # within 2 % of a fixed 1e-4 bound (2 failures in 40 runs)
+        mean_lim = 5e-5 + (2.0 ** -12 if out16 else 0.0) * float(ref.abs().mean())
+        assert float(d.mean()) < mean_lim, (c, float(d.mean()), mean_lim)

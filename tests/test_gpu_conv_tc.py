@@ -87,7 +87,7 @@ def test_tc_conv_epilogues_and_slices():
     cin, cout, h, w = 32, 64, 40, 48
     sd = _sd(cin, cout, 3, seed=5)
     x, r1, r2 = _rand(1, cin, h, w, seed=1), _rand(1, cout, h, w, seed=2), _rand(1, cout, h, w, seed=3)
-    q = torch.rand(cout) + 0.5
+    q = torch.rand(cout, generator=torch.Generator().manual_seed(11)) + 0.5
     conv = F.conv2d(x, sd["c.weight"], sd["c.bias"], 1, 1)
     net = layers.Net(sd, dev())
     xa = to_act(x, cstride=48, coff=8)
@@ -153,7 +153,7 @@ def test_tc_conv_planar_shuffle(cin, cout, k, h, w):
     x = _rand(1, cin, h, w, seed=6)
     c4 = cout // 4
     r1 = _rand(1, c4, 2 * h, 2 * w, seed=7)
-    q = torch.rand(c4) + 0.5
+    q = torch.rand(c4, generator=torch.Generator().manual_seed(11)) + 0.5
     conv = F.conv2d(x, sd["c.weight"], sd["c.bias"], 1, k // 2)
     net = layers.Net(sd, dev())
     xa = to_act(x)
@@ -247,7 +247,7 @@ def test_tc_conv_tma_store_epilogue(cin, cout, k, h, w):
     a wider buffer whose neighbours must stay untouched; ragged tiles and N-tiled outputs."""
     sd = _sd(cin, cout, k, seed=31)
     x, r1 = _rand(1, cin, h, w, seed=8), _rand(1, cout, h, w, seed=9)
-    q = torch.rand(cout) + 0.5
+    q = torch.rand(cout, generator=torch.Generator().manual_seed(11)) + 0.5
     conv = F.conv2d(x, sd["c.weight"], sd["c.bias"], 1, k // 2)
     net = layers.Net(sd, dev())
     xa = to_act(x)
@@ -285,7 +285,7 @@ def test_tc_conv_f16_input(cin, cout, k, stride, h, w):
     ref = F.conv2d(x.half().float(), w16, sd["c.bias"], stride, pad)
     ho, wo = ref.shape[2], ref.shape[3]
     r1 = _rand(1, cout, ho, wo, seed=12)
-    q = torch.rand(cout) + 0.5
+    q = torch.rand(cout, generator=torch.Generator().manual_seed(11)) + 0.5
     net = layers.Net(sd, dev())
     out = ops.conv(xa, net.cw("c"), stride=stride, pad=pad, act=0.1,
                    res=to_act(r1) if cout % 4 == 0 else None,
@@ -393,7 +393,7 @@ def test_tc_conv_f16_residual(cin, cout, k, h, w, res16, out16):
     epilogue (rows of 64 and 128 bytes overlap, so the warp reads before anyone writes)."""
     sd = _sd(cin, cout, k, seed=51)
     x, r1 = _rand(1, cin, h, w, seed=14), _rand(1, cout, h, w, seed=15)
-    q = torch.rand(cout) + 0.5
+    q = torch.rand(cout, generator=torch.Generator().manual_seed(11)) + 0.5
     net = layers.Net(sd, dev())
     res = ops.copy(to_act(r1), f16=True) if res16 else to_act(r1)
     rr = r1.half().float() if res16 else r1
