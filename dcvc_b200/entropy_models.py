@@ -138,6 +138,21 @@ def index_edges(distribution):
     return torch.cat((torch.zeros(1), hi.view(torch.float32)))
 
 
+def search_lut(cdf, sizes):
+    """The interleaved / compat decoders' search table (dcvc_tables.lut): lut[r][b] = the largest
+    symbol s of row r with cdf[r][s] <= 256 b, i.e. the symbol the first cumulative value of
+    bucket b falls in; the symbol of any value of the bucket then lies in [lut[b], lut[b + 1]].
+    uint8 [rows][256], or None when a row has more than 256 symbols (stride > 257)."""
+    if cdf.shape[1] > 257:
+        return None
+    lut = np.zeros((cdf.shape[0], 256), dtype=np.uint8)
+    starts = np.arange(256, dtype=np.int64) * 256
+    for r in range(cdf.shape[0]):
+        row = np.asarray(cdf[r, :max(int(sizes[r]) - 1, 1)], dtype=np.int64)
+        lut[r] = np.clip(np.searchsorted(row, starts, side="right") - 1, 0, 255)
+    return lut
+
+
 class DeviceTables:
     """One table set {cdf, sizes, offsets} resident on the device."""
 
@@ -149,12 +164,8 @@ class DeviceTables:
         # search table of the interleaved decoder (dcvc_tables.lut): per row and 256-wide bucket of
         # the 16-bit cumulative value, the symbol its first value falls in
         self.lut = None
-        if cdf.shape[1] <= 257:
-            lut = np.zeros((cdf.shape[0], 256), dtype=np.uint8)
-            starts = np.arange(256, dtype=np.int64) * 256
-            for r in range(cdf.shape[0]):
-                row = np.asarray(cdf[r, :max(int(sizes[r]) - 1, 1)], dtype=np.int64)
-                lut[r] = np.clip(np.searchsorted(row, starts, side="right") - 1, 0, 255)
+        lut = search_lut(cdf, sizes)
+        if lut is not None:
             self.lut = torch.from_numpy(lut).to(device)
         self.c = _lib.Tables(self.cdf.data_ptr(), self.sizes.data_ptr(), self.offsets.data_ptr(),
                              cdf.shape[0], cdf.shape[1],

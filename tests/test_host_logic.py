@@ -175,3 +175,32 @@ def test_padding_and_latent_shapes():
     assert get_padding_size(1088, 1920, 64) == (0, 0, 0, 0)
     assert get_downsampled_shape(1080, 1920, 64) == (17, 30)
     assert get_downsampled_shape(2160, 3840, 16) == (135, 240)
+
+
+def test_search_lut_brackets_every_cumulative_value():
+    """dcvc_tables.lut (entropy_models.search_lut): for every 16-bit cumulative value the symbol
+    the reference's linear search finds (rans.cpp:289-292) lies in [lut[b], lut[b + 1]] of its
+    bucket b = cum >> 8 (the row's last symbol closing the last bucket), on the real Gaussian /
+    Laplace tables and on a row of all-ones-but-one frequencies."""
+    import numpy as np
+    from dcvc_b200 import entropy_models as em
+    for dist in ("gaussian", "laplace"):
+        cdf, sizes, _ = em.gaussian_tables(dist)
+        lut = em.search_lut(cdf, sizes)
+        assert lut is not None and lut.shape == (cdf.shape[0], 256)
+        cum = np.arange(65536, dtype=np.int64)
+        for r in (0, 1, cdf.shape[0] // 2, cdf.shape[0] - 1):
+            n = int(sizes[r])
+            row = np.asarray(cdf[r, :n], dtype=np.int64)
+            assert row[0] == 0 and row[n - 1] == 65536
+            sym = np.searchsorted(row, cum, side="right") - 1          # largest s with cdf[s] <= cum
+            lo = lut[r][cum >> 8].astype(np.int64)
+            hi = np.where((cum >> 8) < 255, lut[r][np.minimum((cum >> 8) + 1, 255)], n - 2)
+            assert np.all(lo <= sym) and np.all(sym <= hi), (dist, r)
+    # many one-count symbols in one bucket
+    n = 200
+    row = np.concatenate(([0], np.cumsum(np.r_[np.ones(n - 2, dtype=np.int64), 65536 - (n - 2)])))
+    cdf = row[None, :].astype(np.int32)
+    lut = em.search_lut(cdf, np.array([n], dtype=np.int32))
+    assert lut[0, 0] == 0 and lut[0, 1] == n - 2 and lut[0, 255] == n - 2
+    assert em.search_lut(np.zeros((1, 300), dtype=np.int32), np.array([300])) is None
