@@ -204,3 +204,45 @@ def test_search_lut_brackets_every_cumulative_value():
     lut = em.search_lut(cdf, np.array([n], dtype=np.int32))
     assert lut[0, 0] == 0 and lut[0, 1] == n - 2 and lut[0, 255] == n - 2
     assert em.search_lut(np.zeros((1, 300), dtype=np.int32), np.array([300])) is None
+
+
+def test_graph_helpers_recognise_dpb_views_and_placement():
+    """dcvc_b200.graphs: a dpb entry (an NCHW view of an NHWC buffer, possibly a channel slice) is
+    recognised with its buffer, channel offset and count; tensors that are not such views are
+    not; tensor.placed hands out the preassigned buffer only for the layout asked for."""
+    import torch
+    from dcvc_b200 import graphs, tensor
+    from dcvc_b200.tensor import Act
+    buf = torch.arange(6 * 10 * 8, dtype=torch.float32).reshape(6, 10, 8)
+    a = Act(buf, 4, 3)                                   # channels 4..6 of an 8-wide buffer
+    v = a.nchw()
+    assert tuple(v.shape) == (1, 3, 6, 10)
+    back = graphs._as_act(v)
+    assert back is not None and back.buf.data_ptr() == buf.data_ptr()
+    assert (back.c0, back.c, back.h, back.w) == (4, 3, 6, 10)
+    assert torch.equal(back.buf, buf)
+    assert graphs._as_act(torch.zeros(1, 3, 6, 10)) is None            # plain NCHW: not a view
+    assert graphs._as_act(torch.zeros(2, 3, 6, 10)) is None
+    s = graphs._Static({"ref_frame": v, "ref_y": None})
+    assert s.views["ref_y"] is None and tuple(s.views["ref_frame"].shape) == (1, 3, 6, 10)
+    assert s.bufs["ref_frame"][0].shape == buf.shape and s.acts["ref_frame"].c0 == 4
+    s.load({"ref_frame": v, "ref_y": None})
+    assert torch.equal(s.views["ref_frame"], v)
+    dpb = {k: None for k in graphs.DPB_KEYS}
+    dpb["ref_frame"] = s.views["ref_frame"]
+    assert graphs._is_static(dpb)
+    dpb["ref_frame"] = v
+    assert not graphs._is_static(dpb)
+    assert graphs._sig(dpb) != graphs._sig({**dpb, "ref_frame": s.views["ref_frame"]})
+    assert tensor.placed("ref_y", 6, 10, 3) is None
+    tensor.PLACEMENT = {"ref_y": Act(buf, 0, 8)}
+    try:
+        assert tensor.placed("ref_y", 6, 10, 8).buf.data_ptr() == buf.data_ptr()
+        assert tensor.placed("other", 6, 10, 8) is None
+        try:
+            tensor.placed("ref_y", 6, 10, 4)
+            raise RuntimeError("a layout mismatch must be refused")
+        except AssertionError:
+            pass
+    finally:
+        tensor.PLACEMENT = None
