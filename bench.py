@@ -18,8 +18,10 @@ checkpoints offline).
                  host cores (oracle/_ref; the oracle port when that copy is absent), measured.
   parity       : symbol flips / x_hat RMS / bits of the benchmarked mode against mode 0, and
                  encoder == decoder, on the first frames of the sequence (outside the timing).
-  arms         : the sequential (drop-in) schedule and the reference-compatible bitstream, timed
-                 beside the pipelined headline.
+  arms         : the sequential schedule, the reference's own `encode_decode(output_path)` call
+                 order (frame files on tmpfs) and the reference-compatible bitstream, timed beside
+                 the pipelined headline.
+  P frames are replayed from CUDA graphs (dcvc_b200.graphs; --graphs 0: eager launches).
   gpu_reference: the UNMODIFIED reference (PyTorch/cuDNN + host rANS) on this same GPU.
 
 N > 1 (torchrun): every rank codes its own sequence (independent GOPs; weak scaling); the only
