@@ -138,6 +138,16 @@ def test_compat_stream_decodes_with_oracle():
         dec = o_i.decompress(res[0][0], h, w, True, 1)
     assert abs(psnr(dec["x_hat"], frames[0:1]) - psnr(res[0][1], frames[0:1])) < 0.02
     assert float((dec["x_hat"] - res[0][1]).abs().max()) < 2e-2
+    # the P frame's stream too, from the oracle's own decoded I frame
+    o_p = co.OracleDMC(sd_p, 1)
+    o_p.update()
+    dpb = {"ref_frame": dec["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+           "ref_y": None, "ref_mv_y": None}
+    with torch.no_grad():
+        decp = o_p.decompress(dpb, res[1][0], h, w, True, 1, 1)
+    xp = decp["dpb"]["ref_frame"]
+    assert abs(psnr(xp, frames[1:2]) - psnr(res[1][1], frames[1:2])) < 0.02
+    assert float((xp - res[1][1]).abs().max()) < 2e-2
 
 
 def test_estimate_mode_matches_oracle():
