@@ -242,3 +242,34 @@ def test_1080p_vs_cpu_oracle(restore_mode):
             assert r["x_hat_rms"] < (1e-3 if k.startswith("I") else 2e-4), (k, r)
             assert r["y_flip_frac"] < (2e-3 if k.startswith("I") else 1e-4), (k, r)
             assert abs(r["d_bits_pct"]) < 0.5, (k, r)
+
+
+def test_4k_frame_pair_latent_135_padded_to_136(restore_mode):
+    """3840x2160, the largest size the reference's configs name: the y latent is 135 x 240, which
+    pad_for_y / slice_to_y (DCVC-DC/src/models/common_model.py:70-86) round up to 136 rows for the
+    hyper codec and crop back; an intra frame has 8.4 M symbols (the coder's workspace is sized
+    from the frame).  One I + one P frame, interleaved coder, benchmarked mode: encoder
+    reconstruction == decoder reconstruction bit for bit (every dpb entry), the streams decode,
+    and the latents have the cropped shape."""
+    h, w = 2160, 3840
+    ops.set_conv_mode(1)
+    i_net, p_net, _, _ = _models()
+    x = synth.synth_frames(2, h, w, seed=1).to(dev())
+    with torch.no_grad():
+        enc = i_net.compress(x[0:1], Q_IN_CKPT, Q_INDEX)
+        dec = i_net.decompress(enc["bit_stream"], h, w, Q_IN_CKPT, Q_INDEX)
+        assert torch.equal(enc["x_hat"], dec["x_hat"])
+        assert tuple(dec["x_hat"].shape) == (1, 3, h, w)
+        dpb = {"ref_frame": dec["x_hat"], "ref_feature": None, "ref_mv_feature": None,
+               "ref_y": None, "ref_mv_y": None}
+        encp = p_net.compress(x[1:2], dpb, Q_IN_CKPT, Q_INDEX, 1)
+        decp = p_net.decompress(dpb, encp["bit_stream"], h, w, Q_IN_CKPT, Q_INDEX, 1)
+        for key in KEYS:
+            assert torch.equal(encp["dpb"][key], decp["dpb"][key]), key
+        assert tuple(decp["dpb"]["ref_y"].shape) == (1, 128, 135, 240)
+        assert tuple(decp["dpb"]["ref_mv_y"].shape) == (1, 64, 135, 240)
+        assert tuple(decp["dpb"]["ref_feature"].shape) == (1, 48, h, w)
+        mse = float((decp["dpb"]["ref_frame"] - x[1:2]).pow(2).mean())
+        assert mse == mse and 0.0 < len(encp["bit_stream"]) < 8 * h * w      # finite, sane
+    _report("4k_pair", {"i_bytes": len(enc["bit_stream"]), "p_bytes": len(encp["bit_stream"]),
+                        "p_mse": mse})
