@@ -350,13 +350,22 @@ class DMC(HemCompressionModel):
         t = layers.subpel(net, cf + ".conv3_up", c3, f16_out=True)
         layers.res_block(net, cf + ".res_block3_up", t, out=cat2.slice(0, 64))
         t, ta = layers.conv_for_res_block(net, cf + ".conv3_out", c3, 0.01, f16_out=True)
-        ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3, f16_out=f16, x_act=ta)
+        # the contexts are written straight into the decoder-side concatenation buffers
+        # ([up 64 | ctx3 64], [up 64 | ctx2 64], [feature 32 | ctx1 64]; _recon recognises them):
+        # no copy there, and binary16 like every tensor only convolutions and copies read
+        D3 = Act.new(H // 4, W // 4, 128, dev, f16=f16)
+        D2 = Act.new(H // 2, W // 2, 128, dev, f16=f16)
+        R = Act.new(H, W, 96, dev, f16=f16)
+        ctx3 = layers.res_block(net, cf + ".res_block3_out", t, res2=c3, out=D3.slice(64, 64),
+                                x_act=ta)
         t = layers.subpel(net, cf + ".conv2_up", cat2, f16_out=True)
         layers.res_block(net, cf + ".res_block2_up", t, out=cat1.slice(0, 64))
         t, ta = layers.conv_for_res_block(net, cf + ".conv2_out", cat2, 0.01, f16_out=True)
-        ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2, f16_out=f16, x_act=ta)
+        ctx2 = layers.res_block(net, cf + ".res_block2_out", t, res2=c2, out=D2.slice(64, 64),
+                                x_act=ta)
         t, ta = layers.conv_for_res_block(net, cf + ".conv1_out", cat1, 0.01, f16_out=True)
-        ctx1 = layers.res_block(net, cf + ".res_block1_out", t, res2=c1, f16_out=f16, x_act=ta)
+        ctx1 = layers.res_block(net, cf + ".res_block1_out", t, res2=c1, out=R.slice(32, 64),
+                                x_act=ta)
         return ctx1, ctx2, ctx3
 
     def _contextual_encoder(self, x, ctx1, ctx2, ctx3):
@@ -383,19 +392,24 @@ class DMC(HemCompressionModel):
         net, dev = self.net, y_hat.device
         cd = "contextual_decoder"
         t = layers.subpel(net, cd + ".up1", y_hat, f16_out=True)
-        d3 = Act.new(ctx3.h, ctx3.w, 128, dev, f16=ctx3.f16)
+        def cat_buffer(ctx, total, at):
+            """[new `at` channels | ctx]: the buffer ctx already lives in (_motion_compensation),
+            else a new one with ctx copied in"""
+            if ctx.cs == total and ctx.c0 == at and ctx.c == total - at:
+                return Act(ctx.buf, 0, total)
+            b = Act.new(ctx.h, ctx.w, total, dev, f16=ctx.f16)
+            ops.copy(ctx, out=b.slice(at, total - at))
+            return b
+        d3 = cat_buffer(ctx3, 128, 64)
         layers.subpel(net, cd + ".up2", t, out=d3.slice(0, 64))
-        ops.copy(ctx3, out=d3.slice(64, 64))
         t = layers.res_block(net, cd + ".res1", d3, 0.1, True, f16_out=True)
-        d2 = Act.new(ctx2.h, ctx2.w, 128, dev, f16=ctx2.f16)
+        d2 = cat_buffer(ctx2, 128, 64)
         layers.subpel(net, cd + ".up3", t, out=d2.slice(0, 64))
-        ops.copy(ctx2, out=d2.slice(64, 64))
         t = layers.res_block(net, cd + ".res2", d2, 0.1, True, f16_out=True)
         # recon_generation_net(recon_image_feature, context1) (:301): first_conv reads
         # [feature 32 | context1 64]
-        r = Act.new(ctx1.h, ctx1.w, 96, dev, f16=ctx1.f16)
+        r = cat_buffer(ctx1, 96, 32)
         layers.subpel(net, cd + ".up4", t, out=r.slice(0, 32))
-        ops.copy(ctx1, out=r.slice(32, 64))
         rg = "recon_generation_net"
         t = ops.conv(r, net.cw(rg + ".first_conv"), f16_out=True)
         t = hem_unet(net, rg + ".unet_1", t, f16_out=True)
